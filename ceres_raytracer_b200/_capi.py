@@ -1,0 +1,91 @@
+"""ctypes binding of libceres_b200.so (include/ceres_b200.h).  No fallback: if the CUDA library is missing and
+cannot be built, importing the entry points raises."""
+import ctypes as C
+import os
+
+from . import build as _build
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = 0, 1, 2, 3, 4
+NO_SHADOWS, COMPACT_ROWS = 1, 2
+MISS = 0xFFFFFFFF
+
+
+class CeresError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"ceres_b200 error {code}: {msg}")
+        self.code = code
+
+
+class Camera(C.Structure):
+    """ceres_camera = Camera<float> of include/render.hpp:16-22."""
+    _fields_ = [("eye", C.c_float * 3), ("dir", C.c_float * 3), ("up", C.c_float * 3), ("fov", C.c_float)]
+
+
+class Shard(C.Structure):
+    _fields_ = [("block_rows", C.c_uint32), ("index", C.c_uint32), ("count", C.c_uint32)]
+
+
+class Tuning(C.Structure):
+    _fields_ = [("variant", C.c_uint32), ("primary_block", C.c_uint32), ("shadow_block", C.c_uint32),
+                ("ctas_per_sm", C.c_uint32), ("reserved", C.c_uint32 * 4)]
+
+
+# every symbol include/ceres_b200.h declares (tests/test_capi_symbols.py checks the header against this list)
+SYMBOLS = [
+    "ceres_scene_create", "ceres_scene_destroy", "ceres_scene_set_tuning", "ceres_scene_device_bytes",
+    "ceres_render", "ceres_render_shard", "ceres_render_sequence", "ceres_render_device",
+    "ceres_scene_set_stats", "ceres_scene_get_stats", "ceres_trace_rays", "ceres_frame_setup",
+    "ceres_quantize_device", "ceres_host_alloc", "ceres_host_free", "ceres_abi_version", "ceres_device_count",
+    "ceres_kernel_launch_count", "ceres_last_error",
+]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if _build.needs_build():
+        try:
+            _build.build()
+        except Exception as e:  # no nvcc on the box and no prebuilt library: fail loudly, never fall back
+            if not os.path.exists(path):
+                raise RuntimeError(f"libceres_b200.so is missing and could not be built ({e}); "
+                                   "ceres_raytracer_b200 has no CPU fallback") from e
+    L = C.CDLL(path)
+    vp, sz, u32, u64 = C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint64
+    camp, shp = C.POINTER(Camera), C.POINTER(Shard)
+    L.ceres_scene_create.argtypes = [vp, sz, vp, vp, vp, sz, C.c_int, C.POINTER(vp)]
+    L.ceres_scene_destroy.argtypes = [vp]
+    L.ceres_scene_destroy.restype = None
+    L.ceres_scene_set_tuning.argtypes = [vp, C.POINTER(Tuning)]
+    L.ceres_scene_device_bytes.argtypes = [vp]
+    L.ceres_scene_device_bytes.restype = sz
+    L.ceres_render.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp, vp]
+    L.ceres_render_shard.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp, vp]
+    L.ceres_render_sequence.argtypes = [vp, sz, vp, sz, sz, C.c_uint, vp, vp]
+    L.ceres_render_device.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp, vp, vp]
+    L.ceres_scene_set_stats.argtypes = [vp, C.c_int]
+    L.ceres_scene_get_stats.argtypes = [vp, vp]
+    L.ceres_trace_rays.argtypes = [vp, vp, sz, vp, vp]
+    L.ceres_frame_setup.argtypes = [camp, sz, sz, vp]
+    L.ceres_quantize_device.argtypes = [vp, vp, sz, sz, vp, vp]
+    L.ceres_host_alloc.argtypes = [sz]
+    L.ceres_host_alloc.restype = vp
+    L.ceres_host_free.argtypes = [vp]
+    L.ceres_host_free.restype = None
+    L.ceres_abi_version.restype = C.c_int
+    L.ceres_device_count.restype = C.c_int
+    L.ceres_kernel_launch_count.restype = u64
+    L.ceres_last_error.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != OK:
+        raise CeresError(rc, lib().ceres_last_error().decode(errors="replace"))

@@ -1,0 +1,920 @@
+// ceres_b200.cu -- B200 (sm_100a) implementation of the ceres-raytracer render loop behind the C ABI of
+// include/ceres_b200.h.  Written from scratch; citations are to the reference behaviour each piece reproduces
+// (paths relative to the upstream repository).
+//
+// Pipeline per frame (all on one stream, 3 launches, no host synchronisation inside):
+//   primary_kernel  camera ray generation (render.hpp:105-113) + ordered eager-leaf closest-hit BVH traversal
+//                   (single_ray_traverser.hpp:65-126) + Moeller-Trumbore (triangle.hpp:95-115).  Miss pixels are
+//                   zeroed in place; hits are ballot-compacted into a 16-byte record queue.
+//   shadow_kernel   persistent warps steal 32-record chunks from the queue, rebuild the shadow ray
+//                   (render.hpp:120-136) and run an any-hit traversal (only bool(hit) is used, render.hpp:137-150).
+//   shade_kernel    coalesced pass over the queue: smooth_shading (render.hpp:56-84) for lit records, zeros for
+//                   occluded ones, framebuffer + id writes, frame counters (render.hpp:115,119,138,148,155).
+//
+// Arithmetic: every floating-point operation of the path is issued through the round-to-nearest intrinsics
+// (__fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn/__fsqrt_rn never contract), the slab test uses __fmaf_rn exactly where
+// the reference calls fast_multiply_add (utilities.hpp:37-40), so results are those of the reference built with
+// -ffp-contract=off regardless of nvcc's -fmad setting.
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <cfloat>
+#include <string>
+#include <vector>
+#include <atomic>
+#include <new>
+
+#include "../../include/ceres_b200.h"
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+static std::atomic<uint64_t> g_launches{0};
+
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CUDA_TRY(expr)                                                                                      \
+    do {                                                                                                    \
+        cudaError_t e_ = (expr);                                                                            \
+        if (e_ != cudaSuccess)                                                                              \
+            return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? CERES_ERR_NO_DEVICE  \
+                                                                                     : CERES_ERR_CUDA,      \
+                        std::string(#expr) + ": " + cudaGetErrorString(e_));                                \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------ device data
+// Node pair = the two sibling nodes of the reference (bvh.hpp:13-17,25-30) in one 64-byte, 64-byte-aligned record:
+//   q[0] = L.minx L.maxx L.miny L.maxy   q[1] = L.minz L.maxz L.count L.first
+//   q[2] = R.minx R.maxx R.miny R.maxy   q[3] = R.minz R.maxz R.count R.first
+// `first` of an inner node is the index of its child PAIR; of a leaf the first slot in the leaf-ordered triangle
+// array (= index into Bvh::primitive_indices, so the per-test indirection of primitive_intersectors.hpp:17-20
+// disappears).  Triangles are the reference's 48-byte {p0,e1,e2,n} records (triangle.hpp:27) permuted into leaf
+// order and read as 3 x float4.
+struct DevScene {
+    const float4* pairs;
+    const float4* tris;     // 3 float4 per slot
+    const float4* norms;    // 3 float4 per slot: n0.xyz n1.x | n1.yz n2.xy | n2.z 0 0 0
+    const uint32_t* slot_id;  // slot -> primitive index of the reference (bvh.primitive_indices[slot])
+    uint32_t root_leaf_count;  // != 0: the root itself is a leaf (single_ray_traverser.hpp:72-73)
+    uint32_t stack_depth;      // entries of traversal stack needed (<= 64, single_ray_traverser.hpp:14)
+};
+
+struct FrameCounters {
+    uint32_t qcount;        // primary hits appended to the queue
+    uint32_t shadow_next;   // work-stealing cursor of the shadow kernel
+    uint32_t occluded;      // shadow rays that hit something
+    uint32_t done_blocks;   // shade kernel: blocks finished (last one publishes the counters)
+    unsigned long long stats[6];  // S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow (statistics mode only)
+};
+
+struct Frame {
+    float eye[3], dir[3], iu[3], iv[3], sun[3];
+    uint32_t W, H;             // full frame
+    uint32_t rows_local;       // rows rendered by this shard
+    uint32_t block_rows, shard_index, shard_count;
+    uint32_t compact;          // outputs packed by local row
+    uint32_t shadows;
+    float* pixels;
+    uint32_t* ids;
+    unsigned long long* out_counters;   // [rays, hits]
+    unsigned long long* out_stats;      // 8 x u64 or null
+    uint4* queue;
+    FrameCounters* ctr;
+};
+
+// ------------------------------------------------------------------------------------------------ device math
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float rcp(float a) { return __fdiv_rn(1.0f, a); }
+// vector.hpp:134-141: sum = a0*b0; sum += a1*b1; sum += a2*b2
+__device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return add(add(mul(ax, bx), mul(ay, by)), mul(az, bz));
+}
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 vadd(V3 a, V3 b) { return mk(add(a.x, b.x), add(a.y, b.y), add(a.z, b.z)); }
+__device__ __forceinline__ V3 vsub(V3 a, V3 b) { return mk(sub(a.x, b.x), sub(a.y, b.y), sub(a.z, b.z)); }
+__device__ __forceinline__ V3 vscale(V3 a, float s) { return mk(mul(a.x, s), mul(a.y, s), mul(a.z, s)); }
+__device__ __forceinline__ float vdot(V3 a, V3 b) { return dot3(a.x, a.y, a.z, b.x, b.y, b.z); }
+// vector.hpp:159-167
+__device__ __forceinline__ V3 vcross(V3 a, V3 b) {
+    return mk(sub(mul(a.y, b.z), mul(a.z, b.y)), sub(mul(a.z, b.x), mul(a.x, b.z)), sub(mul(a.x, b.y), mul(a.y, b.x)));
+}
+// vector.hpp:143-154: inv = 1/sqrt(dot(v,v)); v*inv
+__device__ __forceinline__ V3 vnormalize(V3 a) {
+    float inv = rcp(__fsqrt_rn(vdot(a, a)));
+    return vscale(a, inv);
+}
+
+struct Tri { V3 p0, e1, e2, n; };
+__device__ __forceinline__ Tri load_tri(const float4* __restrict__ tris, uint32_t slot) {
+    const float4* p = tris + 3ull * slot;
+    float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    Tri t;
+    t.p0 = mk(a.x, a.y, a.z); t.e1 = mk(a.w, b.x, b.y); t.e2 = mk(b.z, b.w, c.x); t.n = mk(c.y, c.z, c.w);
+    return t;
+}
+
+struct Hit { uint32_t slot; float t, u, v; };
+
+// triangle.hpp:95-115.  Returns true and updates (t,u,v) when the ray hits within [tmin, tmax].
+__device__ __forceinline__ bool tri_test(const Tri& tr, V3 o, V3 d, float tmin, float tmax, float& t, float& u, float& v) {
+    V3 c = vsub(tr.p0, o);
+    V3 r = vcross(d, c);
+    float inv_det = rcp(vdot(tr.n, d));
+    float uu = mul(vdot(r, tr.e2), inv_det);
+    float vv = mul(vdot(r, tr.e1), inv_det);
+    float ww = sub(sub(1.0f, uu), vv);
+    if (uu >= 0.0f && vv >= 0.0f && ww >= 0.0f) {
+        float tt = mul(vdot(tr.n, c), inv_det);
+        if (tt >= tmin && tt <= tmax) { t = tt; u = uu; v = vv; return true; }
+    }
+    return false;
+}
+
+// Ordered, eager-leaf, stack-based traversal (single_ray_traverser.hpp:65-126) over node pairs.
+//   * both children are slab-tested with the tmax seen at the start of the step (:86-87);
+//   * a hit leaf is intersected immediately, left before right, slots ascending (:89-107, :51-62), `t <= tmax`
+//     lets a later equal-t triangle replace an earlier one (triangle.hpp:110);
+//   * both inner children alive: the nearer entry goes first, ties keep the left one, the other's child pair is
+//     pushed (:109-115).
+// Slab test = node_intersectors.hpp:34-47,96-100: entry_k = fma(bounds[2k+oct_k], inv_k, so_k),
+// exit_k = fma(bounds[2k+1-oct_k], inv_k, so_k); the robust_max/min chains (utilities.hpp:57-67) are evaluated with
+// fmaxf/fminf, which return the same value whenever the right-hand accumulator is not NaN (tmin/tmax never are);
+// only the sign of a zero result can differ, and entry/exit are only ever compared.
+// ANY = true: return at the first accepted triangle (used for shadow rays, where only the boolean is consumed; the
+// boolean does not depend on traversal order because tmax never shrinks before the first hit).
+template <bool ANY, bool STATS>
+__device__ __forceinline__ bool traverse(const DevScene& sc, V3 o, V3 d, float tmin, float tmax,
+                                         uint32_t* __restrict__ stack, uint32_t stride, Hit& best,
+                                         uint32_t& n_steps, uint32_t& n_tests) {
+    bool found = false;
+    const float4* __restrict__ tris = sc.tris;
+    if (sc.root_leaf_count) {  // single_ray_traverser.hpp:72-73
+        if (STATS) n_tests += sc.root_leaf_count;
+        for (uint32_t s = 0; s < sc.root_leaf_count; ++s) {
+            Tri tr = load_tri(tris, s);
+            float t, u, v;
+            if (tri_test(tr, o, d, tmin, tmax, t, u, v)) {
+                best.slot = s; best.t = t; best.u = u; best.v = v; found = true; tmax = t;
+                if (ANY) return true;
+            }
+        }
+        return found;
+    }
+    // FastNodeIntersector (node_intersectors.hpp:20-26,89-94; vector.hpp:69-74)
+    const bool ox = signbit(d.x), oy = signbit(d.y), oz = signbit(d.z);
+    const float eps = FLT_EPSILON;
+    const float ix = rcp(fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x);
+    const float iy = rcp(fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y);
+    const float iz = rcp(fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z);
+    const float sx = mul(-o.x, ix), sy = mul(-o.y, iy), sz = mul(-o.z, iz);
+
+    const float4* __restrict__ pairs = sc.pairs;
+    uint32_t cur = 0;  // child pair of the root
+    uint32_t sp = 0;
+    for (;;) {
+        if (STATS) n_steps++;
+        const float4* pp = pairs + 4ull * cur;
+        const float4 q0 = __ldg(pp), q1 = __ldg(pp + 1), q2 = __ldg(pp + 2), q3 = __ldg(pp + 3);
+        float le, lx, re, rx;
+        {
+            float e0 = __fmaf_rn(ox ? q0.y : q0.x, ix, sx), x0 = __fmaf_rn(ox ? q0.x : q0.y, ix, sx);
+            float e1 = __fmaf_rn(oy ? q0.w : q0.z, iy, sy), x1 = __fmaf_rn(oy ? q0.z : q0.w, iy, sy);
+            float e2 = __fmaf_rn(oz ? q1.y : q1.x, iz, sz), x2 = __fmaf_rn(oz ? q1.x : q1.y, iz, sz);
+            le = fmaxf(e0, fmaxf(e1, fmaxf(e2, tmin)));
+            lx = fminf(x0, fminf(x1, fminf(x2, tmax)));
+        }
+        {
+            float e0 = __fmaf_rn(ox ? q2.y : q2.x, ix, sx), x0 = __fmaf_rn(ox ? q2.x : q2.y, ix, sx);
+            float e1 = __fmaf_rn(oy ? q2.w : q2.z, iy, sy), x1 = __fmaf_rn(oy ? q2.z : q2.w, iy, sy);
+            float e2 = __fmaf_rn(oz ? q3.y : q3.x, iz, sz), x2 = __fmaf_rn(oz ? q3.x : q3.y, iz, sz);
+            re = fmaxf(e0, fmaxf(e1, fmaxf(e2, tmin)));
+            rx = fminf(x0, fminf(x1, fminf(x2, tmax)));
+        }
+        const uint32_t cL = __float_as_uint(q1.z), fL = __float_as_uint(q1.w);
+        const uint32_t cR = __float_as_uint(q3.z), fR = __float_as_uint(q3.w);
+        const bool hitL = le <= lx, hitR = re <= rx;
+
+        // leaves: left range then right range
+        uint32_t s = 0, e = 0, s2 = 0, e2 = 0;
+        if (hitL && cL) { s = fL; e = fL + cL; }
+        if (hitR && cR) { s2 = fR; e2 = fR + cR; }
+        if (s == e) { s = s2; e = e2; s2 = e2; }
+        while (s < e) {
+            if (STATS) n_tests++;
+            Tri tr = load_tri(tris, s);
+            float t, u, v;
+            if (tri_test(tr, o, d, tmin, tmax, t, u, v)) {
+                best.slot = s; best.t = t; best.u = u; best.v = v; found = true; tmax = t;
+                if (ANY) return true;
+            }
+            ++s;
+            if (s == e) { s = s2; e = e2; s2 = e2; }
+        }
+
+        const bool goL = hitL && !cL, goR = hitR && !cR;
+        if (goL && goR) {
+            const bool swap = le > re;  // ties keep left first
+            const uint32_t nearc = swap ? fR : fL, farc = swap ? fL : fR;
+            stack[sp * stride] = farc;
+            ++sp;
+            cur = nearc;
+        } else if (goL || goR) {
+            cur = goL ? fL : fR;
+        } else {
+            if (sp == 0) break;
+            --sp;
+            cur = stack[sp * stride];
+        }
+    }
+    return found;
+}
+
+// ------------------------------------------------------------------------------------------------ ray setup
+// local row -> frame row for a row-block shard
+__device__ __forceinline__ uint32_t frame_row(const Frame& f, uint32_t lrow) {
+    if (f.shard_count <= 1) return lrow;
+    uint32_t blk = lrow / f.block_rows;
+    return (blk * f.shard_count + f.shard_index) * f.block_rows + (lrow - blk * f.block_rows);
+}
+
+// render.hpp:109-111
+__device__ __forceinline__ V3 primary_dir(const Frame& f, uint32_t i, uint32_t j) {
+    float u = sub(__fdiv_rn(mul(2.0f, add((float)i, 0.5f)), (float)f.W), 1.0f);
+    float v = sub(__fdiv_rn(mul(2.0f, add((float)j, 0.5f)), (float)f.H), 1.0f);
+    V3 iu = mk(f.iu[0], f.iu[1], f.iu[2]), iv = mk(f.iv[0], f.iv[1], f.iv[2]), dir = mk(f.dir[0], f.dir[1], f.dir[2]);
+    return vnormalize(vadd(vadd(vscale(iu, u), vscale(iv, v)), dir));
+}
+
+// render.hpp:120-135: hit point with the reference's barycentric convention (Q1), offset along -normal, sun line
+__device__ __forceinline__ void shadow_setup(const Tri& tr, float u, float v, V3 sun, V3& P, V3& sun_line) {
+    V3 normal = vnormalize(tr.n);
+    V3 p1 = vsub(tr.p0, tr.e1), p2 = vadd(tr.p0, tr.e2);       // triangle.hpp:36-37
+    float w = sub(sub(1.0f, u), v);
+    P = vadd(vadd(vscale(tr.p0, u), vscale(p1, v)), vscale(p2, w));
+    const float scale = -0.00001f;
+    P = vadd(P, vscale(normal, scale));
+    sun_line = vnormalize(vsub(sun, P));
+}
+
+// ------------------------------------------------------------------------------------------------ kernels
+#define PRIMARY_THREADS 256
+#define OCCLUDED_BIT 0x80000000u
+
+// One thread per pixel; a warp covers an 8x4 pixel tile, a CTA 32x8 pixels.
+template <bool STATS>
+__global__ void __launch_bounds__(PRIMARY_THREADS) primary_kernel(const DevScene sc, const Frame f) {
+    extern __shared__ uint32_t smem_stack[];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t i = blockIdx.x * 32u + (warp & 3u) * 8u + (lane & 7u);
+    const uint32_t lrow = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
+    const bool valid = i < f.W && lrow < f.rows_local;
+    const uint32_t j = frame_row(f, lrow);
+
+    bool found = false;
+    Hit best; best.slot = 0; best.t = best.u = best.v = 0.0f;
+    uint32_t n_steps = 0, n_tests = 0;
+    if (valid) {
+        V3 view = primary_dir(f, i, j);
+        V3 eye = mk(f.eye[0], f.eye[1], f.eye[2]);
+        found = traverse<false, STATS>(sc, eye, view, 0.0f, FLT_MAX, smem_stack + tid, PRIMARY_THREADS, best, n_steps, n_tests);
+    }
+    __syncwarp();
+    const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
+    if (valid && !found) {   // render.hpp:116-117
+        float* p = f.pixels + 3 * opix;
+        p[0] = 0.0f; p[1] = 0.0f; p[2] = 0.0f;
+        if (f.ids) f.ids[opix] = CERES_MISS;
+    }
+    // ballot compaction of the hits into the record queue (one atomic per warp)
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, found);
+    if (m) {
+        const int leader = __ffs(m) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader) base = atomicAdd(&f.ctr->qcount, (uint32_t)__popc(m));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if (found) {
+            const uint32_t at = base + __popc(m & ((1u << lane) - 1u));
+            // pixel is stored as (local row, column) so that the later passes can rebuild both the frame row and
+            // the output position
+            f.queue[at] = make_uint4(lrow * f.W + i, best.slot, __float_as_uint(best.u), __float_as_uint(best.v));
+        }
+    }
+    if (STATS) {
+        unsigned long long s_m = found ? 0 : n_steps, t_m = found ? 0 : n_tests;
+        unsigned long long s_h = found ? n_steps : 0, t_h = found ? n_tests : 0;
+        for (int o = 16; o; o >>= 1) {
+            s_m += __shfl_xor_sync(0xFFFFFFFFu, s_m, o); t_m += __shfl_xor_sync(0xFFFFFFFFu, t_m, o);
+            s_h += __shfl_xor_sync(0xFFFFFFFFu, s_h, o); t_h += __shfl_xor_sync(0xFFFFFFFFu, t_h, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&f.ctr->stats[0], s_m); atomicAdd(&f.ctr->stats[1], t_m);
+            atomicAdd(&f.ctr->stats[2], s_h); atomicAdd(&f.ctr->stats[3], t_h);
+        }
+    }
+}
+
+// Persistent warps; each steals 32 consecutive records (= one ballot-compacted group of neighbouring pixels).
+#define SHADOW_THREADS 256
+template <bool STATS>
+__global__ void __launch_bounds__(SHADOW_THREADS) shadow_kernel(const DevScene sc, const Frame f) {
+    extern __shared__ uint32_t smem_stack[];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t total = f.ctr->qcount;
+    const V3 sun = mk(f.sun[0], f.sun[1], f.sun[2]);
+    uint32_t occl = 0;
+    unsigned long long st_s = 0, st_t = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&f.ctr->shadow_next, 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= total) break;
+        const uint32_t r = base + lane;
+        if (r < total) {
+            uint4 rec = f.queue[r];
+            Tri tr = load_tri(sc.tris, rec.y);
+            V3 P, sun_line;
+            shadow_setup(tr, __uint_as_float(rec.z), __uint_as_float(rec.w), sun, P, sun_line);
+            Hit h; h.slot = 0; h.t = h.u = h.v = 0.0f;
+            uint32_t n_steps = 0, n_tests = 0;
+            bool hit = traverse<true, STATS>(sc, P, sun_line, 0.0f, FLT_MAX, smem_stack + tid, SHADOW_THREADS, h, n_steps, n_tests);
+            if (hit) { f.queue[r].y = rec.y | OCCLUDED_BIT; occl++; }
+            if (STATS) { st_s += n_steps; st_t += n_tests; }
+        }
+        __syncwarp();
+    }
+    for (int o = 16; o; o >>= 1) occl += __shfl_xor_sync(0xFFFFFFFFu, occl, o);
+    if (lane == 0 && occl) atomicAdd(&f.ctr->occluded, occl);
+    if (STATS) {
+        for (int o = 16; o; o >>= 1) { st_s += __shfl_xor_sync(0xFFFFFFFFu, st_s, o); st_t += __shfl_xor_sync(0xFFFFFFFFu, st_t, o); }
+        if (lane == 0) { atomicAdd(&f.ctr->stats[4], st_s); atomicAdd(&f.ctr->stats[5], st_t); }
+    }
+}
+
+// render.hpp:46-54,56-84.  pow(double(x), 24) by repeated squaring in double (5 roundings, relative error
+// < 3e-16, then narrowed to float like the reference's `return std::pow(...)` in a float function).
+__device__ __forceinline__ float spec_pow24(float x) {
+    double b = (double)x;
+    double b2 = __dmul_rn(b, b), b3 = __dmul_rn(b2, b), b6 = __dmul_rn(b3, b3), b12 = __dmul_rn(b6, b6);
+    return (float)__dmul_rn(b12, b12);
+}
+__device__ __forceinline__ float clamp01(float x) { return x < 0.0f ? 0.0f : (1.0f < x ? 1.0f : x); }
+
+#define SHADE_THREADS 256
+__global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc, const Frame f) {
+    const uint32_t total = f.ctr->qcount;
+    const V3 sun = mk(f.sun[0], f.sun[1], f.sun[2]);
+    for (uint32_t r = blockIdx.x * SHADE_THREADS + threadIdx.x; r < total; r += gridDim.x * SHADE_THREADS) {
+        const uint4 rec = f.queue[r];
+        const uint32_t lrow = rec.x / f.W, i = rec.x - lrow * f.W;
+        const uint32_t j = frame_row(f, lrow);
+        const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
+        const uint32_t slot = rec.y & ~OCCLUDED_BIT;
+        float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+        if (!(rec.y & OCCLUDED_BIT)) {
+            const float u = __uint_as_float(rec.z), v = __uint_as_float(rec.w);
+            Tri tr = load_tri(sc.tris, slot);
+            V3 P, sun_line;
+            shadow_setup(tr, u, v, sun, P, sun_line);
+            V3 view = primary_dir(f, i, j);
+            V3 mview = vscale(view, -1.0f);                      // render.hpp:66
+            V3 h = vnormalize(vadd(sun_line, mview));            // render.hpp:53
+            const float4* np = sc.norms + 3ull * slot;
+            float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2);
+            V3 nk[3] = {mk(a.x, a.y, a.z), mk(a.w, b.x, b.y), mk(b.z, b.w, c.x)};
+            float wk[3] = {u, v, sub(sub(1.0f, u), v)};
+            const float amb = 0.2f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                // lambertian (render.hpp:46-49): abs of the left-to-right sum
+                float diffuse = mul(0.5f, fabsf(add(add(mul(sun_line.x, nk[k].x), mul(sun_line.y, nk[k].y)), mul(sun_line.z, nk[k].z))));
+                float specular = mul(0.8f, spec_pow24(vdot(nk[k], h)));
+                float ad = add(amb, diffuse);
+                c0 = add(c0, mul(wk[k], clamp01(add(mul(ad, 0.5f), specular))));
+                c1 = add(c1, mul(wk[k], clamp01(add(mul(ad, 0.0f), specular))));
+                c2 = add(c2, mul(wk[k], clamp01(add(mul(ad, 0.8f), specular))));
+            }
+        }
+        float* p = f.pixels + 3 * opix;
+        p[0] = c0; p[1] = c1; p[2] = c2;
+        if (f.ids) f.ids[opix] = __ldg(sc.slot_id + slot);
+    }
+    // the last CTA publishes the frame counters and re-arms the per-frame state for the next frame
+    __shared__ bool last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        last = atomicAdd(&f.ctr->done_blocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        const unsigned long long hits = total, occ = f.ctr->occluded;
+        const unsigned long long rays = (unsigned long long)f.W * f.rows_local + hits + 0ull;   // render.hpp:115,138
+        if (f.out_counters) {
+            f.out_counters[0] = f.shadows ? rays : (unsigned long long)f.W * f.rows_local;
+            f.out_counters[1] = hits + occ;                                                       // render.hpp:119,148
+        }
+        if (f.out_stats) {
+            for (int k = 0; k < 6; ++k) f.out_stats[k] = f.ctr->stats[k];
+            f.out_stats[6] = f.shadows ? rays : (unsigned long long)f.W * f.rows_local;
+            f.out_stats[7] = hits + occ;
+        }
+        f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0;
+        for (int k = 0; k < 6; ++k) f.ctr->stats[k] = 0;
+        __threadfence();
+    }
+}
+
+// Known-answer kernel: closest-hit traversal of caller-supplied rays.
+__global__ void __launch_bounds__(256) trace_rays_kernel(const DevScene sc, const float* __restrict__ rays, uint32_t n,
+                                                          uint32_t* __restrict__ out_id, float* __restrict__ out_tuv) {
+    extern __shared__ uint32_t smem_stack[];
+    const uint32_t k = blockIdx.x * 256u + threadIdx.x;
+    if (k >= n) return;
+    const float* r = rays + 8ull * k;
+    Hit best; best.slot = 0; best.t = best.u = best.v = 0.0f;
+    uint32_t a = 0, b = 0;
+    bool found = traverse<false, false>(sc, mk(r[0], r[1], r[2]), mk(r[3], r[4], r[5]), r[6], r[7], smem_stack + threadIdx.x, 256, best, a, b);
+    out_id[k] = found ? __ldg(sc.slot_id + best.slot) : CERES_MISS;
+    out_tuv[3ull * k] = found ? best.t : 0.0f;
+    out_tuv[3ull * k + 1] = found ? best.u : 0.0f;
+    out_tuv[3ull * k + 2] = found ? best.v : 0.0f;
+}
+
+// static.cpp:135-147: rows top-down from j = height..1, uint8(max(min(p*255,255),0)) (truncation) -- one thread
+// per output pixel.
+__global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__ px, uint32_t W, uint32_t H, uint8_t* __restrict__ out) {
+    const size_t n = (size_t)W * H;
+    for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < n; k += (size_t)gridDim.x * 256u) {
+        const uint32_t row_out = (uint32_t)(k / W), i = (uint32_t)(k - (size_t)row_out * W);
+        const uint32_t j = H - 1u - row_out;
+        const float* p = px + 3 * ((size_t)j * W + i);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float x = mul(p[c], 255.0f);
+            // std::min(x, 255) = (255 < x) ? 255 : x ; std::max(y, 0) = (y < 0) ? 0 : y   (first arg returned on NaN)
+            float y = (255.0f < x) ? 255.0f : x;
+            float z = (y < 0.0f) ? 0.0f : y;
+            out[3 * k + c] = (uint8_t)(int)z;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+struct ceres_scene {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    DevScene dev{};
+    void* d_pairs = nullptr; void* d_tris = nullptr; void* d_norms = nullptr; void* d_slot_id = nullptr;
+    size_t scene_bytes = 0;
+    uint32_t tri_count = 0;
+    FrameCounters* d_ctr = nullptr;
+    uint4* d_queue = nullptr; size_t queue_cap = 0;
+    float* d_pixels = nullptr; size_t pixels_cap = 0;      // staging for the host-buffer API
+    uint32_t* d_ids = nullptr; size_t ids_cap = 0;
+    unsigned long long* d_out = nullptr;                    // 2 counters + 8 stats
+    unsigned long long* h_out = nullptr;                    // pinned mirror
+    void* reg_ptr = nullptr; size_t reg_bytes = 0;          // host framebuffer currently page-locked by us
+    bool stats = false;
+    ceres_tuning tune{};
+    int shadow_blocks_per_sm = 0, shadow_blocks_per_sm_stats = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; }
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct RefNode { float bounds[6]; uint32_t primitive_count; uint32_t first_child_or_primitive; };
+static_assert(sizeof(RefNode) == 32, "bvh.hpp:25-30");
+
+// render.hpp:91-97 in binary32, source order (this translation unit's host code is compiled with
+// -ffp-contract=off; tanf is the host libm's, as in the reference)
+void frame_setup_host(const ceres_camera* cam, size_t width, size_t height, float* dir, float* iu, float* iv) {
+    auto dot = [](const float* a, const float* b) { float s = a[0] * b[0]; s += a[1] * b[1]; s += a[2] * b[2]; return s; };
+    auto normalize = [&](float* a) { float inv = 1.0f / std::sqrt(dot(a, a)); a[0] = a[0] * inv; a[1] = a[1] * inv; a[2] = a[2] * inv; };
+    auto cross = [](const float* a, const float* b, float* c) {
+        c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0];
+    };
+    for (int k = 0; k < 3; ++k) dir[k] = cam->dir[k];
+    normalize(dir);
+    cross(dir, cam->up, iu); normalize(iu);
+    cross(iu, dir, iv); normalize(iv);
+    float image_w = std::tan(cam->fov * float(3.14159265 * (1.0 / 180.0) * 0.5));
+    float ratio = float(height) / float(width);
+    for (int k = 0; k < 3; ++k) { iu[k] = iu[k] * image_w; iv[k] = iv[k] * image_w * ratio; }
+}
+
+uint32_t shard_rows(size_t H, const ceres_shard* sh) {
+    if (!sh || sh->count <= 1) return (uint32_t)H;
+    uint32_t n = 0;
+    const uint32_t br = sh->block_rows;
+    for (size_t b = sh->index; b * br < H; b += sh->count) {
+        size_t lo = b * br, hi = lo + br; if (hi > H) hi = H;
+        n += (uint32_t)(hi - lo);
+    }
+    return n;
+}
+
+template <typename T>
+int ensure(T*& p, size_t& cap, size_t need) {
+    if (need <= cap) return CERES_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    CUDA_TRY(cudaMalloc((void**)&p, need * sizeof(T)));
+    cap = need;
+    return CERES_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ceres_abi_version(void) { return CERES_B200_ABI_VERSION; }
+const char* ceres_last_error(void) { return g_err.c_str(); }
+uint64_t ceres_kernel_launch_count(void) { return g_launches.load(); }
+
+int ceres_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+void* ceres_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); g_err = "cudaMallocHost failed"; return nullptr; }
+    return p;
+}
+void ceres_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int ceres_frame_setup(const ceres_camera* camera, size_t width, size_t height, float out[9]) {
+    if (!camera || !out || !width || !height) return fail(CERES_ERR_INVALID, "ceres_frame_setup: null/zero argument");
+    frame_setup_host(camera, width, height, out, out + 3, out + 6);
+    return CERES_OK;
+}
+
+int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* prim_idx, const void* tris_v,
+                       const void* norms_v, size_t tri_count, int device, ceres_scene** out) {
+    if (!out) return fail(CERES_ERR_INVALID, "ceres_scene_create: out is null");
+    *out = nullptr;
+    if (!nodes_v || !prim_idx || !tris_v || !node_count || !tri_count)
+        return fail(CERES_ERR_INVALID, "ceres_scene_create: null or empty scene arrays");
+    if (tri_count >= 0x7FFFFFFFull || node_count >= 0xFFFFFFFFull)
+        return fail(CERES_ERR_INVALID, "ceres_scene_create: scene too large for 31-bit slots");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) return fail(CERES_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(CERES_ERR_INVALID, "ceres_scene_create: bad device index");
+
+    const RefNode* nodes = static_cast<const RefNode*>(nodes_v);
+    const float* tris = static_cast<const float*>(tris_v);
+    const float* norms = static_cast<const float*>(norms_v);
+
+    // ---- flatten: walk the tree from the root, give every inner node's children one pair record ----------------
+    std::vector<float> pairs;            // 16 floats per pair
+    uint32_t root_leaf_count = 0, depth_max = 1;
+    std::vector<uint32_t> slot_id(tri_count);
+    for (size_t k = 0; k < tri_count; ++k) {
+        if (prim_idx[k] >= tri_count) return fail(CERES_ERR_INVALID, "ceres_scene_create: primitive index out of range");
+        slot_id[k] = (uint32_t)prim_idx[k];
+    }
+    const RefNode& root = nodes[0];
+    if (root.primitive_count != 0) {
+        if (root.first_child_or_primitive != 0 || root.primitive_count != tri_count)
+            return fail(CERES_ERR_INVALID, "ceres_scene_create: leaf root must cover all primitives from slot 0");
+        root_leaf_count = root.primitive_count;
+        pairs.assign(16, 0.0f);
+    } else {
+        // depth-first, left child first: pair index = order of first visit.  (pair_of_node, depth) work list.
+        struct Item { uint32_t first_child; uint32_t pair; uint32_t depth; };
+        std::vector<Item> work;
+        pairs.reserve((node_count / 2 + 1) * 16);
+        auto new_pair = [&]() { uint32_t id = (uint32_t)(pairs.size() / 16); pairs.resize(pairs.size() + 16); return id; };
+        size_t visited = 1;
+        work.push_back({root.first_child_or_primitive, new_pair(), 1});
+        while (!work.empty()) {
+            Item it = work.back(); work.pop_back();
+            if ((size_t)it.first_child + 1 >= node_count)
+                return fail(CERES_ERR_INVALID, "ceres_scene_create: child index out of range");
+            visited += 2;
+            if (visited > node_count) return fail(CERES_ERR_INVALID, "ceres_scene_create: BVH is not a tree (cycle or shared nodes)");
+            if (it.depth > depth_max) depth_max = it.depth;
+            uint32_t child_pair[2] = {0, 0};
+            for (int c = 0; c < 2; ++c) {
+                const RefNode& n = nodes[it.first_child + c];
+                float* q = &pairs[(size_t)it.pair * 16 + 8 * c];
+                for (int b = 0; b < 6; ++b) q[b] = n.bounds[b];
+                uint32_t cnt = n.primitive_count, first = n.first_child_or_primitive;
+                if (cnt != 0) {
+                    if ((size_t)first + cnt > tri_count) return fail(CERES_ERR_INVALID, "ceres_scene_create: leaf range out of bounds");
+                } else {
+                    first = new_pair();
+                    child_pair[c] = first;
+                }
+                std::memcpy(&pairs[(size_t)it.pair * 16 + 8 * c + 6], &cnt, 4);
+                std::memcpy(&pairs[(size_t)it.pair * 16 + 8 * c + 7], &first, 4);
+            }
+            for (int c = 1; c >= 0; --c) {
+                const RefNode& n = nodes[it.first_child + c];
+                if (n.primitive_count == 0) work.push_back({n.first_child_or_primitive, child_pair[c], it.depth + 1});
+            }
+        }
+    }
+    if (depth_max > 64) return fail(CERES_ERR_UNSUPPORTED, "ceres_scene_create: BVH deeper than the reference's 64-entry stack");
+
+    // leaf-ordered triangles and normals
+    std::vector<float> tri_slots(tri_count * 12), norm_slots(tri_count * 12, 0.0f);
+    for (size_t s = 0; s < tri_count; ++s) {
+        std::memcpy(&tri_slots[s * 12], tris + (size_t)slot_id[s] * 12, 48);
+        if (norms) std::memcpy(&norm_slots[s * 12], norms + (size_t)slot_id[s] * 9, 36);
+    }
+
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CERES_ERR_CUDA, "cudaSetDevice failed");
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(CERES_ERR_NO_DEVICE, std::string("device is not Blackwell-class (sm_100a required): ") + prop.name);
+
+    ceres_scene* s = new (std::nothrow) ceres_scene;
+    if (!s) return fail(CERES_ERR_INVALID, "out of host memory");
+    s->device = device;
+    s->sm_count = prop.multiProcessorCount;
+    s->tri_count = (uint32_t)tri_count;
+    auto bail = [&](int code) { ceres_scene_destroy(s); return code; };
+#define TRY_S(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); return bail(CERES_ERR_CUDA); } } while (0)
+    TRY_S(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    const size_t pb = pairs.size() * 4, tb = tri_slots.size() * 4, nb = norm_slots.size() * 4, ib = slot_id.size() * 4;
+    TRY_S(cudaMalloc(&s->d_pairs, pb));
+    TRY_S(cudaMalloc(&s->d_tris, tb));
+    TRY_S(cudaMalloc(&s->d_norms, nb));
+    TRY_S(cudaMalloc(&s->d_slot_id, ib));
+    TRY_S(cudaMalloc((void**)&s->d_ctr, sizeof(FrameCounters)));
+    TRY_S(cudaMalloc((void**)&s->d_out, 10 * sizeof(unsigned long long)));
+    TRY_S(cudaMallocHost((void**)&s->h_out, 10 * sizeof(unsigned long long)));
+    TRY_S(cudaMemcpy(s->d_pairs, pairs.data(), pb, cudaMemcpyHostToDevice));
+    TRY_S(cudaMemcpy(s->d_tris, tri_slots.data(), tb, cudaMemcpyHostToDevice));
+    TRY_S(cudaMemcpy(s->d_norms, norm_slots.data(), nb, cudaMemcpyHostToDevice));
+    TRY_S(cudaMemcpy(s->d_slot_id, slot_id.data(), ib, cudaMemcpyHostToDevice));
+    TRY_S(cudaMemset(s->d_ctr, 0, sizeof(FrameCounters)));
+    TRY_S(cudaMemset(s->d_out, 0, 10 * sizeof(unsigned long long)));
+#undef TRY_S
+    s->scene_bytes = pb + tb + nb + ib;
+    s->dev.pairs = (const float4*)s->d_pairs;
+    s->dev.tris = (const float4*)s->d_tris;
+    s->dev.norms = (const float4*)s->d_norms;
+    s->dev.slot_id = (const uint32_t*)s->d_slot_id;
+    s->dev.root_leaf_count = root_leaf_count;
+    s->dev.stack_depth = depth_max;
+    *out = s;
+    return CERES_OK;
+}
+
+void ceres_scene_destroy(ceres_scene* s) {
+    if (!s) return;
+    DeviceGuard guard(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->reg_ptr) cudaHostUnregister(s->reg_ptr);
+    cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
+    cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_out);
+    if (s->h_out) cudaFreeHost(s->h_out);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    cudaGetLastError();
+    delete s;
+}
+
+size_t ceres_scene_device_bytes(const ceres_scene* s) { return s ? s->scene_bytes : 0; }
+
+int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
+    if (!s) return fail(CERES_ERR_INVALID, "null scene");
+    if (t) s->tune = *t; else s->tune = ceres_tuning{};
+    s->shadow_blocks_per_sm = s->shadow_blocks_per_sm_stats = 0;
+    return CERES_OK;
+}
+
+int ceres_scene_set_stats(ceres_scene* s, int enable) {
+    if (!s) return fail(CERES_ERR_INVALID, "null scene");
+    s->stats = enable != 0;
+    return CERES_OK;
+}
+
+int ceres_scene_get_stats(ceres_scene* s, uint64_t stats[8]) {
+    if (!s || !stats) return fail(CERES_ERR_INVALID, "null argument");
+    DeviceGuard guard(s->device);
+    unsigned long long tmp[10];
+    CUDA_TRY(cudaMemcpy(tmp, s->d_out, sizeof tmp, cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 8; ++k) stats[k] = tmp[2 + k];
+    return CERES_OK;
+}
+
+int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
+                        unsigned flags, const ceres_shard* shard, void* stream_v, float* d_pixels, uint32_t* d_ids,
+                        uint64_t* d_counters) {
+    if (!s || !cam || !sun || !d_pixels) return fail(CERES_ERR_INVALID, "ceres_render_device: null argument");
+    if (!width || !height || width > 65535u * 32u || (uint64_t)width * height >= (1ull << 32))
+        return fail(CERES_ERR_INVALID, "ceres_render_device: bad image size");
+    if (shard && shard->count > 1 && (shard->block_rows == 0 || shard->index >= shard->count))
+        return fail(CERES_ERR_INVALID, "ceres_render_device: bad shard");
+    DeviceGuard guard(s->device);
+    cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
+
+    Frame f{};
+    for (int k = 0; k < 3; ++k) { f.eye[k] = cam->eye[k]; f.sun[k] = sun[k]; }
+    frame_setup_host(cam, width, height, f.dir, f.iu, f.iv);
+    f.W = (uint32_t)width; f.H = (uint32_t)height;
+    f.rows_local = shard_rows(height, shard);
+    const bool sharded = shard && shard->count > 1;
+    f.block_rows = sharded ? shard->block_rows : (uint32_t)height;
+    f.shard_index = sharded ? shard->index : 0;
+    f.shard_count = sharded ? shard->count : 1;
+    f.compact = (flags & CERES_COMPACT_ROWS) ? 1u : 0u;
+    f.shadows = (flags & CERES_NO_SHADOWS) ? 0u : 1u;
+    f.pixels = d_pixels; f.ids = d_ids;
+    f.out_counters = d_counters ? (unsigned long long*)d_counters : s->d_out;
+    f.out_stats = s->stats ? s->d_out + 2 : nullptr;
+    f.ctr = s->d_ctr;
+    if (f.rows_local == 0) return CERES_OK;
+
+    const size_t npix = (size_t)f.rows_local * width;
+    if (int rc = ensure(s->d_queue, s->queue_cap, npix)) return rc;
+    f.queue = s->d_queue;
+
+    const size_t smem_p = (size_t)s->dev.stack_depth * 4 * PRIMARY_THREADS;
+    const size_t smem_s = (size_t)s->dev.stack_depth * 4 * SHADOW_THREADS;
+    dim3 grid((unsigned)((width + 31) / 32), (unsigned)((f.rows_local + 7) / 8));
+    if (grid.y > 65535u) return fail(CERES_ERR_INVALID, "ceres_render_device: image too tall");
+    if (s->stats) primary_kernel<true><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
+    else primary_kernel<false><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
+    g_launches++;
+    if (f.shadows) {
+        int& bps = s->stats ? s->shadow_blocks_per_sm_stats : s->shadow_blocks_per_sm;
+        if (bps == 0) {
+            if (s->tune.ctas_per_sm) bps = (int)s->tune.ctas_per_sm;
+            else if (s->stats) CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, shadow_kernel<true>, SHADOW_THREADS, smem_s));
+            else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, shadow_kernel<false>, SHADOW_THREADS, smem_s));
+            if (bps < 1) bps = 1;
+        }
+        const unsigned g = (unsigned)(s->sm_count * bps);
+        if (s->stats) shadow_kernel<true><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
+        else shadow_kernel<false><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
+        g_launches++;
+    }
+    shade_kernel<<<(unsigned)(s->sm_count * 4), SHADE_THREADS, 0, st>>>(s->dev, f);
+    g_launches++;
+    CUDA_TRY(cudaGetLastError());
+    return CERES_OK;
+}
+
+static int pin_host_buffer(ceres_scene* s, void* p, size_t bytes) {
+    // The reference's callers reuse one framebuffer for every frame (anim.cpp:76,105); page-lock it once so the
+    // D2H copy runs at PCIe speed, and keep the registration until another buffer shows up.
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost) return CERES_OK;  // already pinned
+    cudaGetLastError();
+    if (s->reg_ptr == p && s->reg_bytes >= bytes) return CERES_OK;
+    if (s->reg_ptr) { cudaHostUnregister(s->reg_ptr); s->reg_ptr = nullptr; s->reg_bytes = 0; }
+    if (cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) { s->reg_ptr = p; s->reg_bytes = bytes; }
+    else cudaGetLastError();  // pageable copy still works, just slower
+    return CERES_OK;
+}
+
+int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
+                       unsigned flags, const ceres_shard* shard, float* pixels, uint32_t* ids, uint64_t counters[2]) {
+    if (!s || !pixels) return fail(CERES_ERR_INVALID, "ceres_render: null argument");
+    DeviceGuard guard(s->device);
+    const size_t npix = width * height;
+    if (int rc = ensure(s->d_pixels, s->pixels_cap, npix * 3)) return rc;
+    if (ids) if (int rc = ensure(s->d_ids, s->ids_cap, npix)) return rc;
+    // device staging is written in COMPACT form (the shard's rows packed); rows are scattered to their frame
+    // position by the copies below, so a shard moves only its own bytes over PCIe.
+    const bool sharded = shard && shard->count > 1;
+    const unsigned dev_flags = flags | (sharded ? CERES_COMPACT_ROWS : 0u);
+    if (int rc = ceres_render_device(s, cam, sun, width, height, dev_flags, shard, nullptr, s->d_pixels, ids ? s->d_ids : nullptr, nullptr)) return rc;
+    const uint32_t rows = shard_rows(height, shard);
+    const bool want_compact = (flags & CERES_COMPACT_ROWS) != 0;
+    if (!sharded || want_compact) {
+        const size_t n = (size_t)rows * width;
+        pin_host_buffer(s, pixels, n * 3 * sizeof(float));
+        CUDA_TRY(cudaMemcpyAsync(pixels, s->d_pixels, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+        if (ids) CUDA_TRY(cudaMemcpyAsync(ids, s->d_ids, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+    } else {
+        pin_host_buffer(s, pixels, npix * 3 * sizeof(float));
+        const uint32_t br = shard->block_rows;
+        size_t lrow = 0;
+        for (size_t b = shard->index; b * br < height; b += shard->count) {
+            size_t lo = b * br, hi = lo + br; if (hi > height) hi = height;
+            const size_t n = (hi - lo) * width;
+            CUDA_TRY(cudaMemcpyAsync(pixels + 3 * lo * width, s->d_pixels + 3 * lrow * width, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+            if (ids) CUDA_TRY(cudaMemcpyAsync(ids + lo * width, s->d_ids + lrow * width, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+            lrow += hi - lo;
+        }
+    }
+    CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (counters) { counters[0] = s->h_out[0]; counters[1] = s->h_out[1]; }
+    return CERES_OK;
+}
+
+int ceres_render(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
+                 unsigned flags, float* pixels, uint32_t* ids, uint64_t counters[2]) {
+    return ceres_render_shard(s, cam, sun, width, height, flags & ~CERES_COMPACT_ROWS, nullptr, pixels, ids, counters);
+}
+
+int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height,
+                          unsigned flags, float* pixels_all, uint64_t* counters_all) {
+    if (!s || !cams || !pixels_all) return fail(CERES_ERR_INVALID, "ceres_render_sequence: null argument");
+    if (!n_frames) return CERES_OK;
+    DeviceGuard guard(s->device);
+    const size_t npix = width * height, fbytes = npix * 3 * sizeof(float);
+    // two device framebuffers: frame k renders on the scene stream while frame k-1 drains over PCIe on a copy stream
+    float* d_fb[2] = {nullptr, nullptr};
+    unsigned long long* d_cnt = nullptr;
+    cudaStream_t copy = nullptr;
+    cudaEvent_t rendered[2] = {nullptr, nullptr}, copied[2] = {nullptr, nullptr};
+    int rc = CERES_OK;
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(s->stream);
+        if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
+        for (int k = 0; k < 2; ++k) { cudaFree(d_fb[k]); if (rendered[k]) cudaEventDestroy(rendered[k]); if (copied[k]) cudaEventDestroy(copied[k]); }
+        cudaFree(d_cnt);
+    };
+#define TRY_Q(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); cleanup(); return CERES_ERR_CUDA; } } while (0)
+    TRY_Q(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+        TRY_Q(cudaMalloc((void**)&d_fb[k], fbytes));
+        TRY_Q(cudaEventCreateWithFlags(&rendered[k], cudaEventDisableTiming));
+        TRY_Q(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
+    }
+    TRY_Q(cudaMalloc((void**)&d_cnt, n_frames * 2 * sizeof(unsigned long long)));
+    pin_host_buffer(s, pixels_all, n_frames * fbytes);
+    for (size_t k = 0; k < n_frames; ++k) {
+        const float* c = cams + 13 * k;
+        ceres_camera cam;
+        for (int q = 0; q < 3; ++q) { cam.eye[q] = c[q]; cam.dir[q] = c[3 + q]; cam.up[q] = c[6 + q]; }
+        cam.fov = c[9];
+        const int b = (int)(k & 1);
+        if (k >= 2) TRY_Q(cudaStreamWaitEvent(s->stream, copied[b], 0));
+        rc = ceres_render_device(s, &cam, c + 10, width, height, flags & ~CERES_COMPACT_ROWS, nullptr, nullptr, d_fb[b], nullptr,
+                                 (uint64_t*)(d_cnt + 2 * k));
+        if (rc) { cleanup(); return rc; }
+        TRY_Q(cudaEventRecord(rendered[b], s->stream));
+        TRY_Q(cudaStreamWaitEvent(copy, rendered[b], 0));
+        TRY_Q(cudaMemcpyAsync(pixels_all + k * npix * 3, d_fb[b], fbytes, cudaMemcpyDeviceToHost, copy));
+        TRY_Q(cudaEventRecord(copied[b], copy));
+    }
+    TRY_Q(cudaStreamSynchronize(s->stream));
+    TRY_Q(cudaStreamSynchronize(copy));
+    if (counters_all) TRY_Q(cudaMemcpy(counters_all, d_cnt, n_frames * 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+#undef TRY_Q
+    cleanup();
+    return CERES_OK;
+}
+
+int ceres_trace_rays(ceres_scene* s, const float* rays, size_t n, uint32_t* out_id, float* out_tuv) {
+    if (!s || !rays || !out_id || !out_tuv) return fail(CERES_ERR_INVALID, "ceres_trace_rays: null argument");
+    if (n >= (1ull << 31)) return fail(CERES_ERR_INVALID, "ceres_trace_rays: too many rays");
+    if (!n) return CERES_OK;
+    for (size_t k = 0; k < n; ++k)
+        if (std::isnan(rays[8 * k + 6]) || std::isnan(rays[8 * k + 7]))
+            return fail(CERES_ERR_INVALID, "ceres_trace_rays: tmin/tmax must not be NaN");
+    DeviceGuard guard(s->device);
+    float* d_rays = nullptr; uint32_t* d_id = nullptr; float* d_tuv = nullptr;
+    auto cleanup = [&]() { cudaFree(d_rays); cudaFree(d_id); cudaFree(d_tuv); };
+#define TRY_T(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); cleanup(); return CERES_ERR_CUDA; } } while (0)
+    TRY_T(cudaMalloc((void**)&d_rays, n * 8 * sizeof(float)));
+    TRY_T(cudaMalloc((void**)&d_id, n * sizeof(uint32_t)));
+    TRY_T(cudaMalloc((void**)&d_tuv, n * 3 * sizeof(float)));
+    TRY_T(cudaMemcpyAsync(d_rays, rays, n * 8 * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    trace_rays_kernel<<<(unsigned)((n + 255) / 256), 256, (size_t)s->dev.stack_depth * 4 * 256, s->stream>>>(s->dev, d_rays, (uint32_t)n, d_id, d_tuv);
+    g_launches++;
+    TRY_T(cudaGetLastError());
+    TRY_T(cudaMemcpyAsync(out_id, d_id, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+    TRY_T(cudaMemcpyAsync(out_tuv, d_tuv, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    TRY_T(cudaStreamSynchronize(s->stream));
+#undef TRY_T
+    cleanup();
+    return CERES_OK;
+}
+
+int ceres_quantize_device(ceres_scene* s, const float* d_pixels, size_t width, size_t height, void* stream_v, uint8_t* d_rgb8) {
+    if (!s || !d_pixels || !d_rgb8 || !width || !height) return fail(CERES_ERR_INVALID, "ceres_quantize_device: null/zero argument");
+    DeviceGuard guard(s->device);
+    cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
+    quantize_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(d_pixels, (uint32_t)width, (uint32_t)height, d_rgb8);
+    g_launches++;
+    CUDA_TRY(cudaGetLastError());
+    return CERES_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+/* ceres_b200.h -- C ABI of the B200-native ceres-raytracer render loop.
+ *
+ * This is the drop-in boundary for ONE call of the reference:
+ *
+ *     std::pair<int,int> render(const Camera<Scalar>&, const Vector3<Scalar>& sun_position, const Bvh<Scalar>&,
+ *                               const Triangle<Scalar>* triangles, std::array<Vector3<Scalar>,3>* tri_norms,
+ *                               Scalar* pixels, size_t width, size_t height);      (include/render.hpp:86-89)
+ *
+ * as called from the frame loop of include/anim.cpp:105 and from include/static.cpp:130.  The reference has no
+ * FFI layer; the functions below are what a binding of that call would bind (see INTEGRATION.md for the C++
+ * shim with the identical template signature, include/ceres/render.hpp, and for a ctypes stub).
+ *
+ * Plain pointers and sizes only.  All input arrays use the reference's own POD layouts (Scalar = float):
+ *   nodes      bvh::Bvh<float>::Node, 32 B  {float bounds[6] /*minx,maxx,miny,maxy,minz,maxz*\/;
+ *                                            uint32 primitive_count; uint32 first_child_or_primitive}
+ *                                                                                   (lib/bvh/bvh.hpp:25-30)
+ *   prim_idx   size_t[tri_count]            Bvh::primitive_indices                  (lib/bvh/bvh.hpp:94)
+ *   tris       bvh::Triangle<float>, 48 B   {p0, e1, e2, n}                          (lib/bvh/triangle.hpp:27)
+ *   tri_norms  std::array<Vector3<float>,3>, 36 B                                    (lib/obj_norms.hpp:113-115)
+ *
+ * There is NO CPU fallback: every entry point that computes fails with CERES_ERR_NO_DEVICE / CERES_ERR_CUDA when
+ * no sm_100 device is usable.  Scalar = double (anim -d, include/anim.cpp:154-155) is not provided.
+ * A ceres_scene is not thread-safe; use one per host thread / per GPU.
+ */
+#ifndef CERES_B200_H
+#define CERES_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CERES_B200_ABI_VERSION 1
+
+enum {
+    CERES_OK = 0,
+    CERES_ERR_INVALID = 1,     /* bad argument / malformed BVH */
+    CERES_ERR_CUDA = 2,        /* a CUDA runtime call failed; see ceres_last_error() */
+    CERES_ERR_NO_DEVICE = 3,   /* no usable GPU (the library never computes on the CPU) */
+    CERES_ERR_UNSUPPORTED = 4
+};
+
+/* flags for the render calls */
+#define CERES_NO_SHADOWS   1u  /* skip the sun shadow ray (render.hpp:135-137) and shade every primary hit
+                                  ("primary rays only", BASELINE.json configs 1-2; not a mode of the reference) */
+#define CERES_COMPACT_ROWS 2u  /* sharded render: write the shard's rows packed, not at their frame position */
+
+#define CERES_MISS 0xFFFFFFFFu /* value of ids[] where the primary ray hit nothing */
+
+typedef struct ceres_scene ceres_scene;
+
+/* Camera<float>, include/render.hpp:16-22 (fov in degrees) */
+typedef struct ceres_camera {
+    float eye[3];
+    float dir[3];
+    float up[3];
+    float fov;
+} ceres_camera;
+
+/* Row-block sharding of one frame across GPUs: rows are grouped in blocks of `block_rows`,
+ * block b belongs to shard b % count.  {0,0,1} or NULL = the whole frame. */
+typedef struct ceres_shard {
+    uint32_t block_rows;
+    uint32_t index;
+    uint32_t count;
+} ceres_shard;
+
+/* Kernel tuning knobs (0 = library default).  Exposed so bench.py/tests can sweep them; results never depend
+ * on them. */
+typedef struct ceres_tuning {
+    uint32_t variant;            /* 0 default; see DESIGN.md "kernel variants" */
+    uint32_t primary_block;      /* threads per CTA, primary kernel */
+    uint32_t shadow_block;       /* threads per CTA, shadow kernel */
+    uint32_t ctas_per_sm;        /* persistent CTAs per SM */
+    uint32_t reserved[4];
+} ceres_tuning;
+
+/* ---- scene ------------------------------------------------------------------------------------------------- */
+
+/* Flattens the reference BVH + triangles + normals and uploads them ONCE to `device` (replaces the per-call
+ * pointer arguments bvh/triangles/tri_norms of render.hpp:86-89; the reference also builds them once, outside
+ * the frame loop, anim.cpp:46-65).  tri_norms may be NULL (zeros; shading then yields NaN exactly as the
+ * reference would with zero normals). */
+int ceres_scene_create(const void* nodes, size_t node_count, const size_t* prim_idx, const void* tris,
+                       const void* tri_norms, size_t tri_count, int device, ceres_scene** out);
+void ceres_scene_destroy(ceres_scene* scene);
+int ceres_scene_set_tuning(ceres_scene* scene, const ceres_tuning* tuning);
+/* bytes of device memory held by the flattened scene */
+size_t ceres_scene_device_bytes(const ceres_scene* scene);
+
+/* ---- render: host buffers (the drop-in for render.hpp:86-156) ------------------------------------------------ */
+
+/* pixels: caller-owned HOST buffer of 3*width*height floats, layout pixels[3*(width*j+i)+c], row j=0 is v=-1,
+ * every pixel written (render.hpp:107,117,144-149).  ids (nullable): HOST uint32[width*height], primitive index of
+ * the primary hit (hit->primitive_index, render.hpp:120) or CERES_MISS.  counters (nullable): [0] = rays
+ * (= width*height + primary hits), [1] = hits (= primary hits + occluded shadow rays), the pair render()
+ * returns (render.hpp:155).  Blocks until the frame is in `pixels`. */
+int ceres_render(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
+                 size_t width, size_t height, unsigned flags, float* pixels, uint32_t* ids, uint64_t counters[2]);
+
+/* Same, one shard of the frame.  Without CERES_COMPACT_ROWS only the shard's rows of pixels/ids are written. */
+int ceres_render_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
+                       size_t width, size_t height, unsigned flags, const ceres_shard* shard,
+                       float* pixels, uint32_t* ids, uint64_t counters[2]);
+
+/* N frames with one upload of the camera path: cams = n_frames x 13 floats (eye[3],dir[3],up[3],fov,sun[3]),
+ * the per-frame values of anim.cpp:87-89; pixels_all = n_frames frames back to back; counters_all (nullable)
+ * 2 per frame.  D2H of frame k overlaps the render of frame k+1. */
+int ceres_render_sequence(ceres_scene* scene, size_t n_frames, const float* cams, size_t width, size_t height,
+                          unsigned flags, float* pixels_all, uint64_t* counters_all);
+
+/* ---- render: device buffers (asynchronous; used by bench.py, multi-GPU gather and the host calls above) ------- */
+
+/* Enqueues the frame on `stream` (a cudaStream_t; NULL = the scene's own stream) and returns.  d_pixels / d_ids /
+ * d_counters are DEVICE pointers on the scene's device (d_ids, d_counters nullable; d_counters = 2 x uint64). */
+int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
+                        size_t width, size_t height, unsigned flags, const ceres_shard* shard, void* stream,
+                        float* d_pixels, uint32_t* d_ids, uint64_t* d_counters);
+
+/* Per-frame work statistics of the LAST ceres_render_device call on this scene, read back after the stream has
+ * been synchronised: stats[0..7] = {S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow,rays,hits} where S = node-pair
+ * steps and T = triangle tests actually executed by the GPU (shadow rays exit at the first hit, so S_shadow and
+ * T_shadow are smaller than the reference's closest-hit figures).  Only filled when the scene was put in
+ * statistics mode with ceres_scene_set_stats(scene, 1) (slower kernels). */
+int ceres_scene_set_stats(ceres_scene* scene, int enable);
+int ceres_scene_get_stats(ceres_scene* scene, uint64_t stats[8]);
+
+/* ---- known-answer entry points (tests) ----------------------------------------------------------------------- */
+
+/* Closest-hit traversal of arbitrary rays through the scene (single_ray_traverser.hpp:142-154 with
+ * ClosestPrimitiveIntersector).  rays: HOST n x 8 floats (origin[3], direction[3], tmin, tmax).  out_id: HOST
+ * uint32[n]; out_tuv: HOST n x 3 floats (t,u,v; zeros on miss). */
+int ceres_trace_rays(ceres_scene* scene, const float* rays, size_t n, uint32_t* out_id, float* out_tuv);
+
+/* Frame setup of render.hpp:91-97 on the host: out = dir[3], image_u[3], image_v[3]. */
+int ceres_frame_setup(const ceres_camera* camera, size_t width, size_t height, float out[9]);
+
+/* ---- framebuffer post-processing on the device (the step after the path, static.cpp:135-147) ------------------ */
+
+/* float RGB -> 8-bit, vertically flipped (row height-1 first), uint8(max(min(p*255,255),0)): the payload of the
+ * reference's P6 PPM.  d_rgb8: DEVICE 3*width*height bytes. */
+int ceres_quantize_device(ceres_scene* scene, const float* d_pixels, size_t width, size_t height, void* stream,
+                          uint8_t* d_rgb8);
+
+/* ---- pinned host memory helpers ------------------------------------------------------------------------------ */
+void* ceres_host_alloc(size_t bytes);
+void ceres_host_free(void* p);
+
+/* ---- misc --------------------------------------------------------------------------------------------------- */
+int ceres_abi_version(void);
+int ceres_device_count(void);
+/* launches of this library's kernels since load (all scenes); bench.py reports the delta as gpu_launches */
+uint64_t ceres_kernel_launch_count(void);
+/* thread-local description of the last failure */
+const char* ceres_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CERES_B200_H */
