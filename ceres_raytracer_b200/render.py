@@ -1,0 +1,208 @@
+"""Host-side mirror of the reference's render interface (include/render.hpp) over the C ABI.
+
+    Camera(eye, dir, up, fov)                                   render.hpp:16-22
+    render(camera, sun_position, scene, pixels, width, height)  render.hpp:86-89 -> (rays, hits)
+
+`scene` replaces the (bvh, triangles, tri_norms) triple: it is created once from the reference's POD arrays and
+lives on the GPU (the reference also builds them once, outside the frame loop, anim.cpp:46-65).
+numpy arrays are host buffers; torch CUDA tensors are used only as device memory / streams for the *_device calls.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from typing import Sequence
+
+import numpy as np
+
+from . import _capi
+from ._capi import NO_SHADOWS, COMPACT_ROWS, MISS, CeresError  # noqa: F401
+
+NODE_DT = np.dtype([("bounds", "<f4", (6,)), ("primitive_count", "<u4"), ("first_child_or_primitive", "<u4")])
+
+
+@dataclass
+class Camera:
+    """Camera<float> (render.hpp:16-22); fov in degrees."""
+    eye: Sequence[float]
+    dir: Sequence[float]
+    up: Sequence[float]
+    fov: float
+
+    def c(self):
+        cam = _capi.Camera()
+        for k in range(3):
+            cam.eye[k], cam.dir[k], cam.up[k] = float(self.eye[k]), float(self.dir[k]), float(self.up[k])
+        cam.fov = float(self.fov)
+        return cam
+
+    def as_array(self):
+        return np.asarray(list(self.eye) + list(self.dir) + list(self.up) + [self.fov], np.float32)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _shard(shard):
+    if shard is None:
+        return None
+    block_rows, index, count = shard
+    return _capi.Shard(int(block_rows), int(index), int(count))
+
+
+def shard_rows(H, shard):
+    """Frame rows owned by a shard (block_rows, index, count), in local order."""
+    if shard is None or shard[2] <= 1:
+        return np.arange(H)
+    br, idx, cnt = shard
+    rows = []
+    b = idx
+    while b * br < H:
+        rows.extend(range(b * br, min((b + 1) * br, H)))
+        b += cnt
+    return np.asarray(rows, dtype=np.int64)
+
+
+def frame_setup(camera, width, height):
+    """dir, image_u, image_v of render.hpp:91-97."""
+    out = np.empty(9, np.float32)
+    _capi.check(_capi.lib().ceres_frame_setup(C.byref(camera.c()), width, height, _p(out)))
+    return out[0:3].copy(), out[3:6].copy(), out[6:9].copy()
+
+
+class Scene:
+    """Flattened BVH + triangles + normals resident on one GPU (ceres_scene)."""
+
+    def __init__(self, nodes, prim_indices, triangles, tri_norms=None, device=0):
+        L = _capi.lib()
+        nodes = np.ascontiguousarray(nodes)
+        if nodes.dtype.itemsize != 32:
+            nodes = np.ascontiguousarray(nodes).view(np.uint8).reshape(-1, 32)
+        idx = np.ascontiguousarray(prim_indices, dtype=np.uint64)
+        tris = np.ascontiguousarray(triangles, dtype=np.float32).reshape(-1, 12)
+        norms = np.ascontiguousarray(tri_norms, dtype=np.float32).reshape(-1, 9) if tri_norms is not None else None
+        if idx.shape[0] != tris.shape[0] or (norms is not None and norms.shape[0] != tris.shape[0]):
+            raise ValueError("prim_indices / triangles / tri_norms length mismatch")
+        h = C.c_void_p()
+        _capi.check(L.ceres_scene_create(_p(nodes), nodes.shape[0], _p(idx), _p(tris), _p(norms), tris.shape[0],
+                                         int(device), C.byref(h)))
+        self._h, self._L = h, L
+        self.device = int(device)
+        self.node_count, self.tri_count = int(nodes.shape[0]), int(tris.shape[0])
+
+    @classmethod
+    def from_pod(cls, pod, device=0):
+        return cls(pod["nodes"], pod["prim_indices"], pod["triangles"], pod.get("norms"), device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ceres_scene_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def device_bytes(self):
+        return int(self._L.ceres_scene_device_bytes(self._h))
+
+    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0):
+        t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm)
+        _capi.check(self._L.ceres_scene_set_tuning(self._h, C.byref(t)))
+
+    def set_stats(self, enable):
+        _capi.check(self._L.ceres_scene_set_stats(self._h, int(bool(enable))))
+
+    def get_stats(self):
+        out = np.zeros(8, np.uint64)
+        _capi.check(self._L.ceres_scene_get_stats(self._h, _p(out)))
+        names = ["S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "rays", "hits"]
+        return {k: int(v) for k, v in zip(names, out)}
+
+    # ---- host buffers ---------------------------------------------------------------------------------------
+    def render(self, camera, sun_position, width, height, flags=0, pixels=None, want_ids=False, shard=None):
+        """Returns (pixels[H,W,3] float32, ids[H,W] uint32 or None, (rays, hits))."""
+        rows = len(shard_rows(height, shard)) if (shard is not None and flags & COMPACT_ROWS) else height
+        if pixels is None:
+            pixels = np.zeros((rows, width, 3), np.float32) if shard is not None else np.empty((rows, width, 3), np.float32)
+        if pixels.dtype != np.float32 or not pixels.flags.c_contiguous or pixels.size != rows * width * 3:
+            raise ValueError("pixels must be a C-contiguous float32 buffer of 3*width*height")
+        ids = (np.full((rows, width), MISS, np.uint32) if shard is not None else np.empty((rows, width), np.uint32)) if want_ids else None
+        sun = np.asarray(sun_position, np.float32)
+        cnt = np.zeros(2, np.uint64)
+        sh = _shard(shard)
+        _capi.check(self._L.ceres_render_shard(self._h, C.byref(camera.c()), _p(sun), width, height, flags,
+                                               C.byref(sh) if sh is not None else None, _p(pixels), _p(ids), _p(cnt)))
+        return pixels, ids, (int(cnt[0]), int(cnt[1]))
+
+    def render_sequence(self, cams, width, height, flags=0, pixels_all=None):
+        """cams: (n,13) float32 rows of eye,dir,up,fov,sun.  Returns (pixels[n,H,W,3], counters[n,2])."""
+        cams = np.ascontiguousarray(cams, np.float32).reshape(-1, 13)
+        n = cams.shape[0]
+        if pixels_all is None:
+            pixels_all = np.empty((n, height, width, 3), np.float32)
+        cnt = np.zeros((n, 2), np.uint64)
+        _capi.check(self._L.ceres_render_sequence(self._h, n, _p(cams), width, height, flags, _p(pixels_all), _p(cnt)))
+        return pixels_all, cnt
+
+    def trace_rays(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        ids = np.empty(rays.shape[0], np.uint32)
+        tuv = np.empty((rays.shape[0], 3), np.float32)
+        _capi.check(self._L.ceres_trace_rays(self._h, _p(rays), rays.shape[0], _p(ids), _p(tuv)))
+        return ids, tuv
+
+    # ---- device buffers (torch tensors as plain device memory) -----------------------------------------------
+    def render_device(self, camera, sun_position, width, height, flags=0, shard=None, pixels=None, ids=None,
+                      counters=None, stream=None):
+        """Enqueue one frame on `stream` (int cudaStream_t; default torch's current stream).  pixels: float32 CUDA
+        tensor with 3*rows*width elements; ids: int32/uint32 CUDA tensor or None; counters: int64 CUDA tensor[2]."""
+        import torch
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        sun = np.asarray(sun_position, np.float32)
+        sh = _shard(shard)
+        _capi.check(self._L.ceres_render_device(
+            self._h, C.byref(camera.c()), _p(sun), width, height, flags, C.byref(sh) if sh is not None else None,
+            C.c_void_p(stream), C.c_void_p(pixels.data_ptr()), C.c_void_p(ids.data_ptr()) if ids is not None else None,
+            C.c_void_p(counters.data_ptr()) if counters is not None else None))
+
+    def quantize_device(self, pixels, width, height, out, stream=None):
+        import torch
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        _capi.check(self._L.ceres_quantize_device(self._h, C.c_void_p(pixels.data_ptr()), width, height,
+                                                  C.c_void_p(stream), C.c_void_p(out.data_ptr())))
+
+
+def render(camera, sun_position, scene, pixels, width, height, flags=0):
+    """Drop-in for render.hpp:86-156: fills `pixels` (float32, 3*width*height, index 3*(width*j+i)) and returns
+    the pair (rays, hits) of render.hpp:155."""
+    _, _, counters = scene.render(camera, sun_position, width, height, flags=flags, pixels=pixels)
+    return counters
+
+
+def kernel_launch_count():
+    return int(_capi.lib().ceres_kernel_launch_count())
+
+
+def device_count():
+    return int(_capi.lib().ceres_device_count())
+
+
+def write_ppm(path, pixels):
+    """static.cpp:135-147: P6, rows from j=height-1 down to 0, uint8(max(min(p*255,255),0))."""
+    H, W, _ = pixels.shape
+    x = pixels.astype(np.float32) * np.float32(255)
+    x = np.where(np.float32(255) < x, np.float32(255), x)
+    x = np.where(x < 0, np.float32(0), x)
+    with np.errstate(invalid="ignore"):
+        b = np.nan_to_num(x, nan=0.0).astype(np.uint8)[::-1]
+    with open(path, "wb") as f:
+        f.write(f"P6 {W} {H} 255\n".encode())
+        f.write(b.tobytes())
+    return b

@@ -1,0 +1,206 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the oracle on the same inputs.
+
+Bars (BASELINE.json north_star): per-pixel hit triangle IDs, hit/miss/occlusion states, t/u/v and the (rays, hits)
+counters are BIT-EXACT against the strict oracle; shaded RGB within RGB_ATOL absolute per channel (the only
+non-bit-exact step is pow(double, 24), evaluated by repeated squaring on the GPU and by glibc pow in the
+reference; both are then narrowed to float); PPM bytes equal except for <= PPM_MAX_DIFF_FRACTION of bytes off by
+one LSB."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import scene_pod
+from oracle import port
+
+pytestmark = pytest.mark.gpu
+
+RGB_ATOL = 1e-6
+PPM_MAX_DIFF_FRACTION = 1e-5
+SUN = np.array([-50, -20, 0], np.float32)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def cr():
+    import ceres_raytracer_b200 as cr
+    return cr
+
+
+@pytest.fixture(scope="module")
+def bunny(cr, bunny_pod):
+    s = cr.Scene.from_pod(bunny_pod)
+    yield s
+    s.close()
+
+
+@pytest.fixture(scope="module")
+def dragon(cr, dragon_pod):
+    s = cr.Scene.from_pod(dragon_pod)
+    yield s
+    s.close()
+
+
+def check_frame(cr, scene, pod, cam, sun, W, H, flags, golden=None):
+    px, ids, (rays, hits) = scene.render(cam, sun, W, H, flags=flags, want_ids=True)
+    o = port.render(pod, cam.as_array(), sun, W, H, flags)
+    assert np.array_equal(ids, o["ids"]), f"{int((ids != o['ids']).sum())} hit ids differ"
+    assert (rays, hits) == (o["stats"]["rays"], o["stats"]["hits"])
+    lit_gpu = (px != 0).any(axis=2)
+    # every lit pixel of the oracle has a non-zero colour (ambient term), so the state can be compared exactly
+    assert np.array_equal(lit_gpu, o["state"] == 1)
+    d = np.abs(px.astype(np.float64) - o["pixels"].astype(np.float64))
+    assert d.max() <= RGB_ATOL, f"max |dRGB| = {d.max()}"
+    exact = float((px.view(np.uint32) == o["pixels"].view(np.uint32)).mean())
+    b_gpu = cr.write_ppm(os.devnull, px)
+    b_cpu = cr.write_ppm(os.devnull, o["pixels"])
+    diff = b_gpu.astype(np.int16) - b_cpu.astype(np.int16)
+    assert np.abs(diff).max() <= 1 and (diff != 0).mean() <= PPM_MAX_DIFF_FRACTION
+    if golden is not None:
+        assert sha(ids) == golden["ids_sha256"]
+        assert (rays, hits) == (golden["stats"]["rays"], golden["stats"]["hits"])
+    return exact
+
+
+def test_trace_rays_kat(bunny, kat):
+    ids, tuv = bunny.trace_rays(kat["trace_rays"])
+    assert np.array_equal(ids, kat["trace_ids"])
+    assert np.array_equal(tuv.view(np.uint32), kat["trace_tuv"].view(np.uint32))
+
+
+@pytest.mark.parametrize("tag,flags", [("shadow", 0), ("primary", 1)])
+def test_bunny_golden_frames(cr, bunny, bunny_frames, tag, flags):
+    cam = cr.Camera(bunny_frames["cam"][0:3], bunny_frames["cam"][3:6], bunny_frames["cam"][6:9], float(bunny_frames["cam"][9]))
+    px, ids, (rays, hits) = bunny.render(cam, bunny_frames["sun"], 320, 180, flags=flags, want_ids=True)
+    assert np.array_equal(ids, bunny_frames[f"{tag}_ids"])
+    assert np.abs(px - bunny_frames[f"{tag}_rgb"]).max() <= RGB_ATOL
+    st = bunny_frames[f"{tag}_stats"]
+    assert (rays, hits) == (int(st[6]), int(st[7]))
+
+
+@pytest.mark.parametrize("W,H,flags", [(1920, 1080, 1), (1920, 1080, 0), (1, 1, 0), (33, 7, 0), (1000, 9, 1)])
+def test_bunny_vs_oracle(cr, bunny, bunny_pod, W, H, flags):
+    check_frame(cr, bunny, bunny_pod, cr.configs.BUNNY_CAMERA, SUN, W, H, flags)
+
+
+@pytest.mark.parametrize("W,H,flags,key", [
+    (1920, 1080, 1, "dragon_1920x1080_primary"),   # BASELINE config 2
+    (1920, 1080, 0, "dragon_1920x1080_shadow"),
+    (3840, 2160, 0, "dragon_3840x2160_shadow"),    # BASELINE config 3 (metric config)
+])
+def test_dragon_vs_oracle(cr, dragon, dragon_pod, frame_hashes, W, H, flags, key):
+    exact = check_frame(cr, dragon, dragon_pod, cr.configs.DRAGON_CAMERA, SUN, W, H, flags, frame_hashes[key])
+    assert exact > 0.999
+
+
+def test_inside_and_degenerate_cameras(cr, dragon, dragon_pod):
+    # camera inside the model's bounding box, axis-aligned view (zero direction components -> safe_inverse path)
+    for cam in (cr.Camera((0, 0, 2), (0, 0, -1), (0, 1, 0), 90), cr.Camera((0, -3, 2), (1, 0, 0), (0, 0, 1), 120),
+                cr.Camera((0, -15, 2), (0, 1, 0), (0, 0, 1), 1.0)):
+        check_frame(cr, dragon, dragon_pod, cam, np.array([10, -30, 40], np.float32), 640, 360, 0)
+
+
+@pytest.mark.parametrize("count", [2, 3, 8])
+def test_row_block_shards_reassemble_exactly(cr, dragon, count):
+    cam, W, H = cr.configs.DRAGON_CAMERA, 1280, 720
+    full, ids_full, cnt_full = dragon.render(cam, SUN, W, H, want_ids=True)
+    frame = np.full_like(full, np.nan)
+    ids = np.zeros_like(ids_full)
+    rays = hits = 0
+    for k in range(count):
+        sh = (16, k, count)
+        # in-place rows
+        px, idk, (r, h) = dragon.render(cam, SUN, W, H, shard=sh, want_ids=True)
+        rows = cr.shard_rows(H, sh)
+        frame[rows] = px[rows]
+        ids[rows] = idk[rows]
+        rays += r; hits += h
+        # compact rows
+        pc, ic, _ = dragon.render(cam, SUN, W, H, flags=cr.COMPACT_ROWS, shard=sh, want_ids=True)
+        assert np.array_equal(pc.view(np.uint32), px[rows].view(np.uint32)) and np.array_equal(ic, idk[rows])
+    assert np.array_equal(frame.view(np.uint32), full.view(np.uint32))
+    assert np.array_equal(ids, ids_full)
+    assert (rays, hits) == cnt_full
+
+
+def test_device_api_sequence_and_quantize(cr, dragon, dragon_pod, kat):
+    import torch
+    W, H = 640, 360
+    cams = np.concatenate([kat["turntable"][:4, :]], axis=0)
+    px_all, cnt = dragon.render_sequence(cams, W, H)
+    for k in range(cams.shape[0]):
+        c = cams[k]
+        cam = cr.Camera(c[0:3], c[3:6], c[6:9], float(c[9]))
+        px, _, counters = dragon.render(cam, c[10:13], W, H)
+        assert np.array_equal(px.view(np.uint32), px_all[k].view(np.uint32))
+        assert counters == (int(cnt[k, 0]), int(cnt[k, 1]))
+        o = port.render(dragon_pod, c[0:10], c[10:13], W, H, 0)
+        assert counters == (o["stats"]["rays"], o["stats"]["hits"])
+    # device-resident frame + on-device 8-bit flip/quantise == PPM payload of static.cpp:135-147
+    d_px = torch.empty(H * W * 3, dtype=torch.float32, device="cuda")
+    d_cnt = torch.zeros(2, dtype=torch.int64, device="cuda")
+    d_q = torch.empty(H * W * 3, dtype=torch.uint8, device="cuda")
+    cam = cr.configs.DRAGON_CAMERA
+    dragon.render_device(cam, SUN, W, H, pixels=d_px, counters=d_cnt)
+    dragon.quantize_device(d_px, W, H, d_q)
+    torch.cuda.synchronize()
+    px, _, counters = dragon.render(cam, SUN, W, H)
+    assert np.array_equal(d_px.cpu().numpy().view(np.uint32), px.ravel().view(np.uint32))
+    assert tuple(d_cnt.cpu().tolist()) == counters
+    assert np.array_equal(d_q.cpu().numpy().reshape(H, W, 3), cr.write_ppm(os.devnull, px))
+
+
+def test_gpu_statistics_match_oracle_for_primary_rays(cr, dragon, dragon_pod):
+    W, H = 960, 540
+    dragon.set_stats(True)
+    try:
+        dragon.render(cr.configs.DRAGON_CAMERA, SUN, W, H)
+        st = dragon.get_stats()
+    finally:
+        dragon.set_stats(False)
+    o = port.render(dragon_pod, cr.configs.DRAGON_CAMERA.as_array(), SUN, W, H, 0, want_pixels=False)["stats"]
+    for k in ("S_miss", "T_miss", "S_hit", "T_hit", "rays", "hits"):
+        assert st[k] == o[k], k          # same tree walked in the same order
+    assert 0 < st["S_shadow"] <= o["S_shadow"] and 0 < st["T_shadow"] <= o["T_shadow"]   # any-hit exits early
+
+
+def test_tiny_scenes_root_leaf_and_single_pair(cr):
+    # 1 triangle -> the root is a leaf (single_ray_traverser.hpp:72-73); hand-built POD, no builder needed
+    tri = port.make_triangles(np.array([[-1, -1, 5, 1, -1, 5, 0, 1, 5]], np.float32))
+    nodes = np.zeros(1, cr.NODE_DT)
+    nodes[0]["bounds"] = [-1, 1, -1, 1, 5, 5]; nodes[0]["primitive_count"] = 1
+    pod = {"nodes": nodes, "prim_indices": np.array([0], np.uint64), "triangles": tri,
+           "norms": np.tile(np.array([0, 0, -1], np.float32), (1, 3))}
+    cam = cr.Camera((0, 0, 0), (0, 0, 1), (0, 1, 0), 60)
+    with cr.Scene.from_pod(pod) as s:
+        check_frame(cr, s, pod, cam, np.array([0, 0, -10], np.float32), 64, 48, 0)
+    # 2 triangles under one inner root; the second exactly behind the first (shadowing) and coplanar duplicates
+    tri2 = port.make_triangles(np.array([[-1, -1, 5, 1, -1, 5, 0, 1, 5], [-1, -1, 5, 1, -1, 5, 0, 1, 5],
+                                         [-2, -2, 3, 2, -2, 3, 0, 2, 3]], np.float32))
+    nodes = np.zeros(3, cr.NODE_DT)
+    nodes[0]["bounds"] = [-2, 2, -2, 2, 3, 5]; nodes[0]["first_child_or_primitive"] = 1
+    nodes[1]["bounds"] = [-1, 1, -1, 1, 5, 5]; nodes[1]["primitive_count"] = 2; nodes[1]["first_child_or_primitive"] = 0
+    nodes[2]["bounds"] = [-2, 2, -2, 2, 3, 3]; nodes[2]["primitive_count"] = 1; nodes[2]["first_child_or_primitive"] = 2
+    pod = {"nodes": nodes, "prim_indices": np.array([1, 0, 2], np.uint64), "triangles": tri2,
+           "norms": np.tile(np.array([0, 0, -1], np.float32), (3, 3))}
+    with cr.Scene.from_pod(pod) as s:
+        check_frame(cr, s, pod, cam, np.array([0, 0, 100], np.float32), 64, 48, 0)
+        check_frame(cr, s, pod, cr.Camera((0, 0, 10), (0, 0, -1), (0, 1, 0), 60), np.array([0, 0, -100], np.float32), 64, 48, 0)
+
+
+def test_invalid_arguments_fail_loudly(cr, bunny_pod):
+    bad = dict(bunny_pod)
+    bad["prim_indices"] = bunny_pod["prim_indices"].copy()
+    bad["prim_indices"][0] = 10 ** 9
+    with pytest.raises(cr.CeresError):
+        cr.Scene.from_pod(bad)
+    with cr.Scene.from_pod(bunny_pod) as s:
+        with pytest.raises(cr.CeresError):
+            s.render(cr.configs.BUNNY_CAMERA, SUN, 0, 10)
+        rays = np.zeros((1, 8), np.float32); rays[0, 7] = np.nan
+        with pytest.raises(cr.CeresError):
+            s.trace_rays(rays)
