@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric (Mrays/s, ms/frame; dragon.obj 3840x2160 with shadow rays) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one frame of the hot path (render.hpp:86-156) over the reference-built dragon scene.  Rays are the
+reference's own counter: W*H + primary hits (render.hpp:115,138) = 9 450 006 per frame.
+  value        device-resident throughput: scene in HBM, frame left in HBM (CUDA events on the launch stream; L2 is
+               flushed before every timed frame)
+  e2e          the same frame through the reference-facing C-ABI call ceres_render() with a HOST framebuffer: the
+               device->host copy of the float RGB frame and of the counters is inside the timed region
+  roofline     dominant kernel: algorithmic bytes / its CUDA-event duration vs the measured HBM peak
+  cpu_baseline the reference's own render() (oracle/_ref, its flags, all host threads) on the same frame
+N > 1 (torchrun): the frame is split in interleaved 16-row blocks, one shard per GPU, scene replicated, finished
+blocks gathered on rank 0 with NCCL; time = max over ranks; scaling is strong (one frame, more GPUs).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = "dragon_4k_shadow"
+METRIC = "Mrays/s (dragon.obj 3840x2160, primary + shadow rays)"
+UNIT = "Mrays/s"
+DATA = "dragon.obj loaded + BVH built by the reference code (tests/golden/dragon_scene.npz); no synthetic substitute needed"
+
+
+def load_scene_pod(name):
+    """The reference-loaded, reference-built scene (obj_norms.hpp loader, rotate_triangles, SweepSah + layout
+    optimiser), dumped by tests/golden/make_golden.py.  It is INPUT DATA for both arms."""
+    p = os.path.join(ROOT, "tests", "golden", name + "_scene.npz")
+    if not os.path.exists(p):
+        raise SystemExit(f"{p} missing: run tests/golden/make_golden.py where /root/reference exists")
+    with np.load(p) as z:
+        return {k: z[k] for k in z.files}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_frames(pod, cam, sun, W, H, frames, warmup=1, budget_s=None):
+    """Times the reference's own render() on the host cores.  Returns (seconds per frame list, kind, cores, rays)."""
+    from oracle import ref, port
+    if ref.available("fast"):
+        s = ref.RefScene.from_pod(pod, "fast")       # the reference's own flags (CMakeLists.txt:5,11-13)
+        for _ in range(warmup):
+            _, _, _, sec0 = s.render(cam, sun, W, H)
+            if budget_s:
+                frames = int(min(frames, max(2, budget_s / max(sec0, 1e-3))))
+        secs, rays = [], 0
+        for _ in range(frames):
+            _, rays, _, sec = s.render(cam, sun, W, H)
+            secs.append(sec)
+        cores = ref.threads("fast")
+        s.close()
+        return secs, "reference", cores, rays
+    secs, rays = [], 0
+    for k in range(warmup + frames):
+        t0 = time.perf_counter()
+        r = port.render(pod, cam, sun, W, H, 0, want_pixels=True)
+        if k >= warmup:
+            secs.append(time.perf_counter() - t0)
+        rays = r["stats"]["rays"]
+    return secs, "port", port.threads(), rays
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import ceres_raytracer_b200.configs as cfg
+    name, cam, sun, W, H, flags = cfg.WORKLOADS[WORKLOAD]
+    pod = load_scene_pod(name)
+    secs, kind, cores, rays = cpu_reference_frames(pod, cam.as_array(), np.asarray(sun, np.float32), W, H,
+                                                   frames=args.steps, warmup=args.warmup)
+    ms = 1e3 * float(np.sum(secs)) / len(secs)
+    val = rays / (ms * 1e-3) / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": DATA,
+        "config": {"workload": WORKLOAD, "width": W, "height": H, "rays_per_frame": rays, "l2": "n/a (CPU)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{len(secs)} full {W}x{H} frames, unmodified render() (render.hpp:86-156), "
+                                   f"best {min(secs)*1e3:.1f} ms, median {np.median(secs)*1e3:.1f} ms"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def algorithmic_bytes(st, W, rows, lit):
+    """Per-kernel algorithmic bytes of one frame from the work the GPU executed (DESIGN.md 'roofline'):
+    64 B per node-pair step, 48 B per triangle test, 16 B per queue record, 12 B per pixel written."""
+    P, Hh = W * rows, st["hits_primary"]
+    return {
+        "primary": 64 * (st["S_miss"] + st["S_hit"]) + 48 * (st["T_miss"] + st["T_hit"]) + 12 * (P - Hh) + 16 * Hh,
+        "shadow": 64 * st["S_shadow"] + 48 * st["T_shadow"] + 16 * Hh + 48 * Hh + 4 * st["occluded"],
+        "shade": 16 * Hh + (48 + 36) * lit + 12 * Hh,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default=WORKLOAD)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    import ceres_raytracer_b200 as cr
+    cfg = cr.configs
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N ...")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    warmup = max(args.warmup, 3)
+
+    name, cam, sun, W, H, flags = cfg.WORKLOADS[args.workload]
+    sun = np.asarray(sun, np.float32)
+    pod = load_scene_pod(name)
+    scene = cr.Scene.from_pod(pod, device=local)
+    shard = (cfg.TILE_BLOCK_ROWS, rank, world) if world > 1 else None
+    n_rows = len(cr.shard_rows(H, shard))
+    rows_max = len(cr.shard_rows(H, (cfg.TILE_BLOCK_ROWS, 0, world))) if world > 1 else H
+
+    d_band = torch.zeros(rows_max * W * 3, dtype=torch.float32, device=dev)      # this rank's rows, packed
+    d_cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+    d_frame = d_band
+    gather_list = None
+    if world > 1 and rank == 0:
+        gather_list = [torch.empty_like(d_band) for _ in range(world)]
+        d_frame = torch.empty(H * W * 3, dtype=torch.float32, device=dev)
+        row_index = [torch.as_tensor(cr.shard_rows(H, (cfg.TILE_BLOCK_ROWS, r, world)), device=dev) for r in range(world)]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)         # > 126 MB L2
+    rflags = flags | (cr.COMPACT_ROWS if world > 1 else 0)
+
+    def frame():
+        scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
+        if world > 1:
+            dist.gather(d_band, gather_list, dst=0)
+            if rank == 0:
+                fv = d_frame.view(H, W * 3)
+                for r in range(world):
+                    idx = row_index[r]
+                    fv.index_copy_(0, idx, gather_list[r].view(rows_max, W * 3)[: idx.numel()])
+            dist.all_reduce(d_cnt)      # frame counters = sum over shards
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(warmup):
+        flush.fill_(1)
+        frame()
+    barrier()
+    counters = d_cnt.cpu().tolist()
+    rays_frame, hits_frame = int(counters[0]), int(counters[1])
+
+    # ---- timed region: K frames, each preceded by an L2 flush that is outside its event pair ------------------
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = cr.kernel_launch_count()
+    scene.set_profiling(True)            # per-kernel CUDA events on the launch stream, inside the timed region
+    with ClockSampler(local) as clocks:
+        barrier()
+        for a, b in ev:
+            flush.fill_(1)
+            a.record()
+            frame()
+            b.record()
+        barrier()
+    launches = cr.kernel_launch_count() - launches0
+    kms, kframes = scene.kernel_ms()
+    scene.set_profiling(False)
+    ms_step = allmax(sum(a.elapsed_time(b) for a, b in ev) / args.steps)
+
+    # back-to-back frames without flush (warm L2), for context
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        frame()
+    b.record()
+    barrier()
+    ms_warm = allmax(a.elapsed_time(b) / args.steps)
+
+    # ---- work actually executed by this rank's kernels (statistics build of the same kernels, untimed) ----------
+    scene.set_stats(True)
+    scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
+    torch.cuda.synchronize()
+    st = scene.get_stats()
+    scene.set_stats(False)
+    local_rays, local_hits = st["rays"], st["hits"]
+    st["hits_primary"] = local_rays - W * n_rows if not (flags & cr.NO_SHADOWS) else None
+    if st["hits_primary"] is None:      # primary-only: every hit is lit, hits counter = primary hits
+        st["hits_primary"] = local_hits
+        st["occluded"] = 0
+    else:
+        st["occluded"] = local_hits - st["hits_primary"]
+    lit = st["hits_primary"] - st["occluded"]
+    abytes = algorithmic_bytes(st, W, n_rows, lit)
+    kavg = {k: kms[k] / max(kframes, 1) for k in ("primary", "shadow", "shade", "total")}
+    dominant = max(("primary", "shadow", "shade"), key=lambda k: kavg[k])
+    peak, peak_src = measured_peak()
+    achieved = abytes[dominant] / (kavg[dominant] * 1e-3) / 1e9 if kavg[dominant] > 0 else 0.0
+    whole = sum(abytes.values()) / (kavg["total"] * 1e-3) / 1e9 if kavg["total"] > 0 else 0.0
+    ncu_traffic = None
+    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")     # dram bytes per launch from the committed ncu --set full capture
+    if os.path.exists(tp):
+        try:
+            ncu_traffic = json.load(open(tp)).get(dominant)
+        except Exception:
+            pass
+
+    # ---- end to end through the reference-facing call with a HOST framebuffer ------------------------------------
+    # N = 1: ceres_render() (the drop-in for render.hpp:86-156) into a page-locked host buffer: launch + D2H of the
+    # float frame + counters inside the timed region.  N > 1: shard render + NCCL gather + D2H of the frame on rank 0.
+    steps_e2e = args.steps
+    if world == 1:
+        hb = cr.PinnedBuffer((H, W, 3), np.float32)
+        for _ in range(2):
+            scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)
+        torch.cuda.synchronize()
+        t_e2e = 0.0
+        for _ in range(steps_e2e):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            _, _, cnt_e2e = scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)
+            t_e2e += time.perf_counter() - t0
+        assert cnt_e2e == (rays_frame, hits_frame)
+        d2h = 3 * W * H * 4 + 16
+    else:
+        h_frame = torch.empty(H * W * 3, dtype=torch.float32, pin_memory=True) if rank == 0 else None
+        h_cnt = torch.empty(2, dtype=torch.int64, pin_memory=True)
+        t_e2e = 0.0
+        for k in range(steps_e2e + 2):
+            flush.fill_(1)
+            barrier()
+            t0 = time.perf_counter()
+            frame()
+            if rank == 0:
+                h_frame.copy_(d_frame, non_blocking=True)
+            h_cnt.copy_(d_cnt, non_blocking=True)
+            torch.cuda.synchronize()
+            if k >= 2:
+                t_e2e += time.perf_counter() - t0
+        d2h = 3 * W * H * 4 + 16
+    ms_e2e = allmax(1e3 * t_e2e / steps_e2e)
+
+    # ---- CPU baseline: the reference's own render() on this box's host cores (rank 0, N = 1 only) ------------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            secs, kind, cores, rays_cpu = cpu_reference_frames(pod, cam.as_array(), sun, W, H, frames=8, warmup=1, budget_s=12.0)
+            ms_cpu = 1e3 * float(np.mean(secs))
+            cpu = {"value": rays_cpu / (ms_cpu * 1e-3) / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
+                   "ms_per_frame": ms_cpu,
+                   "sample": f"{len(secs)} full {W}x{H} frames of the same workload, unmodified render() with the reference's flags "
+                             f"(best {min(secs)*1e3:.1f} ms, median {np.median(secs)*1e3:.1f} ms)"}
+        except Exception as e:      # the baseline is reporting only; never fail the GPU line for it
+            cpu = {"value": None, "unit": UNIT, "cores": None, "kind": "unavailable", "sample": str(e)[:200]}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": rays_frame / (ms_step * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": DATA,
+            "config": {"workload": args.workload, "width": W, "height": H, "rays_per_frame": rays_frame,
+                       "hits_counter": hits_frame, "scene_device_bytes": scene.device_bytes,
+                       "sharding": f"{world} x interleaved {cfg.TILE_BLOCK_ROWS}-row blocks, NCCL gather to rank 0" if world > 1 else "none",
+                       "l2": "flushed (256 MiB fill) before every timed frame", "ms_per_step_warm_l2": ms_warm},
+            "e2e": {"value": rays_frame / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": d2h,
+                    "path": "ceres_render() -> page-locked host framebuffer" if world == 1 else
+                            "ceres_render_device(shard) + NCCL gather + D2H of the frame on rank 0"},
+            "gpu_launches": launches,
+            "kernels_ms": kavg,
+            "roofline": {"bound": "hbm", "kernel": dominant + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": ncu_traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": abytes[dominant],
+                         "whole_frame": {"achieved": whole, "frac": whole / peak, "bytes": sum(abytes.values())},
+                         "work": {k: st[k] for k in ("S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "hits_primary", "occluded")},
+                         "note": "scene (3 MB) is L1/L2-resident: the HBM peak is the conservative denominator SURVEY.md 8(d) asks for"},
+            "clocks": clocks.summary(),
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

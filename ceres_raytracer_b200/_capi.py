@@ -29,7 +29,7 @@ class Shard(C.Structure):
 
 class Tuning(C.Structure):
     _fields_ = [("variant", C.c_uint32), ("primary_block", C.c_uint32), ("shadow_block", C.c_uint32),
-                ("ctas_per_sm", C.c_uint32), ("reserved", C.c_uint32 * 4)]
+                ("ctas_per_sm", C.c_uint32), ("band_bytes", C.c_uint32), ("reserved", C.c_uint32 * 3)]
 
 
 # every symbol include/ceres_b200.h declares (tests/test_capi_symbols.py checks the header against this list)
@@ -37,7 +37,8 @@ SYMBOLS = [
     "ceres_scene_create", "ceres_scene_destroy", "ceres_scene_set_tuning", "ceres_scene_device_bytes",
     "ceres_render", "ceres_render_shard", "ceres_render_sequence", "ceres_render_device",
     "ceres_scene_set_stats", "ceres_scene_get_stats", "ceres_trace_rays", "ceres_frame_setup",
-    "ceres_quantize_device", "ceres_host_alloc", "ceres_host_free", "ceres_abi_version", "ceres_device_count",
+    "ceres_scene_set_profiling", "ceres_scene_get_kernel_ms", "ceres_host_register", "ceres_host_unregister",
+    "ceres_host_is_pinned", "ceres_quantize_device", "ceres_host_alloc", "ceres_host_free", "ceres_abi_version", "ceres_device_count",
     "ceres_kernel_launch_count", "ceres_last_error",
 ]
 
@@ -78,6 +79,11 @@ def lib():
     L.ceres_host_alloc.restype = vp
     L.ceres_host_free.argtypes = [vp]
     L.ceres_host_free.restype = None
+    L.ceres_host_register.argtypes = [vp, sz]
+    L.ceres_host_unregister.argtypes = [vp]
+    L.ceres_host_is_pinned.argtypes = [vp]
+    L.ceres_scene_set_profiling.argtypes = [vp, C.c_int]
+    L.ceres_scene_get_kernel_ms.argtypes = [vp, vp, vp]
     L.ceres_abi_version.restype = C.c_int
     L.ceres_device_count.restype = C.c_int
     L.ceres_kernel_launch_count.restype = u64

@@ -26,6 +26,7 @@
 #include <vector>
 #include <atomic>
 #include <new>
+#include <algorithm>
 
 #include "../../include/ceres_b200.h"
 
@@ -71,7 +72,9 @@ struct FrameCounters {
 struct Frame {
     float eye[3], dir[3], iu[3], iv[3], sun[3];
     uint32_t W, H;             // full frame
-    uint32_t rows_local;       // rows rendered by this shard
+    uint32_t row_begin;        // first local row of this launch (a frame may be rendered in several row bands)
+    uint32_t row_end;          // one past the last local row of this launch
+    uint32_t accumulate;       // add this launch's counters to out_counters instead of overwriting them
     uint32_t block_rows, shard_index, shard_count;
     uint32_t compact;          // outputs packed by local row
     uint32_t shadows;
@@ -270,8 +273,8 @@ __global__ void __launch_bounds__(PRIMARY_THREADS) primary_kernel(const DevScene
     extern __shared__ uint32_t smem_stack[];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t i = blockIdx.x * 32u + (warp & 3u) * 8u + (lane & 7u);
-    const uint32_t lrow = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
-    const bool valid = i < f.W && lrow < f.rows_local;
+    const uint32_t lrow = f.row_begin + blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
+    const bool valid = i < f.W && lrow < f.row_end;
     const uint32_t j = frame_row(f, lrow);
 
     bool found = false;
@@ -413,15 +416,17 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
     if (last && threadIdx.x == 0) {
         __threadfence();
         const unsigned long long hits = total, occ = f.ctr->occluded;
-        const unsigned long long rays = (unsigned long long)f.W * f.rows_local + hits + 0ull;   // render.hpp:115,138
+        const unsigned long long prim = (unsigned long long)f.W * (f.row_end - f.row_begin);
+        const unsigned long long rays = f.shadows ? prim + hits : prim;                          // render.hpp:115,138
+        const unsigned long long nh = hits + occ;                                                 // render.hpp:119,148
         if (f.out_counters) {
-            f.out_counters[0] = f.shadows ? rays : (unsigned long long)f.W * f.rows_local;
-            f.out_counters[1] = hits + occ;                                                       // render.hpp:119,148
+            f.out_counters[0] = (f.accumulate ? f.out_counters[0] : 0ull) + rays;
+            f.out_counters[1] = (f.accumulate ? f.out_counters[1] : 0ull) + nh;
         }
         if (f.out_stats) {
-            for (int k = 0; k < 6; ++k) f.out_stats[k] = f.ctr->stats[k];
-            f.out_stats[6] = f.shadows ? rays : (unsigned long long)f.W * f.rows_local;
-            f.out_stats[7] = hits + occ;
+            for (int k = 0; k < 6; ++k) f.out_stats[k] = (f.accumulate ? f.out_stats[k] : 0ull) + f.ctr->stats[k];
+            f.out_stats[6] = (f.accumulate ? f.out_stats[6] : 0ull) + rays;
+            f.out_stats[7] = (f.accumulate ? f.out_stats[7] : 0ull) + nh;
         }
         f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0;
         for (int k = 0; k < 6; ++k) f.ctr->stats[k] = 0;
@@ -465,10 +470,13 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------ host side
+#define CERES_MAX_BANDS 32
 struct ceres_scene {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;                     // D2H of finished row bands
+    cudaEvent_t band_done[CERES_MAX_BANDS] = {};
     DevScene dev{};
     void* d_pairs = nullptr; void* d_tris = nullptr; void* d_norms = nullptr; void* d_slot_id = nullptr;
     size_t scene_bytes = 0;
@@ -479,8 +487,10 @@ struct ceres_scene {
     uint32_t* d_ids = nullptr; size_t ids_cap = 0;
     unsigned long long* d_out = nullptr;                    // 2 counters + 8 stats
     unsigned long long* h_out = nullptr;                    // pinned mirror
-    void* reg_ptr = nullptr; size_t reg_bytes = 0;          // host framebuffer currently page-locked by us
     bool stats = false;
+    bool profile = false;                                   // CUDA events around each kernel of every frame
+    std::vector<cudaEvent_t> prof_events;                   // 4 per frame: start, after primary, after shadow, after shade
+    size_t prof_frames = 0;
     ceres_tuning tune{};
     int shadow_blocks_per_sm = 0, shadow_blocks_per_sm_stats = 0;
 };
@@ -538,6 +548,18 @@ int ensure(T*& p, size_t& cap, size_t need) {
     return CERES_OK;
 }
 
+// Host framebuffers: a buffer the caller page-locked (ceres_host_alloc / ceres_host_register, or any
+// cudaHostAlloc'ed memory) is written by DMA straight from the device; anything else goes through the driver's
+// pageable-copy path.  The library never keeps a registration of caller memory across calls: the caller may free
+// and re-map the same virtual address between frames (numpy does), and a stale registration would then DMA into
+// pages that no longer back the buffer.
+bool host_is_pinned(const void* p) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) == cudaSuccess) return attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return false;
+}
+
 }  // namespace
 
 extern "C" {
@@ -558,6 +580,17 @@ void* ceres_host_alloc(size_t bytes) {
     return p;
 }
 void ceres_host_free(void* p) { if (p) cudaFreeHost(p); }
+int ceres_host_register(void* p, size_t bytes) {
+    if (!p || !bytes) return fail(CERES_ERR_INVALID, "ceres_host_register: null/zero argument");
+    CUDA_TRY(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+    return CERES_OK;
+}
+int ceres_host_unregister(void* p) {
+    if (!p) return fail(CERES_ERR_INVALID, "ceres_host_unregister: null argument");
+    CUDA_TRY(cudaHostUnregister(p));
+    return CERES_OK;
+}
+int ceres_host_is_pinned(const void* p) { return p && host_is_pinned(p) ? 1 : 0; }
 
 int ceres_frame_setup(const ceres_camera* camera, size_t width, size_t height, float out[9]) {
     if (!camera || !out || !width || !height) return fail(CERES_ERR_INVALID, "ceres_frame_setup: null/zero argument");
@@ -655,6 +688,8 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     auto bail = [&](int code) { ceres_scene_destroy(s); return code; };
 #define TRY_S(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); return bail(CERES_ERR_CUDA); } } while (0)
     TRY_S(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    TRY_S(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < CERES_MAX_BANDS; ++k) TRY_S(cudaEventCreateWithFlags(&s->band_done[k], cudaEventDisableTiming));
     const size_t pb = pairs.size() * 4, tb = tri_slots.size() * 4, nb = norm_slots.size() * 4, ib = slot_id.size() * 4;
     TRY_S(cudaMalloc(&s->d_pairs, pb));
     TRY_S(cudaMalloc(&s->d_tris, tb));
@@ -685,10 +720,12 @@ void ceres_scene_destroy(ceres_scene* s) {
     if (!s) return;
     DeviceGuard guard(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
-    if (s->reg_ptr) cudaHostUnregister(s->reg_ptr);
+    if (s->copy_stream) { cudaStreamSynchronize(s->copy_stream); cudaStreamDestroy(s->copy_stream); }
+    for (int k = 0; k < CERES_MAX_BANDS; ++k) if (s->band_done[k]) cudaEventDestroy(s->band_done[k]);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_out);
     if (s->h_out) cudaFreeHost(s->h_out);
+    for (cudaEvent_t e : s->prof_events) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
@@ -709,6 +746,31 @@ int ceres_scene_set_stats(ceres_scene* s, int enable) {
     return CERES_OK;
 }
 
+int ceres_scene_set_profiling(ceres_scene* s, int enable) {
+    if (!s) return fail(CERES_ERR_INVALID, "null scene");
+    s->profile = enable != 0;
+    s->prof_frames = 0;
+    return CERES_OK;
+}
+
+int ceres_scene_get_kernel_ms(ceres_scene* s, double ms[4], uint64_t* frames) {
+    if (!s || !ms) return fail(CERES_ERR_INVALID, "null argument");
+    DeviceGuard guard(s->device);
+    for (int k = 0; k < 4; ++k) ms[k] = 0.0;
+    for (size_t fidx = 0; fidx < s->prof_frames; ++fidx) {
+        cudaEvent_t* e = &s->prof_events[4 * fidx];
+        CUDA_TRY(cudaEventSynchronize(e[3]));
+        float a = 0, b = 0, c = 0, t = 0;
+        CUDA_TRY(cudaEventElapsedTime(&a, e[0], e[1]));
+        CUDA_TRY(cudaEventElapsedTime(&b, e[1], e[2]));
+        CUDA_TRY(cudaEventElapsedTime(&c, e[2], e[3]));
+        CUDA_TRY(cudaEventElapsedTime(&t, e[0], e[3]));
+        ms[0] += a; ms[1] += b; ms[2] += c; ms[3] += t;
+    }
+    if (frames) *frames = s->prof_frames;
+    return CERES_OK;
+}
+
 int ceres_scene_get_stats(ceres_scene* s, uint64_t stats[8]) {
     if (!s || !stats) return fail(CERES_ERR_INVALID, "null argument");
     DeviceGuard guard(s->device);
@@ -718,22 +780,20 @@ int ceres_scene_get_stats(ceres_scene* s, uint64_t stats[8]) {
     return CERES_OK;
 }
 
-int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
-                        unsigned flags, const ceres_shard* shard, void* stream_v, float* d_pixels, uint32_t* d_ids,
-                        uint64_t* d_counters) {
-    if (!s || !cam || !sun || !d_pixels) return fail(CERES_ERR_INVALID, "ceres_render_device: null argument");
+// Fills the per-frame constants (everything but the row range).
+static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
+                         unsigned flags, const ceres_shard* shard, float* d_pixels, uint32_t* d_ids, uint64_t* d_counters,
+                         Frame& f, uint32_t& rows_local) {
+    if (!s || !cam || !sun || !d_pixels) return fail(CERES_ERR_INVALID, "ceres_render: null argument");
     if (!width || !height || width > 65535u * 32u || (uint64_t)width * height >= (1ull << 32))
-        return fail(CERES_ERR_INVALID, "ceres_render_device: bad image size");
+        return fail(CERES_ERR_INVALID, "ceres_render: bad image size");
     if (shard && shard->count > 1 && (shard->block_rows == 0 || shard->index >= shard->count))
-        return fail(CERES_ERR_INVALID, "ceres_render_device: bad shard");
-    DeviceGuard guard(s->device);
-    cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
-
-    Frame f{};
+        return fail(CERES_ERR_INVALID, "ceres_render: bad shard");
+    f = Frame{};
     for (int k = 0; k < 3; ++k) { f.eye[k] = cam->eye[k]; f.sun[k] = sun[k]; }
     frame_setup_host(cam, width, height, f.dir, f.iu, f.iv);
     f.W = (uint32_t)width; f.H = (uint32_t)height;
-    f.rows_local = shard_rows(height, shard);
+    rows_local = shard_rows(height, shard);
     const bool sharded = shard && shard->count > 1;
     f.block_rows = sharded ? shard->block_rows : (uint32_t)height;
     f.shard_index = sharded ? shard->index : 0;
@@ -744,19 +804,38 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
     f.out_counters = d_counters ? (unsigned long long*)d_counters : s->d_out;
     f.out_stats = s->stats ? s->d_out + 2 : nullptr;
     f.ctr = s->d_ctr;
-    if (f.rows_local == 0) return CERES_OK;
+    return CERES_OK;
+}
 
-    const size_t npix = (size_t)f.rows_local * width;
-    if (int rc = ensure(s->d_queue, s->queue_cap, npix)) return rc;
+// Enqueues the three kernels for local rows [row_begin, row_end) of the frame on `st`.
+static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row_end, bool accumulate, cudaStream_t st) {
+    if (row_end <= row_begin) return CERES_OK;
+    f.row_begin = row_begin; f.row_end = row_end; f.accumulate = accumulate ? 1u : 0u;
+    const uint32_t rows = row_end - row_begin;
+    const size_t npix = (size_t)rows * f.W;
+    if (npix > s->queue_cap) {
+        // growing the queue frees the old one: wait for frames that may still be using it
+        CUDA_TRY(cudaDeviceSynchronize());
+        if (int rc = ensure(s->d_queue, s->queue_cap, npix)) return rc;
+    }
     f.queue = s->d_queue;
 
     const size_t smem_p = (size_t)s->dev.stack_depth * 4 * PRIMARY_THREADS;
     const size_t smem_s = (size_t)s->dev.stack_depth * 4 * SHADOW_THREADS;
-    dim3 grid((unsigned)((width + 31) / 32), (unsigned)((f.rows_local + 7) / 8));
-    if (grid.y > 65535u) return fail(CERES_ERR_INVALID, "ceres_render_device: image too tall");
+    dim3 grid((unsigned)((f.W + 31) / 32), (unsigned)((rows + 7) / 8));
+    if (grid.y > 65535u) return fail(CERES_ERR_INVALID, "ceres_render: image too tall");
+    cudaEvent_t* pe = nullptr;
+    if (s->profile) {
+        if (s->prof_events.size() < 4 * (s->prof_frames + 1)) {
+            for (int k = 0; k < 4; ++k) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); s->prof_events.push_back(e); }
+        }
+        pe = &s->prof_events[4 * s->prof_frames++];
+        CUDA_TRY(cudaEventRecord(pe[0], st));
+    }
     if (s->stats) primary_kernel<true><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
     else primary_kernel<false><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
     g_launches++;
+    if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
     if (f.shadows) {
         int& bps = s->stats ? s->shadow_blocks_per_sm_stats : s->shadow_blocks_per_sm;
         if (bps == 0) {
@@ -770,58 +849,87 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
         else shadow_kernel<false><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
         g_launches++;
     }
+    if (pe) CUDA_TRY(cudaEventRecord(pe[2], st));
     shade_kernel<<<(unsigned)(s->sm_count * 4), SHADE_THREADS, 0, st>>>(s->dev, f);
     g_launches++;
+    if (pe) CUDA_TRY(cudaEventRecord(pe[3], st));
     CUDA_TRY(cudaGetLastError());
     return CERES_OK;
 }
 
-static int pin_host_buffer(ceres_scene* s, void* p, size_t bytes) {
-    // The reference's callers reuse one framebuffer for every frame (anim.cpp:76,105); page-lock it once so the
-    // D2H copy runs at PCIe speed, and keep the registration until another buffer shows up.
-    cudaPointerAttributes attr;
-    if (cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost) return CERES_OK;  // already pinned
-    cudaGetLastError();
-    if (s->reg_ptr == p && s->reg_bytes >= bytes) return CERES_OK;
-    if (s->reg_ptr) { cudaHostUnregister(s->reg_ptr); s->reg_ptr = nullptr; s->reg_bytes = 0; }
-    if (cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) { s->reg_ptr = p; s->reg_bytes = bytes; }
-    else cudaGetLastError();  // pageable copy still works, just slower
-    return CERES_OK;
+int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
+                        unsigned flags, const ceres_shard* shard, void* stream_v, float* d_pixels, uint32_t* d_ids,
+                        uint64_t* d_counters) {
+    Frame f; uint32_t rows_local = 0;
+    if (int rc = prepare_frame(s, cam, sun, width, height, flags, shard, d_pixels, d_ids, d_counters, f, rows_local)) return rc;
+    DeviceGuard guard(s->device);
+    cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
+    if (rows_local == 0) {
+        if (d_counters) CUDA_TRY(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint64_t), st));
+        return CERES_OK;
+    }
+    return launch_rows(s, f, 0, rows_local, false, st);
 }
 
+// Host-framebuffer render.  The shard's rows are rendered in bands on the scene stream; each finished band is
+// copied to the caller's buffer on a second stream while the next band renders, so the PCIe transfer (the larger
+// cost at 4K: 99.5 MB of float RGB) hides the kernels instead of following them.
 int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
                        unsigned flags, const ceres_shard* shard, float* pixels, uint32_t* ids, uint64_t counters[2]) {
     if (!s || !pixels) return fail(CERES_ERR_INVALID, "ceres_render: null argument");
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
-    if (int rc = ensure(s->d_pixels, s->pixels_cap, npix * 3)) return rc;
-    if (ids) if (int rc = ensure(s->d_ids, s->ids_cap, npix)) return rc;
     // device staging is written in COMPACT form (the shard's rows packed); rows are scattered to their frame
     // position by the copies below, so a shard moves only its own bytes over PCIe.
     const bool sharded = shard && shard->count > 1;
     const unsigned dev_flags = flags | (sharded ? CERES_COMPACT_ROWS : 0u);
-    if (int rc = ceres_render_device(s, cam, sun, width, height, dev_flags, shard, nullptr, s->d_pixels, ids ? s->d_ids : nullptr, nullptr)) return rc;
-    const uint32_t rows = shard_rows(height, shard);
+    Frame f; uint32_t rows = 0;
+    {
+        float dummy; // prepare_frame validates before we size the staging buffers
+        if (int rc = prepare_frame(s, cam, sun, width, height, dev_flags, shard, &dummy, nullptr, nullptr, f, rows)) return rc;
+    }
+    if (int rc = ensure(s->d_pixels, s->pixels_cap, npix * 3)) return rc;
+    if (ids) if (int rc = ensure(s->d_ids, s->ids_cap, npix)) return rc;
+    f.pixels = s->d_pixels; f.ids = ids ? s->d_ids : nullptr;
+    if (rows == 0) { if (counters) counters[0] = counters[1] = 0; return CERES_OK; }
+
     const bool want_compact = (flags & CERES_COMPACT_ROWS) != 0;
-    if (!sharded || want_compact) {
-        const size_t n = (size_t)rows * width;
-        pin_host_buffer(s, pixels, n * 3 * sizeof(float));
-        CUDA_TRY(cudaMemcpyAsync(pixels, s->d_pixels, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
-        if (ids) CUDA_TRY(cudaMemcpyAsync(ids, s->d_ids, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
-    } else {
-        pin_host_buffer(s, pixels, npix * 3 * sizeof(float));
-        const uint32_t br = shard->block_rows;
-        size_t lrow = 0;
-        for (size_t b = shard->index; b * br < height; b += shard->count) {
-            size_t lo = b * br, hi = lo + br; if (hi > height) hi = height;
-            const size_t n = (hi - lo) * width;
-            CUDA_TRY(cudaMemcpyAsync(pixels + 3 * lo * width, s->d_pixels + 3 * lrow * width, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
-            if (ids) CUDA_TRY(cudaMemcpyAsync(ids + lo * width, s->d_ids + lrow * width, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
-            lrow += hi - lo;
+    const bool scatter = sharded && !want_compact;
+    // band height: a multiple of the kernel tile (8 rows) and, when rows are scattered, of the shard's row blocks;
+    // ~6 MB of float RGB per band, at most CERES_MAX_BANDS bands
+    const uint32_t unit = scatter ? shard->block_rows : 8u;
+    size_t band_rows = s->tune.band_bytes ? s->tune.band_bytes / (width * 12) : (6u << 20) / (width * 12);
+    if (!host_is_pinned(pixels)) band_rows = rows;       // pageable destination: the copy is synchronous anyway
+    band_rows = (band_rows / unit) * unit;
+    if (band_rows < unit) band_rows = unit;
+    if ((rows + band_rows - 1) / band_rows > CERES_MAX_BANDS) {
+        band_rows = (rows + CERES_MAX_BANDS - 1) / CERES_MAX_BANDS;
+        band_rows = ((band_rows + unit - 1) / unit) * unit;
+    }
+    size_t nb = 0;
+    for (uint32_t r0 = 0; r0 < rows; r0 += (uint32_t)band_rows, ++nb) {
+        const uint32_t r1 = (uint32_t)std::min<size_t>(rows, r0 + band_rows);
+        if (int rc = launch_rows(s, f, r0, r1, nb != 0, s->stream)) return rc;
+        CUDA_TRY(cudaEventRecord(s->band_done[nb], s->stream));
+        CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->band_done[nb], 0));
+        if (!scatter) {
+            const size_t off = (size_t)r0 * width, n = (size_t)(r1 - r0) * width;
+            CUDA_TRY(cudaMemcpyAsync(pixels + 3 * off, s->d_pixels + 3 * off, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
+            if (ids) CUDA_TRY(cudaMemcpyAsync(ids + off, s->d_ids + off, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->copy_stream));
+        } else {
+            const uint32_t br = shard->block_rows;
+            for (uint32_t lrow = r0; lrow < r1; lrow += br) {       // r0 is a multiple of br
+                const size_t blk = (size_t)(lrow / br) * shard->count + shard->index;
+                const size_t lo = blk * br, hi = std::min<size_t>(height, lo + br);
+                const size_t n = (hi - lo) * width;
+                CUDA_TRY(cudaMemcpyAsync(pixels + 3 * lo * width, s->d_pixels + 3 * (size_t)lrow * width, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
+                if (ids) CUDA_TRY(cudaMemcpyAsync(ids + lo * width, s->d_ids + (size_t)lrow * width, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->copy_stream));
+            }
         }
     }
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
     if (counters) { counters[0] = s->h_out[0]; counters[1] = s->h_out[1]; }
     return CERES_OK;
 }
@@ -857,7 +965,6 @@ int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, si
         TRY_Q(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
     }
     TRY_Q(cudaMalloc((void**)&d_cnt, n_frames * 2 * sizeof(unsigned long long)));
-    pin_host_buffer(s, pixels_all, n_frames * fbytes);
     for (size_t k = 0; k < n_frames; ++k) {
         const float* c = cams + 13 * k;
         ceres_camera cam;

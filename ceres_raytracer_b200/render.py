@@ -49,6 +49,15 @@ def _shard(shard):
     return _capi.Shard(int(block_rows), int(index), int(count))
 
 
+def _stream_handle(stream, device):
+    """cudaStream_t for the C ABI.  Default: torch's current stream.  The C ABI reads NULL as "the scene's own
+    stream", so the legacy default stream (handle 0) is passed as cudaStreamLegacy (0x1)."""
+    if stream is None:
+        import torch
+        stream = torch.cuda.current_stream(device).cuda_stream
+    return int(stream) or 1
+
+
 def shard_rows(H, shard):
     """Frame rows owned by a shard (block_rows, index, count), in local order."""
     if shard is None or shard[2] <= 1:
@@ -110,8 +119,8 @@ class Scene:
     def device_bytes(self):
         return int(self._L.ceres_scene_device_bytes(self._h))
 
-    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0):
-        t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm)
+    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, band_bytes=0):
+        t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm, band_bytes)
         _capi.check(self._L.ceres_scene_set_tuning(self._h, C.byref(t)))
 
     def set_stats(self, enable):
@@ -122,6 +131,17 @@ class Scene:
         _capi.check(self._L.ceres_scene_get_stats(self._h, _p(out)))
         names = ["S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "rays", "hits"]
         return {k: int(v) for k, v in zip(names, out)}
+
+    def set_profiling(self, enable):
+        """Per-kernel CUDA-event timing of every render_device call (see kernel_ms)."""
+        _capi.check(self._L.ceres_scene_set_profiling(self._h, int(bool(enable))))
+
+    def kernel_ms(self):
+        """Sums over the frames recorded since set_profiling(True): ({primary,shadow,shade,total} ms, frames)."""
+        ms = np.zeros(4, np.float64)
+        n = C.c_uint64(0)
+        _capi.check(self._L.ceres_scene_get_kernel_ms(self._h, _p(ms), C.byref(n)))
+        return dict(zip(["primary", "shadow", "shade", "total"], ms.tolist())), int(n.value)
 
     # ---- host buffers ---------------------------------------------------------------------------------------
     def render(self, camera, sun_position, width, height, flags=0, pixels=None, want_ids=False, shard=None):
@@ -161,9 +181,7 @@ class Scene:
                       counters=None, stream=None):
         """Enqueue one frame on `stream` (int cudaStream_t; default torch's current stream).  pixels: float32 CUDA
         tensor with 3*rows*width elements; ids: int32/uint32 CUDA tensor or None; counters: int64 CUDA tensor[2]."""
-        import torch
-        if stream is None:
-            stream = torch.cuda.current_stream(self.device).cuda_stream
+        stream = _stream_handle(stream, self.device)
         sun = np.asarray(sun_position, np.float32)
         sh = _shard(shard)
         _capi.check(self._L.ceres_render_device(
@@ -172,9 +190,7 @@ class Scene:
             C.c_void_p(counters.data_ptr()) if counters is not None else None))
 
     def quantize_device(self, pixels, width, height, out, stream=None):
-        import torch
-        if stream is None:
-            stream = torch.cuda.current_stream(self.device).cuda_stream
+        stream = _stream_handle(stream, self.device)
         _capi.check(self._L.ceres_quantize_device(self._h, C.c_void_p(pixels.data_ptr()), width, height,
                                                   C.c_void_p(stream), C.c_void_p(out.data_ptr())))
 
@@ -184,6 +200,35 @@ def render(camera, sun_position, scene, pixels, width, height, flags=0):
     the pair (rays, hits) of render.hpp:155."""
     _, _, counters = scene.render(camera, sun_position, width, height, flags=flags, pixels=pixels)
     return counters
+
+
+class PinnedBuffer:
+    """Page-locked host memory from ceres_host_alloc, exposed as a numpy array (`.array`).  A framebuffer living
+    here is filled by DMA directly from the device."""
+
+    def __init__(self, shape, dtype=np.float32):
+        L = _capi.lib()
+        self._L = L
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._ptr = L.ceres_host_alloc(n)
+        if not self._ptr:
+            raise CeresError(_capi.ERR_CUDA, L.ceres_last_error().decode(errors="replace"))
+        buf = (C.c_char * n).from_address(self._ptr)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def close(self):
+        if getattr(self, "_ptr", None):
+            self.array = None
+            self._L.ceres_host_free(self._ptr)
+            self._ptr = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
 
 
 def kernel_launch_count():

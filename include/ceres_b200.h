@@ -74,7 +74,8 @@ typedef struct ceres_tuning {
     uint32_t primary_block;      /* threads per CTA, primary kernel */
     uint32_t shadow_block;       /* threads per CTA, shadow kernel */
     uint32_t ctas_per_sm;        /* persistent CTAs per SM */
-    uint32_t reserved[4];
+    uint32_t band_bytes;         /* host-framebuffer calls: float RGB bytes per pipelined row band */
+    uint32_t reserved[3];
 } ceres_tuning;
 
 /* ---- scene ------------------------------------------------------------------------------------------------- */
@@ -113,7 +114,8 @@ int ceres_render_sequence(ceres_scene* scene, size_t n_frames, const float* cams
 
 /* ---- render: device buffers (asynchronous; used by bench.py, multi-GPU gather and the host calls above) ------- */
 
-/* Enqueues the frame on `stream` (a cudaStream_t; NULL = the scene's own stream) and returns.  d_pixels / d_ids /
+/* Enqueues the frame on `stream` (a cudaStream_t; NULL = the scene's own stream, cudaStreamLegacy (0x1) = the
+ * legacy default stream) and returns.  d_pixels / d_ids /
  * d_counters are DEVICE pointers on the scene's device (d_ids, d_counters nullable; d_counters = 2 x uint64). */
 int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                         size_t width, size_t height, unsigned flags, const ceres_shard* shard, void* stream,
@@ -126,6 +128,13 @@ int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const fl
  * statistics mode with ceres_scene_set_stats(scene, 1) (slower kernels). */
 int ceres_scene_set_stats(ceres_scene* scene, int enable);
 int ceres_scene_get_stats(ceres_scene* scene, uint64_t stats[8]);
+
+/* Per-kernel timing.  While enabled, every ceres_render_device call records CUDA events on its launch stream
+ * before/after each of its kernels.  ceres_scene_get_kernel_ms waits for the recorded frames and returns the SUMS
+ * over the frames recorded since the last ceres_scene_set_profiling call: ms[0] primary, ms[1] shadow, ms[2] shade,
+ * ms[3] first-to-last event; *frames (nullable) = number of frames summed. */
+int ceres_scene_set_profiling(ceres_scene* scene, int enable);
+int ceres_scene_get_kernel_ms(ceres_scene* scene, double ms[4], uint64_t* frames);
 
 /* ---- known-answer entry points (tests) ----------------------------------------------------------------------- */
 
@@ -145,8 +154,14 @@ int ceres_quantize_device(ceres_scene* scene, const float* d_pixels, size_t widt
                           uint8_t* d_rgb8);
 
 /* ---- pinned host memory helpers ------------------------------------------------------------------------------ */
+/* A framebuffer that is page-locked (allocated here, registered here, or by any cudaHostAlloc) is filled by DMA
+ * directly; any other host pointer is accepted and goes through the driver's pageable-copy path (slower).  The
+ * library never registers caller memory behind the caller's back. */
 void* ceres_host_alloc(size_t bytes);
 void ceres_host_free(void* p);
+int ceres_host_register(void* p, size_t bytes);   /* cudaHostRegister; caller unregisters before freeing */
+int ceres_host_unregister(void* p);
+int ceres_host_is_pinned(const void* p);
 
 /* ---- misc --------------------------------------------------------------------------------------------------- */
 int ceres_abi_version(void);

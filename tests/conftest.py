@@ -44,13 +44,15 @@ def frame_hashes():
 
 def scene_pod(name):
     """Reference-built scene dumps (oracle/_ref/scenes, made by oracle/make_scenes.py); None when absent."""
-    p = os.path.join(SCENES, name + ".npz")
-    return load_npz(p) if os.path.exists(p) else None
+    for p in (os.path.join(GOLDEN, name + "_scene.npz"), os.path.join(SCENES, name + ".npz")):
+        if os.path.exists(p):
+            return load_npz(p)
+    return None
 
 
 @pytest.fixture(scope="session")
 def dragon_pod():
     pod = scene_pod("dragon")
     if pod is None:
-        pytest.skip("oracle/_ref/scenes/dragon.npz not built (needs /root/reference at build time)")
+        pytest.skip("tests/golden/dragon_scene.npz missing (tests/golden/make_golden.py)")
     return pod

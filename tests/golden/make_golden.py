@@ -3,6 +3,7 @@
 
 Run in the build container (needs /root/reference):   python tests/golden/make_golden.py
 Outputs (all small, committed):
+  dragon_scene.npz       same for dragon.obj after rotate x 90 (static.cpp:72-73,83-88)
   bunny_scene.npz        the reference-loaded, reference-built bunny scene (POD arrays), so golden tests need no _ref
   bunny_frames.npz       320x180 frames (ids, state, tuv, rgb, stats) in shadow and primary-only mode
   kat.npz                known-answer vectors: slab test, triangle test, smooth_shading, 20k traced rays, turntable
@@ -60,6 +61,10 @@ def main():
     bunny = ref.RefScene.load_obj(os.path.join(ref_root, "data/bunny.obj"), 1, -145.0, 0, "strict")
     pod = bunny.pod()
     np.savez_compressed(os.path.join(HERE, "bunny_scene.npz"), **pod)
+    # dragon: static.cpp scene (rotate x 90), same loader/builder; input data of bench.py and the dragon parity tests
+    dragon = ref.RefScene.load_obj(os.path.join(ref_root, "data/dragon.obj"), 0, 90.0, 0, "strict")
+    np.savez_compressed(os.path.join(HERE, "dragon_scene.npz"), **dragon.pod())
+    dragon.close()
 
     frames = {}
     for tag, flags in (("shadow", 0), ("primary", 1)):
@@ -112,12 +117,11 @@ def main():
                         trace_rays=trace, trace_ids=tr_ids, trace_tuv=tr_tuv, turntable=turn)
     print("KAT: tri hits", int(thit.sum()), "/", n, "; traced hits", int((tr_ids != ref.MISS).sum()), "/ 20000")
 
-    # ---- frame hashes for the BASELINE configs (scenes come from oracle/_ref/scenes/*.npz at test time)
+    # ---- frame hashes for the BASELINE configs (scenes = the *_scene.npz fixtures above)
     hashes = {}
-    scenes_dir = os.path.join(ROOT, "oracle", "_ref", "scenes")
     for name, cam, confs in (("bunny", BUNNY_CAM, [(1920, 1080, 1), (1920, 1080, 0)]),
                              ("dragon", DRAGON_CAM, [(1920, 1080, 1), (1920, 1080, 0), (3840, 2160, 0)])):
-        spod = dict(np.load(os.path.join(scenes_dir, name + ".npz")))
+        spod = dict(np.load(os.path.join(HERE, name + "_scene.npz")))
         s = ref.RefScene.from_pod(spod, "strict")
         sf = ref.RefScene.from_pod(spod, "fast")
         for W, H, flags in confs:

@@ -204,3 +204,27 @@ def test_invalid_arguments_fail_loudly(cr, bunny_pod):
         rays = np.zeros((1, 8), np.float32); rays[0, 7] = np.nan
         with pytest.raises(cr.CeresError):
             s.trace_rays(rays)
+
+
+@pytest.mark.parametrize("band_bytes", [1, 200_000, 3_000_000])
+def test_band_pipelined_host_render_is_identical(cr, dragon, band_bytes):
+    """ceres_render() renders the frame in row bands and copies each finished band while the next one renders; the
+    result must not depend on the band size, on the destination being page-locked or pageable, or on sharding."""
+    cam, W, H = cr.configs.DRAGON_CAMERA, 1000, 531
+    ref_px, ref_ids, ref_cnt = dragon.render(cam, SUN, W, H, want_ids=True)       # pageable numpy buffer: one band
+    with cr.PinnedBuffer((H, W, 3)) as hb:
+        dragon.set_tuning(band_bytes=band_bytes)
+        try:
+            hb.array[:] = np.nan
+            px, ids, cnt = dragon.render(cam, SUN, W, H, pixels=hb.array, want_ids=True)
+            assert np.array_equal(px.view(np.uint32), ref_px.view(np.uint32))
+            assert np.array_equal(ids, ref_ids) and cnt == ref_cnt
+            # sharded, rows scattered in place into the page-locked frame
+            hb.array[:] = np.nan
+            tot = [0, 0]
+            for k in range(3):
+                _, _, c = dragon.render(cam, SUN, W, H, pixels=hb.array, shard=(16, k, 3))
+                tot[0] += c[0]; tot[1] += c[1]
+            assert np.array_equal(hb.array.view(np.uint32), ref_px.view(np.uint32)) and tuple(tot) == ref_cnt
+        finally:
+            dragon.set_tuning()
