@@ -900,6 +900,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     const uint32_t unit = scatter ? shard->block_rows : 8u;
     size_t band_rows = s->tune.band_bytes ? s->tune.band_bytes / (width * 12) : (6u << 20) / (width * 12);
     if (!host_is_pinned(pixels)) band_rows = rows;       // pageable destination: the copy is synchronous anyway
+    if (band_rows >= rows) band_rows = ((rows + unit - 1) / unit) * unit;   // one band: never split off a remainder
     band_rows = (band_rows / unit) * unit;
     if (band_rows < unit) band_rows = unit;
     if ((rows + band_rows - 1) / band_rows > CERES_MAX_BANDS) {
