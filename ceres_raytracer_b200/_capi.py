@@ -35,7 +35,7 @@ class Tuning(C.Structure):
 # every symbol include/ceres_b200.h declares (tests/test_capi_symbols.py checks the header against this list)
 SYMBOLS = [
     "ceres_scene_create", "ceres_scene_destroy", "ceres_scene_set_tuning", "ceres_scene_device_bytes",
-    "ceres_render", "ceres_render_shard", "ceres_render_sequence", "ceres_render_device",
+    "ceres_render", "ceres_render_shard", "ceres_render_multi", "ceres_render_sequence", "ceres_render_device",
     "ceres_scene_set_stats", "ceres_scene_get_stats", "ceres_trace_rays", "ceres_frame_setup",
     "ceres_scene_set_profiling", "ceres_scene_get_kernel_ms", "ceres_host_register", "ceres_host_unregister",
     "ceres_host_is_pinned", "ceres_quantize_device", "ceres_host_alloc", "ceres_host_free", "ceres_abi_version", "ceres_device_count",
@@ -68,6 +68,7 @@ def lib():
     L.ceres_scene_device_bytes.restype = sz
     L.ceres_render.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp, vp]
     L.ceres_render_shard.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp, vp]
+    L.ceres_render_multi.argtypes = [C.POINTER(vp), C.c_int, camp, vp, sz, sz, C.c_uint, vp, vp, vp]
     L.ceres_render_sequence.argtypes = [vp, sz, vp, sz, sz, C.c_uint, vp, vp]
     L.ceres_render_device.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp, vp, vp]
     L.ceres_scene_set_stats.argtypes = [vp, C.c_int]

@@ -27,6 +27,7 @@
 #include <atomic>
 #include <new>
 #include <algorithm>
+#include <thread>
 
 #include "../../include/ceres_b200.h"
 
@@ -938,6 +939,35 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
 int ceres_render(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
                  unsigned flags, float* pixels, uint32_t* ids, uint64_t counters[2]) {
     return ceres_render_shard(s, cam, sun, width, height, flags & ~CERES_COMPACT_ROWS, nullptr, pixels, ids, counters);
+}
+
+// One frame on several GPUs of the box from ONE process: scene k renders the row blocks b = k (mod n) and writes
+// them by DMA straight into their place in the caller's host frame -- every GPU drains over its own PCIe link, so
+// there is no gather step and no collective.  One host thread per GPU.
+int ceres_render_multi(ceres_scene* const* scenes, int n, const ceres_camera* cam, const float sun[3], size_t width,
+                       size_t height, unsigned flags, float* pixels, uint32_t* ids, uint64_t counters[2]) {
+    if (!scenes || n < 1) return fail(CERES_ERR_INVALID, "ceres_render_multi: no scenes");
+    for (int k = 0; k < n; ++k) if (!scenes[k]) return fail(CERES_ERR_INVALID, "ceres_render_multi: null scene");
+    if (n == 1) return ceres_render(scenes[0], cam, sun, width, height, flags, pixels, ids, counters);
+    std::vector<int> rc(n, CERES_OK);
+    std::vector<std::string> err(n);
+    std::vector<uint64_t> cnt(2 * (size_t)n, 0);
+    auto work = [&](int k) {
+        ceres_shard sh{CERES_TILE_BLOCK_ROWS, (uint32_t)k, (uint32_t)n};
+        rc[k] = ceres_render_shard(scenes[k], cam, sun, width, height, flags & ~CERES_COMPACT_ROWS, &sh, pixels, ids, &cnt[2 * k]);
+        if (rc[k]) err[k] = g_err;      // g_err is thread-local
+    };
+    std::vector<std::thread> threads;
+    for (int k = 1; k < n; ++k) threads.emplace_back(work, k);
+    work(0);
+    for (auto& t : threads) t.join();
+    uint64_t rays = 0, hits = 0;
+    for (int k = 0; k < n; ++k) {
+        if (rc[k]) return fail(rc[k], "GPU shard " + std::to_string(k) + ": " + err[k]);
+        rays += cnt[2 * k]; hits += cnt[2 * k + 1];
+    }
+    if (counters) { counters[0] = rays; counters[1] = hits; }
+    return CERES_OK;
 }
 
 int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height,

@@ -1,0 +1,187 @@
+// include/ceres/render.hpp -- drop-in replacement for the reference's include/render.hpp.
+//
+// Put this directory before the reference's include/ on the include path (or copy the file over include/render.hpp)
+// and link libceres_b200.so: static.cpp / anim.cpp / any caller of
+//
+//     std::pair<int,int> render(const Camera<Scalar>&, const bvh::Vector3<Scalar>& sun_position,
+//                               const bvh::Bvh<Scalar>&, const bvh::Triangle<Scalar>* triangles,
+//                               std::array<bvh::Vector3<Scalar>,3>* tri_norms, Scalar* pixels,
+//                               size_t width, size_t height);                      (reference render.hpp:86-89)
+//
+// compile unchanged and render on the B200 through the C ABI of ceres_b200.h.  Same include guard as the reference
+// header, same names: Camera (render.hpp:16-22), rotate_triangles<Axis> (render.hpp:24-44), render (render.hpp:86-156).
+// The shading helpers lambertian / blinn_phong_spec / smooth_shading (render.hpp:46-84) are device code now and are
+// not re-exported.
+//
+// Written from scratch against the POD layouts of lib/bvh (Node 32 B, Triangle<float> 48 B, tri_norms 36 B); the
+// only reference code this header needs is the lib/bvh type definitions of the caller's own tree.
+//
+// Differences a caller can observe:
+//   * Scalar = float only.  render<double> (anim -d, anim.cpp:154-155) fails to compile with a static_assert: the
+//     GPU path has no double variant and there is NO CPU fallback.
+//   * tri_norms may be nullptr (static.cpp:130 passes nullptr, which does not even deduce against the reference
+//     signature): normals are then taken as zero, as the reference would read them if it could.
+//   * errors (no GPU, CUDA failure, malformed BVH) throw std::runtime_error; the reference has no error path.
+//   * the scene (bvh, triangles, tri_norms) is flattened and uploaded on the first call and re-used while the same
+//     arrays are passed again (the reference builds them once, outside the frame loop, anim.cpp:46-65).  The cache
+//     key is the three pointers + counts + a sampled fingerprint of the contents; call ceres::invalidate_scene()
+//     after modifying geometry in place if you want to be certain.
+#ifndef __RENDER_H
+#define __RENDER_H
+
+#include <array>
+#include <cmath>
+#include <cstddef>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <utility>
+
+#include <bvh/bvh.hpp>
+#include <bvh/triangle.hpp>
+#include <bvh/vector.hpp>
+
+#include "ceres_b200.h"
+#if __has_include("transform.hpp")
+#include "transform.hpp"      // the reference's render.hpp pulls it in for anim.cpp (render.hpp:14)
+#endif
+
+template <typename Scalar>
+struct Camera {
+    bvh::Vector3<Scalar> eye;
+    bvh::Vector3<Scalar> dir;
+    bvh::Vector3<Scalar> up;
+    Scalar fov;
+};
+
+// render.hpp:24-44: rotation about a coordinate axis, every triangle rebuilt from its rotated corners so that the
+// edges and the normal are recomputed by the Triangle constructor.  Host code (scene preparation, outside the
+// timed path).
+template <size_t Axis, typename Scalar>
+static void rotate_triangles(Scalar degrees, bvh::Triangle<Scalar>* triangles, size_t triangle_count) {
+    static_assert(Axis < 3, "axis is 0 (x), 1 (y) or 2 (z)");
+    const Scalar angle = degrees * Scalar(3.14159265359) / Scalar(180);
+    const Scalar c = std::cos(angle), s = std::sin(angle);
+    constexpr size_t A = (Axis + 1) % 3, B = (Axis + 2) % 3;      // the plane that turns
+    auto turn = [c, s](const bvh::Vector3<Scalar>& p) {
+        bvh::Vector3<Scalar> q = p;
+        // x: (y,z) -> (y c - z s, y s + z c);  y: (z,x) -> (z c - x s, z s + x c) written as the reference orders
+        // its terms (x c + z s, -x s + z c);  z: (x,y) -> (x c - y s, x s + y c)
+        if (Axis == 1) { q[0] = p[0] * c + p[2] * s; q[2] = -p[0] * s + p[2] * c; }
+        else           { q[A] = p[A] * c - p[B] * s; q[B] = p[A] * s + p[B] * c; }
+        return q;
+    };
+    #pragma omp parallel for
+    for (size_t i = 0; i < triangle_count; ++i) {
+        const auto a = turn(triangles[i].p0), b = turn(triangles[i].p1()), d = turn(triangles[i].p2());
+        triangles[i] = bvh::Triangle<Scalar>(a, b, d);
+    }
+}
+
+namespace ceres {
+
+namespace detail {
+
+struct SceneCache {
+    ceres_scene* scene = nullptr;
+    const void* nodes = nullptr; const void* tris = nullptr; const void* norms = nullptr;
+    size_t node_count = 0, tri_count = 0;
+    uint64_t fingerprint = 0;
+    ~SceneCache() { if (scene) ceres_scene_destroy(scene); }
+};
+inline SceneCache& cache() { static SceneCache c; return c; }
+
+// FNV-1a over up to 64 evenly spaced 32-byte windows: cheap enough to run every frame, catches in-place edits
+inline uint64_t sample(const void* p, size_t bytes, uint64_t h) {
+    const unsigned char* b = static_cast<const unsigned char*>(p);
+    if (!b || !bytes) return h;
+    const size_t windows = 64, span = 32;
+    const size_t step = bytes > windows * span ? (bytes - span) / (windows - 1) : span;
+    for (size_t off = 0; off + span <= bytes; off += step)
+        for (size_t k = 0; k < span; ++k) { h ^= b[off + k]; h *= 1099511628211ull; }
+    return h;
+}
+
+[[noreturn]] inline void fail(const char* what) {
+    throw std::runtime_error(std::string(what) + ": " + ceres_last_error());
+}
+
+}  // namespace detail
+
+inline void invalidate_scene() {
+    auto& c = detail::cache();
+    if (c.scene) ceres_scene_destroy(c.scene);
+    c = detail::SceneCache{};
+}
+
+// GPU used by render(); default device 0 (CERES_DEVICE in the environment overrides)
+inline int device() {
+    const char* e = std::getenv("CERES_DEVICE");
+    return e ? std::atoi(e) : 0;
+}
+
+// the flattened, GPU-resident form of (bvh, triangles, tri_norms); created on first use
+inline ceres_scene* scene_for(const bvh::Bvh<float>& bvh, const bvh::Triangle<float>* triangles,
+                              const std::array<bvh::Vector3<float>, 3>* tri_norms) {
+    static_assert(sizeof(bvh::Bvh<float>::Node) == 32, "lib/bvh/bvh.hpp:25-30");
+    static_assert(sizeof(bvh::Triangle<float>) == 48, "lib/bvh/triangle.hpp:27");
+    static_assert(sizeof(std::array<bvh::Vector3<float>, 3>) == 36, "lib/obj_norms.hpp:113-115");
+    auto& c = detail::cache();
+    // number of primitives = sum of leaf counts = what primitive_indices holds; the reference passes no count, so
+    // derive it from the tree once per new tree
+    const void* nodes = bvh.nodes.get();
+    size_t tri_count = c.tri_count;
+    const bool same_arrays = c.scene && c.nodes == nodes && c.tris == triangles && c.norms == tri_norms &&
+                             c.node_count == bvh.node_count;
+    if (!same_arrays) {
+        tri_count = 0;
+        for (size_t k = 0; k < bvh.node_count; ++k) tri_count += bvh.nodes[k].primitive_count;
+    }
+    uint64_t fp = 1469598103934665603ull;
+    fp = detail::sample(nodes, bvh.node_count * 32, fp);
+    fp = detail::sample(triangles, tri_count * 48, fp);
+    fp = detail::sample(tri_norms, tri_norms ? tri_count * 36 : 0, fp);
+    if (same_arrays && fp == c.fingerprint) return c.scene;
+    invalidate_scene();
+    ceres_scene* s = nullptr;
+    if (ceres_scene_create(nodes, bvh.node_count, bvh.primitive_indices.get(), triangles, tri_norms, tri_count,
+                           device(), &s) != CERES_OK)
+        detail::fail("ceres_scene_create");
+    c.scene = s; c.nodes = nodes; c.tris = triangles; c.norms = tri_norms;
+    c.node_count = bvh.node_count; c.tri_count = tri_count; c.fingerprint = fp;
+    return s;
+}
+
+}  // namespace ceres
+
+template <typename Scalar>
+std::pair<int, int> render(const Camera<Scalar>& camera, const bvh::Vector3<Scalar>& sun_position,
+                           const bvh::Bvh<Scalar>& bvh, const bvh::Triangle<Scalar>* triangles,
+                           std::array<bvh::Vector3<Scalar>, 3>* tri_norms, Scalar* pixels,
+                           size_t width, size_t height) {
+    static_assert(std::is_same<Scalar, float>::value,
+                  "ceres_b200 renders Scalar = float only; there is no double GPU path and no CPU fallback");
+    ceres_scene* scene = ceres::scene_for(bvh, triangles, tri_norms);
+    ceres_camera cam;
+    for (int k = 0; k < 3; ++k) { cam.eye[k] = camera.eye[k]; cam.dir[k] = camera.dir[k]; cam.up[k] = camera.up[k]; }
+    cam.fov = camera.fov;
+    const float sun[3] = {sun_position[0], sun_position[1], sun_position[2]};
+    uint64_t counters[2] = {0, 0};
+    if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, counters) != CERES_OK)
+        ceres::detail::fail("ceres_render");
+    return std::pair<int, int>(static_cast<int>(counters[0]), static_cast<int>(counters[1]));   // render.hpp:155
+}
+
+// static.cpp:130 calls render(..., nullptr, ...): give that call something to bind to
+template <typename Scalar>
+std::pair<int, int> render(const Camera<Scalar>& camera, const bvh::Vector3<Scalar>& sun_position,
+                           const bvh::Bvh<Scalar>& bvh, const bvh::Triangle<Scalar>* triangles, std::nullptr_t,
+                           Scalar* pixels, size_t width, size_t height) {
+    return render<Scalar>(camera, sun_position, bvh, triangles,
+                          static_cast<std::array<bvh::Vector3<Scalar>, 3>*>(nullptr), pixels, width, height);
+}
+
+#endif  // __RENDER_H

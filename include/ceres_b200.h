@@ -11,7 +11,7 @@
  * shim with the identical template signature, include/ceres/render.hpp, and for a ctypes stub).
  *
  * Plain pointers and sizes only.  All input arrays use the reference's own POD layouts (Scalar = float):
- *   nodes      bvh::Bvh<float>::Node, 32 B  {float bounds[6] /*minx,maxx,miny,maxy,minz,maxz*\/;
+ *   nodes      bvh::Bvh<float>::Node, 32 B  {float bounds[6] (minx,maxx,miny,maxy,minz,maxz);
  *                                            uint32 primitive_count; uint32 first_child_or_primitive}
  *                                                                                   (lib/bvh/bvh.hpp:25-30)
  *   prim_idx   size_t[tri_count]            Bvh::primitive_indices                  (lib/bvh/bvh.hpp:94)
@@ -105,6 +105,13 @@ int ceres_render(ceres_scene* scene, const ceres_camera* camera, const float sun
 int ceres_render_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                        size_t width, size_t height, unsigned flags, const ceres_shard* shard,
                        float* pixels, uint32_t* ids, uint64_t counters[2]);
+
+/* One frame on n GPUs from one process: scenes[k] (created on device k from the same arrays) renders the row blocks
+ * b = k (mod n) of CERES_TILE_BLOCK_ROWS rows and DMA-writes them in place into the host frame; counters are summed.
+ * No collective: every GPU drains its rows over its own PCIe link. */
+#define CERES_TILE_BLOCK_ROWS 16u
+int ceres_render_multi(ceres_scene* const* scenes, int n, const ceres_camera* camera, const float sun_position[3],
+                       size_t width, size_t height, unsigned flags, float* pixels, uint32_t* ids, uint64_t counters[2]);
 
 /* N frames with one upload of the camera path: cams = n_frames x 13 floats (eye[3],dir[3],up[3],fov,sun[3]),
  * the per-frame values of anim.cpp:87-89; pixels_all = n_frames frames back to back; counters_all (nullable)

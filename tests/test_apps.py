@@ -1,0 +1,157 @@
+"""The drop-in executables (apps/render, apps/anim -- C++ host code over the C ABI) against the reference's own code.
+
+The reference tree does not travel to the GPU box, so the OBJ input is synthesised here (a bumpy torus with shared
+vertices, quads, negative indices and CRLF line ends -- the loader features obj_norms.hpp:77-105 handles); the
+expected output comes from oracle/_ref/libceres_ref_strict.so (the reference's loader, builders, rotate_triangles and
+render() compiled unchanged), which does travel.  Bars as in test_gpu_parity.py: ids bit-exact, RGB 1e-6, PPM bytes
+equal up to one LSB on <= 1e-5 of the bytes."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RENDER = os.path.join(ROOT, "apps", "_build", "render")
+ANIM = os.path.join(ROOT, "apps", "_build", "anim")
+RGB_ATOL = 1e-6
+
+
+def write_torus_obj(path, nu=96, nv=48):
+    u = np.linspace(0, 2 * np.pi, nu, endpoint=False)
+    v = np.linspace(0, 2 * np.pi, nv, endpoint=False)
+    uu, vv = np.meshgrid(u, v, indexing="ij")
+    r = 0.35 + 0.05 * np.sin(5 * uu) * np.cos(3 * vv)
+    x = (1.0 + r * np.cos(vv)) * np.cos(uu)
+    y = r * np.sin(vv)
+    z = (1.0 + r * np.cos(vv)) * np.sin(uu)
+    nvert = nu * nv
+    lines = ["# synthetic torus", "o torus", "s 1"]
+    for a, b, c in zip(x.ravel(), y.ravel(), z.ravel()):
+        lines.append(f"v {a:.7f} {b:.7f} {c:.7f}")
+    lines.append("vn 0 1 0")            # ignored by the loader
+    k = 0
+    for i in range(nu):
+        for j in range(nv):
+            a, b = i * nv + j, i * nv + (j + 1) % nv
+            c, d = ((i + 1) % nu) * nv + (j + 1) % nv, ((i + 1) % nu) * nv + j
+            if k % 3 == 0:      # quad -> fan-triangulated by the loader
+                lines.append(f"f {a+1} {b+1} {c+1} {d+1}")
+            elif k % 3 == 1:    # two triangles with v/vt/vn style indices
+                lines.append(f"f {a+1}//1 {b+1}//1 {c+1}//1")
+                lines.append(f"f {a+1}//1 {c+1}//1 {d+1}//1")
+            else:               # negative (relative) indices
+                lines.append(f"f {a-nvert} {b-nvert} {c-nvert}")
+                lines.append(f"f {a-nvert} {c-nvert} {d-nvert}")
+            k += 1
+    with open(path, "wb") as f:
+        f.write(("\r\n".join(lines) + "\r\n").encode())
+
+
+def read_ppm(path):
+    with open(path, "rb") as f:
+        head = f.readline().split()
+        assert head[0] == b"P6"
+        W, H, mx = int(head[1]), int(head[2]), int(head[3])
+        data = np.frombuffer(f.read(), np.uint8 if mx < 256 else ">u2")
+    return data.reshape(H, W, 3)
+
+
+def quantise(px):
+    x = px.astype(np.float32) * np.float32(255)
+    x = np.where(np.float32(255) < x, np.float32(255), x)
+    x = np.where(x < 0, np.float32(0), x)
+    return x.astype(np.uint8)[::-1]
+
+
+needs_binaries = pytest.mark.skipif(not (os.path.exists(RENDER) and os.path.exists(ANIM) and ref.available("strict")),
+                                    reason="apps/_build or oracle/_ref not built (run __graft_entry__.build() where /root/reference exists)")
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("builder,bcode,extra", [("binned", 1, []), ("sweep", 0, ["--dump-ids"]), ("sweep", 0, ["--no-shadow", "--dump-ids"])])
+def test_render_binary_matches_reference(tmp_path, builder, bcode, extra):
+    obj = str(tmp_path / "torus.obj")
+    write_torus_obj(obj)
+    W, H = 640, 360
+    out = str(tmp_path / "render.ppm")
+    cmd = [RENDER, obj, "--eye", "0.3", "1.2", "-3.0", "--dir", "-0.1", "-0.35", "1", "--rotate", "y", "-145", "--sun", "-50", "60", "-20",
+           "--width", str(W), "--height", str(H), "-o", out, "--builder", builder, "--dump-rgb", str(tmp_path / "rgb.f32")]
+    want_ids = "--dump-ids" in extra
+    extra = [e for e in extra if e != "--dump-ids"]
+    if want_ids:
+        cmd += ["--dump-ids", str(tmp_path / "ids.u32")]
+    r = subprocess.run(cmd + extra, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "BVH of" in r.stdout and "Rendering image (640x360)" in r.stdout and "Rays:" in r.stdout
+
+    s = ref.RefScene.load_obj(obj, rot_axis=1, rot_deg=-145.0, builder=bcode)
+    cam = ref.cam_array((0.3, 1.2, -3.0), (-0.1, -0.35, 1), (0, 1, 0), 60)
+    sun = np.array([-50, 60, -20], np.float32)
+    flags = 1 if "--no-shadow" in extra else 0
+    o = s.render_ex(cam, sun, W, H, flags)
+    rays, hits = o["stats"]["rays"], o["stats"]["hits"]
+    assert f"Rays: {rays}\tHits: {hits}" in r.stdout
+    assert 0.1 < (o["ids"] != ref.MISS).mean() < 0.9
+    rgb = np.fromfile(str(tmp_path / "rgb.f32"), np.float32).reshape(H, W, 3)
+    assert np.abs(rgb - o["pixels"]).max() <= RGB_ATOL
+    if want_ids:
+        ids = np.fromfile(str(tmp_path / "ids.u32"), np.uint32).reshape(H, W)
+        assert np.array_equal(ids, o["ids"])
+    img = read_ppm(out)
+    d = img.astype(np.int16) - quantise(o["pixels"]).astype(np.int16)
+    assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-5
+    if not flags:
+        # the unmodified reference render() itself
+        px, rrays, rhits, _ = s.render(cam, sun, W, H)
+        assert (rrays, rhits) == (rays, hits) and np.abs(rgb - px).max() <= RGB_ATOL
+    s.close()
+
+
+@pytest.mark.gpu
+@needs_binaries
+def test_anim_binary_matches_reference_turntable(tmp_path):
+    obj = str(tmp_path / "torus.obj")
+    write_torus_obj(obj, 64, 32)
+    W, H, n = 200, 320, 5
+    # upstream camera (-150,-20,0) looks along +x from far away; scale the torus up so that it fills the view
+    with open(obj, "rb") as f:
+        txt = f.read().decode().replace("\r\n", "\n").split("\n")
+    with open(obj, "w") as f:
+        for line in txt:
+            if line.startswith("v "):
+                a, b, c = (float(t) * 40 for t in line.split()[1:4])
+                f.write(f"v {a:.5f} {b:.5f} {c:.5f}\n")
+            else:
+                f.write(line + "\n")
+    out = str(tmp_path / "turn.mp4")
+    r = subprocess.run([ANIM, "--input", obj, "--frames", str(n), "--width", str(W), "--height", str(H), out],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    s = ref.RefScene.load_obj(obj, builder=0)
+    cams = ref.turntable(ref.cam_array((-150, -20, 0), (1, -0.1, 0), (0, -1, 0), 60), [-500, 300, 10], [0, 1, 0], n)
+    total = 0
+    for k in range(n):
+        px, rays, hits, _ = s.render(cams[k, :10], cams[k, 10:13], W, H)
+        assert f"Rays: {rays}\tHits: {hits}" in r.stdout
+        total += rays
+        img = read_ppm(str(tmp_path / f"turn_{k:04d}.ppm"))
+        d = img.astype(np.int16) - quantise(px).astype(np.int16)
+        assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-5
+        assert (img != 0).any()
+    assert f"Total Rays: {total}" in r.stdout
+    s.close()
+    # -d is refused loudly
+    r = subprocess.run([ANIM, "-d", out], capture_output=True, text=True)
+    assert r.returncode != 0 and "double" in r.stderr
+
+
+@needs_binaries
+def test_binaries_fail_loudly_without_gpu_or_input(tmp_path):
+    r = subprocess.run([RENDER, str(tmp_path / "missing.obj")], capture_output=True, text=True)
+    assert r.returncode != 0 and "empty or cannot be loaded" in r.stderr
+    r = subprocess.run([RENDER, "--bogus"], capture_output=True, text=True)
+    assert r.returncode == 2
