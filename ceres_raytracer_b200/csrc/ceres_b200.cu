@@ -67,6 +67,8 @@ struct FrameCounters {
     uint32_t shadow_next;   // work-stealing cursor of the shadow kernel
     uint32_t occluded;      // shadow rays that hit something
     uint32_t done_blocks;   // shade kernel: blocks finished (last one publishes the counters)
+    uint32_t primary_next;  // work-stealing cursor of the persistent primary wave
+    uint32_t pad_[3];
     unsigned long long stats[6];  // S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow (statistics mode only)
 };
 
@@ -79,6 +81,11 @@ struct Frame {
     uint32_t block_rows, shard_index, shard_count;
     uint32_t compact;          // outputs packed by local row
     uint32_t shadows;
+    // persistent primary wave: conservative screen rectangle of the scene, in local rows / columns of this launch,
+    // cut into 8x4-pixel tiles (work item = tile * 32 + pixel in tile)
+    uint32_t rect_x0, rect_x1, rect_row0, rect_row1, tiles_x, work_items;
+    uint32_t refill_min;                            // refill a warp when at least this many ray slots are idle (1..32)
+    uint32_t cull_i0, cull_i1, cull_l0, cull_l1;   // host only: the rectangle for the whole frame (columns, LOCAL rows)
     float* pixels;
     uint32_t* ids;
     unsigned long long* out_counters;   // [rays, hits]
@@ -429,7 +436,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
             f.out_stats[6] = (f.accumulate ? f.out_stats[6] : 0ull) + rays;
             f.out_stats[7] = (f.accumulate ? f.out_stats[7] : 0ull) + nh;
         }
-        f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0;
+        f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0; f.ctr->primary_next = 0;
         for (int k = 0; k < 6; ++k) f.ctr->stats[k] = 0;
         __threadfence();
     }
@@ -470,6 +477,8 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
     }
 }
 
+#include "trace_persistent.cuh"
+
 // ------------------------------------------------------------------------------------------------ host side
 #define CERES_MAX_BANDS 32
 struct ceres_scene {
@@ -494,6 +503,8 @@ struct ceres_scene {
     size_t prof_frames = 0;
     ceres_tuning tune{};
     int shadow_blocks_per_sm = 0, shadow_blocks_per_sm_stats = 0;
+    int trace_blocks_per_sm[4] = {0, 0, 0, 0};              // [wave*2 + stats]
+    float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
 };
 
 namespace {
@@ -686,6 +697,7 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     s->device = device;
     s->sm_count = prop.multiProcessorCount;
     s->tri_count = (uint32_t)tri_count;
+    for (int b = 0; b < 6; ++b) s->bounds[b] = root.bounds[b];
     auto bail = [&](int code) { ceres_scene_destroy(s); return code; };
 #define TRY_S(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); return bail(CERES_ERR_CUDA); } } while (0)
     TRY_S(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
@@ -738,6 +750,7 @@ int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");
     if (t) s->tune = *t; else s->tune = ceres_tuning{};
     s->shadow_blocks_per_sm = s->shadow_blocks_per_sm_stats = 0;
+    for (int k = 0; k < 4; ++k) s->trace_blocks_per_sm[k] = 0;
     return CERES_OK;
 }
 
@@ -781,6 +794,54 @@ int ceres_scene_get_stats(ceres_scene* s, uint64_t stats[8]) {
     return CERES_OK;
 }
 
+// host copy of frame_row()
+static uint32_t frame_row_host(const Frame& f, uint32_t lrow) {
+    if (f.shard_count <= 1) return lrow;
+    const uint32_t blk = lrow / f.block_rows;
+    return (blk * f.shard_count + f.shard_index) * f.block_rows + (lrow - blk * f.block_rows);
+}
+
+// Conservative screen rectangle of the scene: pixels outside it cannot hit anything, so the primary wave never traces
+// them (their colour is the 0 the clear pass wrote, render.hpp:116-117).  The root box is inflated by 1e-4 of the
+// scene/eye scale -- three orders of magnitude above the rounding error of the binary32 slab test and of the
+// normalised ray direction -- its 8 corners are projected in double precision, and the rectangle gets one more pixel
+// of margin.  Any corner at or behind the eye plane, or any non-finite value, disables the culling.
+static void cull_rectangle(const float bounds[6], Frame& f, uint32_t rows_local) {
+    f.cull_i0 = 0; f.cull_i1 = f.W; f.cull_l0 = 0; f.cull_l1 = rows_local;
+    double scale = 0.0;
+    for (int k = 0; k < 6; ++k) scale = std::max(scale, std::fabs((double)bounds[k]));
+    for (int k = 0; k < 3; ++k) scale = std::max(scale, std::fabs((double)f.eye[k]));
+    if (!std::isfinite(scale) || !(scale > 0.0)) return;
+    const double m = 1e-4 * scale;
+    auto dot = [](const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; };
+    double iu[3], iv[3], dir[3];
+    for (int k = 0; k < 3; ++k) { iu[k] = f.iu[k]; iv[k] = f.iv[k]; dir[k] = f.dir[k]; }
+    const double iu2 = dot(iu, iu), iv2 = dot(iv, iv), d2 = dot(dir, dir);
+    if (!(iu2 > 0.0) || !(iv2 > 0.0) || !(d2 > 0.0) || !std::isfinite(iu2 + iv2 + d2)) return;
+    double umin = INFINITY, umax = -INFINITY, vmin = INFINITY, vmax = -INFINITY;
+    for (int c = 0; c < 8; ++c) {
+        double p[3];
+        for (int k = 0; k < 3; ++k) p[k] = ((c >> k) & 1 ? (double)bounds[2 * k + 1] + m : (double)bounds[2 * k] - m) - (double)f.eye[k];
+        const double z = dot(p, dir) / d2;
+        if (!(z > 1e-6 * scale)) return;
+        const double u = dot(p, iu) / iu2 / z, v = dot(p, iv) / iv2 / z;
+        umin = std::min(umin, u); umax = std::max(umax, u); vmin = std::min(vmin, v); vmax = std::max(vmax, v);
+    }
+    if (!std::isfinite(umin + umax + vmin + vmax)) return;
+    // pixel centre i sits at u = 2 (i + 0.5) / W - 1  (render.hpp:109)
+    auto lo_px = [](double u, double n) { double x = std::floor((u + 1.0) * n / 2.0 - 0.5) - 1.0; return x < 0.0 ? 0.0 : (x > n ? n : x); };
+    auto hi_px = [](double u, double n) { double x = std::ceil((u + 1.0) * n / 2.0 - 0.5) + 2.0; return x < 0.0 ? 0.0 : (x > n ? n : x); };
+    const uint32_t i0 = (uint32_t)lo_px(umin, f.W), i1 = (uint32_t)hi_px(umax, f.W);
+    const uint32_t j0 = (uint32_t)lo_px(vmin, f.H), j1 = (uint32_t)hi_px(vmax, f.H);
+    f.cull_i0 = i0; f.cull_i1 = i1 > i0 ? i1 : i0;
+    // frame rows [j0, j1) -> local rows of this shard (frame_row is increasing in the local row)
+    uint32_t l0 = 0;
+    while (l0 < rows_local && frame_row_host(f, l0) < j0) ++l0;
+    uint32_t l1 = l0;
+    while (l1 < rows_local && frame_row_host(f, l1) < j1) ++l1;
+    f.cull_l0 = l0; f.cull_l1 = l1;
+}
+
 // Fills the per-frame constants (everything but the row range).
 static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
                          unsigned flags, const ceres_shard* shard, float* d_pixels, uint32_t* d_ids, uint64_t* d_counters,
@@ -805,6 +866,8 @@ static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float su
     f.out_counters = d_counters ? (unsigned long long*)d_counters : s->d_out;
     f.out_stats = s->stats ? s->d_out + 2 : nullptr;
     f.ctr = s->d_ctr;
+    if (s->tune.variant != 2) cull_rectangle(s->bounds, f, rows_local);
+    else { f.cull_i0 = 0; f.cull_i1 = f.W; f.cull_l0 = 0; f.cull_l1 = rows_local; }
     return CERES_OK;
 }
 
@@ -833,22 +896,57 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         pe = &s->prof_events[4 * s->prof_frames++];
         CUDA_TRY(cudaEventRecord(pe[0], st));
     }
-    if (s->stats) primary_kernel<true><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
-    else primary_kernel<false><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
-    g_launches++;
-    if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
-    if (f.shadows) {
-        int& bps = s->stats ? s->shadow_blocks_per_sm_stats : s->shadow_blocks_per_sm;
-        if (bps == 0) {
-            if (s->tune.ctas_per_sm) bps = (int)s->tune.ctas_per_sm;
-            else if (s->stats) CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, shadow_kernel<true>, SHADOW_THREADS, smem_s));
-            else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, shadow_kernel<false>, SHADOW_THREADS, smem_s));
-            if (bps < 1) bps = 1;
-        }
-        const unsigned g = (unsigned)(s->sm_count * bps);
-        if (s->stats) shadow_kernel<true><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
-        else shadow_kernel<false><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
+    if (s->tune.variant == 1) {
+        // legacy wave kernels: one thread per pixel, no culling, no refill (kept for A/B measurements)
+        if (s->stats) primary_kernel<true><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
+        else primary_kernel<false><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
         g_launches++;
+        if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
+        if (f.shadows) {
+            int& bps = s->stats ? s->shadow_blocks_per_sm_stats : s->shadow_blocks_per_sm;
+            if (bps == 0) {
+                if (s->tune.ctas_per_sm) bps = (int)s->tune.ctas_per_sm;
+                else if (s->stats) CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, shadow_kernel<true>, SHADOW_THREADS, smem_s));
+                else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, shadow_kernel<false>, SHADOW_THREADS, smem_s));
+                if (bps < 1) bps = 1;
+            }
+            const unsigned g = (unsigned)(s->sm_count * bps);
+            if (s->stats) shadow_kernel<true><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
+            else shadow_kernel<false><<<g, SHADOW_THREADS, smem_s, st>>>(s->dev, f);
+            g_launches++;
+        }
+    } else {
+        // clear -> persistent primary wave over the culled rectangle -> persistent shadow wave
+        const uint32_t r0 = std::max(row_begin, f.cull_l0), r1 = std::min(row_end, f.cull_l1);
+        f.rect_x0 = f.cull_i0; f.rect_x1 = f.cull_i1; f.rect_row0 = r0; f.rect_row1 = r1 > r0 ? r1 : r0;
+        f.tiles_x = (f.rect_x1 - f.rect_x0 + 7u) / 8u;
+        const uint64_t tiles = (uint64_t)f.tiles_x * ((f.rect_row1 - f.rect_row0 + 3u) / 4u);
+        if (tiles * 32u >= (1ull << 32)) return fail(CERES_ERR_INVALID, "ceres_render: image too large");
+        f.work_items = (uint32_t)(tiles * 32u);
+        f.refill_min = s->tune.reserved[0] ? std::min(32u, s->tune.reserved[0]) : REFILL_MIN;
+        clear_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(f);
+        g_launches++;
+        // launch helper: persistent grid = SMs x resident CTAs of this instantiation
+        auto launch_wave = [&](int wave, auto kernel, int threads) -> int {
+            const size_t smem_t = (size_t)s->dev.stack_depth * 4 * threads;
+            int& bps = s->trace_blocks_per_sm[wave * 2 + (s->stats ? 1 : 0)];
+            if (bps == 0) {
+                if (s->tune.ctas_per_sm) bps = (int)s->tune.ctas_per_sm;
+                else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, threads, smem_t) != cudaSuccess) bps = 1;
+                if (bps < 1) bps = 1;
+            }
+            kernel<<<(unsigned)(s->sm_count * bps), threads, smem_t, st>>>(s->dev, f);
+            g_launches++;
+            return 0;
+        };
+        const bool wide_p = s->tune.primary_block == 256, wide_s = s->tune.shadow_block == 256;
+        if (s->stats) { if (wide_p) launch_wave(0, trace_kernel<WAVE_PRIMARY, true, 256>, 256); else launch_wave(0, trace_kernel<WAVE_PRIMARY, true, 128>, 128); }
+        else { if (wide_p) launch_wave(0, trace_kernel<WAVE_PRIMARY, false, 256>, 256); else launch_wave(0, trace_kernel<WAVE_PRIMARY, false, 128>, 128); }
+        if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
+        if (f.shadows) {
+            if (s->stats) { if (wide_s) launch_wave(1, trace_kernel<WAVE_SHADOW, true, 256>, 256); else launch_wave(1, trace_kernel<WAVE_SHADOW, true, 128>, 128); }
+            else { if (wide_s) launch_wave(1, trace_kernel<WAVE_SHADOW, false, 256>, 256); else launch_wave(1, trace_kernel<WAVE_SHADOW, false, 128>, 128); }
+        }
     }
     if (pe) CUDA_TRY(cudaEventRecord(pe[2], st));
     shade_kernel<<<(unsigned)(s->sm_count * 4), SHADE_THREADS, 0, st>>>(s->dev, f);

@@ -1,0 +1,283 @@
+// trace_persistent.cuh -- persistent-warp, lane-refilling traversal kernel (included by ceres_b200.cu after the
+// device math helpers).
+//
+// One kernel template serves both ray waves of a frame:
+//   WAVE_PRIMARY  work item k = pixel k of the culled tile rectangle (8x4-pixel tiles, 32 consecutive items = one
+//                 tile, so a freshly filled warp is as coherent as a screen tile); closest-hit traversal; hits are
+//                 ballot-compacted into the record queue.  Misses write NOTHING: the framebuffer was cleared by
+//                 clear_kernel, and pixels outside the conservative screen rectangle of the scene are never traced.
+//   WAVE_SHADOW   work item k = queue record k; the shadow ray of render.hpp:120-136, any-hit traversal; an occluded
+//                 record gets its OCCLUDED bit set.
+// Scheduling: `SMs x occupancy` CTAs stay resident; every warp owns 32 ray slots.  When at least REFILL_MIN slots of
+// a warp are idle it retires the finished rays (one atomic per warp for the queue append), grabs as many new work
+// items as it has idle lanes with ONE atomicAdd on the global cursor, and sets the new rays up in those lanes while
+// the other lanes keep their rays.  SIMD lanes therefore stay busy although ray lengths differ wildly (1 to 127
+// node-pair steps on the dragon).  The per-ray semantics are untouched: every lane walks its own ray through
+// exactly the reference's sequence of slab tests and triangle tests (see traverse() in ceres_b200.cu for the
+// citations), so the hit ids stay bit-exact.
+//
+// The traversal stack lives in shared memory, one column per thread (word index = depth * blockDim + tid: bank =
+// lane, conflict-free), addressed through a running word offset so that a push/pop is one STS/LDS + one add.
+
+#define WAVE_PRIMARY 0
+#define WAVE_SHADOW 1
+#define TRACE_THREADS 128
+#define REFILL_MIN 32u       // default: refill a warp only when all 32 ray slots are idle (coherence wins)
+
+struct RaySlot {
+    float ox, oy, oz, dx, dy, dz;      // origin, direction
+    float ix, iy, iz, sx, sy, sz;      // safe inverse direction, scaled origin (node_intersectors.hpp:89-94)
+    float tmax;                         // ray.tmax, shrinks with every accepted hit (single_ray_traverser.hpp:58)
+    float u, v;                         // best hit so far (its t is tmax)
+    uint32_t slot;                      // leaf slot of the best hit
+    uint32_t cur;                       // node pair to test next
+    uint32_t sp;                        // word offset of the next free stack entry in this thread's column
+    uint32_t item;                      // work item being traced
+    bool found;
+};
+
+__device__ __forceinline__ void ray_begin(RaySlot& r, V3 o, V3 d, uint32_t tid) {
+    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    const float eps = FLT_EPSILON;                                   // vector.hpp:69-74
+    r.ix = rcp(fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x);
+    r.iy = rcp(fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y);
+    r.iz = rcp(fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z);
+    r.sx = mul(-o.x, r.ix); r.sy = mul(-o.y, r.iy); r.sz = mul(-o.z, r.iz);
+    r.tmax = FLT_MAX; r.u = 0.0f; r.v = 0.0f; r.slot = 0; r.cur = 0; r.sp = tid; r.found = false;
+}
+
+// One node-pair step of single_ray_traverser.hpp:82-123 for this lane's ray, including the eager leaf tests.
+// Returns false when the traversal is over (stack empty, or first hit in ANY mode).
+template <bool ANY, bool STATS, int STRIDE>
+__device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const float4* __restrict__ tris, RaySlot& r,
+                                         uint32_t* __restrict__ stack, uint32_t tid, uint32_t& n_steps, uint32_t& n_tests) {
+    if (STATS) n_steps++;
+    const float4* pp = pairs + 4ull * r.cur;
+    const float4 q0 = __ldg(pp), q1 = __ldg(pp + 1), q2 = __ldg(pp + 2), q3 = __ldg(pp + 3);
+    // octant = signbit(direction) = signbit(inverse) (safe_inverse keeps the sign, -0 included)
+    const bool nx = __float_as_int(r.ix) < 0, ny = __float_as_int(r.iy) < 0, nz = __float_as_int(r.iz) < 0;
+    const float tmax = r.tmax;
+    float le, lx, re, rx;
+    {
+        const float e0 = __fmaf_rn(nx ? q0.y : q0.x, r.ix, r.sx), x0 = __fmaf_rn(nx ? q0.x : q0.y, r.ix, r.sx);
+        const float e1 = __fmaf_rn(ny ? q0.w : q0.z, r.iy, r.sy), x1 = __fmaf_rn(ny ? q0.z : q0.w, r.iy, r.sy);
+        const float e2 = __fmaf_rn(nz ? q1.y : q1.x, r.iz, r.sz), x2 = __fmaf_rn(nz ? q1.x : q1.y, r.iz, r.sz);
+        le = fmaxf(e0, fmaxf(e1, fmaxf(e2, 0.0f)));          // tmin = 0 for every ray of render() (ray.hpp:19)
+        lx = fminf(x0, fminf(x1, fminf(x2, tmax)));
+    }
+    {
+        const float e0 = __fmaf_rn(nx ? q2.y : q2.x, r.ix, r.sx), x0 = __fmaf_rn(nx ? q2.x : q2.y, r.ix, r.sx);
+        const float e1 = __fmaf_rn(ny ? q2.w : q2.z, r.iy, r.sy), x1 = __fmaf_rn(ny ? q2.z : q2.w, r.iy, r.sy);
+        const float e2 = __fmaf_rn(nz ? q3.y : q3.x, r.iz, r.sz), x2 = __fmaf_rn(nz ? q3.x : q3.y, r.iz, r.sz);
+        re = fmaxf(e0, fmaxf(e1, fmaxf(e2, 0.0f)));
+        rx = fminf(x0, fminf(x1, fminf(x2, tmax)));
+    }
+    const uint32_t cL = __float_as_uint(q1.z), fL = __float_as_uint(q1.w);
+    const uint32_t cR = __float_as_uint(q3.z), fR = __float_as_uint(q3.w);
+    const bool hitL = le <= lx, hitR = re <= rx;
+
+    // leaves: the left range, then the right range, slots ascending (single_ray_traverser.hpp:89-107,51-62)
+    const uint32_t nL = hitL ? cL : 0u, nR = hitR ? cR : 0u;
+    const uint32_t nT = nL + nR;
+    if (nT) {
+        const V3 o = mk(r.ox, r.oy, r.oz), d = mk(r.dx, r.dy, r.dz);
+        for (uint32_t k = 0; k < nT; ++k) {
+            const uint32_t s = k < nL ? fL + k : fR + (k - nL);
+            if (STATS) n_tests++;
+            const Tri tr = load_tri(tris, s);
+            float t, u, v;
+            if (tri_test(tr, o, d, 0.0f, r.tmax, t, u, v)) {
+                r.slot = s; r.u = u; r.v = v; r.tmax = t; r.found = true;
+                if (ANY) return false;
+            }
+        }
+    }
+
+    const bool goL = hitL && cL == 0u, goR = hitR && cR == 0u;
+    if (goL || goR) {
+        const bool right_first = goR && (!goL || le > re);       // ties keep the left child first (:111-112)
+        if (goL && goR) {
+            stack[r.sp] = right_first ? fL : fR;
+            r.sp += STRIDE;
+        }
+        r.cur = right_first ? fR : fL;
+        return true;
+    }
+    if (r.sp == tid) return false;
+    r.sp -= STRIDE;
+    r.cur = stack[r.sp];
+    return true;
+}
+
+// work item -> pixel of the culled tile rectangle.  Returns false for the padding pixels of edge tiles.
+__device__ __forceinline__ bool item_pixel(const Frame& f, uint32_t item, uint32_t& i, uint32_t& lrow) {
+    const uint32_t tile = item >> 5, p = item & 31u;
+    const uint32_t ty = tile / f.tiles_x, tx = tile - ty * f.tiles_x;
+    i = f.rect_x0 + tx * 8u + (p & 7u);
+    lrow = f.rect_row0 + ty * 4u + (p >> 3);
+    return i < f.rect_x1 && lrow < f.rect_row1;
+}
+
+template <int WAVE, bool STATS, int THREADS>
+__global__ void __launch_bounds__(THREADS) trace_kernel(const DevScene sc, const Frame f) {
+    extern __shared__ uint32_t smem_stack[];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t total = WAVE == WAVE_PRIMARY ? f.work_items : f.ctr->qcount;
+    uint32_t* cursor = WAVE == WAVE_PRIMARY ? &f.ctr->primary_next : &f.ctr->shadow_next;
+    const float4* __restrict__ pairs = sc.pairs;
+    const float4* __restrict__ tris = sc.tris;
+    const V3 sun = mk(f.sun[0], f.sun[1], f.sun[2]);
+    const V3 eye = mk(f.eye[0], f.eye[1], f.eye[2]);
+
+    RaySlot r;
+    r.found = false; r.item = 0; r.sp = tid; r.cur = 0; r.tmax = 0.0f; r.u = r.v = 0.0f; r.slot = 0;
+    r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.ix = r.iy = r.iz = r.sx = r.sy = r.sz = 0.0f;
+    bool active = false;        // this lane holds a ray in flight
+    bool retire = false;        // this lane holds a finished ray whose result is not yet published
+    bool exhausted = false;     // warp-uniform: the cursor ran past the last work item
+    uint32_t n_steps = 0, n_tests = 0, occl = 0;
+    unsigned long long st[4] = {0, 0, 0, 0};   // STATS: S_miss,T_miss,S_hit,T_hit (primary) / S,T in [0],[1] (shadow)
+
+    for (;;) {
+        // ---- retire finished rays, refill idle lanes --------------------------------------------------------
+        if (WAVE == WAVE_PRIMARY) {
+            const bool out = retire && r.found;
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, out);
+            if (m) {
+                const int leader = __ffs(m) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(&f.ctr->qcount, (uint32_t)__popc(m));
+                base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                if (out) {
+                    uint32_t i, lrow;
+                    item_pixel(f, r.item, i, lrow);
+                    f.queue[base + __popc(m & lt_mask)] = make_uint4(lrow * f.W + i, r.slot, __float_as_uint(r.u), __float_as_uint(r.v));
+                }
+            }
+        }
+        if (STATS && retire) {
+            if (WAVE == WAVE_PRIMARY) { st[r.found ? 2 : 0] += n_steps; st[r.found ? 3 : 1] += n_tests; }
+            else { st[0] += n_steps; st[1] += n_tests; }
+            n_steps = n_tests = 0;
+        }
+        retire = false;
+        if (!exhausted) {
+            const unsigned idle = ~__ballot_sync(0xFFFFFFFFu, active);
+            const int leader = __ffs(idle) - 1;     // idle != 0 here: the inner loop only exits with idle lanes
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xFFFFFFFFu, base, leader);
+            exhausted = base + (uint32_t)__popc(idle) >= total;
+            const uint32_t item = base + __popc(idle & lt_mask);
+            if (!active && item < total) {
+                r.item = item;
+                bool have = true;
+                if (WAVE == WAVE_PRIMARY) {
+                    uint32_t i, lrow;
+                    have = item_pixel(f, item, i, lrow);
+                    if (have) ray_begin(r, eye, primary_dir(f, i, frame_row(f, lrow)), tid);
+                } else {
+                    const uint4 rec = f.queue[item];
+                    const Tri tr = load_tri(tris, rec.y);
+                    V3 P, sun_line;
+                    shadow_setup(tr, __uint_as_float(rec.z), __uint_as_float(rec.w), sun, P, sun_line);
+                    ray_begin(r, P, sun_line, tid);
+                }
+                if (have) {
+                    if (sc.root_leaf_count) {
+                        // the root itself is a leaf (single_ray_traverser.hpp:72-73): its triangles are the whole scene
+                        const V3 o = mk(r.ox, r.oy, r.oz), d = mk(r.dx, r.dy, r.dz);
+                        for (uint32_t s = 0; s < sc.root_leaf_count; ++s) {
+                            if (STATS) n_tests++;
+                            float t, u, v;
+                            if (tri_test(load_tri(tris, s), o, d, 0.0f, r.tmax, t, u, v)) {
+                                r.slot = s; r.u = u; r.v = v; r.tmax = t; r.found = true;
+                                if (WAVE == WAVE_SHADOW) break;
+                            }
+                        }
+                        retire = true;
+                        if (WAVE == WAVE_SHADOW && r.found) { atomicOr(&f.queue[item].y, OCCLUDED_BIT); occl++; }
+                    } else {
+                        active = true;
+                    }
+                }
+            }
+        }
+        const unsigned act = __ballot_sync(0xFFFFFFFFu, active);
+        if (!act) {
+            if (exhausted && !__any_sync(0xFFFFFFFFu, retire)) break;
+            continue;
+        }
+        // ---- trace until enough lanes have gone idle to make a refill worthwhile -----------------------------------
+        if (f.refill_min >= 32u || exhausted) {
+            // whole-warp refill: every lane runs its ray to the end, the warp reconverges after the loop
+            const bool had_ray = active;
+            while (active) {
+                active = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+            }
+            if (had_ray) {
+                retire = true;
+                if (WAVE == WAVE_SHADOW && r.found) { atomicOr(&f.queue[r.item].y, OCCLUDED_BIT); occl++; }
+            }
+        } else {
+            const uint32_t keep_going = 32u - f.refill_min;    // leave the loop when active lanes <= this
+            for (;;) {
+                if (active) {
+                    active = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                    if (!active) {
+                        retire = true;
+                        if (WAVE == WAVE_SHADOW && r.found) { atomicOr(&f.queue[r.item].y, OCCLUDED_BIT); occl++; }
+                    }
+                }
+                const unsigned a = __ballot_sync(0xFFFFFFFFu, active);
+                if ((uint32_t)__popc(a) <= keep_going) break;
+            }
+        }
+    }
+
+    if (WAVE == WAVE_SHADOW) {
+        for (int o = 16; o; o >>= 1) occl += __shfl_xor_sync(0xFFFFFFFFu, occl, o);
+        if (lane == 0 && occl) atomicAdd(&f.ctr->occluded, occl);
+    }
+    if (STATS) {
+        for (int k = 0; k < 4; ++k)
+            for (int o = 16; o; o >>= 1) st[k] += __shfl_xor_sync(0xFFFFFFFFu, st[k], o);
+        if (lane == 0) {
+            if (WAVE == WAVE_PRIMARY) { for (int k = 0; k < 4; ++k) atomicAdd(&f.ctr->stats[k], st[k]); }
+            else { atomicAdd(&f.ctr->stats[4], st[0]); atomicAdd(&f.ctr->stats[5], st[1]); }
+        }
+    }
+}
+
+// Zeroes the launch's rows of the framebuffer (render.hpp:116-117,149: every pixel that is not a lit hit is 0) and
+// marks the ids CERES_MISS; shade_kernel then overwrites the hit pixels.  16-byte stores where the row start allows.
+__global__ void __launch_bounds__(256) clear_kernel(const Frame f) {
+    const uint32_t rows = f.row_end - f.row_begin;
+    const size_t row_floats = 3ull * f.W;
+    if (f.compact || f.shard_count <= 1) {
+        // the launch's rows are contiguous in the output
+        float* base = f.pixels + (size_t)f.row_begin * row_floats;
+        const size_t n = (size_t)rows * row_floats;
+        const size_t head = (16u - ((uintptr_t)base & 15u)) / 4u % 4u;      // floats up to the first 16-B boundary
+        const size_t nv = n > head ? (n - head) / 4 : 0;
+        float4* v = reinterpret_cast<float4*>(base + head);
+        for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < nv; k += (size_t)gridDim.x * 256u) v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (blockIdx.x == 0) {
+            for (size_t k = threadIdx.x; k < head && k < n; k += 256u) base[k] = 0.0f;
+            for (size_t k = head + nv * 4 + threadIdx.x; k < n; k += 256u) base[k] = 0.0f;
+        }
+        if (f.ids) {
+            uint32_t* ib = f.ids + (size_t)f.row_begin * f.W;
+            const size_t ni = (size_t)rows * f.W;
+            for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < ni; k += (size_t)gridDim.x * 256u) ib[k] = CERES_MISS;
+        }
+    } else {
+        for (uint32_t lr = f.row_begin + blockIdx.x; lr < f.row_end; lr += gridDim.x) {
+            const size_t j = frame_row(f, lr);
+            float* p = f.pixels + j * row_floats;
+            for (size_t k = threadIdx.x; k < row_floats; k += 256u) p[k] = 0.0f;
+            if (f.ids) for (uint32_t k = threadIdx.x; k < f.W; k += 256u) f.ids[j * f.W + k] = CERES_MISS;
+        }
+    }
+}

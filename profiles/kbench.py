@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Kernel A/B bench (development tool): per-kernel CUDA-event times of the frame kernels for each tuning variant, with
+the hit-id hash checked against the golden value so that a fast-but-wrong variant is caught in the same run.
+
+    python profiles/kbench.py [--workload dragon_4k_shadow] [--variants 0,1,2] [--frames 20] [--ctas 0]
+"""
+import argparse
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="dragon_4k_shadow")
+    ap.add_argument("--variants", default="0,1,2")
+    ap.add_argument("--frames", type=int, default=20)
+    ap.add_argument("--ctas", default="0")
+    ap.add_argument("--refill", default="0")
+    ap.add_argument("--block", type=int, default=0)
+    args = ap.parse_args()
+    import torch
+    import ceres_raytracer_b200 as cr
+    name, cam, sun, W, H, flags = cr.configs.WORKLOADS[args.workload]
+    sun = np.asarray(sun, np.float32)
+    with np.load(os.path.join(ROOT, "tests", "golden", name + "_scene.npz")) as z:
+        pod = {k: z[k] for k in z.files}
+    golden = json.load(open(os.path.join(ROOT, "tests", "golden", "frame_hashes.json")))
+    key = f"{name}_{W}x{H}_{'primary' if flags & 1 else 'shadow'}"
+    scene = cr.Scene.from_pod(pod)
+    dev = torch.device("cuda", 0)
+    d_px = torch.empty(H * W * 3, dtype=torch.float32, device=dev)
+    d_ids = torch.empty(H * W, dtype=torch.int32, device=dev)
+    d_cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ref_px = None
+    for ctas, refill in [(int(c), int(r)) for c in args.ctas.split(",") for r in args.refill.split(",")]:
+        for v in [int(x) for x in args.variants.split(",")]:
+            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block)
+            d_px.fill_(float("nan"))
+            scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, ids=d_ids, counters=d_cnt)
+            torch.cuda.synchronize()
+            ids = d_ids.cpu().numpy().view(np.uint32).reshape(H, W)
+            ok = hashlib.sha256(ids.tobytes()).hexdigest() == golden[key]["ids_sha256"] if key in golden else None
+            cnt = tuple(d_cnt.cpu().tolist())
+            cnt_ok = cnt == (golden[key]["stats"]["rays"], golden[key]["stats"]["hits"]) if key in golden else None
+            px = d_px.cpu().numpy()
+            if ref_px is None:
+                ref_px = px
+            same_px = bool(np.array_equal(px.view(np.uint32), ref_px.view(np.uint32)))
+            for _ in range(3):
+                scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, counters=d_cnt)
+            torch.cuda.synchronize()
+            scene.set_profiling(True)
+            for _ in range(args.frames):
+                flush.fill_(1)
+                scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, counters=d_cnt)
+            torch.cuda.synchronize()
+            ms, n = scene.kernel_ms()
+            scene.set_profiling(False)
+            print(f"variant {v} ctas/SM {ctas} refill {refill}: primary {ms['primary']/n*1e3:7.1f} us  shadow {ms['shadow']/n*1e3:7.1f} us  "
+                  f"shade {ms['shade']/n*1e3:6.1f} us  total {ms['total']/n*1e3:7.1f} us   ids_ok={ok} counters_ok={cnt_ok} "
+                  f"pixels_same_as_first={same_px}", flush=True)
+    scene.set_tuning()
+
+
+if __name__ == "__main__":
+    main()
