@@ -157,7 +157,8 @@ def algorithmic_bytes(st, W, rows, lit):
     64 B per node-pair step, 48 B per triangle test, 16 B per queue record, 12 B per pixel written."""
     P, Hh = W * rows, st["hits_primary"]
     return {
-        "primary": 64 * (st["S_miss"] + st["S_hit"]) + 48 * (st["T_miss"] + st["T_hit"]) + 12 * (P - Hh) + 16 * Hh,
+        # clear pass (12 B per pixel of the launch) + primary wave: node pairs, triangles, one queue record per hit
+        "primary": 64 * (st["S_miss"] + st["S_hit"]) + 48 * (st["T_miss"] + st["T_hit"]) + 12 * P + 16 * Hh,
         "shadow": 64 * st["S_shadow"] + 48 * st["T_shadow"] + 16 * Hh + 48 * Hh + 4 * st["occluded"],
         "shade": 16 * Hh + (48 + 36) * lit + 12 * Hh,
     }

@@ -10,7 +10,7 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.jso
 if [ -s gpurun_out/bench.json ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
       python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
-  ncu --set full --clock-control none --import-source on -k regex:'primary_kernel|shadow_kernel|shade_kernel' -s 9 -c 3 \
+  ncu --set full --clock-control none --import-source on -k regex:'trace_kernel|shade_kernel|clear_kernel' -s 12 -c 4 \
       -o gpurun_out/frame_full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 fi
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err

@@ -156,16 +156,26 @@ def test_device_api_sequence_and_quantize(cr, dragon, dragon_pod, kat):
 
 def test_gpu_statistics_match_oracle_for_primary_rays(cr, dragon, dragon_pod):
     W, H = 960, 540
-    dragon.set_stats(True)
-    try:
-        dragon.render(cr.configs.DRAGON_CAMERA, SUN, W, H)
-        st = dragon.get_stats()
-    finally:
-        dragon.set_stats(False)
     o = port.render(dragon_pod, cr.configs.DRAGON_CAMERA.as_array(), SUN, W, H, 0, want_pixels=False)["stats"]
-    for k in ("S_miss", "T_miss", "S_hit", "T_hit", "rays", "hits"):
-        assert st[k] == o[k], k          # same tree walked in the same order
-    assert 0 < st["S_shadow"] <= o["S_shadow"] and 0 < st["T_shadow"] <= o["T_shadow"]   # any-hit exits early
+    got = {}
+    for variant in (0, 1, 2):       # 0 persistent waves + screen-rectangle culling, 1 legacy kernels, 2 persistent, no culling
+        dragon.set_tuning(variant=variant)
+        dragon.set_stats(True)
+        try:
+            dragon.render(cr.configs.DRAGON_CAMERA, SUN, W, H)
+            got[variant] = st = dragon.get_stats()
+        finally:
+            dragon.set_stats(False)
+            dragon.set_tuning()
+        # same tree walked in the same order: every ray that hits does exactly the oracle's work
+        for k in ("T_miss", "S_hit", "T_hit", "rays", "hits"):
+            assert st[k] == o[k], (variant, k)
+        assert 0 < st["S_shadow"] <= o["S_shadow"] and 0 < st["T_shadow"] <= o["T_shadow"]   # any-hit exits early
+    # without culling the missing rays walk the oracle's steps too; culling only removes rays that fail at the root
+    assert got[1]["S_miss"] == o["S_miss"] and got[2]["S_miss"] == o["S_miss"]
+    assert got[0]["S_miss"] < o["S_miss"]
+    culled = o["S_miss"] - got[0]["S_miss"]
+    assert culled <= W * H - (o["rays"] - W * H)      # at most one root step per missing pixel was skipped
 
 
 def test_tiny_scenes_root_leaf_and_single_pair(cr):
