@@ -14,7 +14,7 @@ HEADER = os.path.join(ROOT, "include", "ceres_b200.h")
 # must not contract either.
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
-    "-Xcompiler", "-fPIC,-ffp-contract=off", "-shared",
+    "-Xcompiler", "-fPIC,-ffp-contract=off,-mavx2", "-shared",
 ]
 
 
@@ -29,7 +29,8 @@ def needs_build():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(p) > t for p in (SRC, HEADER))
+    deps = [SRC, HEADER] + [os.path.join(HERE, 'csrc', n) for n in os.listdir(os.path.join(HERE, 'csrc'))]
+    return any(os.path.getmtime(p) > t for p in deps)
 
 
 def build(force=False, verbose=False):

@@ -25,11 +25,13 @@
 #include <string>
 #include <vector>
 #include <atomic>
+#include <chrono>
 #include <new>
 #include <algorithm>
 #include <thread>
 
 #include "../../include/ceres_b200.h"
+#include "host_fill.hpp"
 
 // ------------------------------------------------------------------------------------------------ errors
 static thread_local std::string g_err;
@@ -970,9 +972,12 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
     return launch_rows(s, f, 0, rows_local, false, st);
 }
 
-// Host-framebuffer render.  The shard's rows are rendered in bands on the scene stream; each finished band is
-// copied to the caller's buffer on a second stream while the next band renders, so the PCIe transfer (the larger
-// cost at 4K: 99.5 MB of float RGB) hides the kernels instead of following them.
+// Host-framebuffer render (the drop-in for render.hpp:86-156).
+//   * Only the conservative screen rectangle of the scene is rendered and copied: its rows are traced in bands on the
+//     scene stream, and each finished band is DMA-copied (columns of the rectangle only, cudaMemcpy2DAsync) on a
+//     second stream while the next band renders.
+//   * Everything outside the rectangle is 0 by construction (render.hpp:116-117; ids: CERES_MISS) and is written by
+//     the host-fill pool (host_fill.hpp) concurrently with the GPU work -- zeros never cross PCIe.
 int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
                        unsigned flags, const ceres_shard* shard, float* pixels, uint32_t* ids, uint64_t counters[2]) {
     if (!s || !pixels) return fail(CERES_ERR_INVALID, "ceres_render: null argument");
@@ -994,43 +999,92 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
 
     const bool want_compact = (flags & CERES_COMPACT_ROWS) != 0;
     const bool scatter = sharded && !want_compact;
-    // band height: a multiple of the kernel tile (8 rows) and, when rows are scattered, of the shard's row blocks;
-    // ~6 MB of float RGB per band, at most CERES_MAX_BANDS bands
-    const uint32_t unit = scatter ? shard->block_rows : 8u;
-    size_t band_rows = s->tune.band_bytes ? s->tune.band_bytes / (width * 12) : (6u << 20) / (width * 12);
-    if (!host_is_pinned(pixels)) band_rows = rows;       // pageable destination: the copy is synchronous anyway
-    if (band_rows >= rows) band_rows = ((rows + unit - 1) / unit) * unit;   // one band: never split off a remainder
-    band_rows = (band_rows / unit) * unit;
-    if (band_rows < unit) band_rows = unit;
-    if ((rows + band_rows - 1) / band_rows > CERES_MAX_BANDS) {
-        band_rows = (rows + CERES_MAX_BANDS - 1) / CERES_MAX_BANDS;
-        band_rows = ((band_rows + unit - 1) / unit) * unit;
-    }
-    size_t nb = 0;
-    for (uint32_t r0 = 0; r0 < rows; r0 += (uint32_t)band_rows, ++nb) {
-        const uint32_t r1 = (uint32_t)std::min<size_t>(rows, r0 + band_rows);
-        if (int rc = launch_rows(s, f, r0, r1, nb != 0, s->stream)) return rc;
-        CUDA_TRY(cudaEventRecord(s->band_done[nb], s->stream));
-        CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->band_done[nb], 0));
-        if (!scatter) {
-            const size_t off = (size_t)r0 * width, n = (size_t)(r1 - r0) * width;
-            CUDA_TRY(cudaMemcpyAsync(pixels + 3 * off, s->d_pixels + 3 * off, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
-            if (ids) CUDA_TRY(cudaMemcpyAsync(ids + off, s->d_ids + off, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->copy_stream));
-        } else {
-            const uint32_t br = shard->block_rows;
-            for (uint32_t lrow = r0; lrow < r1; lrow += br) {       // r0 is a multiple of br
-                const size_t blk = (size_t)(lrow / br) * shard->count + shard->index;
-                const size_t lo = blk * br, hi = std::min<size_t>(height, lo + br);
-                const size_t n = (hi - lo) * width;
-                CUDA_TRY(cudaMemcpyAsync(pixels + 3 * lo * width, s->d_pixels + 3 * (size_t)lrow * width, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
-                if (ids) CUDA_TRY(cudaMemcpyAsync(ids + lo * width, s->d_ids + (size_t)lrow * width, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->copy_stream));
+    auto out_row = [&](uint32_t lrow) -> size_t { return scatter ? (size_t)frame_row_host(f, lrow) : (size_t)lrow; };
+    // rectangle in local rows / columns (whole shard when culling is off)
+    const uint32_t l0 = std::min(f.cull_l0, rows), l1 = std::max(l0, std::min(f.cull_l1, rows));
+    const uint32_t i0 = std::min<uint32_t>(f.cull_i0, (uint32_t)width), i1 = std::max(i0, std::min<uint32_t>(f.cull_i1, (uint32_t)width));
+    const bool empty = l1 == l0 || i1 == i0;
+
+    // ---- host fill of everything outside the rectangle ---------------------------------------------------------
+    ceres_host::Job job;
+    {
+        auto fill_rows = [&](uint32_t a, uint32_t b) {       // local rows [a, b), full width; merge rows contiguous in the output
+            uint32_t r = a;
+            while (r < b) {
+                uint32_t e = r + 1;
+                while (e < b && out_row(e) == out_row(e - 1) + 1) ++e;
+                job.add(pixels + 3 * out_row(r) * width, (size_t)(e - r) * width * 12, 0x00);
+                if (ids) job.add(ids + out_row(r) * width, (size_t)(e - r) * width * 4, 0xFF);
+                r = e;
+            }
+        };
+        if (empty) fill_rows(0, rows);
+        else {
+            fill_rows(0, l0);
+            fill_rows(l1, rows);
+            for (uint32_t r = l0; r < l1 && (i0 > 0 || i1 < width); ++r) {
+                const size_t o = out_row(r) * width;
+                if (i0 > 0) { job.add(pixels + 3 * o, (size_t)i0 * 12, 0x00); if (ids) job.add(ids + o, (size_t)i0 * 4, 0xFF); }
+                if (i1 < width) { job.add(pixels + 3 * (o + i1), (width - i1) * 12, 0x00); if (ids) job.add(ids + o + i1, (width - i1) * 4, 0xFF); }
             }
         }
     }
+    static const bool trace_timing = std::getenv("CERES_TRACE_TIMING") != nullptr;
+    auto now_us = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = trace_timing ? now_us() : 0.0;
+    ceres_host::Pool& pool = ceres_host::Pool::instance();
+    pool.submit(&job);
+    const double t_submit = trace_timing ? now_us() : 0.0;
+    struct Waiter { ceres_host::Pool& p; ceres_host::Job* j; ~Waiter() { p.wait(j); } } waiter{pool, &job};   // also on error paths
+
+    const uint64_t prim_outside = (uint64_t)width * (rows - (empty ? 0 : l1 - l0));
+    if (empty) {
+        if (counters) { counters[0] = (uint64_t)width * rows; counters[1] = 0; }
+        return CERES_OK;
+    }
+
+    // ---- GPU: bands of the rectangle's rows, each copied while the next one renders --------------------------------
+    const uint32_t rrows = l1 - l0, rcols = i1 - i0;
+    const uint32_t unit = 4u;                                                     // tile height of the primary wave
+    size_t band_rows = (s->tune.band_bytes ? s->tune.band_bytes : (6u << 20)) / ((size_t)rcols * 12);
+    if (!host_is_pinned(pixels)) band_rows = rrows;      // pageable destination: the copy is synchronous anyway
+    if (band_rows >= rrows) band_rows = ((rrows + unit - 1) / unit) * unit;       // one band: never split off a remainder
+    band_rows = (band_rows / unit) * unit;
+    if (band_rows < unit) band_rows = unit;
+    if ((rrows + band_rows - 1) / band_rows > CERES_MAX_BANDS) {
+        band_rows = (rrows + CERES_MAX_BANDS - 1) / CERES_MAX_BANDS;
+        band_rows = ((band_rows + unit - 1) / unit) * unit;
+    }
+    size_t nb = 0;
+    for (uint32_t r0 = l0; r0 < l1; r0 += (uint32_t)band_rows, ++nb) {
+        const uint32_t r1 = (uint32_t)std::min<size_t>(l1, r0 + band_rows);
+        if (int rc = launch_rows(s, f, r0, r1, nb != 0, s->stream)) return rc;
+        CUDA_TRY(cudaEventRecord(s->band_done[nb], s->stream));
+        CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->band_done[nb], 0));
+        uint32_t r = r0;
+        while (r < r1) {                                  // runs of rows that are contiguous in the caller's frame
+            uint32_t e = r + 1;
+            while (e < r1 && out_row(e) == out_row(e - 1) + 1) ++e;
+            const size_t src = (size_t)r * width + i0, dst = out_row(r) * width + i0;
+            CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, (size_t)rcols * 12, e - r,
+                                       cudaMemcpyDeviceToHost, s->copy_stream));
+            if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, (size_t)rcols * 4, e - r,
+                                                cudaMemcpyDeviceToHost, s->copy_stream));
+            r = e;
+        }
+    }
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+    const double t_launched = trace_timing ? now_us() : 0.0;
+    pool.wait(&job);                                      // this thread helps with the fill while the GPU works
+    const double t_filled = trace_timing ? now_us() : 0.0;
     CUDA_TRY(cudaStreamSynchronize(s->stream));
+    const double t_kernels = trace_timing ? now_us() : 0.0;
     CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
-    if (counters) { counters[0] = s->h_out[0]; counters[1] = s->h_out[1]; }
+    if (trace_timing)
+        std::fprintf(stderr, "ceres_render timing [us]: segments %zu bands %zu | job built+submitted %.0f, launches issued %.0f, fill done %.0f, "
+                     "kernels done %.0f, copies done %.0f\n", job.segs.size(), nb, t_submit - t_begin, t_launched - t_begin,
+                     t_filled - t_begin, t_kernels - t_begin, now_us() - t_begin);
+    if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
     return CERES_OK;
 }
 
