@@ -429,14 +429,12 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
         const unsigned long long prim = (unsigned long long)f.W * (f.row_end - f.row_begin);
         const unsigned long long rays = f.shadows ? prim + hits : prim;                          // render.hpp:115,138
         const unsigned long long nh = hits + occ;                                                 // render.hpp:119,148
-        if (f.out_counters) {
-            f.out_counters[0] = (f.accumulate ? f.out_counters[0] : 0ull) + rays;
-            f.out_counters[1] = (f.accumulate ? f.out_counters[1] : 0ull) + nh;
-        }
+        // several launches (row bands, possibly on concurrent streams) add into the same frame counters; the host
+        // zeroes them before the first launch of a frame
+        if (f.out_counters) { atomicAdd(&f.out_counters[0], rays); atomicAdd(&f.out_counters[1], nh); }
         if (f.out_stats) {
-            for (int k = 0; k < 6; ++k) f.out_stats[k] = (f.accumulate ? f.out_stats[k] : 0ull) + f.ctr->stats[k];
-            f.out_stats[6] = (f.accumulate ? f.out_stats[6] : 0ull) + rays;
-            f.out_stats[7] = (f.accumulate ? f.out_stats[7] : 0ull) + nh;
+            for (int k = 0; k < 6; ++k) atomicAdd(&f.out_stats[k], f.ctr->stats[k]);
+            atomicAdd(&f.out_stats[6], rays); atomicAdd(&f.out_stats[7], nh);
         }
         f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0; f.ctr->primary_next = 0;
         for (int k = 0; k < 6; ++k) f.ctr->stats[k] = 0;
@@ -483,12 +481,16 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 
 // ------------------------------------------------------------------------------------------------ host side
 #define CERES_MAX_BANDS 32
+#define CERES_MAX_SUB 8
 struct ceres_scene {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;                     // D2H of finished row bands
     cudaEvent_t band_done[CERES_MAX_BANDS] = {};
+    cudaStream_t sub_stream[CERES_MAX_SUB] = {};           // concurrent sub-frames (row bands) of one frame
+    cudaEvent_t sub_done[CERES_MAX_SUB] = {};
+    cudaEvent_t fork_ev = nullptr;
     DevScene dev{};
     void* d_pairs = nullptr; void* d_tris = nullptr; void* d_norms = nullptr; void* d_slot_id = nullptr;
     size_t scene_bytes = 0;
@@ -501,12 +503,14 @@ struct ceres_scene {
     unsigned long long* h_out = nullptr;                    // pinned mirror
     bool stats = false;
     bool profile = false;                                   // CUDA events around each kernel of every frame
+    bool profile_kernels = true;                            // false while sub-frames run concurrently (frame total only)
     std::vector<cudaEvent_t> prof_events;                   // 4 per frame: start, after primary, after shadow, after shade
     size_t prof_frames = 0;
     ceres_tuning tune{};
     int shadow_blocks_per_sm = 0, shadow_blocks_per_sm_stats = 0;
     int trace_blocks_per_sm[4] = {0, 0, 0, 0};              // [wave*2 + stats]
     float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
+    uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
 };
 
 namespace {
@@ -705,19 +709,28 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     TRY_S(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY_S(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
     for (int k = 0; k < CERES_MAX_BANDS; ++k) TRY_S(cudaEventCreateWithFlags(&s->band_done[k], cudaEventDisableTiming));
+    // earlier bands get higher priority: they finish (and start their copy) first, later bands fill their tails
+    int prio_lo = 0, prio_hi = 0;
+    TRY_S(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));       // lo = numerically largest = least urgent
+    for (int k = 0; k < CERES_MAX_SUB; ++k) {
+        const int prio = std::min(prio_lo, prio_hi + k);
+        TRY_S(cudaStreamCreateWithPriority(&s->sub_stream[k], cudaStreamNonBlocking, prio));
+        TRY_S(cudaEventCreateWithFlags(&s->sub_done[k], cudaEventDisableTiming));
+    }
+    TRY_S(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
     const size_t pb = pairs.size() * 4, tb = tri_slots.size() * 4, nb = norm_slots.size() * 4, ib = slot_id.size() * 4;
     TRY_S(cudaMalloc(&s->d_pairs, pb));
     TRY_S(cudaMalloc(&s->d_tris, tb));
     TRY_S(cudaMalloc(&s->d_norms, nb));
     TRY_S(cudaMalloc(&s->d_slot_id, ib));
-    TRY_S(cudaMalloc((void**)&s->d_ctr, sizeof(FrameCounters)));
+    TRY_S(cudaMalloc((void**)&s->d_ctr, CERES_MAX_SUB * sizeof(FrameCounters)));
     TRY_S(cudaMalloc((void**)&s->d_out, 10 * sizeof(unsigned long long)));
     TRY_S(cudaMallocHost((void**)&s->h_out, 10 * sizeof(unsigned long long)));
     TRY_S(cudaMemcpy(s->d_pairs, pairs.data(), pb, cudaMemcpyHostToDevice));
     TRY_S(cudaMemcpy(s->d_tris, tri_slots.data(), tb, cudaMemcpyHostToDevice));
     TRY_S(cudaMemcpy(s->d_norms, norm_slots.data(), nb, cudaMemcpyHostToDevice));
     TRY_S(cudaMemcpy(s->d_slot_id, slot_id.data(), ib, cudaMemcpyHostToDevice));
-    TRY_S(cudaMemset(s->d_ctr, 0, sizeof(FrameCounters)));
+    TRY_S(cudaMemset(s->d_ctr, 0, CERES_MAX_SUB * sizeof(FrameCounters)));
     TRY_S(cudaMemset(s->d_out, 0, 10 * sizeof(unsigned long long)));
 #undef TRY_S
     s->scene_bytes = pb + tb + nb + ib;
@@ -737,6 +750,11 @@ void ceres_scene_destroy(ceres_scene* s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->copy_stream) { cudaStreamSynchronize(s->copy_stream); cudaStreamDestroy(s->copy_stream); }
     for (int k = 0; k < CERES_MAX_BANDS; ++k) if (s->band_done[k]) cudaEventDestroy(s->band_done[k]);
+    for (int k = 0; k < CERES_MAX_SUB; ++k) {
+        if (s->sub_stream[k]) { cudaStreamSynchronize(s->sub_stream[k]); cudaStreamDestroy(s->sub_stream[k]); }
+        if (s->sub_done[k]) cudaEventDestroy(s->sub_done[k]);
+    }
+    if (s->fork_ev) cudaEventDestroy(s->fork_ev);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_out);
     if (s->h_out) cudaFreeHost(s->h_out);
@@ -781,6 +799,7 @@ int ceres_scene_get_kernel_ms(ceres_scene* s, double ms[4], uint64_t* frames) {
         CUDA_TRY(cudaEventElapsedTime(&b, e[1], e[2]));
         CUDA_TRY(cudaEventElapsedTime(&c, e[2], e[3]));
         CUDA_TRY(cudaEventElapsedTime(&t, e[0], e[3]));
+        if (a + b < 0.002f) c = 0.0f;      // frame rendered as concurrent sub-frames: only the total is meaningful
         ms[0] += a; ms[1] += b; ms[2] += c; ms[3] += t;
     }
     if (frames) *frames = s->prof_frames;
@@ -793,6 +812,7 @@ int ceres_scene_get_stats(ceres_scene* s, uint64_t stats[8]) {
     unsigned long long tmp[10];
     CUDA_TRY(cudaMemcpy(tmp, s->d_out, sizeof tmp, cudaMemcpyDeviceToHost));
     for (int k = 0; k < 8; ++k) stats[k] = tmp[2 + k];
+    stats[6] += s->rays_outside;
     return CERES_OK;
 }
 
@@ -874,24 +894,22 @@ static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float su
 }
 
 // Enqueues the three kernels for local rows [row_begin, row_end) of the frame on `st`.
-static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row_end, bool accumulate, cudaStream_t st) {
+static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row_end, cudaStream_t st, int sub) {
     if (row_end <= row_begin) return CERES_OK;
-    f.row_begin = row_begin; f.row_end = row_end; f.accumulate = accumulate ? 1u : 0u;
+    f.row_begin = row_begin; f.row_end = row_end; f.accumulate = 1u;
     const uint32_t rows = row_end - row_begin;
-    const size_t npix = (size_t)rows * f.W;
-    if (npix > s->queue_cap) {
-        // growing the queue frees the old one: wait for frames that may still be using it
-        CUDA_TRY(cudaDeviceSynchronize());
-        if (int rc = ensure(s->d_queue, s->queue_cap, npix)) return rc;
-    }
-    f.queue = s->d_queue;
+    // every launch owns the queue region of its rows and one FrameCounters slot, so that bands of one frame can run
+    // concurrently on different streams (the caller has sized the queue for the whole shard)
+    if ((size_t)row_end * f.W > s->queue_cap) return fail(CERES_ERR_INVALID, "internal: queue not sized for the frame");
+    f.queue = s->d_queue + (size_t)row_begin * f.W;
+    f.ctr = s->d_ctr + sub;
 
     const size_t smem_p = (size_t)s->dev.stack_depth * 4 * PRIMARY_THREADS;
     const size_t smem_s = (size_t)s->dev.stack_depth * 4 * SHADOW_THREADS;
     dim3 grid((unsigned)((f.W + 31) / 32), (unsigned)((rows + 7) / 8));
     if (grid.y > 65535u) return fail(CERES_ERR_INVALID, "ceres_render: image too tall");
     cudaEvent_t* pe = nullptr;
-    if (s->profile) {
+    if (s->profile && s->profile_kernels) {
         if (s->prof_events.size() < 4 * (s->prof_frames + 1)) {
             for (int k = 0; k < 4; ++k) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); s->prof_events.push_back(e); }
         }
@@ -958,6 +976,81 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
     return CERES_OK;
 }
 
+}  // extern "C" (a C++ template follows)
+
+// defaults from the sweeps in profiles/r1/: device-resident frames gain ~2 % from 2 bands and lose beyond 4; host frames
+// want many bands so that the first copy starts early
+#define CERES_SUBFRAMES_DEVICE 2u
+#define CERES_SUBFRAMES_HOST 8u
+
+// Renders local rows [a, b) of the frame, forked from and joined back to stream `st`.
+// The rows are cut into up to CERES_MAX_SUB row bands ("sub-frames"), each enqueued on its own stream with its own
+// queue region and counters.  Why: every wave kernel ends with a latency-bound tail (the last warps walk 100+ dependent
+// node steps while the rest of the GPU idles, ~30-50 us per wave on the dragon); with concurrent bands the tail of one
+// band's wave is filled by the next band's bulk, and in the host path a finished band is copied while others render.
+// hook(band, r0, r1, stream) may enqueue follow-up work (the D2H copies) behind a band's kernels.
+template <class Hook>
+static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, cudaStream_t st, uint32_t default_sub, Hook&& hook) {
+    if (b <= a) return CERES_OK;
+    const size_t need = (size_t)b * f.W;
+    if (need > s->queue_cap) {
+        CUDA_TRY(cudaDeviceSynchronize());      // growing the queue frees the old one: wait for frames still using it
+        if (int rc = ensure(s->d_queue, s->queue_cap, need)) return rc;
+    }
+    CUDA_TRY(cudaMemsetAsync(f.out_counters, 0, 2 * sizeof(unsigned long long), st));
+    if (f.out_stats) CUDA_TRY(cudaMemsetAsync(f.out_stats, 0, 8 * sizeof(unsigned long long), st));
+    const uint32_t rows = b - a;
+    uint32_t nsub = s->tune.reserved[1] ? s->tune.reserved[1] : default_sub;
+    nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (rows + 31u) / 32u);
+    if (nsub <= 1) {
+        s->profile_kernels = true;
+        if (int rc = launch_rows(s, f, a, b, st, 0)) return rc;
+        return hook(0u, a, b, st);
+    }
+    cudaEvent_t* pe = nullptr;
+    if (s->profile) {       // concurrent bands: only the frame total is meaningful
+        if (s->prof_events.size() < 4 * (s->prof_frames + 1))
+            for (int k = 0; k < 4; ++k) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); s->prof_events.push_back(e); }
+        pe = &s->prof_events[4 * s->prof_frames++];
+        for (int k = 0; k < 3; ++k) CUDA_TRY(cudaEventRecord(pe[k], st));
+    }
+    s->profile_kernels = false;
+    // CERES_TRACE_TIMING: device timeline of the bands (kernels done / copies done, relative to the fork)
+    static const bool dbg = std::getenv("CERES_TRACE_TIMING") != nullptr;
+    static cudaEvent_t dbg_ev[1 + 2 * CERES_MAX_SUB] = {};
+    if (dbg && !dbg_ev[0]) for (auto& e : dbg_ev) CUDA_TRY(cudaEventCreate(&e));
+    if (dbg) CUDA_TRY(cudaEventRecord(dbg_ev[0], st));
+    CUDA_TRY(cudaEventRecord(s->fork_ev, st));
+    uint32_t band_rows = ((rows + nsub - 1) / nsub + 3u) / 4u * 4u;
+    uint32_t k = 0;
+    for (uint32_t r0 = a; r0 < b; r0 += band_rows, ++k) {
+        const uint32_t r1 = std::min(b, r0 + band_rows);
+        cudaStream_t bs = s->sub_stream[k];
+        CUDA_TRY(cudaStreamWaitEvent(bs, s->fork_ev, 0));
+        if (int rc = launch_rows(s, f, r0, r1, bs, (int)k)) return rc;
+        if (dbg) CUDA_TRY(cudaEventRecord(dbg_ev[1 + 2 * k], bs));
+        if (int rc = hook(k, r0, r1, bs)) return rc;
+        if (dbg) CUDA_TRY(cudaEventRecord(dbg_ev[2 + 2 * k], bs));
+        CUDA_TRY(cudaEventRecord(s->sub_done[k], bs));
+        CUDA_TRY(cudaStreamWaitEvent(st, s->sub_done[k], 0));
+    }
+    s->profile_kernels = true;
+    if (pe) CUDA_TRY(cudaEventRecord(pe[3], st));
+    if (dbg) {
+        CUDA_TRY(cudaStreamSynchronize(st));
+        std::fprintf(stderr, "band timeline [us] (kernels done / hook done):");
+        for (uint32_t q = 0; q < k; ++q) {
+            float t1 = 0, t2 = 0;
+            cudaEventElapsedTime(&t1, dbg_ev[0], dbg_ev[1 + 2 * q]); cudaEventElapsedTime(&t2, dbg_ev[0], dbg_ev[2 + 2 * q]);
+            std::fprintf(stderr, " %.0f/%.0f", t1 * 1e3, t2 * 1e3);
+        }
+        std::fprintf(stderr, "\n");
+    }
+    return CERES_OK;
+}
+
+extern "C" {
+
 int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
                         unsigned flags, const ceres_shard* shard, void* stream_v, float* d_pixels, uint32_t* d_ids,
                         uint64_t* d_counters) {
@@ -969,7 +1062,8 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
         if (d_counters) CUDA_TRY(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint64_t), st));
         return CERES_OK;
     }
-    return launch_rows(s, f, 0, rows_local, false, st);
+    s->rays_outside = 0;
+    return render_rows(s, f, 0, rows_local, st, CERES_SUBFRAMES_DEVICE, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; });
 }
 
 // Host-framebuffer render (the drop-in for render.hpp:86-156).
@@ -1032,6 +1126,8 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     static const bool trace_timing = std::getenv("CERES_TRACE_TIMING") != nullptr;
     auto now_us = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t_begin = trace_timing ? now_us() : 0.0;
+    static const bool no_fill = std::getenv("CERES_DEBUG_NO_FILL") != nullptr;     // timing experiments only
+    if (no_fill) job.segs.clear();
     ceres_host::Pool& pool = ceres_host::Pool::instance();
     pool.submit(&job);
     const double t_submit = trace_timing ? now_us() : 0.0;
@@ -1043,43 +1139,31 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
         return CERES_OK;
     }
 
-    // ---- GPU: bands of the rectangle's rows, each copied while the next one renders --------------------------------
-    const uint32_t rrows = l1 - l0, rcols = i1 - i0;
-    const uint32_t unit = 4u;                                                     // tile height of the primary wave
-    size_t band_rows = (s->tune.band_bytes ? s->tune.band_bytes : (6u << 20)) / ((size_t)rcols * 12);
-    if (!host_is_pinned(pixels)) band_rows = rrows;      // pageable destination: the copy is synchronous anyway
-    if (band_rows >= rrows) band_rows = ((rrows + unit - 1) / unit) * unit;       // one band: never split off a remainder
-    band_rows = (band_rows / unit) * unit;
-    if (band_rows < unit) band_rows = unit;
-    if ((rrows + band_rows - 1) / band_rows > CERES_MAX_BANDS) {
-        band_rows = (rrows + CERES_MAX_BANDS - 1) / CERES_MAX_BANDS;
-        band_rows = ((band_rows + unit - 1) / unit) * unit;
-    }
-    size_t nb = 0;
-    for (uint32_t r0 = l0; r0 < l1; r0 += (uint32_t)band_rows, ++nb) {
-        const uint32_t r1 = (uint32_t)std::min<size_t>(l1, r0 + band_rows);
-        if (int rc = launch_rows(s, f, r0, r1, nb != 0, s->stream)) return rc;
-        CUDA_TRY(cudaEventRecord(s->band_done[nb], s->stream));
-        CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->band_done[nb], 0));
+    // ---- GPU: concurrent row bands of the rectangle; each band is copied as soon as its own kernels are done ---------
+    const uint32_t rcols = i1 - i0;
+    const size_t nb = 0;
+    auto copy_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
         uint32_t r = r0;
         while (r < r1) {                                  // runs of rows that are contiguous in the caller's frame
             uint32_t e = r + 1;
             while (e < r1 && out_row(e) == out_row(e - 1) + 1) ++e;
             const size_t src = (size_t)r * width + i0, dst = out_row(r) * width + i0;
             CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, (size_t)rcols * 12, e - r,
-                                       cudaMemcpyDeviceToHost, s->copy_stream));
+                                       cudaMemcpyDeviceToHost, bs));
             if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, (size_t)rcols * 4, e - r,
-                                                cudaMemcpyDeviceToHost, s->copy_stream));
+                                                cudaMemcpyDeviceToHost, bs));
             r = e;
         }
-    }
+        return CERES_OK;
+    };
+    s->rays_outside = prim_outside;
+    if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, copy_band)) return rc;
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
     const double t_launched = trace_timing ? now_us() : 0.0;
     pool.wait(&job);                                      // this thread helps with the fill while the GPU works
     const double t_filled = trace_timing ? now_us() : 0.0;
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     const double t_kernels = trace_timing ? now_us() : 0.0;
-    CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
     if (trace_timing)
         std::fprintf(stderr, "ceres_render timing [us]: segments %zu bands %zu | job built+submitted %.0f, launches issued %.0f, fill done %.0f, "
                      "kernels done %.0f, copies done %.0f\n", job.segs.size(), nb, t_submit - t_begin, t_launched - t_begin,

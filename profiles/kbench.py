@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--ctas", default="0")
     ap.add_argument("--refill", default="0")
     ap.add_argument("--block", type=int, default=0)
+    ap.add_argument("--sub", default="1")
     args = ap.parse_args()
     import torch
     import ceres_raytracer_b200 as cr
@@ -40,9 +41,9 @@ def main():
     d_cnt = torch.zeros(2, dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     ref_px = None
-    for ctas, refill in [(int(c), int(r)) for c in args.ctas.split(",") for r in args.refill.split(",")]:
+    for ctas, refill, sub in [(int(c), int(r), int(q)) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",")]:
         for v in [int(x) for x in args.variants.split(",")]:
-            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block)
+            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block, subframes=sub)
             d_px.fill_(float("nan"))
             scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, ids=d_ids, counters=d_cnt)
             torch.cuda.synchronize()
@@ -64,7 +65,7 @@ def main():
             torch.cuda.synchronize()
             ms, n = scene.kernel_ms()
             scene.set_profiling(False)
-            print(f"variant {v} ctas/SM {ctas} refill {refill}: primary {ms['primary']/n*1e3:7.1f} us  shadow {ms['shadow']/n*1e3:7.1f} us  "
+            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub}: primary {ms['primary']/n*1e3:7.1f} us  shadow {ms['shadow']/n*1e3:7.1f} us  "
                   f"shade {ms['shade']/n*1e3:6.1f} us  total {ms['total']/n*1e3:7.1f} us   ids_ok={ok} counters_ok={cnt_ok} "
                   f"pixels_same_as_first={same_px}", flush=True)
     scene.set_tuning()
