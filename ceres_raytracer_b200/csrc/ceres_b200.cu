@@ -87,6 +87,7 @@ struct Frame {
     // cut into 8x4-pixel tiles (work item = tile * 32 + pixel in tile)
     uint32_t rect_x0, rect_x1, rect_row0, rect_row1, tiles_x, work_items;
     uint32_t refill_min;                            // refill a warp when at least this many ray slots are idle (1..32)
+    uint32_t chunk;                                 // work items a warp takes from the global cursor at a time (multiple of 32)
     uint32_t cull_i0, cull_i1, cull_l0, cull_l1;   // host only: the rectangle for the whole frame (columns, LOCAL rows)
     float* pixels;
     uint32_t* ids;
@@ -944,6 +945,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         if (tiles * 32u >= (1ull << 32)) return fail(CERES_ERR_INVALID, "ceres_render: image too large");
         f.work_items = (uint32_t)(tiles * 32u);
         f.refill_min = s->tune.reserved[0] ? std::min(32u, s->tune.reserved[0]) : REFILL_MIN;
+        f.chunk = s->tune.reserved[2] ? (s->tune.reserved[2] + 31u) / 32u * 32u : TRACE_CHUNK;
         clear_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(f);
         g_launches++;
         // launch helper: persistent grid = SMs x resident CTAs of this instantiation
@@ -978,9 +980,10 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
 
 }  // extern "C" (a C++ template follows)
 
-// defaults from the sweeps in profiles/r1/: device-resident frames gain ~2 % from 2 bands and lose beyond 4; host frames
+// defaults from the sweeps in profiles/r1/: device-resident frames gain only ~2 % from 2-3 bands and lose beyond 4 (so
+// they stay serial, which also keeps the per-kernel event timing meaningful); host frames
 // want many bands so that the first copy starts early
-#define CERES_SUBFRAMES_DEVICE 2u
+#define CERES_SUBFRAMES_DEVICE 1u
 #define CERES_SUBFRAMES_HOST 8u
 
 // Renders local rows [a, b) of the frame, forked from and joined back to stream `st`.
@@ -1001,7 +1004,9 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
     if (f.out_stats) CUDA_TRY(cudaMemsetAsync(f.out_stats, 0, 8 * sizeof(unsigned long long), st));
     const uint32_t rows = b - a;
     uint32_t nsub = s->tune.reserved[1] ? s->tune.reserved[1] : default_sub;
-    nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (rows + 31u) / 32u);
+    // a band must be worth its four launches: at least 256 Ki pixels of the rectangle each
+    const uint64_t rect_px = (uint64_t)rows * (f.cull_i1 > f.cull_i0 ? f.cull_i1 - f.cull_i0 : 1u);
+    nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (uint32_t)std::max<uint64_t>(1u, rect_px >> 18));
     if (nsub <= 1) {
         s->profile_kernels = true;
         if (int rc = launch_rows(s, f, a, b, st, 0)) return rc;

@@ -22,6 +22,7 @@
 #define WAVE_PRIMARY 0
 #define WAVE_SHADOW 1
 #define TRACE_THREADS 128
+#define TRACE_CHUNK 32u
 #define REFILL_MIN 32u       // default: refill a warp only when all 32 ray slots are idle (coherence wins)
 
 struct RaySlot {
@@ -136,6 +137,7 @@ __global__ void __launch_bounds__(THREADS) trace_kernel(const DevScene sc, const
     bool active = false;        // this lane holds a ray in flight
     bool retire = false;        // this lane holds a finished ray whose result is not yet published
     bool exhausted = false;     // warp-uniform: the cursor ran past the last work item
+    uint32_t chunk_next = 0, chunk_end = 0;     // warp-uniform: this warp's private range of work items
     uint32_t n_steps = 0, n_tests = 0, occl = 0;
     unsigned long long st[4] = {0, 0, 0, 0};   // STATS: S_miss,T_miss,S_hit,T_hit (primary) / S,T in [0],[1] (shadow)
 
@@ -163,14 +165,24 @@ __global__ void __launch_bounds__(THREADS) trace_kernel(const DevScene sc, const
         }
         retire = false;
         if (!exhausted) {
+            // The warp owns a private chunk [chunk_next, chunk_end) of consecutive work items (neighbouring pixels /
+            // records) and refills idle lanes from it, so that replacement rays stay coherent with the rays still in
+            // flight; a new chunk costs one atomicAdd on the global cursor.
             const unsigned idle = ~__ballot_sync(0xFFFFFFFFu, active);
-            const int leader = __ffs(idle) - 1;     // idle != 0 here: the inner loop only exits with idle lanes
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(idle));
-            base = __shfl_sync(0xFFFFFFFFu, base, leader);
-            exhausted = base + (uint32_t)__popc(idle) >= total;
-            const uint32_t item = base + __popc(idle & lt_mask);
-            if (!active && item < total) {
+            if (chunk_next >= chunk_end) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(cursor, f.chunk);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                chunk_next = base < total ? base : total;
+                chunk_end = base + f.chunk < total ? base + f.chunk : total;
+            }
+            const uint32_t avail = chunk_end - chunk_next;
+            const uint32_t rank = __popc(idle & lt_mask);
+            const uint32_t item = chunk_next + rank;
+            const bool take = !active && rank < avail;
+            chunk_next += min(avail, (uint32_t)__popc(idle));
+            exhausted = chunk_next >= total;       // own chunk empty and the cursor is past the end
+            if (take) {
                 r.item = item;
                 bool have = true;
                 if (WAVE == WAVE_PRIMARY) {

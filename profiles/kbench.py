@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--refill", default="0")
     ap.add_argument("--block", type=int, default=0)
     ap.add_argument("--sub", default="1")
+    ap.add_argument("--chunk", default="0")
     args = ap.parse_args()
     import torch
     import ceres_raytracer_b200 as cr
@@ -41,9 +42,9 @@ def main():
     d_cnt = torch.zeros(2, dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     ref_px = None
-    for ctas, refill, sub in [(int(c), int(r), int(q)) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",")]:
+    for ctas, refill, sub, chunk in [(int(c), int(r), int(q), int(h)) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",") for h in args.chunk.split(",")]:
         for v in [int(x) for x in args.variants.split(",")]:
-            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block, subframes=sub)
+            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block, subframes=sub, chunk=chunk)
             d_px.fill_(float("nan"))
             scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, ids=d_ids, counters=d_cnt)
             torch.cuda.synchronize()
@@ -65,7 +66,7 @@ def main():
             torch.cuda.synchronize()
             ms, n = scene.kernel_ms()
             scene.set_profiling(False)
-            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub}: primary {ms['primary']/n*1e3:7.1f} us  shadow {ms['shadow']/n*1e3:7.1f} us  "
+            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub} chunk {chunk}: primary {ms['primary']/n*1e3:7.1f} us  shadow {ms['shadow']/n*1e3:7.1f} us  "
                   f"shade {ms['shade']/n*1e3:6.1f} us  total {ms['total']/n*1e3:7.1f} us   ids_ok={ok} counters_ok={cnt_ok} "
                   f"pixels_same_as_first={same_px}", flush=True)
     scene.set_tuning()
