@@ -70,7 +70,10 @@ def main():
     mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
     for r in data:
-        k = r[name_i].split("(")[0].replace("void ", "").split("<")[0].replace("_kernel", "")
+        full = r[name_i].split("(")[0].replace("void ", "")
+        k = full.split("<")[0].replace("_kernel", "")
+        if k == "trace":        # trace_kernel<WAVE, ...>: 0 = primary wave, 1 = shadow wave (bench.py's kernel names)
+            k = "shadow" if full.split("<")[1].split(",")[0].strip() == "1" else "primary"
         traffic[k] = int(float(r[ir]) * mult[units[ir]] + float(r[iw]) * mult[units[iw]])
     lines += ["", "dram read+write bytes per launch: " + json.dumps(traffic)]
     open(out, "w").write("\n".join(lines) + "\n")
