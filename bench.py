@@ -196,31 +196,17 @@ def main():
     sun = np.asarray(sun, np.float32)
     pod = load_scene_pod(name)
     scene = cr.Scene.from_pod(pod, device=local)
-    shard = (cfg.TILE_BLOCK_ROWS, rank, world) if world > 1 else None
-    n_rows = len(cr.shard_rows(H, shard))
-    rows_max = len(cr.shard_rows(H, (cfg.TILE_BLOCK_ROWS, 0, world))) if world > 1 else H
-
-    d_band = torch.zeros(rows_max * W * 3, dtype=torch.float32, device=dev)      # this rank's rows, packed
-    d_cnt = torch.zeros(2, dtype=torch.int64, device=dev)
-    d_frame = d_band
-    gather_list = None
-    if world > 1 and rank == 0:
-        gather_list = [torch.empty_like(d_band) for _ in range(world)]
-        d_frame = torch.empty(H * W * 3, dtype=torch.float32, device=dev)
-        row_index = [torch.as_tensor(cr.shard_rows(H, (cfg.TILE_BLOCK_ROWS, r, world)), device=dev) for r in range(world)]
+    # row-block sharding + the gather that assembles the frame on rank 0 (ceres_raytracer_b200/shard.py)
+    from ceres_raytracer_b200.shard import FrameGather
+    fg = FrameGather(W, H, cfg.TILE_BLOCK_ROWS, rank, world, dev)
+    shard, n_rows = fg.shard, fg.n_rows
+    d_band, d_cnt = fg.band, fg.counters
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)         # > 126 MB L2
     rflags = flags | (cr.COMPACT_ROWS if world > 1 else 0)
 
     def frame():
         scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
-        if world > 1:
-            dist.gather(d_band, gather_list, dst=0)
-            if rank == 0:
-                fv = d_frame.view(H, W * 3)
-                for r in range(world):
-                    idx = row_index[r]
-                    fv.index_copy_(0, idx, gather_list[r].view(rows_max, W * 3)[: idx.numel()])
-            dist.all_reduce(d_cnt)      # frame counters = sum over shards
+        fg.assemble()               # N > 1: NCCL gather to rank 0 + row scatter, counters summed over shards
 
     def barrier():
         if world > 1:
@@ -323,7 +309,7 @@ def main():
             t0 = time.perf_counter()
             frame()
             if rank == 0:
-                h_frame.copy_(d_frame, non_blocking=True)
+                h_frame.copy_(fg.frame, non_blocking=True)
             h_cnt.copy_(d_cnt, non_blocking=True)
             torch.cuda.synchronize()
             if k >= 2:
