@@ -40,7 +40,10 @@ SYMBOLS = [
     "ceres_scene_set_profiling", "ceres_scene_get_kernel_ms", "ceres_host_register", "ceres_host_unregister",
     "ceres_host_is_pinned", "ceres_quantize_device", "ceres_host_alloc", "ceres_host_free", "ceres_abi_version", "ceres_device_count",
     "ceres_kernel_launch_count", "ceres_last_error",
+    "ceres_peer_frame_create", "ceres_peer_frame_open", "ceres_peer_frame_alias", "ceres_peer_frame_destroy",
+    "ceres_peer_frame_pixels", "ceres_peer_frame_ids", "ceres_render_peer", "ceres_peer_frame_error",
 ]
+PEER_HANDLE_BYTES = 64
 
 _lib = None
 
@@ -85,6 +88,17 @@ def lib():
     L.ceres_host_is_pinned.argtypes = [vp]
     L.ceres_scene_set_profiling.argtypes = [vp, C.c_int]
     L.ceres_scene_get_kernel_ms.argtypes = [vp, vp, vp]
+    L.ceres_peer_frame_create.argtypes = [vp, sz, sz, C.c_int, C.c_int, C.POINTER(vp), vp]
+    L.ceres_peer_frame_open.argtypes = [vp, vp, sz, sz, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.ceres_peer_frame_alias.argtypes = [vp, vp, C.c_int, C.POINTER(vp)]
+    L.ceres_peer_frame_destroy.argtypes = [vp]
+    L.ceres_peer_frame_destroy.restype = None
+    L.ceres_peer_frame_pixels.argtypes = [vp]
+    L.ceres_peer_frame_pixels.restype = vp
+    L.ceres_peer_frame_ids.argtypes = [vp]
+    L.ceres_peer_frame_ids.restype = vp
+    L.ceres_render_peer.argtypes = [vp, camp, vp, C.c_uint, vp, vp, vp]
+    L.ceres_peer_frame_error.argtypes = [vp]
     L.ceres_abi_version.restype = C.c_int
     L.ceres_device_count.restype = C.c_int
     L.ceres_kernel_launch_count.restype = u64

@@ -74,6 +74,16 @@ struct FrameCounters {
     unsigned long long stats[6];  // S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow (statistics mode only)
 };
 
+// Control block of a peer frame (lives in rank 0's device memory, mapped by every rank; include/ceres_b200.h).
+struct PeerCtl {
+    uint32_t cleared_epoch;                          // rank 0: the frame has been zeroed for this epoch
+    uint32_t clear_blocks;                           // rank 0: CTAs of the clear pass that have finished
+    uint32_t error;                                  // a bounded wait expired (1 = cleared wait, 2 = done wait)
+    uint32_t pad_;
+    uint32_t done_epoch[CERES_PEER_MAX_RANKS];       // rank r: all my pixels of this epoch are visible system-wide
+    unsigned long long counters[CERES_PEER_MAX_RANKS][2];   // rank r: (rays, hits) of my shard
+};
+
 struct Frame {
     float eye[3], dir[3], iu[3], iv[3], sun[3];
     uint32_t W, H;             // full frame
@@ -95,6 +105,10 @@ struct Frame {
     unsigned long long* out_stats;      // 8 x u64 or null
     uint4* queue;
     FrameCounters* ctr;
+    // peer-frame mode (ceres_render_peer): pixels/ids point into rank 0's memory
+    PeerCtl* peer;
+    uint32_t peer_epoch, peer_rank;
+    uint32_t skip_clear;       // the rows were zeroed by somebody else (rank 0 in peer mode)
 };
 
 // ------------------------------------------------------------------------------------------------ device math
@@ -377,9 +391,39 @@ __device__ __forceinline__ float spec_pow24(float x) {
 }
 __device__ __forceinline__ float clamp01(float x) { return x < 0.0f ? 0.0f : (1.0f < x ? 1.0f : x); }
 
+// ---- system-scope flag helpers of the peer-frame protocol ------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define PEER_WAIT_NS 4000000000ull
+// Bounded wait until *flag >= epoch (epochs are compared as a signed difference so that they may wrap).
+__device__ __forceinline__ bool peer_wait_flag(const uint32_t* flag, uint32_t epoch) {
+    const unsigned long long t0 = global_ns();
+    while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+        __nanosleep(200);
+        if (global_ns() - t0 > PEER_WAIT_NS) return false;
+    }
+    return true;
+}
+
 #define SHADE_THREADS 256
 __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc, const Frame f) {
     const uint32_t total = f.ctr->qcount;
+    if (f.peer && f.peer_rank != 0u) {
+        // my stores land in rank 0's frame: they must not overtake rank 0's clear of this epoch
+        if (threadIdx.x == 0 && !peer_wait_flag(&f.peer->cleared_epoch, f.peer_epoch)) f.peer->error = 1u;
+        __syncthreads();
+    }
     const V3 sun = mk(f.sun[0], f.sun[1], f.sun[2]);
     for (uint32_t r = blockIdx.x * SHADE_THREADS + threadIdx.x; r < total; r += gridDim.x * SHADE_THREADS) {
         const uint4 rec = f.queue[r];
@@ -418,6 +462,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
     }
     // the last CTA publishes the frame counters and re-arms the per-frame state for the next frame
     __shared__ bool last;
+    if (f.peer) __threadfence_system();     // my pixel stores (NVLink) are performed before the CTA is counted done
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
@@ -440,7 +485,44 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
         f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0; f.ctr->primary_next = 0;
         for (int k = 0; k < 6; ++k) f.ctr->stats[k] = 0;
         __threadfence();
+        if (f.peer) {
+            // every CTA fenced its stores at system scope before it was counted; publish counters, then the flag
+            f.peer->counters[f.peer_rank][0] = rays;
+            f.peer->counters[f.peer_rank][1] = nh;
+            __threadfence_system();
+            st_release_sys(&f.peer->done_epoch[f.peer_rank], f.peer_epoch);
+        }
     }
+}
+
+// Peer-frame mode, rank 0: zero the whole frame (ids: CERES_MISS), then publish cleared_epoch.
+__global__ void __launch_bounds__(256) peer_clear_kernel(float4* __restrict__ px4, size_t n4, uint4* __restrict__ id4, size_t ni4,
+                                                         PeerCtl* ctl, uint32_t epoch) {
+    const size_t stride = (size_t)gridDim.x * 256u;
+    for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < n4; k += stride) px4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < ni4; k += stride) id4[k] = make_uint4(CERES_MISS, CERES_MISS, CERES_MISS, CERES_MISS);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        if (atomicAdd(&ctl->clear_blocks, 1u) == gridDim.x - 1) {
+            ctl->clear_blocks = 0;
+            __threadfence_system();
+            st_release_sys(&ctl->cleared_epoch, epoch);
+        }
+    }
+}
+
+// Peer-frame mode, rank 0, last kernel of the frame: wait for every rank's done flag, sum the counters.
+__global__ void __launch_bounds__(32) peer_wait_kernel(PeerCtl* ctl, uint32_t epoch, uint32_t world, unsigned long long* out_counters) {
+    const uint32_t r = threadIdx.x;
+    unsigned long long rays = 0, hits = 0;
+    if (r < world) {
+        if (!peer_wait_flag(&ctl->done_epoch[r], epoch)) ctl->error = 2u;
+        const volatile unsigned long long* c = ctl->counters[r];
+        rays = c[0]; hits = c[1];
+    }
+    for (int o = 16; o; o >>= 1) { rays += __shfl_xor_sync(0xFFFFFFFFu, rays, o); hits += __shfl_xor_sync(0xFFFFFFFFu, hits, o); }
+    if (r == 0 && out_counters) { out_counters[0] = rays; out_counters[1] = hits; }
 }
 
 // Known-answer kernel: closest-hit traversal of caller-supplied rays.
@@ -946,8 +1028,10 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         f.work_items = (uint32_t)(tiles * 32u);
         f.refill_min = s->tune.reserved[0] ? std::min(32u, s->tune.reserved[0]) : REFILL_MIN;
         f.chunk = s->tune.reserved[2] ? (s->tune.reserved[2] + 31u) / 32u * 32u : TRACE_CHUNK;
-        clear_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(f);
-        g_launches++;
+        if (!f.skip_clear) {
+            clear_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(f);
+            g_launches++;
+        }
         // launch helper: persistent grid = SMs x resident CTAs of this instantiation
         auto launch_wave = [&](int wave, auto kernel, int threads) -> int {
             const size_t smem_t = (size_t)s->dev.stack_depth * 4 * threads;
@@ -1004,6 +1088,7 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
     if (f.out_stats) CUDA_TRY(cudaMemsetAsync(f.out_stats, 0, 8 * sizeof(unsigned long long), st));
     const uint32_t rows = b - a;
     uint32_t nsub = s->tune.reserved[1] ? s->tune.reserved[1] : default_sub;
+    if (f.peer) nsub = 1;      // one done flag per rank and frame
     // a band must be worth its four launches: at least 256 Ki pixels of the rectangle each
     const uint64_t rect_px = (uint64_t)rows * (f.cull_i1 > f.cull_i0 ? f.cull_i1 - f.cull_i0 : 1u);
     nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (uint32_t)std::max<uint64_t>(1u, rect_px >> 18));
@@ -1069,6 +1154,173 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
     }
     s->rays_outside = 0;
     return render_rows(s, f, 0, rows_local, st, CERES_SUBFRAMES_DEVICE, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; });
+}
+
+// ---- peer frame (include/ceres_b200.h: "one frame on N GPUs, fused with its gather over NVLink peer memory") ----
+struct ceres_peer_frame {
+    void* base = nullptr;          // the allocation (owner) / the IPC mapping (opened) / the owner's base (alias)
+    bool owner = false, mapped = false;
+    int device = 0, world = 1, rank = 0;
+    size_t W = 0, H = 0;
+    bool with_ids = false;
+    uint32_t epoch = 0;
+    PeerCtl* ctl = nullptr;
+    float* pixels = nullptr;
+    uint32_t* ids = nullptr;
+    size_t n4 = 0, ni4 = 0;
+};
+
+static size_t peer_layout(ceres_peer_frame* pf) {
+    const size_t ctl_bytes = (sizeof(PeerCtl) + 4095) / 4096 * 4096;
+    pf->n4 = (pf->W * pf->H * 3 + 3) / 4;
+    pf->ni4 = pf->with_ids ? (pf->W * pf->H + 3) / 4 : 0;
+    char* b = (char*)pf->base;
+    pf->ctl = (PeerCtl*)b;
+    pf->pixels = (float*)(b + ctl_bytes);
+    pf->ids = pf->with_ids ? (uint32_t*)(b + ctl_bytes + pf->n4 * 16) : nullptr;
+    return ctl_bytes + pf->n4 * 16 + pf->ni4 * 16;
+}
+
+__global__ void peer_publish_kernel(PeerCtl* ctl, uint32_t rank, uint32_t epoch) {
+    ctl->counters[rank][0] = 0; ctl->counters[rank][1] = 0;
+    __threadfence_system();
+    st_release_sys(&ctl->done_epoch[rank], epoch);
+}
+
+// The record queue of the scene is sized when the frame handle is made: growing it later would need a device-wide
+// synchronisation in the middle of a frame that other ranks (possibly on this very device) are waiting on.
+static int peer_size_queue(ceres_scene* s, size_t width, size_t height, int world, int rank) {
+    ceres_shard sh{CERES_TILE_BLOCK_ROWS, (uint32_t)rank, (uint32_t)world};
+    const size_t rows = shard_rows(height, world > 1 ? &sh : nullptr);
+    DeviceGuard guard(s->device);
+    if (rows * width > s->queue_cap) {
+        CUDA_TRY(cudaDeviceSynchronize());
+        if (int rc = ensure(s->d_queue, s->queue_cap, rows * width)) return rc;
+    }
+    return CERES_OK;
+}
+
+static int peer_args_ok(ceres_scene* s, size_t width, size_t height, int world, int rank) {
+    if (!s) return fail(CERES_ERR_INVALID, "ceres_peer_frame: null scene");
+    if (!width || !height || (uint64_t)width * height >= (1ull << 32)) return fail(CERES_ERR_INVALID, "ceres_peer_frame: bad image size");
+    if (world < 1 || world > CERES_PEER_MAX_RANKS || rank < 0 || rank >= world) return fail(CERES_ERR_INVALID, "ceres_peer_frame: bad world/rank");
+    return CERES_OK;
+}
+
+int ceres_peer_frame_create(ceres_scene* s, size_t width, size_t height, int want_ids, int world, ceres_peer_frame** out,
+                            unsigned char* handle_out) {
+    if (int rc = peer_args_ok(s, width, height, world, 0)) return rc;
+    if (!out) return fail(CERES_ERR_INVALID, "ceres_peer_frame_create: null out");
+    static_assert(sizeof(cudaIpcMemHandle_t) <= CERES_PEER_HANDLE_BYTES, "handle size");
+    if (int rc = peer_size_queue(s, width, height, world, 0)) return rc;
+    DeviceGuard guard(s->device);
+    ceres_peer_frame* pf = new (std::nothrow) ceres_peer_frame();
+    if (!pf) return fail(CERES_ERR_INVALID, "out of host memory");
+    pf->owner = true; pf->device = s->device; pf->world = world; pf->rank = 0; pf->W = width; pf->H = height; pf->with_ids = want_ids != 0;
+    const size_t bytes = peer_layout(pf);      // base is null: only the size is meaningful here
+    cudaError_t e = cudaMalloc(&pf->base, bytes);
+    if (e == cudaSuccess) e = cudaMemset(pf->base, 0, bytes);
+    if (e == cudaSuccess && handle_out) {
+        cudaIpcMemHandle_t h;
+        e = cudaIpcGetMemHandle(&h, pf->base);
+        if (e == cudaSuccess) { std::memset(handle_out, 0, CERES_PEER_HANDLE_BYTES); std::memcpy(handle_out, &h, sizeof(h)); }
+    }
+    if (e != cudaSuccess) { cudaFree(pf->base); delete pf; return fail(CERES_ERR_CUDA, std::string("ceres_peer_frame_create: ") + cudaGetErrorString(e)); }
+    peer_layout(pf);
+    *out = pf;
+    return CERES_OK;
+}
+
+int ceres_peer_frame_open(ceres_scene* s, const unsigned char* handle, size_t width, size_t height, int want_ids, int world,
+                          int rank, ceres_peer_frame** out) {
+    if (int rc = peer_args_ok(s, width, height, world, rank)) return rc;
+    if (!out || !handle || rank == 0) return fail(CERES_ERR_INVALID, "ceres_peer_frame_open: bad argument (rank 0 creates the frame)");
+    if (int rc = peer_size_queue(s, width, height, world, rank)) return rc;
+    DeviceGuard guard(s->device);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    void* base = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    ceres_peer_frame* pf = new (std::nothrow) ceres_peer_frame();
+    if (!pf) { cudaIpcCloseMemHandle(base); return fail(CERES_ERR_INVALID, "out of host memory"); }
+    pf->base = base; pf->mapped = true; pf->device = s->device; pf->world = world; pf->rank = rank;
+    pf->W = width; pf->H = height; pf->with_ids = want_ids != 0;
+    peer_layout(pf);
+    *out = pf;
+    return CERES_OK;
+}
+
+int ceres_peer_frame_alias(ceres_peer_frame* owner, ceres_scene* s, int rank, ceres_peer_frame** out) {
+    if (!owner || !owner->owner || !out) return fail(CERES_ERR_INVALID, "ceres_peer_frame_alias: needs the owning frame");
+    if (int rc = peer_args_ok(s, owner->W, owner->H, owner->world, rank)) return rc;
+    if (rank == 0) return fail(CERES_ERR_INVALID, "ceres_peer_frame_alias: rank 0 is the owner");
+    if (int rc = peer_size_queue(s, owner->W, owner->H, owner->world, rank)) return rc;
+    if (s->device != owner->device) {
+        DeviceGuard guard(s->device);
+        int can = 0;
+        CUDA_TRY(cudaDeviceCanAccessPeer(&can, s->device, owner->device));
+        if (!can) return fail(CERES_ERR_UNSUPPORTED, "ceres_peer_frame_alias: no peer access between the two GPUs");
+        cudaError_t e = cudaDeviceEnablePeerAccess(owner->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(CERES_ERR_CUDA, cudaGetErrorString(e));
+        cudaGetLastError();
+    }
+    ceres_peer_frame* pf = new (std::nothrow) ceres_peer_frame(*owner);
+    if (!pf) return fail(CERES_ERR_INVALID, "out of host memory");
+    pf->owner = false; pf->mapped = false; pf->device = s->device; pf->rank = rank; pf->epoch = owner->epoch;
+    *out = pf;
+    return CERES_OK;
+}
+
+void ceres_peer_frame_destroy(ceres_peer_frame* pf) {
+    if (!pf) return;
+    DeviceGuard guard(pf->device);
+    cudaDeviceSynchronize();
+    if (pf->owner) cudaFree(pf->base);
+    else if (pf->mapped) cudaIpcCloseMemHandle(pf->base);
+    delete pf;
+}
+
+float* ceres_peer_frame_pixels(ceres_peer_frame* pf) { return pf ? pf->pixels : nullptr; }
+uint32_t* ceres_peer_frame_ids(ceres_peer_frame* pf) { return pf ? pf->ids : nullptr; }
+
+int ceres_peer_frame_error(ceres_peer_frame* pf) {
+    if (!pf) return -1;
+    DeviceGuard guard(pf->device);
+    uint32_t e = 0;
+    if (cudaMemcpy(&e, &pf->ctl->error, sizeof(e), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (int)e;
+}
+
+int ceres_render_peer(ceres_scene* s, const ceres_camera* cam, const float sun[3], unsigned flags, void* stream_v,
+                      ceres_peer_frame* pf, uint64_t* d_counters) {
+    if (!s || !pf) return fail(CERES_ERR_INVALID, "ceres_render_peer: null argument");
+    if (s->device != pf->device) return fail(CERES_ERR_INVALID, "ceres_render_peer: scene and frame handle belong to different devices");
+    if (s->tune.variant == 1) return fail(CERES_ERR_UNSUPPORTED, "ceres_render_peer: needs the clear-pass kernels (variant 0 or 2)");
+    ceres_shard sh{CERES_TILE_BLOCK_ROWS, (uint32_t)pf->rank, (uint32_t)pf->world};
+    Frame f; uint32_t rows_local = 0;
+    if (int rc = prepare_frame(s, cam, sun, pf->W, pf->H, flags & ~CERES_COMPACT_ROWS, pf->world > 1 ? &sh : nullptr, pf->pixels,
+                               pf->ids, nullptr, f, rows_local)) return rc;
+    DeviceGuard guard(s->device);
+    cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
+    const uint32_t epoch = ++pf->epoch;
+    f.peer = pf->ctl; f.peer_epoch = epoch; f.peer_rank = (uint32_t)pf->rank; f.skip_clear = 1u;
+    if (pf->rank == 0) {
+        peer_clear_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>((float4*)pf->pixels, pf->n4, (uint4*)pf->ids, pf->ni4, pf->ctl, epoch);
+        g_launches++;
+    }
+    s->rays_outside = 0;
+    if (rows_local == 0) {
+        peer_publish_kernel<<<1, 1, 0, st>>>(pf->ctl, (uint32_t)pf->rank, epoch);
+        g_launches++;
+    } else if (int rc = render_rows(s, f, 0, rows_local, st, 1u, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; })) {
+        return rc;
+    }
+    if (pf->rank == 0) {
+        peer_wait_kernel<<<1, 32, 0, st>>>(pf->ctl, epoch, (uint32_t)pf->world, (unsigned long long*)d_counters);
+        g_launches++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return CERES_OK;
 }
 
 // Host-framebuffer render (the drop-in for render.hpp:86-156).

@@ -11,6 +11,8 @@
 The classes only use torch.distributed collectives on plain tensors, so the same code runs over NCCL on CUDA tensors
 (bench.py, N GPUs) and over gloo on CPU tensors (tests/test_shard_gloo.py, world_size 2).
 """
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -61,3 +63,118 @@ class FrameGather:
                 fv.index_copy_(0, idx, self._bands[r].view(self.rows_max, self.row_floats)[: idx.numel()])
         dist.all_reduce(self.counters)
         return self.frame if self.rank == 0 else None
+
+
+class _DevMem:
+    """A raw device pointer presented through __cuda_array_interface__ so that torch can view it without a copy."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3}
+
+
+class PeerFrame:
+    """One frame on N GPUs, fused with its gather over NVLink peer memory (ceres_peer_frame, include/ceres_b200.h).
+
+    Rank 0 owns the device frame; every other rank maps it and its shade kernel stores its row blocks straight into
+    rank 0's memory, so render() is the whole multi-GPU step: no NCCL call, no gather pass.  The 64-byte mapping
+    handle travels once, at construction, through a torch.distributed broadcast (any backend)."""
+
+    def __init__(self, scene, width, height, rank=0, world=1, want_ids=False, owner=None):
+        import ctypes as C
+        from . import _capi
+        self._L, self._scene = _capi.lib(), scene
+        self.W, self.H, self.rank, self.world, self.want_ids = int(width), int(height), rank, world, bool(want_ids)
+        h = C.c_void_p()
+        if owner is not None:          # same process (tests, single-process multi-GPU hosts)
+            _capi.check(self._L.ceres_peer_frame_alias(owner._h, scene._h, rank, C.byref(h)))
+        else:
+            blob = (C.c_ubyte * _capi.PEER_HANDLE_BYTES)()
+            if rank == 0:
+                _capi.check(self._L.ceres_peer_frame_create(scene._h, self.W, self.H, int(want_ids), world, C.byref(h), blob))
+            if world > 1 and dist.is_initialized():      # not initialised: the other ranks are aliases in this process
+                box = [bytes(blob) if rank == 0 else None]
+                dist.broadcast_object_list(box, src=0)
+                if rank != 0:
+                    blob = (C.c_ubyte * _capi.PEER_HANDLE_BYTES).from_buffer_copy(box[0])
+                    _capi.check(self._L.ceres_peer_frame_open(scene._h, blob, self.W, self.H, int(want_ids), world, rank, C.byref(h)))
+        self._h = h
+        self.counters = torch.zeros(2, dtype=torch.int64, device=torch.device("cuda", scene.device)) if rank == 0 else None
+
+    def render(self, camera, sun_position, flags=0, stream=None):
+        """Enqueue this rank's share of the next frame (all ranks call it once per frame)."""
+        import ctypes as C
+        from . import _capi
+        from .render import _stream_handle, _p
+        sun = np.asarray(sun_position, np.float32)
+        cnt = C.c_void_p(self.counters.data_ptr()) if self.counters is not None else None
+        _capi.check(self._L.ceres_render_peer(self._scene._h, C.byref(camera.c()), _p(sun), flags,
+                                              C.c_void_p(_stream_handle(stream, self._scene.device)), self._h, cnt))
+
+    @property
+    def pixels(self):
+        """float32 [H, W, 3] view of the assembled frame in rank 0's memory."""
+        ptr = self._L.ceres_peer_frame_pixels(self._h)
+        return torch.as_tensor(_DevMem(ptr, (self.H, self.W, 3), "<f4"), device=torch.device("cuda", self._scene.device))
+
+    @property
+    def ids(self):
+        ptr = self._L.ceres_peer_frame_ids(self._h)
+        if not ptr:
+            return None
+        return torch.as_tensor(_DevMem(ptr, (self.H, self.W), "<i4"), device=torch.device("cuda", self._scene.device))
+
+    def error(self):
+        return int(self._L.ceres_peer_frame_error(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ceres_peer_frame_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+class SharedHostFrame:
+    """A HOST framebuffer shared by the ranks of one box (a file in /dev/shm mapped by every process and page-locked
+    in each with ceres_host_register).  Every rank renders its row blocks and DMA-writes them in place over ITS OWN
+    PCIe link, so the end-to-end frame needs no gather at all and the drain bandwidth grows with the GPU count
+    (the one-process equivalent is ceres_render_multi).  `array` is the frame, valid on every rank after render()."""
+
+    def __init__(self, name, shape, rank, world, dtype=np.float32, block_rows=None):
+        from . import _capi, configs
+        self._L = _capi.lib()
+        self.rank, self.world = rank, world
+        self.block_rows = block_rows or configs.TILE_BLOCK_ROWS
+        self.path = os.path.join("/dev/shm", name)
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        if rank == 0:
+            with open(self.path, "wb") as f:
+                f.truncate(nbytes)
+        if world > 1:
+            dist.barrier()
+        self.array = np.memmap(self.path, dtype=dtype, mode="r+", shape=tuple(shape))
+        self._ptr, self._nbytes = self.array.ctypes.data, nbytes
+        _capi.check(self._L.ceres_host_register(self._ptr, nbytes))
+        self._cnt = None
+
+    def render(self, scene, camera, sun_position, width, height, flags=0):
+        """Collective: every rank renders + copies its rows; returns the frame's (rays, hits) on every rank."""
+        shard = (self.block_rows, self.rank, self.world) if self.world > 1 else None
+        _, _, cnt = scene.render(camera, sun_position, width, height, flags=flags, pixels=self.array, shard=shard)
+        if self.world <= 1:
+            return cnt
+        if self._cnt is None:
+            dev = torch.device("cuda", scene.device) if dist.get_backend() == "nccl" else torch.device("cpu")
+            self._cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+        self._cnt[0], self._cnt[1] = cnt
+        dist.all_reduce(self._cnt)          # also the completion barrier: all rows have landed when it returns
+        return tuple(self._cnt.tolist())
+
+    def close(self):
+        if getattr(self, "array", None) is not None:
+            self._L.ceres_host_unregister(self._ptr)
+            self.array = None
+            if self.world > 1:
+                dist.barrier()
+            if self.rank == 0 and os.path.exists(self.path):
+                os.unlink(self.path)

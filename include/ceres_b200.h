@@ -128,6 +128,41 @@ int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const fl
                         size_t width, size_t height, unsigned flags, const ceres_shard* shard, void* stream,
                         float* d_pixels, uint32_t* d_ids, uint64_t* d_counters);
 
+/* ---- render: one frame on N GPUs, fused with its "gather" over NVLink peer memory ------------
+ * One process per GPU.  Rank 0 owns the frame: a device allocation holding the float RGB frame (+ optional ids) and
+ * a small control block; the other ranks map it (CUDA IPC) and their kernels store the pixels of their row blocks
+ * STRAIGHT INTO rank 0's memory while they shade -- there is no separate gather pass and no collective call.
+ * Per frame ("epoch" e, counted by every rank in lockstep):
+ *   rank 0   clears the whole frame (render.hpp:116-117: everything that is not a lit hit is 0), publishes
+ *            cleared_epoch = e, renders its own row blocks, then a one-warp kernel waits until done_epoch[r] >= e for
+ *            every rank and sums the ranks' counters into d_counters;
+ *   rank r   traces its row blocks; its shade kernel waits for cleared_epoch >= e, stores its pixels over NVLink,
+ *            fences at system scope and publishes done_epoch[r] = e together with its (rays, hits).
+ * Waits are bounded (about 4 s): on expiry the control block's error word is set and ceres_peer_frame_error reports
+ * it; the GPU is never left spinning.  All ranks must call ceres_render_peer the same number of times. */
+typedef struct ceres_peer_frame ceres_peer_frame;
+#define CERES_PEER_HANDLE_BYTES 64
+#define CERES_PEER_MAX_RANKS 16
+/* rank 0: allocate the frame on the scene's device; handle_out (CERES_PEER_HANDLE_BYTES) is what the other ranks
+ * pass to ceres_peer_frame_open (ship it with any host-side channel, e.g. a torch.distributed broadcast). */
+int ceres_peer_frame_create(ceres_scene* scene, size_t width, size_t height, int want_ids, int world,
+                            ceres_peer_frame** out, unsigned char* handle_out);
+/* rank r > 0 (another process, any GPU of the box with peer access to rank 0's): map rank 0's frame. */
+int ceres_peer_frame_open(ceres_scene* scene, const unsigned char* handle, size_t width, size_t height, int want_ids,
+                          int world, int rank, ceres_peer_frame** out);
+/* rank r > 0 living in the SAME process as the owner (tests; a multi-GPU single-process host): shares the mapping. */
+int ceres_peer_frame_alias(ceres_peer_frame* owner, ceres_scene* scene, int rank, ceres_peer_frame** out);
+void ceres_peer_frame_destroy(ceres_peer_frame* frame);
+/* device pointers of the assembled frame (valid in the calling process; meaningful to read on rank 0) */
+float* ceres_peer_frame_pixels(ceres_peer_frame* frame);
+uint32_t* ceres_peer_frame_ids(ceres_peer_frame* frame);
+/* Enqueue this rank's part of the next frame on `stream`.  d_counters (rank 0 only, nullable): DEVICE 2 x uint64,
+ * receives the frame totals once every rank has delivered. */
+int ceres_render_peer(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3], unsigned flags,
+                      void* stream, ceres_peer_frame* frame, uint64_t* d_counters);
+/* after the stream has been synchronised: 0 = no wait of any rank expired so far */
+int ceres_peer_frame_error(ceres_peer_frame* frame);
+
 /* Per-frame work statistics of the LAST ceres_render_device call on this scene, read back after the stream has
  * been synchronised: stats[0..7] = {S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow,rays,hits} where S = node-pair
  * steps and T = triangle tests actually executed by the GPU (shadow rays exit at the first hit, so S_shadow and
