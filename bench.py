@@ -172,6 +172,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N>1: 'peer' = kernels store into rank 0's frame over NVLink (ceres_render_peer); "
+                         "'nccl' = packed bands + NCCL gather + row scatter")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -204,7 +207,15 @@ def main():
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)         # > 126 MB L2
     rflags = flags | (cr.COMPACT_ROWS if world > 1 else 0)
 
+    pf = None
+    if world > 1 and args.gather == "peer":
+        from ceres_raytracer_b200.shard import PeerFrame
+        pf = PeerFrame(scene, W, H, rank, world)          # the frame lives in rank 0's HBM, every rank's kernels write it
+
     def frame():
+        if pf is not None:
+            pf.render(cam, sun, flags=flags)        # clear (rank 0) + trace + shade-into-rank-0 + wait (rank 0): no collective
+            return
         scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
         fg.assemble()               # N > 1: NCCL gather to rank 0 + row scatter, counters summed over shards
 
@@ -223,8 +234,10 @@ def main():
         flush.fill_(1)
         frame()
     barrier()
-    counters = d_cnt.cpu().tolist()
+    counters = (pf.counters if pf is not None and rank == 0 else d_cnt).cpu().tolist()
     rays_frame, hits_frame = int(counters[0]), int(counters[1])
+    if pf is not None and rank == 0 and pf.error():
+        raise SystemExit("peer frame: a rank did not deliver within the wait bound")
 
     # ---- timed region: K frames, each preceded by an L2 flush that is outside its event pair ------------------
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -300,21 +313,22 @@ def main():
         assert cnt_e2e == (rays_frame, hits_frame)
         d2h = 3 * W * H * 4 + 16
     else:
-        h_frame = torch.empty(H * W * 3, dtype=torch.float32, pin_memory=True) if rank == 0 else None
-        h_cnt = torch.empty(2, dtype=torch.int64, pin_memory=True)
+        # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
+        # DMA-writes them in place over its own PCIe link; the counter all-reduce is the completion barrier.
+        from ceres_raytracer_b200.shard import SharedHostFrame
+        hf = SharedHostFrame(f"ceres_bench_{os.environ.get('MASTER_PORT', '0')}", (H, W, 3), rank, world)
         t_e2e = 0.0
         for k in range(steps_e2e + 2):
             flush.fill_(1)
             barrier()
             t0 = time.perf_counter()
-            frame()
-            if rank == 0:
-                h_frame.copy_(fg.frame, non_blocking=True)
-            h_cnt.copy_(d_cnt, non_blocking=True)
-            torch.cuda.synchronize()
+            cnt_e2e = hf.render(scene, cam, sun, W, H, flags=flags)
             if k >= 2:
                 t_e2e += time.perf_counter() - t0
-        d2h = 3 * W * H * 4 + 16
+        if rank == 0:
+            assert tuple(cnt_e2e) == (rays_frame, hits_frame)
+        hf.close()
+        d2h = 3 * W * H * 4 + 16 * world
     ms_e2e = allmax(1e3 * t_e2e / steps_e2e)
 
     # ---- CPU baseline: the reference's own render() on this box's host cores (rank 0, N = 1 only) ------------------
@@ -337,12 +351,12 @@ def main():
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": DATA,
             "config": {"workload": args.workload, "width": W, "height": H, "rays_per_frame": rays_frame,
                        "hits_counter": hits_frame, "scene_device_bytes": scene.device_bytes,
-                       "sharding": f"{world} x interleaved {cfg.TILE_BLOCK_ROWS}-row blocks, NCCL gather to rank 0" if world > 1 else "none",
+                       "sharding": (f"{world} x interleaved {cfg.TILE_BLOCK_ROWS}-row blocks, " + ("kernels store into rank 0's frame over NVLink peer memory (no collective)" if pf is not None else "NCCL gather to rank 0")) if world > 1 else "none",
                        "l2": "flushed (256 MiB fill) before every timed frame", "ms_per_step_warm_l2": ms_warm},
             "e2e": {"value": rays_frame / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": d2h,
                     "path": "ceres_render() -> page-locked host framebuffer" if world == 1 else
-                            "ceres_render_device(shard) + NCCL gather + D2H of the frame on rank 0"},
+                            "ceres_render_shard() per rank -> one shared page-locked host frame, each GPU drains its rows over its own PCIe link"},
             "gpu_launches": launches,
             "kernels_ms": kavg,
             "roofline": {"bound": "hbm", "kernel": dominant + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
