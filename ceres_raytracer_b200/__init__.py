@@ -4,6 +4,7 @@ raise when the CUDA library or a B200-class GPU is missing."""
 from .render import (Camera, Scene, render, frame_setup, shard_rows, write_ppm, kernel_launch_count, PinnedBuffer, device_count,
                      NO_SHADOWS, COMPACT_ROWS, MISS, CeresError, NODE_DT)
 from . import configs
+from . import scenes
 
 __all__ = ["Camera", "Scene", "render", "frame_setup", "shard_rows", "write_ppm", "kernel_launch_count", "PinnedBuffer",
-           "device_count", "NO_SHADOWS", "COMPACT_ROWS", "MISS", "CeresError", "NODE_DT", "configs"]
+           "device_count", "NO_SHADOWS", "COMPACT_ROWS", "MISS", "CeresError", "NODE_DT", "configs", "scenes"]

@@ -43,6 +43,7 @@ SYMBOLS = [
     "ceres_peer_frame_create", "ceres_peer_frame_open", "ceres_peer_frame_alias", "ceres_peer_frame_destroy",
     "ceres_peer_frame_pixels", "ceres_peer_frame_ids", "ceres_render_peer", "ceres_peer_frame_error",
 ]
+SYMBOLS += ["ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -99,6 +100,10 @@ def lib():
     L.ceres_peer_frame_ids.restype = vp
     L.ceres_render_peer.argtypes = [vp, camp, vp, C.c_uint, vp, vp, vp]
     L.ceres_peer_frame_error.argtypes = [vp]
+    L.ceres_scene_rotate.argtypes = [vp, C.c_int, C.c_float]
+    L.ceres_scene_transform.argtypes = [vp, vp, vp]
+    L.ceres_scene_refit.argtypes = [vp]
+    L.ceres_scene_download.argtypes = [vp, vp, sz, vp, sz]
     L.ceres_abi_version.restype = C.c_int
     L.ceres_device_count.restype = C.c_int
     L.ceres_kernel_launch_count.restype = u64

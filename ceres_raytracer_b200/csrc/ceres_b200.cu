@@ -561,6 +561,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 }
 
 #include "trace_persistent.cuh"
+#include "scene_prep.cuh"
 
 // ------------------------------------------------------------------------------------------------ host side
 #define CERES_MAX_BANDS 32
@@ -578,6 +579,13 @@ struct ceres_scene {
     void* d_pairs = nullptr; void* d_tris = nullptr; void* d_norms = nullptr; void* d_slot_id = nullptr;
     size_t scene_bytes = 0;
     uint32_t tri_count = 0;
+    // scene preparation on the device (scene_prep.cuh): structure kept for refit / download
+    size_t node_count = 0;
+    uint32_t n_pairs = 0;
+    std::vector<uint32_t> h_pair_first_child;               // pair -> reference node index of its left child
+    std::vector<uint32_t> h_slot_id;                        // slot -> primitive index
+    uint32_t* d_parent = nullptr; uint32_t* d_need = nullptr; uint32_t* d_arrived = nullptr;   // made by the first refit
+    float* d_root_bounds = nullptr;
     FrameCounters* d_ctr = nullptr;
     uint4* d_queue = nullptr; size_t queue_cap = 0;
     float* d_pixels = nullptr; size_t pixels_cap = 0;      // staging for the host-buffer API
@@ -718,6 +726,7 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
 
     // ---- flatten: walk the tree from the root, give every inner node's children one pair record ----------------
     std::vector<float> pairs;            // 16 floats per pair
+    std::vector<uint32_t> pair_first_child;
     uint32_t root_leaf_count = 0, depth_max = 1;
     std::vector<uint32_t> slot_id(tri_count);
     for (size_t k = 0; k < tri_count; ++k) {
@@ -735,9 +744,10 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
         struct Item { uint32_t first_child; uint32_t pair; uint32_t depth; };
         std::vector<Item> work;
         pairs.reserve((node_count / 2 + 1) * 16);
-        auto new_pair = [&]() { uint32_t id = (uint32_t)(pairs.size() / 16); pairs.resize(pairs.size() + 16); return id; };
+        pair_first_child.reserve(node_count / 2 + 1);
+        auto new_pair = [&](uint32_t first_child) { uint32_t id = (uint32_t)(pairs.size() / 16); pairs.resize(pairs.size() + 16); pair_first_child.push_back(first_child); return id; };
         size_t visited = 1;
-        work.push_back({root.first_child_or_primitive, new_pair(), 1});
+        work.push_back({root.first_child_or_primitive, new_pair(root.first_child_or_primitive), 1});
         while (!work.empty()) {
             Item it = work.back(); work.pop_back();
             if ((size_t)it.first_child + 1 >= node_count)
@@ -754,7 +764,7 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
                 if (cnt != 0) {
                     if ((size_t)first + cnt > tri_count) return fail(CERES_ERR_INVALID, "ceres_scene_create: leaf range out of bounds");
                 } else {
-                    first = new_pair();
+                    first = new_pair(first);
                     child_pair[c] = first;
                 }
                 std::memcpy(&pairs[(size_t)it.pair * 16 + 8 * c + 6], &cnt, 4);
@@ -823,6 +833,10 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     s->dev.slot_id = (const uint32_t*)s->d_slot_id;
     s->dev.root_leaf_count = root_leaf_count;
     s->dev.stack_depth = depth_max;
+    s->node_count = node_count;
+    s->n_pairs = root_leaf_count ? 0u : (uint32_t)(pairs.size() / 16);
+    s->h_pair_first_child = std::move(pair_first_child);
+    s->h_slot_id = std::move(slot_id);
     *out = s;
     return CERES_OK;
 }
@@ -838,6 +852,7 @@ void ceres_scene_destroy(ceres_scene* s) {
         if (s->sub_done[k]) cudaEventDestroy(s->sub_done[k]);
     }
     if (s->fork_ev) cudaEventDestroy(s->fork_ev);
+    cudaFree(s->d_parent); cudaFree(s->d_need); cudaFree(s->d_arrived); cudaFree(s->d_root_bounds);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_out);
     if (s->h_out) cudaFreeHost(s->h_out);
@@ -848,6 +863,101 @@ void ceres_scene_destroy(ceres_scene* s) {
 }
 
 size_t ceres_scene_device_bytes(const ceres_scene* s) { return s ? s->scene_bytes : 0; }
+
+// ---- scene preparation on the device (scene_prep.cuh) ---------------------------------------------
+// All four calls are synchronous on the scene's stream and must not overlap frames of this scene in flight.
+static int prep_triangles(ceres_scene* s, const PrepParams& q) {
+    DeviceGuard guard(s->device);
+    const unsigned grid = (unsigned)std::min<size_t>(((size_t)s->tri_count + 255) / 256, (size_t)s->sm_count * 16);
+    prep_triangles_kernel<<<grid, 256, 0, s->stream>>>((float4*)s->d_tris, s->tri_count, q);
+    g_launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return CERES_OK;
+}
+
+int ceres_scene_rotate(ceres_scene* s, int axis, float degrees) {
+    if (!s || axis < 0 || axis > 2) return fail(CERES_ERR_INVALID, "ceres_scene_rotate: bad argument");
+    PrepParams q{};
+    q.mode = axis;
+    const float pi = 3.14159265359f;                       // render.hpp:26-28, float arithmetic, host cosf/sinf
+    q.c = std::cos(degrees * pi / 180.0f);
+    q.s = std::sin(degrees * pi / 180.0f);
+    return prep_triangles(s, q);
+}
+
+int ceres_scene_transform(ceres_scene* s, const float a[9], const float v[3]) {
+    if (!s || !a || !v) return fail(CERES_ERR_INVALID, "ceres_scene_transform: null argument");
+    PrepParams q{};
+    q.mode = PREP_AFFINE;
+    for (int k = 0; k < 9; ++k) q.a[k] = a[k];
+    for (int k = 0; k < 3; ++k) q.v[k] = v[k];
+    return prep_triangles(s, q);
+}
+
+int ceres_scene_refit(ceres_scene* s) {
+    if (!s) return fail(CERES_ERR_INVALID, "ceres_scene_refit: null scene");
+    DeviceGuard guard(s->device);
+    if (!s->d_root_bounds) CUDA_TRY(cudaMalloc((void**)&s->d_root_bounds, 6 * sizeof(float)));
+    if (s->dev.root_leaf_count) {
+        // the root is the only node: its box is the leaf box of all triangles (one thread; such scenes are tiny)
+        return fail(CERES_ERR_UNSUPPORTED, "ceres_scene_refit: single-leaf scenes have no hierarchy to refit");
+    }
+    const unsigned grid = (s->n_pairs + 255u) / 256u;
+    if (!s->d_parent) {
+        CUDA_TRY(cudaMalloc((void**)&s->d_parent, (size_t)s->n_pairs * 4));
+        CUDA_TRY(cudaMalloc((void**)&s->d_need, (size_t)s->n_pairs * 4));
+        CUDA_TRY(cudaMalloc((void**)&s->d_arrived, (size_t)s->n_pairs * 4));
+        CUDA_TRY(cudaMemsetAsync(s->d_arrived, 0, (size_t)s->n_pairs * 4, s->stream));
+        refit_links_kernel<<<grid, 256, 0, s->stream>>>((const float4*)s->d_pairs, s->n_pairs, s->d_parent, s->d_need);
+        g_launches++;
+    }
+    refit_kernel<<<grid, 256, 0, s->stream>>>((float*)s->d_pairs, (const float4*)s->d_tris, s->d_parent, s->d_need, s->d_arrived,
+                                              s->n_pairs, s->d_root_bounds);
+    g_launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(s->bounds, s->d_root_bounds, 6 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));       // s->bounds feeds the screen-rectangle culling of the next frame
+    return CERES_OK;
+}
+
+int ceres_scene_download(ceres_scene* s, void* nodes_out, size_t node_count, void* tris_out, size_t tri_count) {
+    if (!s) return fail(CERES_ERR_INVALID, "ceres_scene_download: null scene");
+    if ((nodes_out && node_count != s->node_count) || (tris_out && tri_count != s->tri_count))
+        return fail(CERES_ERR_INVALID, "ceres_scene_download: node/triangle count differs from the scene's");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (tris_out) {
+        std::vector<float> slots((size_t)s->tri_count * 12);
+        CUDA_TRY(cudaMemcpy(slots.data(), s->d_tris, slots.size() * 4, cudaMemcpyDeviceToHost));
+        float* out = static_cast<float*>(tris_out);
+        for (size_t k = 0; k < s->tri_count; ++k) std::memcpy(out + (size_t)s->h_slot_id[k] * 12, &slots[k * 12], 48);
+    }
+    if (nodes_out) {
+        RefNode* out = static_cast<RefNode*>(nodes_out);
+        if (s->dev.root_leaf_count) {
+            for (int b = 0; b < 6; ++b) out[0].bounds[b] = s->bounds[b];
+            out[0].primitive_count = s->dev.root_leaf_count; out[0].first_child_or_primitive = 0;
+            return CERES_OK;
+        }
+        std::vector<float> pairs((size_t)s->n_pairs * 16);
+        CUDA_TRY(cudaMemcpy(pairs.data(), s->d_pairs, pairs.size() * 4, cudaMemcpyDeviceToHost));
+        for (int b = 0; b < 6; ++b) out[0].bounds[b] = s->bounds[b];
+        out[0].primitive_count = 0; out[0].first_child_or_primitive = s->h_pair_first_child[0];
+        for (size_t p = 0; p < s->n_pairs; ++p) {
+            for (int c = 0; c < 2; ++c) {
+                RefNode& n = out[(size_t)s->h_pair_first_child[p] + c];
+                const float* q = &pairs[p * 16 + 8 * c];
+                for (int b = 0; b < 6; ++b) n.bounds[b] = q[b];
+                uint32_t cnt, first;
+                std::memcpy(&cnt, q + 6, 4); std::memcpy(&first, q + 7, 4);
+                n.primitive_count = cnt;
+                n.first_child_or_primitive = cnt ? first : s->h_pair_first_child[first];
+            }
+        }
+    }
+    return CERES_OK;
+}
 
 int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");

@@ -123,6 +123,28 @@ class Scene:
         t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm, band_bytes, (C.c_uint32 * 3)(refill_min, subframes, chunk))
         _capi.check(self._L.ceres_scene_set_tuning(self._h, C.byref(t)))
 
+    # ---- scene preparation on the device ---------------------------------------------------
+    def rotate(self, axis, degrees):
+        """rotate_triangles<axis>(degrees) of render.hpp:24-44 on the resident triangles (call refit() afterwards)."""
+        _capi.check(self._L.ceres_scene_rotate(self._h, int(axis), float(degrees)))
+
+    def transform(self, a, v):
+        """transform_triangles(Transform{a, v}) of transform.hpp:106-129 on the resident triangles."""
+        a = np.ascontiguousarray(a, np.float32).reshape(9)
+        v = np.ascontiguousarray(v, np.float32).reshape(3)
+        _capi.check(self._L.ceres_scene_transform(self._h, _p(a), _p(v)))
+
+    def refit(self):
+        """HierarchyRefitter::refit (hierarchy_refitter.hpp) of the resident BVH to the resident triangles."""
+        _capi.check(self._L.ceres_scene_refit(self._h))
+
+    def download(self):
+        """(nodes, triangles) as the reference would hold them now: NODE_DT[node_count], float32[tri_count, 12]."""
+        nodes = np.zeros(self.node_count, NODE_DT)
+        tris = np.zeros((self.tri_count, 12), np.float32)
+        _capi.check(self._L.ceres_scene_download(self._h, _p(nodes), self.node_count, _p(tris), self.tri_count))
+        return nodes, tris
+
     def set_stats(self, enable):
         _capi.check(self._L.ceres_scene_set_stats(self._h, int(bool(enable))))
 

@@ -91,6 +91,22 @@ int ceres_scene_set_tuning(ceres_scene* scene, const ceres_tuning* tuning);
 /* bytes of device memory held by the flattened scene */
 size_t ceres_scene_device_bytes(const ceres_scene* scene);
 
+/* ---- scene preparation on the device (the step before the path) ------------------------------
+ * For animated objects: move the triangles that already live on the GPU and refit the BVH there, instead of a host
+ * rebuild + re-upload.  Synchronous; must not overlap frames of this scene that are still in flight.
+ *   ceres_scene_rotate     rotate_triangles<Axis> (render.hpp:24-44): axis 0/1/2, degrees; cos/sin on the host
+ *   ceres_scene_transform  transform_triangles (transform.hpp:106-129): a = Transform::a row-major 3x3, v = Transform::v
+ *   ceres_scene_refit      HierarchyRefitter::refit (lib/bvh/hierarchy_refitter.hpp:17-45), leaf box = union of its
+ *                          triangles' bounding_box() (triangle.hpp:39-44); also refreshes the culling rectangle's box
+ *   ceres_scene_download   the scene as the reference would hold it now: nodes_out = node_count x 32 B reference
+ *                          nodes (same numbering as at creation), tris_out = tri_count x 48 B in primitive order
+ *                          (either may be NULL).
+ * tri_norms are NOT transformed -- neither does the reference (render.hpp:24-44 touches only `triangles`). */
+int ceres_scene_rotate(ceres_scene* scene, int axis, float degrees);
+int ceres_scene_transform(ceres_scene* scene, const float a[9], const float v[3]);
+int ceres_scene_refit(ceres_scene* scene);
+int ceres_scene_download(ceres_scene* scene, void* nodes_out, size_t node_count, void* tris_out, size_t tri_count);
+
 /* ---- render: host buffers (the drop-in for render.hpp:86-156) ------------------------------------------------ */
 
 /* pixels: caller-owned HOST buffer of 3*width*height floats, layout pixels[3*(width*j+i)+c], row j=0 is v=-1,

@@ -19,6 +19,7 @@
 #include <stddef.h>
 #include <string.h>
 #include <float.h>
+#include <stdlib.h>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -341,6 +342,69 @@ void co_rotate_triangles(int axis, float degrees, float* tris12, size_t n) {
         }
         *t = tri_make(p[0], p[1], p[2]);
     }
+}
+
+/* include/transform.hpp:106-129: p' = a*p + v, each row summed left to right; the Triangle is rebuilt from the
+ * transformed p0, p1(), p2() (triangle.hpp:30-37).  a is row-major 3x3. */
+void co_transform_triangles(const float* a, const float* tv, float* tris12, size_t n) {
+    for (size_t k = 0; k < n; ++k) {
+        co_tri* t = (co_tri*)(tris12 + 12 * k);
+        vec3 p[3]; p[0] = t->p0; p[1] = tri_p1(t); p[2] = tri_p2(t);
+        for (int q = 0; q < 3; ++q) {
+            vec3 x = p[q];
+            p[q] = v3(a[0] * x.v[0] + a[1] * x.v[1] + a[2] * x.v[2] + tv[0],
+                      a[3] * x.v[0] + a[4] * x.v[1] + a[5] * x.v[2] + tv[1],
+                      a[6] * x.v[0] + a[7] * x.v[1] + a[8] * x.v[2] + tv[2]);
+        }
+        *t = tri_make(p[0], p[1], p[2]);
+    }
+}
+
+/* lib/bvh/hierarchy_refitter.hpp:17-32 + bottom_up_algorithm.hpp:47-85: every leaf box becomes the union of its
+ * primitives' bounding boxes (triangle.hpp:39-44; min/max as bounding_box.hpp:23-33 -> vector.hpp min/max =
+ * std::min/std::max per component), every inner box the union of its two children.  Sequential post-order here;
+ * min/max are exact, so the order of the reference's parallel walk does not matter.
+ * nodes: 32-byte reference nodes {bounds[6] = minx,maxx,miny,maxy,minz,maxz; count; first}. */
+static float fmin_std(float a, float b) { return b < a ? b : a; }   /* std::min(a, b) */
+static float fmax_std(float a, float b) { return a < b ? b : a; }   /* std::max(a, b) */
+void co_refit(void* nodes_v, size_t node_count, const size_t* prim_idx, const float* tris12) {
+    co_node* nodes = (co_node*)nodes_v;
+    /* children always follow their parent in neither layout, so walk with an explicit post-order stack */
+    uint32_t* stack = (uint32_t*)malloc(sizeof(uint32_t) * 2 * 128);
+    size_t cap = 256, sp = 0;
+    stack[sp++] = 0;                       /* entries: node index << 1 | visited */
+    while (sp) {
+        uint32_t e = stack[--sp];
+        uint32_t i = e >> 1;
+        co_node* nd = &nodes[i];
+        if (nd->primitive_count) {
+            float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+            for (uint32_t k = 0; k < nd->primitive_count; ++k) {
+                const co_tri* t = (const co_tri*)(tris12 + 12 * prim_idx[nd->first_child_or_primitive + k]);
+                vec3 p1 = tri_p1(t), p2 = tri_p2(t);
+                for (int c = 0; c < 3; ++c) {
+                    /* bbox(p0).extend(p1).extend(p2), then accumulated into the leaf box */
+                    float mn = fmin_std(fmin_std(t->p0.v[c], p1.v[c]), p2.v[c]);
+                    float mx = fmax_std(fmax_std(t->p0.v[c], p1.v[c]), p2.v[c]);
+                    lo[c] = fmin_std(lo[c], mn); hi[c] = fmax_std(hi[c], mx);
+                }
+            }
+            for (int c = 0; c < 3; ++c) { nd->bounds[2 * c] = lo[c]; nd->bounds[2 * c + 1] = hi[c]; }
+        } else if (e & 1u) {
+            const co_node* l = &nodes[nd->first_child_or_primitive]; const co_node* r = l + 1;
+            for (int c = 0; c < 3; ++c) {
+                nd->bounds[2 * c] = fmin_std(l->bounds[2 * c], r->bounds[2 * c]);
+                nd->bounds[2 * c + 1] = fmax_std(l->bounds[2 * c + 1], r->bounds[2 * c + 1]);
+            }
+        } else {
+            if (sp + 3 > cap) { cap *= 2; stack = (uint32_t*)realloc(stack, sizeof(uint32_t) * cap); }
+            stack[sp++] = (i << 1) | 1u;
+            stack[sp++] = (nd->first_child_or_primitive + 1) << 1;
+            stack[sp++] = nd->first_child_or_primitive << 1;
+        }
+    }
+    free(stack);
+    (void)node_count;
 }
 
 int co_threads(void) {

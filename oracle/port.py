@@ -34,6 +34,8 @@ def lib():
         L.co_smooth_shading.argtypes = [vp, sz, vp]
         L.co_make_triangles.argtypes = [vp, sz, vp]
         L.co_rotate_triangles.argtypes = [C.c_int, C.c_float, vp, sz]
+        L.co_transform_triangles.argtypes = [vp, vp, vp, sz]
+        L.co_refit.argtypes = [vp, sz, vp, vp]
         L.co_threads.restype = C.c_int
         _L = L
     return _L
@@ -119,6 +121,22 @@ def rotate_triangles(axis, degrees, tris12):
     t = _f32(tris12).reshape(-1, 12).copy()
     lib().co_rotate_triangles(axis, degrees, _p(t), t.shape[0])
     return t
+
+
+def transform_triangles(a, v, tris12):
+    """transform.hpp:120-129 with Transform{a (3x3), v}; returns the new (n,12) triangles."""
+    out = _f32(tris12).reshape(-1, 12).copy()
+    lib().co_transform_triangles(_p(_f32(a).reshape(9)), _p(_f32(v).reshape(3)), _p(out), out.shape[0])
+    return out
+
+
+def refit(pod, tris12=None):
+    """hierarchy_refitter.hpp refit of pod's BVH to tris12 (default: pod's triangles); returns the new nodes."""
+    nodes = np.ascontiguousarray(pod["nodes"]).copy()
+    idx = np.ascontiguousarray(pod["prim_indices"], dtype=np.uint64)
+    tris = _f32(pod["triangles"] if tris12 is None else tris12).reshape(-1, 12)
+    lib().co_refit(_p(nodes), nodes.shape[0], _p(idx), _p(tris))
+    return nodes
 
 
 def threads():

@@ -131,6 +131,14 @@ class RefScene:
             "norms": view(self.L.cref_scene_norms(self.h), nt * 36, np.float32).reshape(nt, 9),
         }
 
+    def refit(self, tris12):
+        """HierarchyRefitter::refit (hierarchy_refitter.hpp) to new triangles (n,12 in primitive order)."""
+        t = _f32(tris12).reshape(-1, 12)
+        assert t.shape[0] == self.tri_count
+        self.L.cref_refit.argtypes = [C.c_void_p, C.c_void_p]
+        self.L.cref_refit.restype = None
+        self.L.cref_refit(self.h, _p(t))
+
     def render(self, cam, sun, W, H):
         """The unmodified reference render() (render.hpp:86-156). Returns (pixels[H,W,3], rays, hits, seconds)."""
         cam, sun = _f32(cam), _f32(sun)
@@ -189,6 +197,25 @@ def smooth_shading(inp, kind="strict"):
 def turntable(cam, sun, axis, n_frames, kind="strict"):
     out = np.empty((n_frames, 13), np.float32)
     _lib(kind).cref_turntable(_p(_f32(cam)), _p(_f32(sun)), _p(_f32(axis)), n_frames, _p(out))
+    return out
+
+
+def transform_triangles(a, v, tris12, kind="strict"):
+    """The reference's transform_triangles (transform.hpp:120-129) with Transform{a, v}."""
+    L = _lib(kind)
+    out = _f32(tris12).reshape(-1, 12).copy()
+    L.cref_transform_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    L.cref_transform_triangles.restype = None
+    L.cref_transform_triangles(_p(_f32(a).reshape(9)), _p(_f32(v).reshape(3)), _p(out), out.shape[0])
+    return out
+
+
+def rotate_triangles(axis, degrees, tris12, kind="strict"):
+    L = _lib(kind)
+    out = _f32(tris12).reshape(-1, 12).copy()
+    L.cref_rotate_triangles.argtypes = [C.c_int, C.c_float, C.c_void_p, C.c_size_t]
+    L.cref_rotate_triangles.restype = None
+    L.cref_rotate_triangles(int(axis), float(degrees), _p(out), out.shape[0])
     return out
 
 

@@ -12,6 +12,8 @@
 //   render()                       include/render.hpp:86-156      (cref_render: the unmodified function)
 //   SingleRayTraverser::traverse   lib/bvh/single_ray_traverser.hpp:142-163 (cref_render_ex / cref_trace_rays)
 //   smooth_shading                 include/render.hpp:56-84
+//   transform_triangles / Transform::operator()   include/transform.hpp:106-129   (cref_transform_triangles)
+//   HierarchyRefitter::refit       lib/bvh/hierarchy_refitter.hpp:17-45            (cref_refit)
 //
 // cref_render_ex re-runs the loop body of render.hpp:105-153 through the reference's own traverser with the
 // Statistics overload, so that per-pixel primitive ids, shadow verdicts and S/T step counts can be recorded
@@ -37,6 +39,7 @@
 #include <bvh/single_ray_traverser.hpp>
 #include <bvh/primitive_intersectors.hpp>
 #include <bvh/triangle.hpp>
+#include <bvh/hierarchy_refitter.hpp>
 
 #include "render.hpp"
 #include "obj_norms.hpp"
@@ -129,6 +132,39 @@ void* cref_scene_from_pod(const void* nodes, size_t node_count, const size_t* pr
     std::memcpy(s->bvh.primitive_indices.get(), prim_idx, tri_count * sizeof(size_t));
     s->bvh.node_count = node_count;
     return s;
+}
+
+// ---- scene preparation ----------------------------------------------------------------------
+// tris: n x 12 floats {p0,e1,e2,n}, transformed in place by the reference's transform_triangles with
+// Transform{a (row-major 3x3), v}.
+void cref_transform_triangles(const float* a, const float* v, float* tris, size_t n) {
+    Transform<Scalar> t;
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) t.a[r][c] = a[3 * r + c];
+    t.v = Vector3(v[0], v[1], v[2]);
+    transform_triangles(t, reinterpret_cast<Triangle*>(tris), n);
+}
+
+void cref_rotate_triangles(int axis, float degrees, float* tris, size_t n) {
+    Triangle* t = reinterpret_cast<Triangle*>(tris);
+    if (axis == 0) rotate_triangles<0>(degrees, t, n);
+    else if (axis == 1) rotate_triangles<1>(degrees, t, n);
+    else rotate_triangles<2>(degrees, t, n);
+}
+
+// Refit the scene's BVH to `tris` (n x 12 floats in primitive order; they also replace the scene's triangles) with
+// the reference's HierarchyRefitter.  The reference ships no caller of refit(); the leaf update used here is the
+// builders' own definition of a leaf box: the union of Triangle::bounding_box() over the leaf's primitives in slot
+// order (triangle.hpp:39-44, bounding_box.hpp:23-33).
+void cref_refit(void* h, const float* tris) {
+    auto* s = static_cast<RefScene*>(h);
+    std::memcpy((void*)s->triangles.data(), tris, s->triangles.size() * sizeof(Triangle));
+    bvh::HierarchyRefitter<Bvh> refitter(s->bvh);
+    refitter.refit([&](Bvh::Node& leaf) {
+        auto bbox = bvh::BoundingBox<Scalar>::empty();
+        for (size_t k = 0; k < leaf.primitive_count; ++k)
+            bbox.extend(s->triangles[s->bvh.primitive_indices[leaf.first_child_or_primitive + k]].bounding_box());
+        leaf.bounding_box_proxy() = bbox;
+    });
 }
 
 void cref_scene_destroy(void* h) { delete static_cast<RefScene*>(h); }
