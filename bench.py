@@ -33,6 +33,12 @@ UNIT = "Mrays/s"
 DATA = "dragon.obj loaded + BVH built by the reference code (tests/golden/dragon_scene.npz); no synthetic substitute needed"
 
 
+def metric_name(workload, W, H, flags):
+    if workload == WORKLOAD:
+        return METRIC
+    return f"Mrays/s ({workload}: {W}x{H}, {'primary rays only' if flags & 1 else 'primary + shadow rays'})"
+
+
 def load_scene_pod(name):
     """The reference-loaded, reference-built scene (obj_norms.hpp loader, rotate_triangles, SweepSah + layout
     optimiser), dumped by tests/golden/make_golden.py.  It is INPUT DATA for both arms."""
@@ -41,6 +47,29 @@ def load_scene_pod(name):
         raise SystemExit(f"{p} missing: run tests/golden/make_golden.py where /root/reference exists")
     with np.load(p) as z:
         return {k: z[k] for k in z.files}
+
+
+def load_workload(workload, device=None):
+    """-> (pod, camera, sun, W, H, flags, scene or None).  'grid:<base>:AxBxC' scenes are synthesised from the base
+    scene (ceres_raytracer_b200.scenes); all their boxes come from the device refit, so the scene is created here and
+    the pod gets the downloaded nodes (input data for the CPU arm)."""
+    import ceres_raytracer_b200 as cr
+    name, cam, sun, W, H, flags = cr.configs.WORKLOADS[workload]
+    if not name.startswith("grid:"):
+        return load_scene_pod(name), cam, np.asarray(sun, np.float32), W, H, flags, None
+    _, base, dims = name.split(":")
+    nx, ny, nz = (int(x) for x in dims.split("x"))
+    pod, info = cr.scenes.instanced_grid(load_scene_pod(base), nx, ny, nz)
+    cam, sun = cr.scenes.grid_camera(info)
+    scene = None
+    if device is not None:
+        scene = cr.Scene.from_pod(pod, device=device)
+        scene.refit()
+        pod["nodes"], _ = scene.download()
+    else:       # CPU arm only: the oracle's refit (bit-identical boxes, tests/test_gpu_prep.py)
+        from oracle import port
+        pod["nodes"] = port.refit(pod)
+    return pod, cam, np.asarray(sun, np.float32), W, H, flags, scene
 
 
 def measured_peak():
@@ -131,18 +160,15 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import ceres_raytracer_b200.configs as cfg
-    name, cam, sun, W, H, flags = cfg.WORKLOADS[WORKLOAD]
-    pod = load_scene_pod(name)
-    secs, kind, cores, rays = cpu_reference_frames(pod, cam.as_array(), np.asarray(sun, np.float32), W, H,
-                                                   frames=args.steps, warmup=args.warmup)
+    pod, cam, sun, W, H, flags, _ = load_workload(args.workload)
+    secs, kind, cores, rays = cpu_reference_frames(pod, cam.as_array(), sun, W, H, frames=args.steps, warmup=args.warmup)
     ms = 1e3 * float(np.sum(secs)) / len(secs)
     val = rays / (ms * 1e-3) / 1e6
     line = {
-        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": metric_name(args.workload, W, H, flags), "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": DATA,
-        "config": {"workload": WORKLOAD, "width": W, "height": H, "rays_per_frame": rays, "l2": "n/a (CPU)"},
+        "config": {"workload": args.workload, "width": W, "height": H, "rays_per_frame": rays, "l2": "n/a (CPU)"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                          "sample": f"{len(secs)} full {W}x{H} frames, unmodified render() (render.hpp:86-156), "
                                    f"best {min(secs)*1e3:.1f} ms, median {np.median(secs)*1e3:.1f} ms"},
@@ -172,6 +198,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--verify", action="store_true",
+                    help="after the measurement, render the same frame with the oracle (CPU) and compare hit ids, "
+                         "counters and RGB at the full size (N=1)")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = kernels store into rank 0's frame over NVLink (ceres_render_peer); "
                          "'nccl' = packed bands + NCCL gather + row scatter")
@@ -195,10 +224,9 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     warmup = max(args.warmup, 3)
 
-    name, cam, sun, W, H, flags = cfg.WORKLOADS[args.workload]
-    sun = np.asarray(sun, np.float32)
-    pod = load_scene_pod(name)
-    scene = cr.Scene.from_pod(pod, device=local)
+    pod, cam, sun, W, H, flags, scene = load_workload(args.workload, device=local)
+    if scene is None:
+        scene = cr.Scene.from_pod(pod, device=local)
     # row-block sharding + the gather that assembles the frame on rank 0 (ceres_raytracer_b200/shard.py)
     from ceres_raytracer_b200.shard import FrameGather
     fg = FrameGather(W, H, cfg.TILE_BLOCK_ROWS, rank, world, dev)
@@ -288,7 +316,7 @@ def main():
     whole = sum(abytes.values()) / (kavg["total"] * 1e-3) / 1e9 if kavg["total"] > 0 else 0.0
     ncu_traffic = None
     tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")     # dram bytes per launch from the committed ncu --set full capture
-    if os.path.exists(tp):
+    if os.path.exists(tp) and args.workload == WORKLOAD:
         try:
             ncu_traffic = json.load(open(tp)).get(dominant)
         except Exception:
@@ -344,9 +372,22 @@ def main():
         except Exception as e:      # the baseline is reporting only; never fail the GPU line for it
             cpu = {"value": None, "unit": UNIT, "cores": None, "kind": "unavailable", "sample": str(e)[:200]}
 
+    # ---- --verify: the same frame through the oracle, full size ----------------------------------------------------
+    verified = None
+    if args.verify and world == 1:
+        from oracle import port
+        px, ids, cnt = scene.render(cam, sun, W, H, flags=flags, want_ids=True)
+        o = port.render(pod, cam.as_array(), sun, W, H, flags)
+        verified = {"oracle": "oracle/ceres_oracle.c (strict restatement)", "ids_equal": bool(np.array_equal(ids.reshape(-1), o["ids"].reshape(-1))),
+                    "id_mismatches": int((ids.reshape(-1) != o["ids"].reshape(-1)).sum()),
+                    "counters_equal": bool(cnt == (o["stats"]["rays"], o["stats"]["hits"])),
+                    "max_abs_rgb_diff": float(np.abs(px.reshape(-1) - o["pixels"].reshape(-1)).max()),
+                    "oracle_steps": {k: int(o["stats"][k]) for k in ("S_miss", "S_hit", "S_shadow", "T_miss", "T_hit", "T_shadow") if k in o["stats"]}}
+        del px, ids, o
+
     if rank == 0:
         line = {
-            "metric": METRIC, "value": rays_frame / (ms_step * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
+            "metric": metric_name(args.workload, W, H, flags), "value": rays_frame / (ms_step * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": DATA,
             "config": {"workload": args.workload, "width": W, "height": H, "rays_per_frame": rays_frame,
@@ -364,11 +405,17 @@ def main():
                          "algorithmic_bytes_per_launch": abytes[dominant],
                          "whole_frame": {"achieved": whole, "frac": whole / peak, "bytes": sum(abytes.values())},
                          "work": {k: st[k] for k in ("S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "hits_primary", "occluded")},
-                         "note": "scene (3 MB) is L1/L2-resident: the HBM peak is the conservative denominator SURVEY.md 8(d) asks for"},
+                         "note": ("scene (3 MB) is L1/L2-resident: the HBM peak is the conservative denominator SURVEY.md 8(d) asks for"
+                                  if scene.device_bytes < (64 << 20) else
+                                  f"scene ({scene.device_bytes / 1e9:.2f} GB) exceeds the 126 MB L2: node/triangle fetches are HBM/L2-miss traffic")},
             "clocks": clocks.summary(),
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
+        if verified is not None:
+            line["verified"] = verified
+        if args.workload != WORKLOAD:
+            line["data"] = f"synthetic: {cfg.WORKLOADS[args.workload][0]} (ceres_raytracer_b200.scenes.instanced_grid of the reference-built dragon scene, boxes by device refit)"
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -19,6 +19,11 @@ WORKLOADS = {
     "dragon_1080p_primary": ("dragon", DRAGON_CAMERA, DRAGON_SUN, 1920, 1080, 1),
     "dragon_1080p_shadow": ("dragon", DRAGON_CAMERA, DRAGON_SUN, 1920, 1080, 0),
     "dragon_4k_shadow": ("dragon", DRAGON_CAMERA, DRAGON_SUN, 3840, 2160, 0),
+    # BASELINE.json configs[4] / SURVEY.md 8(d) config 5: the dragon on an 8x8x7 grid (448 copies = 10 523 520
+    # triangles), one flat BVH; camera and sun come from scenes.grid_camera (None here)
+    "grid448_8k_shadow": ("grid:dragon:8x8x7", None, None, 7680, 4320, 0),
+    "grid448_4k_shadow": ("grid:dragon:8x8x7", None, None, 3840, 2160, 0),
+    "grid12_1080p_shadow": ("grid:dragon:3x2x2", None, None, 1920, 1080, 0),
 }
 
 TILE_BLOCK_ROWS = 16   # multi-GPU row-block interleave
