@@ -26,4 +26,12 @@ WORKLOADS = {
     "grid12_1080p_shadow": ("grid:dragon:3x2x2", None, None, 1920, 1080, 0),
 }
 
+# BASELINE.json configs[3] / SURVEY.md 8(d) config 4: 60-frame turntable of the dragon (anim.cpp:77-89,142), frames
+# round-robin over the GPUs.  name: (scene, frames, width, height, flags); the camera path is the reference's own
+# output for the static.cpp camera (tests/golden/kat.npz "turntable", made by tests/golden/make_golden.py)
+SEQUENCES = {
+    "dragon_turntable_1080p": ("dragon", 60, 1920, 1080, 0),
+    "dragon_turntable_4k": ("dragon", 60, 3840, 2160, 0),
+}
+
 TILE_BLOCK_ROWS = 16   # multi-GPU row-block interleave

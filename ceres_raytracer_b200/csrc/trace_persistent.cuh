@@ -23,6 +23,9 @@
 #define WAVE_SHADOW 1
 #define TRACE_THREADS 128
 #define TRACE_CHUNK 32u
+#ifndef TRACE_MIN_CTAS
+#define TRACE_MIN_CTAS(T) (1024 / (T))      // registers capped at 64 per thread: 32 warps per SM
+#endif
 #define REFILL_MIN 32u       // default: refill a warp only when all 32 ray slots are idle (coherence wins)
 
 struct RaySlot {
@@ -120,7 +123,7 @@ __device__ __forceinline__ bool item_pixel(const Frame& f, uint32_t item, uint32
 }
 
 template <int WAVE, bool STATS, int THREADS>
-__global__ void __launch_bounds__(THREADS) trace_kernel(const DevScene sc, const Frame f) {
+__global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_kernel(const DevScene sc, const Frame f) {
     extern __shared__ uint32_t smem_stack[];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;

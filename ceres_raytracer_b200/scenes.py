@@ -9,8 +9,8 @@ tri_norms) on an nx x ny x nz grid, deterministic, no RNG:
   * BVH         ONE flat tree in the reference's node layout (bvh.hpp:25-30, siblings adjacent, root at 0): a balanced
                 top tree over the instances (median split of the grid cells along the longest axis) whose leaves are
                 copies of the scene's own tree with shifted child / slot indices;
-  * bounds      left as placeholders: the boxes of ALL nodes come from a refit (ceres_scene_refit on the GPU, or the
-                oracle's refit in tests), exactly as HierarchyRefitter would produce them for the moved triangles.
+  * bounds      left as placeholders: the boxes of ALL nodes come from a refit (ceres_scene_refit on the GPU, or
+                the checker's CPU refit in tests), exactly as HierarchyRefitter would produce them for the moved triangles.
 
 Scene synthesis is host-side input preparation, outside the render path (the reference builds its scene on the host
 too, anim.cpp:38-65)."""
