@@ -286,6 +286,7 @@ def run_sequence(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_e2e = float(t.item())
     assert int(cnt_e2e[:, 0].sum()) == int(d_cnt[mine].sum(dim=0)[0].item())
+    d2h_seq = scene.last_d2h_bytes * len(mine)       # turntable: the rectangle is (nearly) the same for every frame
     hb.close()
 
     cpu = None
@@ -308,7 +309,7 @@ def run_sequence(args):
                        "sharding": f"frame f -> rank f mod {world}, no collective" if world > 1 else "none",
                        "l2": "flushed (256 MiB fill) before every timed pass; every frame rewrites the frame buffer"},
             "e2e": {"value": rays_total / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 13 * 4 * len(mine),
-                    "d2h_bytes_per_step": (3 * W * H * 4 + 16) * len(mine), "path": "ceres_render_sequence() -> page-locked host frames"},
+                    "d2h_bytes_per_step": d2h_seq, "host_frame_bytes": 3 * W * H * 4 * len(mine), "path": "ceres_render_sequence() -> page-locked host frames"},
             "gpu_launches": launches, "kernels_ms": per_pass,
             "roofline": {"bound": "hbm", "kernel": dominant + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
@@ -477,7 +478,7 @@ def main():
             _, _, cnt_e2e = scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)
             t_e2e += time.perf_counter() - t0
         assert cnt_e2e == (rays_frame, hits_frame)
-        d2h = 3 * W * H * 4 + 16
+        d2h = scene.last_d2h_bytes        # the screen rectangle of the scene + counters; the rest of the frame is host-filled zeros
     else:
         # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
         # DMA-writes them in place over its own PCIe link; the counter all-reduce is the completion barrier.
@@ -494,7 +495,9 @@ def main():
         if rank == 0:
             assert tuple(cnt_e2e) == (rays_frame, hits_frame)
         hf.close()
-        d2h = 3 * W * H * 4 + 16 * world
+        t = torch.tensor([scene.last_d2h_bytes], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        d2h = int(t.item())
     ms_e2e = allmax(1e3 * t_e2e / steps_e2e)
 
     # ---- CPU baseline: the reference's own render() on this box's host cores (rank 0, N = 1 only) ------------------
@@ -533,7 +536,7 @@ def main():
                        "sharding": (f"{world} x interleaved {cfg.TILE_BLOCK_ROWS}-row blocks, " + ("kernels store into rank 0's frame over NVLink peer memory (no collective)" if pf is not None else "NCCL gather to rank 0")) if world > 1 else "none",
                        "l2": "flushed (256 MiB fill) before every timed frame", "ms_per_step_warm_l2": ms_warm},
             "e2e": {"value": rays_frame / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": d2h,
+                    "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": d2h, "host_frame_bytes": 3 * W * H * 4,
                     "path": "ceres_render() -> page-locked host framebuffer" if world == 1 else
                             "ceres_render_shard() per rank -> one shared page-locked host frame, each GPU drains its rows over its own PCIe link"},
             "gpu_launches": launches,

@@ -602,6 +602,7 @@ struct ceres_scene {
     int shadow_blocks_per_sm = 0, shadow_blocks_per_sm_stats = 0;
     int trace_blocks_per_sm[4] = {0, 0, 0, 0};              // [wave*2 + stats]
     float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
+    uint64_t last_d2h_bytes = 0;                            // bytes DMA-copied to the host by the last host-frame render
     uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
 };
 
@@ -864,6 +865,7 @@ void ceres_scene_destroy(ceres_scene* s) {
 }
 
 size_t ceres_scene_device_bytes(const ceres_scene* s) { return s ? s->scene_bytes : 0; }
+uint64_t ceres_scene_last_d2h_bytes(const ceres_scene* s) { return s ? s->last_d2h_bytes : 0; }
 
 // ---- scene preparation on the device (scene_prep.cuh) ---------------------------------------------
 // All four calls are synchronous on the scene's stream and must not overlap frames of this scene in flight.
@@ -1513,6 +1515,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     struct Waiter { ceres_host::Pool& p; ceres_host::Job* j; ~Waiter() { p.wait(j); } } waiter{pool, &job};   // also on error paths
 
     const uint64_t prim_outside = (uint64_t)width * (rows - (empty ? 0 : l1 - l0));
+    s->last_d2h_bytes = empty ? 0 : (uint64_t)(l1 - l0) * (i1 - i0) * (ids ? 16u : 12u) + 2 * sizeof(unsigned long long);
     if (empty) {
         if (counters) { counters[0] = (uint64_t)width * rows; counters[1] = 0; }
         return CERES_OK;

@@ -119,6 +119,11 @@ class Scene:
     def device_bytes(self):
         return int(self._L.ceres_scene_device_bytes(self._h))
 
+    @property
+    def last_d2h_bytes(self):
+        """Bytes the last host-frame render moved over PCIe (the scene's screen rectangle + counters)."""
+        return int(self._L.ceres_scene_last_d2h_bytes(self._h))
+
     def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, band_bytes=0, refill_min=0, subframes=0, chunk=0):
         t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm, band_bytes, (C.c_uint32 * 3)(refill_min, subframes, chunk))
         _capi.check(self._L.ceres_scene_set_tuning(self._h, C.byref(t)))

@@ -90,6 +90,9 @@ void ceres_scene_destroy(ceres_scene* scene);
 int ceres_scene_set_tuning(ceres_scene* scene, const ceres_tuning* tuning);
 /* bytes of device memory held by the flattened scene */
 size_t ceres_scene_device_bytes(const ceres_scene* scene);
+/* bytes the last host-frame render (ceres_render / _shard / one frame of _sequence) moved over PCIe: the screen
+ * rectangle of the scene's rows + the counters; everything else of the frame is zero-filled by host threads */
+uint64_t ceres_scene_last_d2h_bytes(const ceres_scene* scene);
 
 /* ---- scene preparation on the device (the step before the path) ------------------------------
  * For animated objects: move the triangles that already live on the GPU and refit the BVH there, instead of a host

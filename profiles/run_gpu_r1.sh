@@ -14,3 +14,4 @@ if [ -s gpurun_out/bench.json ]; then
       -o gpurun_out/frame_full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 fi
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+python bench.py --workload dragon_turntable_4k --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_seq4k_n1.json 2> gpurun_out/bench_seq4k_n1.err; tail -2 gpurun_out/bench_seq4k_n1.err
