@@ -1524,19 +1524,47 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     // ---- GPU: concurrent row bands of the rectangle; each band is copied as soon as its own kernels are done ---------
     const uint32_t rcols = i1 - i0;
     const size_t nb = 0;
-    auto copy_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
-        uint32_t r = r0;
-        while (r < r1) {                                  // runs of rows that are contiguous in the caller's frame
-            uint32_t e = r + 1;
-            while (e < r1 && out_row(e) == out_row(e - 1) + 1) ++e;
-            const size_t src = (size_t)r * width + i0, dst = out_row(r) * width + i0;
-            CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, (size_t)rcols * 12, e - r,
-                                       cudaMemcpyDeviceToHost, bs));
-            if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, (size_t)rcols * 4, e - r,
-                                                cudaMemcpyDeviceToHost, bs));
-            r = e;
-        }
+    // rows [a, b) that are contiguous in the caller's frame: one pitched DMA
+    auto copy_run = [&](uint32_t a, uint32_t b, cudaStream_t bs) -> int {
+        if (b <= a) return CERES_OK;
+        const size_t src = (size_t)a * width + i0, dst = out_row(a) * width + i0;
+        CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, (size_t)rcols * 12, b - a,
+                                   cudaMemcpyDeviceToHost, bs));
+        if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, (size_t)rcols * 4, b - a,
+                                            cudaMemcpyDeviceToHost, bs));
         return CERES_OK;
+    };
+    auto copy_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
+        if (!scatter) return copy_run(r0, r1, bs);
+        // scattered shard: local block lb (block_rows packed rows) lands at frame block lb * count + index.  The whole
+        // blocks of the band go in ONE strided 3-D DMA (slice = one block; source slices are adjacent, destination
+        // slices are `count` blocks apart); a partial block at either end of the band is a 2-D copy.
+        const uint32_t br = f.block_rows;
+        const uint32_t b0 = (r0 + br - 1) / br, b1 = r1 / br;              // whole local blocks [b0, b1)
+        if (b1 <= b0) {                                                   // the band lies inside one or two blocks
+            const uint32_t mid = std::min(r1, (r0 / br + 1) * br);
+            if (int rc = copy_run(r0, mid, bs)) return rc;
+            return copy_run(mid, r1, bs);
+        }
+        if (int rc = copy_run(r0, b0 * br, bs)) return rc;
+        {
+            const size_t src = (size_t)b0 * br * width + i0, dst = out_row(b0 * br) * width + i0;
+            cudaMemcpy3DParms p3 = {};
+            p3.srcPtr = make_cudaPitchedPtr(s->d_pixels + 3 * src, width * 12, width * 12, br);
+            p3.dstPtr = make_cudaPitchedPtr(pixels + 3 * dst, width * 12, width * 12, (size_t)br * f.shard_count);
+            p3.extent = make_cudaExtent((size_t)rcols * 12, br, b1 - b0);
+            p3.kind = cudaMemcpyDeviceToHost;
+            CUDA_TRY(cudaMemcpy3DAsync(&p3, bs));
+            if (ids) {
+                cudaMemcpy3DParms q3 = {};
+                q3.srcPtr = make_cudaPitchedPtr(s->d_ids + src, width * 4, width * 4, br);
+                q3.dstPtr = make_cudaPitchedPtr(ids + dst, width * 4, width * 4, (size_t)br * f.shard_count);
+                q3.extent = make_cudaExtent((size_t)rcols * 4, br, b1 - b0);
+                q3.kind = cudaMemcpyDeviceToHost;
+                CUDA_TRY(cudaMemcpy3DAsync(&q3, bs));
+            }
+        }
+        return copy_run(b1 * br, r1, bs);
     };
     s->rays_outside = prim_outside;
     if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, copy_band)) return rc;

@@ -140,6 +140,8 @@ class SharedHostFrame:
     PCIe link, so the end-to-end frame needs no gather at all and the drain bandwidth grows with the GPU count
     (the one-process equivalent is ceres_render_multi).  `array` is the frame, valid on every rank after render()."""
 
+    CTL_BYTES = 4096      # control page behind the frame: epoch[r] at word r, (rays, hits) of rank r at words 64 + 2r
+
     def __init__(self, name, shape, rank, world, dtype=np.float32, block_rows=None):
         from . import _capi, configs
         self._L = _capi.lib()
@@ -147,33 +149,44 @@ class SharedHostFrame:
         self.block_rows = block_rows or configs.TILE_BLOCK_ROWS
         self.path = os.path.join("/dev/shm", name)
         nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._frame_bytes = (nbytes + 4095) // 4096 * 4096
         if rank == 0:
             with open(self.path, "wb") as f:
-                f.truncate(nbytes)
+                f.truncate(self._frame_bytes + self.CTL_BYTES)
         if world > 1:
             dist.barrier()
-        self.array = np.memmap(self.path, dtype=dtype, mode="r+", shape=tuple(shape))
+        self._map = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(self._frame_bytes + self.CTL_BYTES,))
+        self.array = self._map[:nbytes].view(dtype).reshape(shape)
+        self._ctl = self._map[self._frame_bytes:].view(np.uint64)
         self._ptr, self._nbytes = self.array.ctypes.data, nbytes
         _capi.check(self._L.ceres_host_register(self._ptr, nbytes))
-        self._cnt = None
+        self._epoch = 0
 
-    def render(self, scene, camera, sun_position, width, height, flags=0):
-        """Collective: every rank renders + copies its rows; returns the frame's (rays, hits) on every rank."""
+    def render(self, scene, camera, sun_position, width, height, flags=0, timeout_s=30.0):
+        """Collective: every rank renders + copies its rows; returns the frame's (rays, hits) on every rank.
+        Completion is a barrier in the shared control page (no NCCL/gloo call on the data path): a rank publishes its
+        counters, then its epoch, and waits until every rank's epoch has reached the frame's."""
+        import time
         shard = (self.block_rows, self.rank, self.world) if self.world > 1 else None
         _, _, cnt = scene.render(camera, sun_position, width, height, flags=flags, pixels=self.array, shard=shard)
         if self.world <= 1:
             return cnt
-        if self._cnt is None:
-            dev = torch.device("cuda", scene.device) if dist.get_backend() == "nccl" else torch.device("cpu")
-            self._cnt = torch.zeros(2, dtype=torch.int64, device=dev)
-        self._cnt[0], self._cnt[1] = cnt
-        dist.all_reduce(self._cnt)          # also the completion barrier: all rows have landed when it returns
-        return tuple(self._cnt.tolist())
+        self._epoch += 1
+        c = self._ctl
+        base = 64 + (self._epoch & 1) * 2 * self.world      # counter slots alternate: a rank may already be one frame ahead
+        c[base + 2 * self.rank], c[base + 2 * self.rank + 1] = cnt
+        c[self.rank] = self._epoch          # x86 stores are not reordered: the counters are visible before the epoch
+        t0 = time.perf_counter()
+        while int(c[: self.world].min()) < self._epoch:
+            if time.perf_counter() - t0 > timeout_s:
+                raise RuntimeError("SharedHostFrame: a rank did not deliver its rows in time")
+        both = c[base: base + 2 * self.world].reshape(self.world, 2).sum(axis=0)
+        return int(both[0]), int(both[1])
 
     def close(self):
         if getattr(self, "array", None) is not None:
             self._L.ceres_host_unregister(self._ptr)
-            self.array = None
+            self.array = self._ctl = self._map = None
             if self.world > 1:
                 dist.barrier()
             if self.rank == 0 and os.path.exists(self.path):
