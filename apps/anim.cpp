@@ -20,6 +20,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <future>
 #include <iostream>
 #include <memory>
 #include <sstream>
@@ -146,9 +147,24 @@ int main(int argc, char** argv) {
         ceres_scene* scene = nullptr;
         if (ceres_scene_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
                                tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
-        Scalar* pixels = static_cast<Scalar*>(ceres_host_alloc(3 * width * height * sizeof(Scalar)));
-        if (!pixels) { errors[g] = ceres_last_error(); ceres_scene_destroy(scene); return; }
-        for (int i = g; i < n_frames; i += gpus) {
+        // two page-locked frames per GPU: frame k is quantised and written by a writer thread while frame k+1 renders
+        // (upstream encodes synchronously inside the frame loop, anim.cpp:112-127)
+        Scalar* buffers[2] = {static_cast<Scalar*>(ceres_host_alloc(3 * width * height * sizeof(Scalar))),
+                              static_cast<Scalar*>(ceres_host_alloc(3 * width * height * sizeof(Scalar)))};
+        if (!buffers[0] || !buffers[1]) {
+            errors[g] = ceres_last_error(); ceres_host_free(buffers[0]); ceres_host_free(buffers[1]); ceres_scene_destroy(scene); return;
+        }
+        std::future<std::string> writing[2];
+        auto drain = [&](int b) {            // wait for the write that last used buffer b; returns false on a write error
+            if (!writing[b].valid()) return true;
+            const std::string err = writing[b].get();
+            if (!err.empty() && errors[g].empty()) errors[g] = err;
+            return err.empty();
+        };
+        int turn = 0;
+        for (int i = g; i < n_frames; i += gpus, turn ^= 1) {
+            if (!drain(turn)) break;
+            Scalar* pixels = buffers[turn];
             ceres_camera cam;
             for (int k = 0; k < 3; ++k) { cam.eye[k] = path[i].camera.eye[k]; cam.dir[k] = path[i].camera.dir[k]; cam.up[k] = path[i].camera.up[k]; }
             cam.fov = path[i].camera.fov;
@@ -164,11 +180,14 @@ int main(int argc, char** argv) {
             frame_rays[i] = (long)(int)cnt[0];
             if (!no_output) {
                 const std::string name = frame_name(out_file, i);
-                const bool ok = ppm16 ? ceres_apps::write_ppm16(name, pixels, width, height) : ceres_apps::write_ppm(name, pixels, width, height);
-                if (!ok) { errors[g] = "cannot write " + name; break; }
+                writing[turn] = std::async(std::launch::async, [=]() -> std::string {
+                    const bool ok = ppm16 ? ceres_apps::write_ppm16(name, pixels, width, height) : ceres_apps::write_ppm(name, pixels, width, height);
+                    return ok ? std::string() : "cannot write " + name;
+                });
             }
         }
-        ceres_host_free(pixels);
+        drain(0); drain(1);
+        ceres_host_free(buffers[0]); ceres_host_free(buffers[1]);
         ceres_scene_destroy(scene);
     };
     std::vector<std::thread> threads;
