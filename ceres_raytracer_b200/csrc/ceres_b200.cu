@@ -62,6 +62,7 @@ struct DevScene {
     const uint32_t* slot_id;  // slot -> primitive index of the reference (bvh.primitive_indices[slot])
     uint32_t root_leaf_count;  // != 0: the root itself is a leaf (single_ray_traverser.hpp:72-73)
     uint32_t stack_depth;      // entries of traversal stack needed (<= 64, single_ray_traverser.hpp:14)
+    unsigned long long* hist;  // statistics mode: 2 x 64 bins of node-pair steps per ray (bin = steps / 4), primary then shadow; may be null
 };
 
 struct FrameCounters {
@@ -587,6 +588,7 @@ struct ceres_scene {
     std::vector<uint32_t> h_slot_id;                        // slot -> primitive index
     uint32_t* d_parent = nullptr; uint32_t* d_need = nullptr; uint32_t* d_arrived = nullptr;   // made by the first refit
     float* d_root_bounds = nullptr;
+    unsigned long long* d_hist = nullptr;                   // step histogram (ceres_scene_get_step_histogram)
     FrameCounters* d_ctr = nullptr;
     uint4* d_queue = nullptr; size_t queue_cap = 0;
     float* d_pixels = nullptr; size_t pixels_cap = 0;      // staging for the host-buffer API
@@ -854,6 +856,7 @@ void ceres_scene_destroy(ceres_scene* s) {
         if (s->sub_done[k]) cudaEventDestroy(s->sub_done[k]);
     }
     if (s->fork_ev) cudaEventDestroy(s->fork_ev);
+    cudaFree(s->d_hist);
     cudaFree(s->d_parent); cudaFree(s->d_need); cudaFree(s->d_arrived); cudaFree(s->d_root_bounds);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_out);
@@ -970,8 +973,23 @@ int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
     return CERES_OK;
 }
 
+int ceres_scene_get_step_histogram(ceres_scene* s, uint64_t hist[128]) {
+    if (!s || !hist) return fail(CERES_ERR_INVALID, "null argument");
+    if (!s->d_hist) return fail(CERES_ERR_INVALID, "ceres_scene_get_step_histogram: statistics mode was never enabled");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaMemcpy(hist, s->d_hist, 128 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemset(s->d_hist, 0, 128 * sizeof(uint64_t)));
+    return CERES_OK;
+}
+
 int ceres_scene_set_stats(ceres_scene* s, int enable) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");
+    if (enable && !s->d_hist) {
+        DeviceGuard guard(s->device);
+        CUDA_TRY(cudaMalloc((void**)&s->d_hist, 128 * sizeof(unsigned long long)));
+        CUDA_TRY(cudaMemset(s->d_hist, 0, 128 * sizeof(unsigned long long)));
+        s->dev.hist = s->d_hist;
+    }
     s->stats = enable != 0;
     return CERES_OK;
 }

@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_kernel
         if (STATS && retire) {
             if (WAVE == WAVE_PRIMARY) { st[r.found ? 2 : 0] += n_steps; st[r.found ? 3 : 1] += n_tests; }
             else { st[0] += n_steps; st[1] += n_tests; }
+            if (sc.hist) atomicAdd(&sc.hist[(WAVE == WAVE_SHADOW ? 64u : 0u) + min(n_steps >> 2, 63u)], 1ull);
             n_steps = n_tests = 0;
         }
         retire = false;

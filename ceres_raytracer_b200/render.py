@@ -159,6 +159,12 @@ class Scene:
         names = ["S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "rays", "hits"]
         return {k: int(v) for k, v in zip(names, out)}
 
+    def step_histogram(self):
+        """(primary[64], shadow[64]) counts of rays by node-pair steps // 4 since the last call (statistics mode)."""
+        out = np.zeros(128, np.uint64)
+        _capi.check(self._L.ceres_scene_get_step_histogram(self._h, _p(out)))
+        return out[:64].copy(), out[64:].copy()
+
     def set_profiling(self, enable):
         """Per-kernel CUDA-event timing of every render_device call (see kernel_ms)."""
         _capi.check(self._L.ceres_scene_set_profiling(self._h, int(bool(enable))))

@@ -189,6 +189,9 @@ int ceres_peer_frame_error(ceres_peer_frame* frame);
  * statistics mode with ceres_scene_set_stats(scene, 1) (slower kernels). */
 int ceres_scene_set_stats(ceres_scene* scene, int enable);
 int ceres_scene_get_stats(ceres_scene* scene, uint64_t stats[8]);
+/* Statistics mode also fills a histogram of node-pair steps per ray, accumulated over the frames rendered since the
+ * last call (the call resets it): hist[b] = primary rays with b = min(steps / 4, 63), hist[64 + b] = shadow rays. */
+int ceres_scene_get_step_histogram(ceres_scene* scene, uint64_t hist[128]);
 
 /* Per-kernel timing.  While enabled, every ceres_render_device call records CUDA events on its launch stream
  * before/after each of its kernels.  ceres_scene_get_kernel_ms waits for the recorded frames and returns the SUMS
