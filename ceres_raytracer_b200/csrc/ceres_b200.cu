@@ -563,6 +563,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 
 #include "trace_persistent.cuh"
 #include "trace_batched.cuh"
+#include "trace_repack.cuh"
 #include "scene_prep.cuh"
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -1177,7 +1178,27 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
             return 0;
         };
         const bool wide_p = s->tune.primary_block == 256, wide_s = s->tune.shadow_block == 256;
-        if (s->tune.variant == 3) {
+        if (s->tune.variant == 4) {
+            // CTA-level repacking of the surviving rays every K steps (trace_repack.cuh)
+            auto launch_repack = [&](int wave, auto kernel, int words) {
+                const size_t smem_t = ((size_t)s->dev.stack_depth + words) * 4 * 128;
+                int& bps = s->trace_blocks_per_sm[wave * 2 + (s->stats ? 1 : 0)];
+                if (bps == 0) {
+                    if (s->tune.ctas_per_sm) bps = (int)s->tune.ctas_per_sm;
+                    else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 128, smem_t) != cudaSuccess) bps = 1;
+                    if (bps < 1) bps = 1;
+                }
+                kernel<<<(unsigned)(s->sm_count * bps), 128, smem_t, st>>>(s->dev, f);
+                g_launches++;
+            };
+            if (s->stats) launch_repack(0, trace_repack_kernel<WAVE_PRIMARY, true, 128>, RepackWords<WAVE_PRIMARY, true>::N);
+            else launch_repack(0, trace_repack_kernel<WAVE_PRIMARY, false, 128>, RepackWords<WAVE_PRIMARY, false>::N);
+            if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
+            if (f.shadows) {
+                if (s->stats) launch_repack(1, trace_repack_kernel<WAVE_SHADOW, true, 128>, RepackWords<WAVE_SHADOW, true>::N);
+                else launch_repack(1, trace_repack_kernel<WAVE_SHADOW, false, 128>, RepackWords<WAVE_SHADOW, false>::N);
+            }
+        } else if (s->tune.variant == 3) {
             // phase-sorted execution (trace_batched.cuh)
             if (s->stats) launch_wave(0, trace_batched_kernel<WAVE_PRIMARY, true, 128>, 128);
             else launch_wave(0, trace_batched_kernel<WAVE_PRIMARY, false, 128>, 128);

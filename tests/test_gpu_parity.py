@@ -234,6 +234,29 @@ def test_gpu_statistics_match_oracle_for_primary_rays(cr, dragon, dragon_pod):
     assert culled <= W * H - (o["rays"] - W * H)      # at most one root step per missing pixel was skipped
 
 
+@pytest.mark.parametrize("variant", [3, 4])
+def test_experimental_trace_variants_render_the_same_frame(cr, dragon, dragon_pod, variant):
+    """Variants 3 (phase-sorted execution, lane refill) and 4 (CTA-level repacking every K steps) only change which
+    lane runs which ray and when: frame, ids, counters and the work statistics must equal the default kernel's."""
+    cam, W, H = cr.configs.DRAGON_CAMERA, 1280, 720
+    ref = dragon.render(cam, SUN, W, H, want_ids=True)
+    dragon.set_stats(True)
+    dragon.render(cam, SUN, W, H)
+    ref_stats = dragon.get_stats()
+    try:
+        for refill in ((32, 8) if variant == 3 else (0,)):
+            dragon.set_tuning(variant=variant, refill_min=refill)
+            px, ids, cnt = dragon.render(cam, SUN, W, H, want_ids=True)
+            assert np.array_equal(px.view(np.uint32), ref[0].view(np.uint32)) and np.array_equal(ids, ref[1]) and cnt == ref[2]
+            st = dragon.get_stats()
+            for k in ("S_miss", "T_miss", "S_hit", "T_hit", "rays", "hits"):
+                assert st[k] == ref_stats[k], (variant, refill, k)
+        check_frame(cr, dragon, dragon_pod, cam, SUN, 640, 360, 0)
+    finally:
+        dragon.set_stats(False)
+        dragon.set_tuning()
+
+
 def test_tiny_scenes_root_leaf_and_single_pair(cr):
     # 1 triangle -> the root is a leaf (single_ray_traverser.hpp:72-73); hand-built POD, no builder needed
     tri = port.make_triangles(np.array([[-1, -1, 5, 1, -1, 5, 0, 1, 5]], np.float32))
