@@ -564,6 +564,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 #include "trace_persistent.cuh"
 #include "trace_batched.cuh"
 #include "trace_repack.cuh"
+#include "trace_shadow_spec.cuh"
 #include "scene_prep.cuh"
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -1211,7 +1212,21 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         if (s->stats) { if (wide_p) launch_wave(0, trace_kernel<WAVE_PRIMARY, true, 256>, 256); else launch_wave(0, trace_kernel<WAVE_PRIMARY, true, 128>, 128); }
         else { if (wide_p) launch_wave(0, trace_kernel<WAVE_PRIMARY, false, 256>, 256); else launch_wave(0, trace_kernel<WAVE_PRIMARY, false, 128>, 128); }
         if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
-        if (f.shadows) {
+        if (f.shadows && s->tune.variant == 5) {
+            // shadow wave with deferred triangle tests (trace_shadow_spec.cuh); ctas_per_sm picks the register budget
+            const size_t smem_t = ((size_t)s->dev.stack_depth + 2 * SPEC_PMAX) * 4 * 128;
+            const unsigned want = s->tune.ctas_per_sm ? s->tune.ctas_per_sm : 8u;
+            auto go = [&](auto kernel) {
+                int bps = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 128, smem_t) != cudaSuccess || bps < 1) bps = 1;
+                kernel<<<(unsigned)(s->sm_count * bps), 128, smem_t, st>>>(s->dev, f);
+                g_launches++;
+            };
+            if (s->stats) go(trace_shadow_spec_kernel<true, 128, 8>);
+            else if (want >= 12) go(trace_shadow_spec_kernel<false, 128, 12>);
+            else if (want >= 10) go(trace_shadow_spec_kernel<false, 128, 10>);
+            else go(trace_shadow_spec_kernel<false, 128, 8>);
+        } else if (f.shadows) {
             if (s->stats) { if (wide_s) launch_wave(1, trace_kernel<WAVE_SHADOW, true, 256>, 256); else launch_wave(1, trace_kernel<WAVE_SHADOW, true, 128>, 128); }
             else { if (wide_s) launch_wave(1, trace_kernel<WAVE_SHADOW, false, 256>, 256); else launch_wave(1, trace_kernel<WAVE_SHADOW, false, 128>, 128); }
         }
@@ -1458,7 +1473,7 @@ int ceres_render_peer(ceres_scene* s, const ceres_camera* cam, const float sun[3
                       ceres_peer_frame* pf, uint64_t* d_counters) {
     if (!s || !pf) return fail(CERES_ERR_INVALID, "ceres_render_peer: null argument");
     if (s->device != pf->device) return fail(CERES_ERR_INVALID, "ceres_render_peer: scene and frame handle belong to different devices");
-    if (s->tune.variant == 1) return fail(CERES_ERR_UNSUPPORTED, "ceres_render_peer: needs the clear-pass kernels (variant 0 or 2)");
+    if (s->tune.variant == 1) return fail(CERES_ERR_UNSUPPORTED, "ceres_render_peer: needs the clear-pass kernels (any variant but 1)");
     ceres_shard sh{CERES_TILE_BLOCK_ROWS, (uint32_t)pf->rank, (uint32_t)pf->world};
     Frame f; uint32_t rows_local = 0;
     if (int rc = prepare_frame(s, cam, sun, pf->W, pf->H, flags & ~CERES_COMPACT_ROWS, pf->world > 1 ? &sh : nullptr, pf->pixels,

@@ -234,10 +234,11 @@ def test_gpu_statistics_match_oracle_for_primary_rays(cr, dragon, dragon_pod):
     assert culled <= W * H - (o["rays"] - W * H)      # at most one root step per missing pixel was skipped
 
 
-@pytest.mark.parametrize("variant", [3, 4])
+@pytest.mark.parametrize("variant", [3, 4, 5])
 def test_experimental_trace_variants_render_the_same_frame(cr, dragon, dragon_pod, variant):
-    """Variants 3 (phase-sorted execution, lane refill) and 4 (CTA-level repacking every K steps) only change which
-    lane runs which ray and when: frame, ids, counters and the work statistics must equal the default kernel's."""
+    """Variants 3 (phase-sorted execution, lane refill), 4 (CTA-level repacking every K steps) and 5 (shadow wave with
+    deferred triangle tests) only change which lane runs which ray and when: frame, ids, counters and the work
+    statistics of the primary wave must equal the default kernel's."""
     cam, W, H = cr.configs.DRAGON_CAMERA, 1280, 720
     ref = dragon.render(cam, SUN, W, H, want_ids=True)
     dragon.set_stats(True)
