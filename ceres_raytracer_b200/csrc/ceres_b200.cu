@@ -566,6 +566,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 #include "trace_repack.cuh"
 #include "trace_shadow_spec.cuh"
 #include "scene_prep.cuh"
+#include "lbvh_build.cuh"
 
 // ------------------------------------------------------------------------------------------------ host side
 #define CERES_MAX_BANDS 32
@@ -964,6 +965,80 @@ int ceres_scene_download(ceres_scene* s, void* nodes_out, size_t node_count, voi
             }
         }
     }
+    return CERES_OK;
+}
+
+// ---- BVH construction on the GPU (lbvh_build.cuh) -----------------------------------------------------
+int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms) {
+    if (!tris || !tri_count || !nodes_out || !prim_idx_out) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: null or empty argument");
+    if (tri_count >= 0x40000000ull) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: too many triangles");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) return fail(CERES_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: bad device index");
+    DeviceGuard guard(device);
+    const int n = (int)tri_count;
+    const size_t n_nodes = 2 * tri_count - 1;
+    float4* d_tris = nullptr; float* d_box = nullptr; unsigned int* d_scene = nullptr;
+    uint32_t *d_code = nullptr, *d_idx = nullptr, *d_code2 = nullptr, *d_idx2 = nullptr, *d_child = nullptr, *d_pi = nullptr, *d_pl = nullptr, *d_arr = nullptr;
+    LbvhNode* d_nodes = nullptr; void* d_tmp = nullptr; size_t tmp_bytes = 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    auto cleanup = [&]() {
+        cudaFree(d_tris); cudaFree(d_box); cudaFree(d_scene); cudaFree(d_code); cudaFree(d_idx); cudaFree(d_code2); cudaFree(d_idx2);
+        cudaFree(d_child); cudaFree(d_pi); cudaFree(d_pl); cudaFree(d_arr); cudaFree(d_nodes); cudaFree(d_tmp);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+    };
+#define TRY_B(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); cleanup(); return CERES_ERR_CUDA; } } while (0)
+    TRY_B(cudaMalloc((void**)&d_tris, tri_count * 48));
+    TRY_B(cudaMalloc((void**)&d_box, tri_count * 24));
+    TRY_B(cudaMalloc((void**)&d_scene, 6 * sizeof(unsigned int)));
+    TRY_B(cudaMalloc((void**)&d_code, tri_count * 4)); TRY_B(cudaMalloc((void**)&d_idx, tri_count * 4));
+    TRY_B(cudaMalloc((void**)&d_code2, tri_count * 4)); TRY_B(cudaMalloc((void**)&d_idx2, tri_count * 4));
+    TRY_B(cudaMalloc((void**)&d_child, 2 * tri_count * 4)); TRY_B(cudaMalloc((void**)&d_pi, tri_count * 4));
+    TRY_B(cudaMalloc((void**)&d_pl, tri_count * 4)); TRY_B(cudaMalloc((void**)&d_arr, tri_count * 4));
+    TRY_B(cudaMalloc((void**)&d_nodes, n_nodes * sizeof(LbvhNode)));
+    TRY_B(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_code, d_code2, d_idx, d_idx2, n, 0, 30));
+    TRY_B(cudaMalloc(&d_tmp, tmp_bytes ? tmp_bytes : 16));
+    TRY_B(cudaMemcpy(d_tris, tris, tri_count * 48, cudaMemcpyHostToDevice));
+    TRY_B(cudaEventCreate(&e0)); TRY_B(cudaEventCreate(&e1));
+    const unsigned int scene_init[6] = {0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u};
+    TRY_B(cudaMemcpy(d_scene, scene_init, sizeof scene_init, cudaMemcpyHostToDevice));
+    TRY_B(cudaEventRecord(e0, 0));
+    const unsigned grid = (unsigned)((tri_count + 255) / 256);
+    lbvh_boxes_kernel<<<grid, 256>>>(d_tris, (uint32_t)n, d_box, d_scene);
+    lbvh_codes_kernel<<<grid, 256>>>(d_box, (uint32_t)n, d_scene, d_code, d_idx);
+    TRY_B(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_code, d_code2, d_idx, d_idx2, n, 0, 30));
+    g_launches += 2;
+    if (n == 1) {
+        LbvhNode root;
+        TRY_B(cudaMemcpy(root.bounds, d_box, 24, cudaMemcpyDeviceToHost));
+        root.primitive_count = 1; root.first_child_or_primitive = 0;
+        std::memcpy(nodes_out, &root, sizeof root);
+        prim_idx_out[0] = 0;
+        if (build_ms) *build_ms = 0.0;
+        cleanup();
+        return CERES_OK;
+    }
+    TRY_B(cudaMemsetAsync(d_arr, 0, tri_count * 4, 0));
+    lbvh_tree_kernel<<<grid, 256>>>(d_code2, n, d_child, d_pi, d_pl);
+    lbvh_emit_kernel<<<grid, 256>>>(d_child, d_idx2, d_box, n, d_nodes);
+    lbvh_fit_kernel<<<grid, 256>>>(d_pi, d_pl, d_arr, n, d_nodes);
+    g_launches += 3;
+    TRY_B(cudaEventRecord(e1, 0));
+    TRY_B(cudaGetLastError());
+    TRY_B(cudaEventSynchronize(e1));
+    float ms = 0.0f;
+    TRY_B(cudaEventElapsedTime(&ms, e0, e1));
+    if (build_ms) *build_ms = ms;
+    TRY_B(cudaMemcpy(nodes_out, d_nodes, n_nodes * sizeof(LbvhNode), cudaMemcpyDeviceToHost));
+    {
+        std::vector<uint32_t> idx(tri_count);
+        TRY_B(cudaMemcpy(idx.data(), d_idx2, tri_count * 4, cudaMemcpyDeviceToHost));
+        for (size_t k = 0; k < tri_count; ++k) prim_idx_out[k] = idx[k];
+    }
+#undef TRY_B
+    cleanup();
     return CERES_OK;
 }
 

@@ -78,6 +78,18 @@ def frame_setup(camera, width, height):
     return out[0:3].copy(), out[3:6].copy(), out[6:9].copy()
 
 
+def build_lbvh(triangles, device=0):
+    """GPU linear-BVH build (ceres_build_lbvh): returns (nodes NODE_DT[2n-1], prim_indices uint64[n], build_ms) in the
+    reference's layout for `triangles` float32[n, 12]."""
+    tris = np.ascontiguousarray(triangles, np.float32).reshape(-1, 12)
+    n = tris.shape[0]
+    nodes = np.zeros(max(2 * n - 1, 1), NODE_DT)
+    idx = np.zeros(max(n, 1), np.uint64)[:n]
+    ms = C.c_double(0.0)
+    _capi.check(_capi.lib().ceres_build_lbvh(_p(tris), n, int(device), _p(nodes), _p(idx), C.byref(ms)))
+    return nodes, idx, float(ms.value)
+
+
 class Scene:
     """Flattened BVH + triangles + normals resident on one GPU (ceres_scene)."""
 

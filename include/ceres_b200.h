@@ -110,6 +110,17 @@ int ceres_scene_transform(ceres_scene* scene, const float a[9], const float v[3]
 int ceres_scene_refit(ceres_scene* scene);
 int ceres_scene_download(ceres_scene* scene, void* nodes_out, size_t node_count, void* tris_out, size_t tri_count);
 
+/* ---- BVH construction on the GPU ---------------------------------------------------------------
+ * A linear BVH (Morton codes of the triangle centres, radix sort, Karras' radix tree; the GPU-friendly builder the
+ * reference sketches in lib/bvh/linear_bvh_builder.hpp:118-185) in the REFERENCE's data structure: nodes_out =
+ * (2 * tri_count - 1) x 32-byte bvh::Bvh<float>::Node with node 0 the root and siblings adjacent (bvh.hpp:25-30),
+ * prim_idx_out = tri_count x size_t Bvh::primitive_indices, one triangle per leaf.  tris: HOST tri_count x 48-byte
+ * Triangle<float>.  Replaces the host build of anim.cpp:46-65 / static.cpp:98-107 where build time matters (10 M
+ * triangles); the tree differs from SweepSah's, so exact-t ties may pick another triangle than the SweepSah tree would --
+ * frames are bit-exact against the reference's traverser walking THIS tree.  build_ms (nullable): device time of the
+ * build kernels without the transfers. */
+int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms);
+
 /* ---- render: host buffers (the drop-in for render.hpp:86-156) ------------------------------------------------ */
 
 /* pixels: caller-owned HOST buffer of 3*width*height floats, layout pixels[3*(width*j+i)+c], row j=0 is v=-1,

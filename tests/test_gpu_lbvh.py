@@ -1,0 +1,69 @@
+"""GPU tests of the BVH builder (ceres_build_lbvh).  The tree is not the one SweepSah builds, so the
+bars are: (1) it is a valid tree in the reference's data structure -- every node reachable exactly once, every triangle
+in exactly one leaf; (2) its boxes are exactly what HierarchyRefitter::refit computes for it (oracle refit is the
+identity on it, bit for bit); (3) frames rendered from it meet the bars of test_gpu_parity.py against the oracle
+walking the same tree."""
+import numpy as np
+import pytest
+
+from oracle import port
+from test_gpu_parity import check_frame, SUN
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cr():
+    import ceres_raytracer_b200 as cr
+    return cr
+
+
+def validate(nodes, idx, n):
+    assert nodes.shape[0] == 2 * n - 1 and sorted(idx.tolist()) == list(range(n))
+    seen = np.zeros(nodes.shape[0], np.int32)
+    slots = np.zeros(n, np.int32)
+    depth_max, stack = 0, [(0, 1)]
+    while stack:
+        i, d = stack.pop()
+        seen[i] += 1
+        depth_max = max(depth_max, d)
+        nd = nodes[i]
+        if nd["primitive_count"]:
+            slots[nd["first_child_or_primitive"]: nd["first_child_or_primitive"] + nd["primitive_count"]] += 1
+        else:
+            c = int(nd["first_child_or_primitive"])
+            stack += [(c, d + 1), (c + 1, d + 1)]
+    assert (seen == 1).all() and (slots == 1).all()
+    return depth_max
+
+
+@pytest.mark.parametrize("scene", ["bunny", "dragon"])
+def test_lbvh_is_valid_refit_exact_and_renders_like_the_oracle(cr, bunny_pod, dragon_pod, scene):
+    pod = dict(bunny_pod if scene == "bunny" else dragon_pod)
+    n = pod["triangles"].shape[0]
+    nodes, idx, ms = cr.build_lbvh(pod["triangles"])
+    depth = validate(nodes, idx, n)
+    assert depth <= 64, depth
+    pod["nodes"], pod["prim_indices"] = nodes, idx
+    assert np.array_equal(port.refit(pod).view(np.uint32), nodes.view(np.uint32))
+    cam = cr.configs.BUNNY_CAMERA if scene == "bunny" else cr.configs.DRAGON_CAMERA
+    with cr.Scene.from_pod(pod) as s:
+        check_frame(cr, s, pod, cam, SUN, 960, 540, 0)
+        check_frame(cr, s, pod, cam, SUN, 640, 360, cr.NO_SHADOWS)
+
+
+def test_lbvh_edge_cases(cr):
+    # one triangle: the root is the leaf; two identical triangles: equal Morton codes, split by position
+    tri = port.make_triangles(np.array([[-1, -1, 5, 1, -1, 5, 0, 1, 5]], np.float32)).reshape(1, 12)
+    nodes, idx, _ = cr.build_lbvh(tri)
+    assert nodes.shape[0] == 1 and nodes[0]["primitive_count"] == 1 and idx.tolist() == [0]
+    two = np.concatenate([tri, tri])
+    nodes, idx, _ = cr.build_lbvh(two)
+    validate(nodes, idx, 2)
+    many = np.concatenate([tri] * 37)             # 37 coincident triangles: the tree must still be a tree
+    nodes, idx, _ = cr.build_lbvh(many)
+    assert validate(nodes, idx, 37) <= 64
+    pod = {"nodes": nodes, "prim_indices": idx, "triangles": many, "norms": np.zeros((37, 9), np.float32)}
+    assert np.array_equal(port.refit(pod).view(np.uint32), nodes.view(np.uint32))
+    with pytest.raises(cr.CeresError):
+        cr.build_lbvh(np.zeros((0, 12), np.float32))
