@@ -453,6 +453,11 @@ def main():
     peak, peak_src = measured_peak()
     achieved = abytes[dominant] / (kavg[dominant] * 1e-3) / 1e9 if kavg[dominant] > 0 else 0.0
     whole = sum(abytes.values()) / (kavg["total"] * 1e-3) / 1e9 if kavg["total"] > 0 else 0.0
+    # second denominator: read bandwidth of an L2-resident working set, measured on this GPU
+    try:
+        l2_peak = cr.probe_read_bandwidth(48 << 20, repeats=20, device=local)
+    except Exception:
+        l2_peak = None
     ncu_traffic = None
     tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")     # dram bytes per launch from the committed ncu --set full capture
     if os.path.exists(tp) and args.workload == WORKLOAD:
@@ -544,6 +549,8 @@ def main():
             "roofline": {"bound": "hbm", "kernel": dominant + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": ncu_traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": abytes[dominant],
+                         "l2": {"peak": l2_peak, "frac": (achieved / l2_peak) if l2_peak else None, "unit": "GB/s",
+                                "peak_source": "measured here: ceres_probe_read_bandwidth, 48 MiB working set, 128-bit __ldg reads"},
                          "whole_frame": {"achieved": whole, "frac": whole / peak, "bytes": sum(abytes.values())},
                          "work": {k: st[k] for k in ("S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "hits_primary", "occluded")},
                          "note": ("scene (3 MB) is L1/L2-resident: the HBM peak is the conservative denominator SURVEY.md 8(d) asks for"

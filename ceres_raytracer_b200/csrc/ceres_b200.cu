@@ -1042,6 +1042,55 @@ int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes
     return CERES_OK;
 }
 
+// ---- read-bandwidth probe ("a measured L2 peak ... with an L2-resident 128-bit __ldg read kernel") ------
+__global__ void __launch_bounds__(256) read_probe_kernel(const float4* __restrict__ buf, size_t n4, int repeats, float* sink) {
+    float acc = 0.0f;
+    const size_t stride = (size_t)gridDim.x * 256u;
+    for (int r = 0; r < repeats; ++r)
+        // every repeat a CTA reads the segments another CTA (on another SM) read before: hits in L2, not in its own L1
+        for (size_t k = (size_t)((blockIdx.x + 37u * (unsigned)r) % gridDim.x) * 256u + threadIdx.x; k < n4; k += stride) {
+            const float4 v = __ldg(buf + k);
+            acc += v.x + v.y + v.z + v.w;
+        }
+    if (acc == 123.456f) *sink = acc;        // never true: keeps the loads alive
+}
+
+int ceres_probe_read_bandwidth(int device, size_t working_set_bytes, int repeats, double* gb_per_s) {
+    if (!gb_per_s || working_set_bytes < 4096 || repeats < 1) return fail(CERES_ERR_INVALID, "ceres_probe_read_bandwidth: bad argument");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) return fail(CERES_ERR_NO_DEVICE, "no CUDA device");
+    if (device < 0 || device >= ndev) return fail(CERES_ERR_INVALID, "bad device index");
+    DeviceGuard guard(device);
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    const size_t n4 = working_set_bytes / 16;
+    float4* buf = nullptr; float* sink = nullptr; cudaEvent_t e0 = nullptr, e1 = nullptr;
+    auto cleanup = [&]() { cudaFree(buf); cudaFree(sink); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); };
+#define TRY_P(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); cleanup(); return CERES_ERR_CUDA; } } while (0)
+    TRY_P(cudaMalloc((void**)&buf, n4 * 16));
+    TRY_P(cudaMalloc((void**)&sink, 4));
+    TRY_P(cudaMemset(buf, 0, n4 * 16));
+    TRY_P(cudaEventCreate(&e0)); TRY_P(cudaEventCreate(&e1));
+    const unsigned grid = (unsigned)prop.multiProcessorCount * 8u;
+    read_probe_kernel<<<grid, 256>>>(buf, n4, 2, sink);                  // warm the caches
+    double best = 0.0;
+    for (int t = 0; t < 5; ++t) {
+        TRY_P(cudaEventRecord(e0, 0));
+        read_probe_kernel<<<grid, 256>>>(buf, n4, repeats, sink);
+        TRY_P(cudaEventRecord(e1, 0));
+        TRY_P(cudaEventSynchronize(e1));
+        float ms = 0.0f;
+        TRY_P(cudaEventElapsedTime(&ms, e0, e1));
+        if (ms > 0.0f) best = std::max(best, (double)n4 * 16.0 * repeats / (ms * 1e-3) / 1e9);
+    }
+    g_launches += 6;
+#undef TRY_P
+    *gb_per_s = best;
+    cleanup();
+    return CERES_OK;
+}
+
 int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");
     if (t) s->tune = *t; else s->tune = ceres_tuning{};

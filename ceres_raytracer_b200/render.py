@@ -78,6 +78,13 @@ def frame_setup(camera, width, height):
     return out[0:3].copy(), out[3:6].copy(), out[6:9].copy()
 
 
+def probe_read_bandwidth(working_set_bytes, repeats=20, device=0):
+    """GB/s of the library's 128-bit read kernel over a working set of this size (ceres_probe_read_bandwidth)."""
+    out = C.c_double(0.0)
+    _capi.check(_capi.lib().ceres_probe_read_bandwidth(int(device), int(working_set_bytes), int(repeats), C.byref(out)))
+    return float(out.value)
+
+
 def build_lbvh(triangles, device=0):
     """GPU linear-BVH build (ceres_build_lbvh): returns (nodes NODE_DT[2n-1], prim_indices uint64[n], build_ms) in the
     reference's layout for `triangles` float32[n, 12]."""

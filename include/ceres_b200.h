@@ -238,6 +238,11 @@ int ceres_host_register(void* p, size_t bytes);   /* cudaHostRegister; caller un
 int ceres_host_unregister(void* p);
 int ceres_host_is_pinned(const void* p);
 
+/* Read bandwidth of this GPU for a working set of the given size, measured with the library's own 128-bit __ldg
+ * read kernel (best of 5): a few MB per SM-resident set -> L1, 16-64 MB -> L2, >= 1 GB -> HBM.  bench.py reports
+ * the cache-resident scene's traffic against the L2 figure next to the HBM roofline. */
+int ceres_probe_read_bandwidth(int device, size_t working_set_bytes, int repeats, double* gb_per_s);
+
 /* ---- misc --------------------------------------------------------------------------------------------------- */
 int ceres_abi_version(void);
 int ceres_device_count(void);
