@@ -36,6 +36,15 @@ inline bool write_ppm(const std::string& path, const float* pixels, size_t width
     return std::fclose(f) == 0 && ok;
 }
 
+// P6 payload that is already quantised and flipped (ceres_render_ppm8)
+inline bool write_ppm_bytes(const std::string& path, const uint8_t* bytes, size_t width, size_t height) {
+    std::FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) return false;
+    std::fprintf(f, "P6 %zu %zu 255\n", width, height);
+    const bool ok = std::fwrite(bytes, 1, 3 * width * height, f) == 3 * width * height;
+    return std::fclose(f) == 0 && ok;
+}
+
 inline bool write_ppm16(const std::string& path, const float* pixels, size_t width, size_t height) {
     std::vector<uint8_t> bytes(6 * width * height);
     #pragma omp parallel for

@@ -15,6 +15,7 @@
 // Additive flags: --dir x y z  --up x y z  --fov deg  --sun x y z  --width W  --height H  -o file.ppm
 //   --no-shadow (primary rays only, BASELINE configs 1-2)  --builder binned|sweep  --gpus N (interleaved 16-row blocks,
 //   one host thread per GPU)  --dump-ids file.u32  --dump-rgb file.f32  --frames K (repeat the render call K times)
+//   --ppm8 (quantise + flip on the GPU and copy the 8-bit image: static.cpp:135-147 done on the device, 1 GPU)
 #include <algorithm>
 #include <chrono>
 #include <cstdint>
@@ -46,6 +47,7 @@ namespace {
 
 struct Options {
     std::string input = "../../data/dragon.obj", output = "render.ppm", dump_ids, dump_rgb, builder = "binned";
+    bool ppm8 = false;
     Camera<Scalar> camera{Vector3(0.0, -15.0, 2.0), Vector3(0, 1, 0), Vector3(0, 0, 1), 60};
     Vector3 sun = Vector3(-50.0, -20.0, 0.0);
     int rotation_axis = 0;
@@ -59,7 +61,7 @@ struct Options {
     std::cerr << "render: " << msg << "\n"
               << "usage: render [file.obj] [--eye x y z] [--rotate x|y|z deg] [--dir x y z] [--up x y z] [--fov deg]\n"
               << "              [--sun x y z] [--width W] [--height H] [-o out.ppm] [--no-shadow] [--builder binned|sweep]\n"
-              << "              [--gpus N] [--dump-ids f.u32] [--dump-rgb f.f32] [--frames K]\n";
+              << "              [--gpus N] [--dump-ids f.u32] [--dump-rgb f.f32] [--frames K] [--ppm8]\n";
     std::exit(2);
 }
 
@@ -90,6 +92,7 @@ Options parse(int argc, char** argv) {
         else if (a == "--builder") { need(i, 1); o.builder = argv[++i]; }
         else if (a == "--gpus") { need(i, 1); o.gpus = std::atoi(argv[++i]); }
         else if (a == "--frames") { need(i, 1); o.frames = std::atoi(argv[++i]); }
+        else if (a == "--ppm8") o.ppm8 = true;
         else if (a == "--dump-ids") { need(i, 1); o.dump_ids = argv[++i]; }
         else if (a == "--dump-rgb") { need(i, 1); o.dump_rgb = argv[++i]; }
         else if (!a.empty() && a[0] != '-' && !have_input) { o.input = a; have_input = true; }
@@ -161,8 +164,32 @@ int main(int argc, char** argv) {
 
     std::pair<int, int> counters(0, 0);
     double render_s = 0;
+    std::vector<uint8_t> rgb8;            // --ppm8: the P6 payload comes from the device
     try {
-        if (opt.gpus == 1 && opt.shadows && ids.empty()) {
+        if (opt.ppm8) {
+            if (opt.gpus != 1 || !ids.empty() || !opt.dump_rgb.empty()) throw std::runtime_error("--ppm8 renders on one GPU and produces only the PPM");
+            ceres_scene* scene = nullptr;
+            if (ceres_scene_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
+                                   tri_norms.data(), reference_count, 0, &scene) != CERES_OK) throw std::runtime_error(ceres_last_error());
+            uint8_t* host8 = static_cast<uint8_t*>(ceres_host_alloc(3 * npix));
+            if (!host8) { ceres_scene_destroy(scene); throw std::runtime_error(ceres_last_error()); }
+            ceres_camera cam;
+            for (int k = 0; k < 3; ++k) { cam.eye[k] = opt.camera.eye[k]; cam.dir[k] = opt.camera.dir[k]; cam.up[k] = opt.camera.up[k]; }
+            cam.fov = opt.camera.fov;
+            const float sun[3] = {opt.sun[0], opt.sun[1], opt.sun[2]};
+            uint64_t cnt[2] = {0, 0};
+            int rc = CERES_OK;
+            for (int f = -1; f < opt.frames && rc == CERES_OK; ++f) {      // f = -1: warm-up
+                auto t1 = std::chrono::high_resolution_clock::now();
+                rc = ceres_render_ppm8(scene, &cam, sun, opt.width, opt.height, opt.shadows ? 0u : CERES_NO_SHADOWS, host8, cnt);
+                if (f >= 0) render_s += seconds_since(t1) / opt.frames;
+            }
+            if (rc == CERES_OK) rgb8.assign(host8, host8 + 3 * npix);
+            ceres_host_free(host8);
+            ceres_scene_destroy(scene);
+            if (rc != CERES_OK) throw std::runtime_error(ceres_last_error());
+            counters = std::pair<int, int>((int)cnt[0], (int)cnt[1]);
+        } else if (opt.gpus == 1 && opt.shadows && ids.empty()) {
             // the reference call, unchanged (static.cpp:130 / anim.cpp:105)
             render(opt.camera, opt.sun, bvh, triangles.data(), tri_norms.data(), pixels, opt.width, opt.height);   // upload + warm-up
             auto t1 = std::chrono::high_resolution_clock::now();
@@ -200,7 +227,8 @@ int main(int argc, char** argv) {
     std::cout << "Rays: " << counters.first << "\tHits: " << counters.second << "\t" << counters.first / render_s / 1e6
               << " Mrays/s" << std::endl;
 
-    if (!ceres_apps::write_ppm(opt.output, pixels, opt.width, opt.height)) {
+    if (opt.ppm8 ? !ceres_apps::write_ppm_bytes(opt.output, rgb8.data(), opt.width, opt.height)
+                 : !ceres_apps::write_ppm(opt.output, pixels, opt.width, opt.height)) {
         std::cerr << "render: cannot write " << opt.output << std::endl;
         return 1;
     }

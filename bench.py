@@ -483,6 +483,21 @@ def main():
             _, _, cnt_e2e = scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)
             t_e2e += time.perf_counter() - t0
         assert cnt_e2e == (rays_frame, hits_frame)
+        # the same frame as 8-bit P6 payload (static.cpp:135-147 on the device; N1): a quarter of the PCIe bytes
+        hb8 = cr.PinnedBuffer((H, W, 3), np.uint8)
+        for _ in range(2):
+            scene.render_ppm8(cam, sun, W, H, flags=flags, out=hb8.array)
+        t_ppm8 = 0.0
+        for _ in range(steps_e2e):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            scene.render_ppm8(cam, sun, W, H, flags=flags, out=hb8.array)
+            t_ppm8 += time.perf_counter() - t0
+        ppm8 = {"value": rays_frame / (t_ppm8 / steps_e2e) / 1e6, "unit": UNIT, "ms_per_step": 1e3 * t_ppm8 / steps_e2e,
+                "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm8() -> page-locked 8-bit P6 payload"}
+        hb8.close()
+        scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)      # last_d2h_bytes of the float path again
         d2h = scene.last_d2h_bytes        # the screen rectangle of the scene + counters; the rest of the frame is host-filled zeros
     else:
         # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
@@ -503,6 +518,8 @@ def main():
         t = torch.tensor([scene.last_d2h_bytes], dtype=torch.int64, device=dev)
         dist.all_reduce(t)
         d2h = int(t.item())
+    if world != 1:
+        ppm8 = None
     ms_e2e = allmax(1e3 * t_e2e / steps_e2e)
 
     # ---- CPU baseline: the reference's own render() on this box's host cores (rank 0, N = 1 only) ------------------
@@ -560,6 +577,8 @@ def main():
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
+        if ppm8 is not None:
+            line["e2e_ppm8"] = ppm8
         if verified is not None:
             line["verified"] = verified
         if args.workload != WORKLOAD:

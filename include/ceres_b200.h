@@ -131,6 +131,12 @@ int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes
 int ceres_render(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                  size_t width, size_t height, unsigned flags, float* pixels, uint32_t* ids, uint64_t counters[2]);
 
+/* The same frame as the payload of the reference's P6 file (static.cpp:135-147): quantised on the device
+ * (uint8(max(min(p*255,255),0)), rows flipped: row 0 = frame row height-1) and only the 8-bit screen rectangle of the
+ * scene copied -- a quarter of the float path's PCIe bytes.  rgb8: HOST 3*width*height bytes. */
+int ceres_render_ppm8(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
+                      size_t width, size_t height, unsigned flags, uint8_t* rgb8, uint64_t counters[2]);
+
 /* Same, one shard of the frame.  Without CERES_COMPACT_ROWS only the shard's rows of pixels/ids are written. */
 int ceres_render_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                        size_t width, size_t height, unsigned flags, const ceres_shard* shard,

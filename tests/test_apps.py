@@ -113,6 +113,23 @@ def test_render_binary_matches_reference(tmp_path, builder, bcode, extra):
 
 @pytest.mark.gpu
 @needs_binaries
+def test_render_binary_ppm8_writes_the_same_file(tmp_path):
+    """--ppm8 (quantise + flip on the device, 8-bit rectangle DMA) and the default float path write identical PPMs."""
+    obj = str(tmp_path / "torus.obj")
+    write_torus_obj(obj)
+    outs = []
+    for k, extra in enumerate(([], ["--ppm8"])):
+        out = str(tmp_path / f"render{k}.ppm")
+        cmd = [RENDER, obj, "--eye", "0.3", "1.2", "-3.0", "--dir", "-0.1", "-0.35", "1", "--rotate", "y", "-145", "--sun", "-50", "60", "-20",
+               "--width", "640", "--height", "360", "-o", out, "--builder", "sweep"] + extra
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        outs.append((open(out, "rb").read(), [l for l in r.stdout.splitlines() if l.startswith("Rays:")][0].split("\t")[:2]))
+    assert outs[0][0] == outs[1][0] and outs[0][1] == outs[1][1]
+
+
+@pytest.mark.gpu
+@needs_binaries
 def test_anim_binary_matches_reference_turntable(tmp_path):
     obj = str(tmp_path / "torus.obj")
     write_torus_obj(obj, 64, 32)

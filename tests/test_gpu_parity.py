@@ -318,3 +318,18 @@ def test_band_pipelined_host_render_is_identical(cr, dragon, band_bytes):
             assert np.array_equal(hb.array.view(np.uint32), ref_px.view(np.uint32)) and tuple(tot) == ref_cnt
         finally:
             dragon.set_tuning()
+
+
+@pytest.mark.parametrize("W,H", [(1280, 720), (333, 217)])
+def test_ppm8_host_path_equals_quantised_float_frame(cr, dragon, bunny, W, H):
+    """ceres_render_ppm8 (device quantise + flip, rectangle-only DMA, host zero fill) against the float frame pushed
+    through the reference's PPM arithmetic (static.cpp:135-147) on the host: byte-identical."""
+    for scene, cam in ((dragon, cr.configs.DRAGON_CAMERA), (bunny, cr.configs.BUNNY_CAMERA)):
+        px, _, cnt = scene.render(cam, SUN, W, H)
+        want = cr.write_ppm(os.devnull, px)
+        with cr.PinnedBuffer((H, W, 3), np.uint8) as hb:
+            hb.array[:] = 0xAB
+            got, cnt8 = scene.render_ppm8(cam, SUN, W, H, out=hb.array)
+            assert np.array_equal(got, want) and cnt8 == cnt
+        got2, _ = scene.render_ppm8(cam, SUN, W, H)               # pageable destination
+        assert np.array_equal(got2, want)
