@@ -101,8 +101,12 @@ __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const
     if (goL || goR) {
         const bool right_first = goR && (!goL || le > re);       // ties keep the left child first (:111-112)
         if (goL && goR) {
-            stack[r.sp] = right_first ? fL : fR;
+            const uint32_t far_pair = right_first ? fL : fR;
+            stack[r.sp] = far_pair;
             r.sp += STRIDE;
+#ifdef CERES_PREFETCH_PUSH
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pairs + 4ull * far_pair));
+#endif
         }
         r.cur = right_first ? fR : fL;
         return true;
