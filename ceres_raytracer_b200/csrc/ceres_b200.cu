@@ -736,6 +736,36 @@ int ceres_frame_setup(const ceres_camera* camera, size_t width, size_t height, f
     return CERES_OK;
 }
 
+// A scene object with its streams, events and per-frame counters, and no geometry yet.
+static int scene_new(int device, int sm_count, ceres_scene** out) {
+    ceres_scene* s = new (std::nothrow) ceres_scene;
+    if (!s) return fail(CERES_ERR_INVALID, "out of host memory");
+    s->device = device;
+    s->sm_count = sm_count;
+    auto bail = [&](int code) { ceres_scene_destroy(s); return code; };
+#define TRY_S(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); return bail(CERES_ERR_CUDA); } } while (0)
+    TRY_S(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    TRY_S(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < CERES_MAX_BANDS; ++k) TRY_S(cudaEventCreateWithFlags(&s->band_done[k], cudaEventDisableTiming));
+    // earlier bands get higher priority: they finish (and start their copy) first, later bands fill their tails
+    int prio_lo = 0, prio_hi = 0;
+    TRY_S(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));       // lo = numerically largest = least urgent
+    for (int k = 0; k < CERES_MAX_SUB; ++k) {
+        const int prio = std::min(prio_lo, prio_hi + k);
+        TRY_S(cudaStreamCreateWithPriority(&s->sub_stream[k], cudaStreamNonBlocking, prio));
+        TRY_S(cudaEventCreateWithFlags(&s->sub_done[k], cudaEventDisableTiming));
+    }
+    TRY_S(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
+    TRY_S(cudaMalloc((void**)&s->d_ctr, CERES_MAX_SUB * sizeof(FrameCounters)));
+    TRY_S(cudaMalloc((void**)&s->d_out, 10 * sizeof(unsigned long long)));
+    TRY_S(cudaMallocHost((void**)&s->h_out, 10 * sizeof(unsigned long long)));
+    TRY_S(cudaMemset(s->d_ctr, 0, CERES_MAX_SUB * sizeof(FrameCounters)));
+    TRY_S(cudaMemset(s->d_out, 0, 10 * sizeof(unsigned long long)));
+#undef TRY_S
+    *out = s;
+    return CERES_OK;
+}
+
 int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* prim_idx, const void* tris_v,
                        const void* norms_v, size_t tri_count, int device, ceres_scene** out) {
     if (!out) return fail(CERES_ERR_INVALID, "ceres_scene_create: out is null");
@@ -820,40 +850,21 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) return fail(CERES_ERR_NO_DEVICE, std::string("device is not Blackwell-class (sm_100a required): ") + prop.name);
 
-    ceres_scene* s = new (std::nothrow) ceres_scene;
-    if (!s) return fail(CERES_ERR_INVALID, "out of host memory");
-    s->device = device;
-    s->sm_count = prop.multiProcessorCount;
+    ceres_scene* s = nullptr;
+    if (int rc = scene_new(device, prop.multiProcessorCount, &s)) return rc;
     s->tri_count = (uint32_t)tri_count;
     for (int b = 0; b < 6; ++b) s->bounds[b] = root.bounds[b];
     auto bail = [&](int code) { ceres_scene_destroy(s); return code; };
 #define TRY_S(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); return bail(CERES_ERR_CUDA); } } while (0)
-    TRY_S(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    TRY_S(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
-    for (int k = 0; k < CERES_MAX_BANDS; ++k) TRY_S(cudaEventCreateWithFlags(&s->band_done[k], cudaEventDisableTiming));
-    // earlier bands get higher priority: they finish (and start their copy) first, later bands fill their tails
-    int prio_lo = 0, prio_hi = 0;
-    TRY_S(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));       // lo = numerically largest = least urgent
-    for (int k = 0; k < CERES_MAX_SUB; ++k) {
-        const int prio = std::min(prio_lo, prio_hi + k);
-        TRY_S(cudaStreamCreateWithPriority(&s->sub_stream[k], cudaStreamNonBlocking, prio));
-        TRY_S(cudaEventCreateWithFlags(&s->sub_done[k], cudaEventDisableTiming));
-    }
-    TRY_S(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
     const size_t pb = pairs.size() * 4, tb = tri_slots.size() * 4, nb = norm_slots.size() * 4, ib = slot_id.size() * 4;
     TRY_S(cudaMalloc(&s->d_pairs, pb));
     TRY_S(cudaMalloc(&s->d_tris, tb));
     TRY_S(cudaMalloc(&s->d_norms, nb));
     TRY_S(cudaMalloc(&s->d_slot_id, ib));
-    TRY_S(cudaMalloc((void**)&s->d_ctr, CERES_MAX_SUB * sizeof(FrameCounters)));
-    TRY_S(cudaMalloc((void**)&s->d_out, 10 * sizeof(unsigned long long)));
-    TRY_S(cudaMallocHost((void**)&s->h_out, 10 * sizeof(unsigned long long)));
     TRY_S(cudaMemcpy(s->d_pairs, pairs.data(), pb, cudaMemcpyHostToDevice));
     TRY_S(cudaMemcpy(s->d_tris, tri_slots.data(), tb, cudaMemcpyHostToDevice));
     TRY_S(cudaMemcpy(s->d_norms, norm_slots.data(), nb, cudaMemcpyHostToDevice));
     TRY_S(cudaMemcpy(s->d_slot_id, slot_id.data(), ib, cudaMemcpyHostToDevice));
-    TRY_S(cudaMemset(s->d_ctr, 0, CERES_MAX_SUB * sizeof(FrameCounters)));
-    TRY_S(cudaMemset(s->d_out, 0, 10 * sizeof(unsigned long long)));
 #undef TRY_S
     s->scene_bytes = pb + tb + nb + ib;
     s->dev.pairs = (const float4*)s->d_pairs;
@@ -991,76 +1002,208 @@ int ceres_scene_download(ceres_scene* s, void* nodes_out, size_t node_count, voi
 }
 
 // ---- BVH construction on the GPU (lbvh_build.cuh) -----------------------------------------------------
-int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms) {
-    if (!tris || !tri_count || !nodes_out || !prim_idx_out) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: null or empty argument");
-    if (tri_count >= 0x40000000ull) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: too many triangles");
+namespace {
+// Working set of one GPU build (lbvh_build.cuh); everything stays on the device until the caller picks what it needs.
+struct LbvhWork {
+    float* box = nullptr; unsigned int* scene = nullptr;
+    uint32_t *code = nullptr, *idx = nullptr, *code2 = nullptr, *idx2 = nullptr, *child = nullptr, *pi = nullptr, *pl = nullptr, *arr = nullptr;
+    LbvhNode* nodes = nullptr; void* tmp = nullptr; size_t tmp_bytes = 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    ~LbvhWork() {
+        cudaFree(box); cudaFree(scene); cudaFree(code); cudaFree(idx); cudaFree(code2); cudaFree(idx2);
+        cudaFree(child); cudaFree(pi); cudaFree(pl); cudaFree(arr); cudaFree(nodes); cudaFree(tmp);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+    }
+};
+
+// Builds the tree of the n triangles at d_tris (legacy stream); w.nodes / w.idx2 hold the reference layout afterwards.
+int lbvh_run(const float4* d_tris, int n, LbvhWork& w, float* ms_out) {
+    const size_t tc = (size_t)n;
+#define TRY_B(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); } while (0)
+    TRY_B(cudaMalloc((void**)&w.box, tc * 24));
+    TRY_B(cudaMalloc((void**)&w.scene, 6 * sizeof(unsigned int)));
+    TRY_B(cudaMalloc((void**)&w.code, tc * 4)); TRY_B(cudaMalloc((void**)&w.idx, tc * 4));
+    TRY_B(cudaMalloc((void**)&w.code2, tc * 4)); TRY_B(cudaMalloc((void**)&w.idx2, tc * 4));
+    TRY_B(cudaMalloc((void**)&w.child, 2 * tc * 4)); TRY_B(cudaMalloc((void**)&w.pi, tc * 4));
+    TRY_B(cudaMalloc((void**)&w.pl, tc * 4)); TRY_B(cudaMalloc((void**)&w.arr, tc * 4));
+    TRY_B(cudaMalloc((void**)&w.nodes, (2 * tc - 1) * sizeof(LbvhNode)));
+    TRY_B(cub::DeviceRadixSort::SortPairs(nullptr, w.tmp_bytes, w.code, w.code2, w.idx, w.idx2, n, 0, 30));
+    TRY_B(cudaMalloc(&w.tmp, w.tmp_bytes ? w.tmp_bytes : 16));
+    TRY_B(cudaEventCreate(&w.e0)); TRY_B(cudaEventCreate(&w.e1));
+    const unsigned int scene_init[6] = {0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u};
+    TRY_B(cudaMemcpy(w.scene, scene_init, sizeof scene_init, cudaMemcpyHostToDevice));
+    TRY_B(cudaEventRecord(w.e0, 0));
+    const unsigned grid = (unsigned)((tc + 255) / 256);
+    lbvh_boxes_kernel<<<grid, 256>>>(d_tris, (uint32_t)n, w.box, w.scene);
+    lbvh_codes_kernel<<<grid, 256>>>(w.box, (uint32_t)n, w.scene, w.code, w.idx);
+    TRY_B(cub::DeviceRadixSort::SortPairs(w.tmp, w.tmp_bytes, w.code, w.code2, w.idx, w.idx2, n, 0, 30));
+    g_launches += 2;
+    if (n > 1) {
+        TRY_B(cudaMemsetAsync(w.arr, 0, tc * 4, 0));
+        lbvh_tree_kernel<<<grid, 256>>>(w.code2, n, w.child, w.pi, w.pl);
+        lbvh_emit_kernel<<<grid, 256>>>(w.child, w.idx2, w.box, n, w.nodes);
+        lbvh_fit_kernel<<<grid, 256>>>(w.pi, w.pl, w.arr, n, w.nodes);
+        g_launches += 3;
+    }
+    TRY_B(cudaEventRecord(w.e1, 0));
+    TRY_B(cudaGetLastError());
+    TRY_B(cudaEventSynchronize(w.e1));
+    float ms = 0.0f;
+    TRY_B(cudaEventElapsedTime(&ms, w.e0, w.e1));
+    if (ms_out) *ms_out = ms;
+#undef TRY_B
+    return CERES_OK;
+}
+
+int lbvh_check_args(const void* tris, size_t tri_count, int device, const char* who) {
+    if (!tris || !tri_count) return fail(CERES_ERR_INVALID, std::string(who) + ": null or empty argument");
+    if (tri_count >= 0x40000000ull) return fail(CERES_ERR_INVALID, std::string(who) + ": too many triangles");
     int ndev = 0;
     CUDA_TRY(cudaGetDeviceCount(&ndev));
     if (ndev <= 0) return fail(CERES_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)");
-    if (device < 0 || device >= ndev) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: bad device index");
+    if (device < 0 || device >= ndev) return fail(CERES_ERR_INVALID, std::string(who) + ": bad device index");
+    return CERES_OK;
+}
+}  // namespace
+
+int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms) {
+    if (!nodes_out || !prim_idx_out) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: null or empty argument");
+    if (int rc = lbvh_check_args(tris, tri_count, device, "ceres_build_lbvh")) return rc;
     DeviceGuard guard(device);
     const int n = (int)tri_count;
-    const size_t n_nodes = 2 * tri_count - 1;
-    float4* d_tris = nullptr; float* d_box = nullptr; unsigned int* d_scene = nullptr;
-    uint32_t *d_code = nullptr, *d_idx = nullptr, *d_code2 = nullptr, *d_idx2 = nullptr, *d_child = nullptr, *d_pi = nullptr, *d_pl = nullptr, *d_arr = nullptr;
-    LbvhNode* d_nodes = nullptr; void* d_tmp = nullptr; size_t tmp_bytes = 0;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    auto cleanup = [&]() {
-        cudaFree(d_tris); cudaFree(d_box); cudaFree(d_scene); cudaFree(d_code); cudaFree(d_idx); cudaFree(d_code2); cudaFree(d_idx2);
-        cudaFree(d_child); cudaFree(d_pi); cudaFree(d_pl); cudaFree(d_arr); cudaFree(d_nodes); cudaFree(d_tmp);
-        if (e0) cudaEventDestroy(e0);
-        if (e1) cudaEventDestroy(e1);
-    };
-#define TRY_B(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); cleanup(); return CERES_ERR_CUDA; } } while (0)
-    TRY_B(cudaMalloc((void**)&d_tris, tri_count * 48));
-    TRY_B(cudaMalloc((void**)&d_box, tri_count * 24));
-    TRY_B(cudaMalloc((void**)&d_scene, 6 * sizeof(unsigned int)));
-    TRY_B(cudaMalloc((void**)&d_code, tri_count * 4)); TRY_B(cudaMalloc((void**)&d_idx, tri_count * 4));
-    TRY_B(cudaMalloc((void**)&d_code2, tri_count * 4)); TRY_B(cudaMalloc((void**)&d_idx2, tri_count * 4));
-    TRY_B(cudaMalloc((void**)&d_child, 2 * tri_count * 4)); TRY_B(cudaMalloc((void**)&d_pi, tri_count * 4));
-    TRY_B(cudaMalloc((void**)&d_pl, tri_count * 4)); TRY_B(cudaMalloc((void**)&d_arr, tri_count * 4));
-    TRY_B(cudaMalloc((void**)&d_nodes, n_nodes * sizeof(LbvhNode)));
-    TRY_B(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_code, d_code2, d_idx, d_idx2, n, 0, 30));
-    TRY_B(cudaMalloc(&d_tmp, tmp_bytes ? tmp_bytes : 16));
-    TRY_B(cudaMemcpy(d_tris, tris, tri_count * 48, cudaMemcpyHostToDevice));
-    TRY_B(cudaEventCreate(&e0)); TRY_B(cudaEventCreate(&e1));
-    const unsigned int scene_init[6] = {0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u};
-    TRY_B(cudaMemcpy(d_scene, scene_init, sizeof scene_init, cudaMemcpyHostToDevice));
-    TRY_B(cudaEventRecord(e0, 0));
-    const unsigned grid = (unsigned)((tri_count + 255) / 256);
-    lbvh_boxes_kernel<<<grid, 256>>>(d_tris, (uint32_t)n, d_box, d_scene);
-    lbvh_codes_kernel<<<grid, 256>>>(d_box, (uint32_t)n, d_scene, d_code, d_idx);
-    TRY_B(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_code, d_code2, d_idx, d_idx2, n, 0, 30));
-    g_launches += 2;
-    if (n == 1) {
+    float4* d_tris = nullptr;
+    LbvhWork w;
+    float ms = 0.0f;
+    int rc = CERES_OK;
+    if (cudaMalloc((void**)&d_tris, tri_count * 48) != cudaSuccess || cudaMemcpy(d_tris, tris, tri_count * 48, cudaMemcpyHostToDevice) != cudaSuccess)
+        rc = fail(CERES_ERR_CUDA, std::string("ceres_build_lbvh: triangle upload: ") + cudaGetErrorString(cudaGetLastError()));
+    if (!rc) rc = lbvh_run(d_tris, n, w, &ms);
+    if (!rc && n == 1) {
         LbvhNode root;
-        TRY_B(cudaMemcpy(root.bounds, d_box, 24, cudaMemcpyDeviceToHost));
+        if (cudaMemcpy(root.bounds, w.box, 24, cudaMemcpyDeviceToHost) != cudaSuccess) rc = fail(CERES_ERR_CUDA, "ceres_build_lbvh: download");
         root.primitive_count = 1; root.first_child_or_primitive = 0;
         std::memcpy(nodes_out, &root, sizeof root);
         prim_idx_out[0] = 0;
-        if (build_ms) *build_ms = 0.0;
-        cleanup();
-        return CERES_OK;
-    }
-    TRY_B(cudaMemsetAsync(d_arr, 0, tri_count * 4, 0));
-    lbvh_tree_kernel<<<grid, 256>>>(d_code2, n, d_child, d_pi, d_pl);
-    lbvh_emit_kernel<<<grid, 256>>>(d_child, d_idx2, d_box, n, d_nodes);
-    lbvh_fit_kernel<<<grid, 256>>>(d_pi, d_pl, d_arr, n, d_nodes);
-    g_launches += 3;
-    TRY_B(cudaEventRecord(e1, 0));
-    TRY_B(cudaGetLastError());
-    TRY_B(cudaEventSynchronize(e1));
-    float ms = 0.0f;
-    TRY_B(cudaEventElapsedTime(&ms, e0, e1));
-    if (build_ms) *build_ms = ms;
-    TRY_B(cudaMemcpy(nodes_out, d_nodes, n_nodes * sizeof(LbvhNode), cudaMemcpyDeviceToHost));
-    {
+        ms = 0.0f;
+    } else if (!rc) {
         std::vector<uint32_t> idx(tri_count);
-        TRY_B(cudaMemcpy(idx.data(), d_idx2, tri_count * 4, cudaMemcpyDeviceToHost));
+        if (cudaMemcpy(nodes_out, w.nodes, (2 * tri_count - 1) * sizeof(LbvhNode), cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(idx.data(), w.idx2, tri_count * 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+            rc = fail(CERES_ERR_CUDA, std::string("ceres_build_lbvh: download: ") + cudaGetErrorString(cudaGetLastError()));
         for (size_t k = 0; k < tri_count; ++k) prim_idx_out[k] = idx[k];
     }
-#undef TRY_B
-    cleanup();
+    if (build_ms) *build_ms = ms;
+    cudaFree(d_tris);
+    return rc;
+}
+
+// ---- a scene straight from the GPU build: the tree never visits the host ------------------------------------------------
+// pair i = the two children of radix-tree inner node i (reference nodes 1 + 2 i, 2 + 2 i); an inner child's
+// first_child_or_primitive 1 + 2 c becomes pair c.
+__global__ void __launch_bounds__(256) lbvh_pairs_kernel(const LbvhNode* __restrict__ nodes, int n, float4* __restrict__ pairs) {
+    const int i = (int)(blockIdx.x * 256u + threadIdx.x);
+    if (i >= n - 1) return;
+    for (int c = 0; c < 2; ++c) {
+        const LbvhNode nd = nodes[1 + 2 * i + c];
+        const uint32_t first = nd.primitive_count ? nd.first_child_or_primitive : (nd.first_child_or_primitive - 1u) >> 1;
+        pairs[4 * (size_t)i + 2 * c] = make_float4(nd.bounds[0], nd.bounds[1], nd.bounds[2], nd.bounds[3]);
+        pairs[4 * (size_t)i + 2 * c + 1] = make_float4(nd.bounds[4], nd.bounds[5], __uint_as_float(nd.primitive_count), __uint_as_float(first));
+    }
+}
+
+// slot k holds triangle idx[k] (48 B) and its vertex normals (9 floats on the host side, padded to 12 here)
+__global__ void __launch_bounds__(256) lbvh_slots_kernel(const float4* __restrict__ tris, const float* __restrict__ norms9,
+                                                         const uint32_t* __restrict__ idx, uint32_t n, float4* __restrict__ tri_slots,
+                                                         float4* __restrict__ norm_slots) {
+    const uint32_t k = blockIdx.x * 256u + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t t = idx[k];
+    for (int q = 0; q < 3; ++q) tri_slots[3ull * k + q] = tris[3ull * t + q];
+    float v[12];
+    for (int q = 0; q < 12; ++q) v[q] = (norms9 && q < 9) ? norms9[9ull * t + q] : 0.0f;
+    for (int q = 0; q < 3; ++q) norm_slots[3ull * k + q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+}
+
+// number of inner nodes above each leaf = the deepest traversal stack the tree can need
+__global__ void __launch_bounds__(256) lbvh_depth_kernel(const uint32_t* __restrict__ par_inner, const uint32_t* __restrict__ par_leaf,
+                                                         int n, unsigned int* depth_max) {
+    const int k = (int)(blockIdx.x * 256u + threadIdx.x);
+    unsigned int d = 0;
+    if (k < n) {
+        d = 1;
+        for (uint32_t p = par_leaf[k] >> 1; p != 0u; p = par_inner[p] >> 1) ++d;
+    }
+    for (int o = 16; o; o >>= 1) d = max(d, __shfl_xor_sync(0xFFFFFFFFu, d, o));
+    if ((threadIdx.x & 31u) == 0u && d) atomicMax(depth_max, d);
+}
+
+int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_count, int device, ceres_scene** out, double* build_ms) {
+    if (!out) return fail(CERES_ERR_INVALID, "ceres_scene_create_lbvh: out is null");
+    *out = nullptr;
+    if (int rc = lbvh_check_args(tris, tri_count, device, "ceres_scene_create_lbvh")) return rc;
+    if (tri_count == 1) {                       // a leaf root has no pair: take the general path
+        RefNode root; size_t idx0 = 0;
+        if (int rc = ceres_build_lbvh(tris, 1, device, &root, &idx0, build_ms)) return rc;
+        return ceres_scene_create(&root, 1, &idx0, tris, norms, 1, device, out);
+    }
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CERES_ERR_CUDA, "cudaSetDevice failed");
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(CERES_ERR_NO_DEVICE, std::string("device is not Blackwell-class (sm_100a required): ") + prop.name);
+    const int n = (int)tri_count;
+    ceres_scene* s = nullptr;
+    if (int rc = scene_new(device, prop.multiProcessorCount, &s)) return rc;
+    float4* d_src = nullptr; float* d_norms9 = nullptr; unsigned int* d_depth = nullptr;
+    auto bail = [&](int code) { cudaFree(d_src); cudaFree(d_norms9); cudaFree(d_depth); ceres_scene_destroy(s); return code; };
+#define TRY_S(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); return bail(CERES_ERR_CUDA); } } while (0)
+    TRY_S(cudaMalloc((void**)&d_src, tri_count * 48));
+    TRY_S(cudaMemcpy(d_src, tris, tri_count * 48, cudaMemcpyHostToDevice));
+    if (norms) {
+        TRY_S(cudaMalloc((void**)&d_norms9, tri_count * 36));
+        TRY_S(cudaMemcpy(d_norms9, norms, tri_count * 36, cudaMemcpyHostToDevice));
+    }
+    float ms = 0.0f;
+    {
+        LbvhWork w;
+        if (int rc = lbvh_run(d_src, n, w, &ms)) return bail(rc);
+        const size_t pb = (tri_count - 1) * 64, tb = tri_count * 48, ib = tri_count * 4;
+        TRY_S(cudaMalloc(&s->d_pairs, pb));
+        TRY_S(cudaMalloc(&s->d_tris, tb));
+        TRY_S(cudaMalloc(&s->d_norms, tb));
+        TRY_S(cudaMalloc((void**)&d_depth, sizeof(unsigned int)));
+        TRY_S(cudaMemset(d_depth, 0, sizeof(unsigned int)));
+        const unsigned grid = (unsigned)((tri_count + 255) / 256);
+        lbvh_pairs_kernel<<<grid, 256>>>(w.nodes, n, (float4*)s->d_pairs);
+        lbvh_slots_kernel<<<grid, 256>>>(d_src, d_norms9, w.idx2, (uint32_t)n, (float4*)s->d_tris, (float4*)s->d_norms);
+        lbvh_depth_kernel<<<grid, 256>>>(w.pi, w.pl, n, d_depth);
+        g_launches += 3;
+        TRY_S(cudaGetLastError());
+        unsigned int depth = 0;
+        TRY_S(cudaMemcpy(&depth, d_depth, sizeof depth, cudaMemcpyDeviceToHost));
+        TRY_S(cudaMemcpy(s->bounds, w.nodes[0].bounds, 24, cudaMemcpyDeviceToHost));
+        s->h_slot_id.resize(tri_count);
+        TRY_S(cudaMemcpy(s->h_slot_id.data(), w.idx2, ib, cudaMemcpyDeviceToHost));
+        s->d_slot_id = w.idx2; w.idx2 = nullptr;            // the sorted primitive indices ARE slot -> primitive
+        if (depth > 64) { fail(CERES_ERR_UNSUPPORTED, "ceres_scene_create_lbvh: tree deeper than the reference's 64-entry stack"); return bail(CERES_ERR_UNSUPPORTED); }
+        s->dev.stack_depth = depth;
+        s->scene_bytes = pb + 2 * tb + ib;
+    }
+#undef TRY_S
+    cudaFree(d_src); cudaFree(d_norms9); cudaFree(d_depth);
+    s->tri_count = (uint32_t)tri_count;
+    s->dev.pairs = (const float4*)s->d_pairs;
+    s->dev.tris = (const float4*)s->d_tris;
+    s->dev.norms = (const float4*)s->d_norms;
+    s->dev.slot_id = (const uint32_t*)s->d_slot_id;
+    s->dev.root_leaf_count = 0;
+    s->node_count = 2 * tri_count - 1;
+    s->n_pairs = (uint32_t)(tri_count - 1);
+    s->h_pair_first_child.resize(tri_count - 1);
+    for (size_t i = 0; i + 1 < tri_count; ++i) s->h_pair_first_child[i] = (uint32_t)(1 + 2 * i);
+    if (build_ms) *build_ms = ms;
+    *out = s;
     return CERES_OK;
 }
 

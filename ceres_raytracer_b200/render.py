@@ -118,6 +118,22 @@ class Scene:
         self.node_count, self.tri_count = int(nodes.shape[0]), int(tris.shape[0])
 
     @classmethod
+    def from_lbvh(cls, triangles, tri_norms=None, device=0):
+        """Scene over a linear BVH built AND kept on the GPU (ceres_scene_create_lbvh); `build_ms` = device build time."""
+        L = _capi.lib()
+        tris = np.ascontiguousarray(triangles, dtype=np.float32).reshape(-1, 12)
+        norms = np.ascontiguousarray(tri_norms, dtype=np.float32).reshape(-1, 9) if tri_norms is not None else None
+        if norms is not None and norms.shape[0] != tris.shape[0]:
+            raise ValueError("triangles / tri_norms length mismatch")
+        h, ms = C.c_void_p(), C.c_double(0.0)
+        _capi.check(L.ceres_scene_create_lbvh(_p(tris), _p(norms), tris.shape[0], int(device), C.byref(h), C.byref(ms)))
+        self = cls.__new__(cls)
+        self._h, self._L, self.device = h, L, int(device)
+        self.node_count, self.tri_count = max(2 * int(tris.shape[0]) - 1, 1), int(tris.shape[0])
+        self.build_ms = float(ms.value)
+        return self
+
+    @classmethod
     def from_pod(cls, pod, device=0):
         return cls(pod["nodes"], pod["prim_indices"], pod["triangles"], pod.get("norms"), device)
 

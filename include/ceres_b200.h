@@ -121,6 +121,12 @@ int ceres_scene_download(ceres_scene* scene, void* nodes_out, size_t node_count,
  * build kernels without the transfers. */
 int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms);
 
+/* The same build, kept on the device: a scene whose tree never visits the host (the host-side flatten of
+ * ceres_scene_create costs more than the build for 10 M triangles).  tris / norms as for ceres_scene_create
+ * (norms nullable); the resulting scene is identical to ceres_scene_create(ceres_build_lbvh(tris)) for rendering,
+ * rotate / transform / refit and download (reference node numbering: children of radix-tree node i at 1 + 2 i, 2 + 2 i). */
+int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_count, int device, ceres_scene** out, double* build_ms);
+
 /* ---- render: host buffers (the drop-in for render.hpp:86-156) ------------------------------------------------ */
 
 /* pixels: caller-owned HOST buffer of 3*width*height floats, layout pixels[3*(width*j+i)+c], row j=0 is v=-1,

@@ -23,6 +23,10 @@ lb = dict(pod, nodes=nodes, prim_indices=idx)
 t0 = time.perf_counter()
 s2 = cr.Scene.from_pod(lb)
 print(f"  ceres_scene_create (host flatten + upload) {1e3*(time.perf_counter()-t0):.1f} ms")
+t0 = time.perf_counter()
+s3 = cr.Scene.from_lbvh(pod["triangles"], pod["norms"])
+print(f"  ceres_scene_create_lbvh (upload + build + device-side scene, tree never on the host) {1e3*(time.perf_counter()-t0):.1f} ms, build kernels {s3.build_ms:.3f} ms")
+s3.close()
 dev = torch.device("cuda", 0)
 px = torch.empty(H * W * 3, dtype=torch.float32, device=dev)
 ids = [torch.empty(H * W, dtype=torch.int32, device=dev) for _ in range(2)]

@@ -67,3 +67,33 @@ def test_lbvh_edge_cases(cr):
     assert np.array_equal(port.refit(pod).view(np.uint32), nodes.view(np.uint32))
     with pytest.raises(cr.CeresError):
         cr.build_lbvh(np.zeros((0, 12), np.float32))
+
+
+def test_scene_from_lbvh_equals_scene_from_the_downloaded_tree(cr, dragon_pod):
+    """ceres_scene_create_lbvh keeps the tree on the device; it must be the scene ceres_scene_create makes from
+    ceres_build_lbvh's output: same download, same frame bit for bit, and a rotate + refit that stays identical."""
+    pod = dict(dragon_pod)
+    nodes, idx, _ = cr.build_lbvh(pod["triangles"])
+    pod["nodes"], pod["prim_indices"] = nodes, idx
+    cam = cr.configs.DRAGON_CAMERA
+    with cr.Scene.from_pod(pod) as a, cr.Scene.from_lbvh(pod["triangles"], pod["norms"]) as b:
+        assert b.build_ms > 0 and b.node_count == a.node_count
+        na, ta = a.download()
+        nb, tb = b.download()
+        assert np.array_equal(na.view(np.uint32), nodes.view(np.uint32))
+        assert np.array_equal(nb.view(np.uint32), nodes.view(np.uint32))
+        assert np.array_equal(ta.view(np.uint32), tb.view(np.uint32))
+        for s in (a, b):
+            s.rotate(2, 17.0)
+            s.refit()
+        na, ta = a.download()
+        nb, tb = b.download()
+        assert np.array_equal(na.view(np.uint32), nb.view(np.uint32)) and np.array_equal(ta.view(np.uint32), tb.view(np.uint32))
+        pa, ia, ca = a.render(cam, SUN, 960, 540, want_ids=True)
+        pb, ib, cb = b.render(cam, SUN, 960, 540, want_ids=True)
+        assert ca == cb and np.array_equal(ia, ib) and np.array_equal(pa.view(np.uint32), pb.view(np.uint32))
+    tri = port.make_triangles(np.array([[-1, -1, 5, 1, -1, 5, 0, 1, 5]], np.float32)).reshape(1, 12)
+    with cr.Scene.from_lbvh(tri) as one:                 # leaf root
+        assert one.node_count == 1
+        _, ids, cnt = one.render(cr.Camera(eye=(0, 0, 0), dir=(0, 0, 1), up=(0, 1, 0), fov=60.0), (0, 0, -10), 64, 64, want_ids=True)
+        assert cnt[1] > 0 and set(np.unique(ids).tolist()) <= {0, 0xFFFFFFFF}
