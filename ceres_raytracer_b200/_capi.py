@@ -23,6 +23,11 @@ class Camera(C.Structure):
     _fields_ = [("eye", C.c_float * 3), ("dir", C.c_float * 3), ("up", C.c_float * 3), ("fov", C.c_float)]
 
 
+class CameraF64(C.Structure):
+    """ceres_camera_f64 = Camera<double> of include/render.hpp:16-22."""
+    _fields_ = [("eye", C.c_double * 3), ("dir", C.c_double * 3), ("up", C.c_double * 3), ("fov", C.c_double)]
+
+
 class Shard(C.Structure):
     _fields_ = [("block_rows", C.c_uint32), ("index", C.c_uint32), ("count", C.c_uint32)]
 
@@ -43,7 +48,7 @@ SYMBOLS = [
     "ceres_peer_frame_create", "ceres_peer_frame_open", "ceres_peer_frame_alias", "ceres_peer_frame_destroy",
     "ceres_peer_frame_pixels", "ceres_peer_frame_ids", "ceres_render_peer", "ceres_peer_frame_error",
 ]
-SYMBOLS += ["ceres_render_ppm8", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download"]
+SYMBOLS += ["ceres_render_ppm8", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -104,6 +109,10 @@ def lib():
     L.ceres_probe_read_bandwidth.argtypes = [C.c_int, sz, C.c_int, vp]
     L.ceres_build_lbvh.argtypes = [vp, sz, C.c_int, vp, vp, vp]
     L.ceres_scene_create_lbvh.argtypes = [vp, vp, sz, C.c_int, vp, vp]
+    L.ceres_scene_f64_create.argtypes = [vp, sz, vp, vp, vp, sz, C.c_int, vp]
+    L.ceres_scene_f64_destroy.argtypes = [vp]
+    L.ceres_scene_f64_destroy.restype = None
+    L.ceres_render_f64.argtypes = [vp, vp, vp, sz, sz, C.c_uint, vp, vp, vp, vp]
     L.ceres_scene_get_step_histogram.argtypes = [vp, vp]
     L.ceres_scene_last_d2h_bytes.argtypes = [vp]
     L.ceres_scene_last_d2h_bytes.restype = u64

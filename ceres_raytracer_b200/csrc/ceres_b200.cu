@@ -2076,3 +2076,5 @@ int ceres_quantize_device(ceres_scene* s, const float* d_pixels, size_t width, s
 }
 
 }  // extern "C"
+
+#include "render_f64.cuh"

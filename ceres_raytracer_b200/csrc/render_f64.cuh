@@ -1,0 +1,373 @@
+// render_f64.cuh -- the render path for Scalar = double (`anim -d`, include/anim.cpp:154-155),
+// included at the end of ceres_b200.cu.
+//
+// The reference's render<double>() (render.hpp:86-156) is the same loop as render<float>() with every Scalar widened:
+// 64-byte nodes with uint64 indices (bvh.hpp:20-28), 96-byte triangles, 72-byte normal triples, std::fma in the slab
+// test (utilities.hpp:46-49), DBL_EPSILON in safe_inverse (vector.hpp:69-74), tmax = DBL_MAX (ray.hpp:17-20) -- and the
+// shading still in float where render.hpp says float (:46-84).  This is a completeness path, not the headline: one
+// kernel, one thread per pixel (a warp owns an 8x4 tile), primary traversal, shadow traversal (any-hit: only bool(hit)
+// is consumed, render.hpp:137-138) and shading in sequence.  Every operation through the *_rn double intrinsics, in the
+// reference's source order, so that hit ids are bit-exact against the strict double build of the reference.
+//
+// Device layout: pair p = the two children of an inner node, 128 bytes: child c at 64 c = double bounds[6], uint32
+// primitive_count, uint32 first (leaf: first slot; inner: pair index), 8 bytes padding.  Triangles (12 doubles) and
+// normals (9 doubles) are permuted into leaf-slot order, slot_id maps a slot back to the primitive index.
+
+namespace f64 {
+
+__device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double rcp(double a) { return __ddiv_rn(1.0, a); }
+__device__ __forceinline__ double dot3(double ax, double ay, double az, double bx, double by, double bz) {   // vector.hpp:134-141
+    return add(add(mul(ax, bx), mul(ay, by)), mul(az, bz));
+}
+struct D3 { double x, y, z; };
+__device__ __forceinline__ D3 normalize(D3 a) {                                                              // vector.hpp:143-154
+    const double inv = rcp(__dsqrt_rn(dot3(a.x, a.y, a.z, a.x, a.y, a.z)));
+    return {mul(a.x, inv), mul(a.y, inv), mul(a.z, inv)};
+}
+
+struct Child { double b[6]; uint32_t count, first; uint32_t pad[2]; };
+static_assert(sizeof(Child) == 64, "128-byte pairs");
+
+struct Scene64 {
+    const Child* pairs;           // 2 per pair
+    const double* tris;           // 12 per slot
+    const double* norms;          // 9 per slot
+    const uint32_t* slot_id;
+    uint32_t root_leaf_count;
+};
+
+struct Frame64 {
+    double eye[3], dir[3], iu[3], iv[3], sun[3];
+    uint32_t width, height, flags;
+    double* pixels; uint32_t* ids;
+    unsigned long long* counters;   // rays beyond W*H (= primary hits), hits
+};
+
+struct Ray64 { D3 o, d; double tmax; int oct[3]; double inv[3], so[3]; };
+
+__device__ __forceinline__ void ray_init(Ray64& r) {            // node_intersectors.hpp:20-26,89-94
+    const double d[3] = {r.d.x, r.d.y, r.d.z}, o[3] = {r.o.x, r.o.y, r.o.z};
+    for (int k = 0; k < 3; ++k) {
+        r.oct[k] = signbit(d[k]) ? 1 : 0;
+        r.inv[k] = rcp(fabs(d[k]) < DBL_EPSILON ? copysign(DBL_EPSILON, d[k]) : d[k]);
+        r.so[k] = mul(-o[k], r.inv[k]);
+    }
+}
+
+__device__ __forceinline__ void slab(const Ray64& r, const Child& c, double& entry, double& exit_) {   // node_intersectors.hpp:34-47,96-100
+    const double e0 = __fma_rn(c.b[0 + r.oct[0]], r.inv[0], r.so[0]);
+    const double e1 = __fma_rn(c.b[2 + r.oct[1]], r.inv[1], r.so[1]);
+    const double e2 = __fma_rn(c.b[4 + r.oct[2]], r.inv[2], r.so[2]);
+    const double x0 = __fma_rn(c.b[1 - r.oct[0]], r.inv[0], r.so[0]);
+    const double x1 = __fma_rn(c.b[3 - r.oct[1]], r.inv[1], r.so[1]);
+    const double x2 = __fma_rn(c.b[5 - r.oct[2]], r.inv[2], r.so[2]);
+    auto rmax = [](double x, double y) { return x > y ? x : y; };          // utilities.hpp:57-67
+    auto rmin = [](double x, double y) { return x < y ? x : y; };
+    entry = rmax(e0, rmax(e1, rmax(e2, 0.0)));                              // tmin = 0 for both ray kinds
+    exit_ = rmin(x0, rmin(x1, rmin(x2, r.tmax)));
+}
+
+struct Hit64 { uint32_t slot; double u, v; bool hit; };
+
+// triangle.hpp:95-115 for the slots [first, first + count), ascending (single_ray_traverser.hpp:41-63)
+template <bool ANY>
+__device__ __forceinline__ void leaf(const Scene64& sc, Ray64& r, uint32_t first, uint32_t count, Hit64& best) {
+    for (uint32_t s = first; s < first + count; ++s) {
+        const double* t = sc.tris + 12ull * s;
+        const double cx = sub(t[0], r.o.x), cy = sub(t[1], r.o.y), cz = sub(t[2], r.o.z);
+        const double rx = sub(mul(r.d.y, cz), mul(r.d.z, cy)), ry = sub(mul(r.d.z, cx), mul(r.d.x, cz)), rz = sub(mul(r.d.x, cy), mul(r.d.y, cx));
+        const double inv_det = rcp(dot3(t[9], t[10], t[11], r.d.x, r.d.y, r.d.z));
+        const double u = mul(dot3(rx, ry, rz, t[6], t[7], t[8]), inv_det);
+        const double v = mul(dot3(rx, ry, rz, t[3], t[4], t[5]), inv_det);
+        const double w = sub(sub(1.0, u), v);
+        if (u >= 0 && v >= 0 && w >= 0) {
+            const double tt = mul(dot3(t[9], t[10], t[11], cx, cy, cz), inv_det);
+            if (tt >= 0.0 && tt <= r.tmax) {
+                best.hit = true; best.slot = s; best.u = u; best.v = v;
+                r.tmax = tt;
+                if (ANY) return;
+            }
+        }
+    }
+}
+
+// single_ray_traverser.hpp:65-126: ordered, eager leaves, far child pushed; ties keep the left child in front
+template <bool ANY>
+__device__ Hit64 traverse(const Scene64& sc, Ray64& r) {
+    Hit64 best; best.hit = false; best.slot = 0xFFFFFFFFu; best.u = best.v = 0.0;
+    if (sc.root_leaf_count) { leaf<ANY>(sc, r, 0u, sc.root_leaf_count, best); return best; }
+    ray_init(r);
+    uint32_t stack[64];
+    int sp = 0;
+    uint32_t pair = 0;
+    const uint32_t NONE = 0xFFFFFFFFu;
+    for (;;) {
+        const Child& l = sc.pairs[2ull * pair];
+        const Child& rt = sc.pairs[2ull * pair + 1];
+        double le, lx, re, rx;
+        slab(r, l, le, lx);
+        slab(r, rt, re, rx);                      // before the left leaf shrinks tmax (:86-87)
+        uint32_t nl = NONE, nr = NONE;
+        if (le <= lx) { if (l.count) leaf<ANY>(sc, r, l.first, l.count, best); else nl = l.first; }
+        if (ANY && best.hit) return best;
+        if (re <= rx) { if (rt.count) leaf<ANY>(sc, r, rt.first, rt.count, best); else nr = rt.first; }
+        if (ANY && best.hit) return best;
+        if (nl != NONE) {
+            if (nr != NONE) {
+                if (le > re) { const uint32_t t = nl; nl = nr; nr = t; }
+                stack[sp++] = nr;
+            }
+            pair = nl;
+        } else if (nr != NONE) {
+            pair = nr;
+        } else {
+            if (sp == 0) break;
+            pair = stack[--sp];
+        }
+    }
+    return best;
+}
+
+__device__ __forceinline__ float clampf01(float x) { return x < 0.0f ? 0.0f : (1.0f < x ? 1.0f : x); }
+
+// render.hpp:56-84 with Scalar = double: float diffuse / specular / colour accumulators, double weights
+__device__ __forceinline__ void smooth_shading(D3 sun_line, const double* nm, D3 view, double u, double v, float* c) {
+    const double w[3] = {u, v, sub(sub(1.0, u), v)};
+    const D3 mv = {mul(view.x, -1.0), mul(view.y, -1.0), mul(view.z, -1.0)};
+    c[0] = c[1] = c[2] = 0.0f;
+    for (int k = 0; k < 3; ++k) {
+        const double nx = nm[3 * k], ny = nm[3 * k + 1], nz = nm[3 * k + 2];
+        const float lam = (float)fabs(dot3(sun_line.x, sun_line.y, sun_line.z, nx, ny, nz));
+        const float diffuse = __fmul_rn(0.5f, lam);
+        const D3 h = normalize({add(sun_line.x, mv.x), add(sun_line.y, mv.y), add(sun_line.z, mv.z)});
+        const double b = dot3(nx, ny, nz, h.x, h.y, h.z);
+        const double b2 = mul(b, b), b3 = mul(b2, b), b6 = mul(b3, b3), b12 = mul(b6, b6);      // pow(b, 24)
+        const float specular = __fmul_rn(0.8f, (float)mul(b12, b12));
+        const float base = __fadd_rn(0.2f, diffuse);
+        const float col[3] = {clampf01(__fadd_rn(__fmul_rn(base, 0.5f), specular)), clampf01(__fadd_rn(__fmul_rn(base, 0.0f), specular)),
+                              clampf01(__fadd_rn(__fmul_rn(base, 0.8f), specular))};
+        for (int q = 0; q < 3; ++q) c[q] = (float)add((double)c[q], mul(w[k], (double)col[q]));
+    }
+}
+
+// One thread per pixel; a warp covers an 8 x 4 tile, a 128-thread CTA a 16 x 8 block.
+__global__ void __launch_bounds__(128) render_kernel(const Scene64 sc, const Frame64 f) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t i = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t j = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    unsigned int primary_hit = 0, hits = 0;
+    if (i < f.width && j < f.height) {
+        const size_t pix = (size_t)f.width * j + i;
+        const double u = sub(__ddiv_rn(mul(2.0, add((double)i, 0.5)), (double)f.width), 1.0);      // render.hpp:109-110
+        const double v = sub(__ddiv_rn(mul(2.0, add((double)j, 0.5)), (double)f.height), 1.0);
+        const D3 view = normalize({add(add(mul(f.iu[0], u), mul(f.iv[0], v)), f.dir[0]), add(add(mul(f.iu[1], u), mul(f.iv[1], v)), f.dir[1]),
+                                   add(add(mul(f.iu[2], u), mul(f.iv[2], v)), f.dir[2])});
+        Ray64 ray; ray.o = {f.eye[0], f.eye[1], f.eye[2]}; ray.d = view; ray.tmax = DBL_MAX;
+        const Hit64 hit = traverse<false>(sc, ray);
+        float rgb[3] = {0.0f, 0.0f, 0.0f};
+        if (hit.hit) {
+            primary_hit = 1; hits = 1;
+            const double* t = sc.tris + 12ull * hit.slot;
+            const D3 normal = normalize({t[9], t[10], t[11]});
+            const double hu = hit.u, hv = hit.v, hw = sub(sub(1.0, hu), hv);
+            double P[3];
+            for (int k = 0; k < 3; ++k) {                                     // u p0 + v p1() + (1-u-v) p2(), render.hpp:129
+                const double p1 = sub(t[k], t[3 + k]), p2 = add(t[k], t[6 + k]);
+                P[k] = add(add(mul(t[k], hu), mul(p1, hv)), mul(p2, hw));
+            }
+            P[0] = add(P[0], mul(normal.x, -0.00001)); P[1] = add(P[1], mul(normal.y, -0.00001)); P[2] = add(P[2], mul(normal.z, -0.00001));
+            const D3 sun_line = normalize({sub(f.sun[0], P[0]), sub(f.sun[1], P[1]), sub(f.sun[2], P[2])});
+            bool occluded = false;
+            if (!(f.flags & CERES_NO_SHADOWS)) {
+                Ray64 sray; sray.o = {P[0], P[1], P[2]}; sray.d = sun_line; sray.tmax = DBL_MAX;
+                occluded = traverse<true>(sc, sray).hit;
+            }
+            if (!occluded) smooth_shading(sun_line, sc.norms + 9ull * hit.slot, view, hu, hv, rgb);
+            else hits = 2;
+        }
+        f.pixels[3 * pix] = (double)rgb[0]; f.pixels[3 * pix + 1] = (double)rgb[1]; f.pixels[3 * pix + 2] = (double)rgb[2];
+        if (f.ids) f.ids[pix] = hit.hit ? sc.slot_id[hit.slot] : 0xFFFFFFFFu;
+    }
+    const unsigned int shadow_rays = (f.flags & CERES_NO_SHADOWS) ? 0u : primary_hit;
+    const unsigned int r = __reduce_add_sync(0xFFFFFFFFu, shadow_rays), h = __reduce_add_sync(0xFFFFFFFFu, hits);
+    if (lane == 0 && (r | h)) { atomicAdd(&f.counters[0], (unsigned long long)r); atomicAdd(&f.counters[1], (unsigned long long)h); }
+}
+
+}  // namespace f64
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+struct ceres_scene_f64 {
+    int device = 0;
+    f64::Scene64 dev{};
+    void* d_pairs = nullptr; double* d_tris = nullptr; double* d_norms = nullptr; uint32_t* d_slot_id = nullptr;
+    double* d_pixels = nullptr; size_t pixels_cap = 0;
+    uint32_t* d_ids = nullptr; size_t ids_cap = 0;
+    unsigned long long* d_counters = nullptr;
+    size_t tri_count = 0, node_count = 0;
+};
+
+namespace {
+struct RefNode64 { double bounds[6]; uint64_t primitive_count; uint64_t first_child_or_primitive; };      // bvh.hpp:20-28
+static_assert(sizeof(RefNode64) == 64, "Bvh<double>::Node");
+}
+
+extern "C" {
+
+int ceres_scene_f64_create(const void* nodes_v, size_t node_count, const size_t* prim_idx, const void* tris_v, const void* norms_v,
+                           size_t tri_count, int device, ceres_scene_f64** out) {
+    if (!out) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: out is null");
+    *out = nullptr;
+    if (!nodes_v || !prim_idx || !tris_v || !node_count || !tri_count) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: null or empty scene arrays");
+    if (tri_count >= 0x7FFFFFFFull || node_count >= 0xFFFFFFFFull) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: scene too large for 32-bit slots");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) return fail(CERES_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: bad device index");
+    const RefNode64* nodes = static_cast<const RefNode64*>(nodes_v);
+    const double* tris = static_cast<const double*>(tris_v);
+    const double* norms = static_cast<const double*>(norms_v);
+    for (size_t k = 0; k < tri_count; ++k)
+        if (prim_idx[k] >= tri_count) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: primitive index out of range");
+
+    // pairs in depth-first order, left child first
+    std::vector<f64::Child> pairs;
+    uint32_t root_leaf_count = 0, depth_max = 1;
+    const RefNode64& root = nodes[0];
+    if (root.primitive_count != 0) {
+        if (root.first_child_or_primitive != 0 || root.primitive_count != tri_count)
+            return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: leaf root must cover all primitives from slot 0");
+        root_leaf_count = (uint32_t)root.primitive_count;
+        pairs.resize(2);
+    } else {
+        struct Item { uint64_t first_child; uint32_t pair, depth; };
+        std::vector<Item> work;
+        pairs.reserve(node_count + 1);
+        auto new_pair = [&]() { const uint32_t id = (uint32_t)(pairs.size() / 2); pairs.resize(pairs.size() + 2); return id; };
+        size_t visited = 1;
+        work.push_back({root.first_child_or_primitive, new_pair(), 1u});
+        while (!work.empty()) {
+            const Item it = work.back(); work.pop_back();
+            if (it.first_child + 1 >= node_count) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: child index out of range");
+            visited += 2;
+            if (visited > node_count) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: BVH is not a tree (cycle or shared nodes)");
+            depth_max = std::max(depth_max, it.depth);
+            uint32_t child_pair[2] = {0, 0};
+            for (int c = 0; c < 2; ++c) {
+                const RefNode64& n = nodes[it.first_child + c];
+                f64::Child ch{};
+                for (int b = 0; b < 6; ++b) ch.b[b] = n.bounds[b];
+                if (n.primitive_count != 0) {
+                    if (n.first_child_or_primitive + n.primitive_count > tri_count) return fail(CERES_ERR_INVALID, "ceres_scene_f64_create: leaf range out of bounds");
+                    ch.count = (uint32_t)n.primitive_count; ch.first = (uint32_t)n.first_child_or_primitive;
+                } else {
+                    ch.count = 0; ch.first = child_pair[c] = new_pair();
+                }
+                pairs[2 * (size_t)it.pair + c] = ch;
+            }
+            for (int c = 1; c >= 0; --c) {
+                const RefNode64& n = nodes[it.first_child + c];
+                if (n.primitive_count == 0) work.push_back({n.first_child_or_primitive, child_pair[c], it.depth + 1});
+            }
+        }
+    }
+    if (depth_max > 64) return fail(CERES_ERR_UNSUPPORTED, "ceres_scene_f64_create: BVH deeper than the reference's 64-entry stack");
+    std::vector<double> tri_slots(tri_count * 12), norm_slots(tri_count * 9, 0.0);
+    std::vector<uint32_t> slot_id(tri_count);
+    for (size_t s = 0; s < tri_count; ++s) {
+        slot_id[s] = (uint32_t)prim_idx[s];
+        std::memcpy(&tri_slots[s * 12], tris + prim_idx[s] * 12, 96);
+        if (norms) std::memcpy(&norm_slots[s * 9], norms + prim_idx[s] * 9, 72);
+    }
+
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CERES_ERR_CUDA, "cudaSetDevice failed");
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(CERES_ERR_NO_DEVICE, std::string("device is not Blackwell-class (sm_100a required): ") + prop.name);
+    ceres_scene_f64* s = new (std::nothrow) ceres_scene_f64;
+    if (!s) return fail(CERES_ERR_INVALID, "out of host memory");
+    s->device = device; s->tri_count = tri_count; s->node_count = node_count;
+#define TRY_D(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); ceres_scene_f64_destroy(s); return CERES_ERR_CUDA; } } while (0)
+    TRY_D(cudaMalloc(&s->d_pairs, pairs.size() * sizeof(f64::Child)));
+    TRY_D(cudaMalloc((void**)&s->d_tris, tri_slots.size() * 8));
+    TRY_D(cudaMalloc((void**)&s->d_norms, norm_slots.size() * 8));
+    TRY_D(cudaMalloc((void**)&s->d_slot_id, slot_id.size() * 4));
+    TRY_D(cudaMalloc((void**)&s->d_counters, 2 * sizeof(unsigned long long)));
+    TRY_D(cudaMemcpy(s->d_pairs, pairs.data(), pairs.size() * sizeof(f64::Child), cudaMemcpyHostToDevice));
+    TRY_D(cudaMemcpy(s->d_tris, tri_slots.data(), tri_slots.size() * 8, cudaMemcpyHostToDevice));
+    TRY_D(cudaMemcpy(s->d_norms, norm_slots.data(), norm_slots.size() * 8, cudaMemcpyHostToDevice));
+    TRY_D(cudaMemcpy(s->d_slot_id, slot_id.data(), slot_id.size() * 4, cudaMemcpyHostToDevice));
+#undef TRY_D
+    s->dev.pairs = (const f64::Child*)s->d_pairs; s->dev.tris = s->d_tris; s->dev.norms = s->d_norms; s->dev.slot_id = s->d_slot_id;
+    s->dev.root_leaf_count = root_leaf_count;
+    *out = s;
+    return CERES_OK;
+}
+
+void ceres_scene_f64_destroy(ceres_scene_f64* s) {
+    if (!s) return;
+    DeviceGuard guard(s->device);
+    cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
+    cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_counters);
+    delete s;
+}
+
+int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height, unsigned flags,
+                     double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms) {
+    if (!s || !cam || !sun || !pixels) return fail(CERES_ERR_INVALID, "ceres_render_f64: null argument");
+    if (!width || !height || (uint64_t)width * height >= (1ull << 31)) return fail(CERES_ERR_INVALID, "ceres_render_f64: bad image size");
+    if ((height + 7) / 8 > 65535u) return fail(CERES_ERR_INVALID, "ceres_render_f64: image too tall");
+    DeviceGuard guard(s->device);
+    const size_t npix = width * height;
+    if (s->pixels_cap < npix) {
+        cudaFree(s->d_pixels); s->d_pixels = nullptr; s->pixels_cap = 0;
+        CUDA_TRY(cudaMalloc((void**)&s->d_pixels, npix * 24));
+        s->pixels_cap = npix;
+    }
+    if (ids && s->ids_cap < npix) {
+        cudaFree(s->d_ids); s->d_ids = nullptr; s->ids_cap = 0;
+        CUDA_TRY(cudaMalloc((void**)&s->d_ids, npix * 4));
+        s->ids_cap = npix;
+    }
+    f64::Frame64 f{};
+    {   // render.hpp:91-97 in binary64, source order (host code of this file is compiled with -ffp-contract=off)
+        auto dot = [](const double* a, const double* b) { double t = a[0] * b[0]; t += a[1] * b[1]; t += a[2] * b[2]; return t; };
+        auto normalize = [&](double* a) { const double inv = 1.0 / std::sqrt(dot(a, a)); a[0] = a[0] * inv; a[1] = a[1] * inv; a[2] = a[2] * inv; };
+        auto cross = [](const double* a, const double* b, double* c) {
+            c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0];
+        };
+        double dir[3] = {cam->dir[0], cam->dir[1], cam->dir[2]}, iu[3], iv[3];
+        normalize(dir);
+        cross(dir, cam->up, iu); normalize(iu);
+        cross(iu, dir, iv); normalize(iv);
+        const double iw = std::tan(cam->fov * (3.14159265 * (1.0 / 180.0) * 0.5));
+        const double ratio = (double)height / (double)width;
+        for (int k = 0; k < 3; ++k) {
+            f.eye[k] = cam->eye[k]; f.dir[k] = dir[k]; f.iu[k] = iu[k] * iw; f.iv[k] = iv[k] * iw * ratio; f.sun[k] = sun[k];
+        }
+    }
+    f.width = (uint32_t)width; f.height = (uint32_t)height; f.flags = flags;
+    f.pixels = s->d_pixels; f.ids = ids ? s->d_ids : nullptr; f.counters = s->d_counters;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    CUDA_TRY(cudaMemset(s->d_counters, 0, 2 * sizeof(unsigned long long)));
+    if (kernel_ms) { CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventRecord(e0, 0)); }
+    f64::render_kernel<<<dim3((unsigned)((width + 15) / 16), (unsigned)((height + 7) / 8)), 128>>>(s->dev, f);
+    g_launches++;
+    if (kernel_ms) cudaEventRecord(e1, 0);
+    cudaError_t err = cudaGetLastError();
+    if (err == cudaSuccess) err = cudaMemcpy(pixels, s->d_pixels, npix * 24, cudaMemcpyDeviceToHost);
+    if (err == cudaSuccess && ids) err = cudaMemcpy(ids, s->d_ids, npix * 4, cudaMemcpyDeviceToHost);
+    unsigned long long c[2] = {0, 0};
+    if (err == cudaSuccess) err = cudaMemcpy(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost);
+    if (kernel_ms && err == cudaSuccess) { float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1); *kernel_ms = ms; }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (err != cudaSuccess) return fail(CERES_ERR_CUDA, std::string("ceres_render_f64: ") + cudaGetErrorString(err));
+    if (counters) { counters[0] = (uint64_t)npix + c[0]; counters[1] = c[1]; }      // render.hpp:115,138 / :119,148
+    return CERES_OK;
+}
+
+}  // extern "C"

@@ -17,6 +17,7 @@ from . import _capi
 from ._capi import NO_SHADOWS, COMPACT_ROWS, MISS, CeresError  # noqa: F401
 
 NODE_DT = np.dtype([("bounds", "<f4", (6,)), ("primitive_count", "<u4"), ("first_child_or_primitive", "<u4")])
+NODE64_DT = np.dtype([("bounds", "<f8", (6,)), ("primitive_count", "<u8"), ("first_child_or_primitive", "<u8")])   # Bvh<double>::Node
 
 
 @dataclass
@@ -328,3 +329,55 @@ def write_ppm(path, pixels):
         f.write(f"P6 {W} {H} 255\n".encode())
         f.write(b.tobytes())
     return b
+
+
+class SceneF64:
+    """A Scalar = double scene on one GPU (ceres_scene_f64; `anim -d`, anim.cpp:154-155).  nodes: NODE64_DT or raw 64-byte
+    records, triangles float64[n, 12], tri_norms float64[n, 9] or None."""
+
+    def __init__(self, nodes, prim_indices, triangles, tri_norms=None, device=0):
+        L = _capi.lib()
+        nodes = np.ascontiguousarray(nodes)
+        if nodes.dtype.itemsize != 64:
+            raise ValueError("double-precision nodes are 64-byte records (bvh.hpp:20-28)")
+        idx = np.ascontiguousarray(prim_indices, dtype=np.uint64)
+        tris = np.ascontiguousarray(triangles, dtype=np.float64).reshape(-1, 12)
+        norms = np.ascontiguousarray(tri_norms, dtype=np.float64).reshape(-1, 9) if tri_norms is not None else None
+        if idx.shape[0] != tris.shape[0] or (norms is not None and norms.shape[0] != tris.shape[0]):
+            raise ValueError("prim_indices / triangles / tri_norms length mismatch")
+        h = C.c_void_p()
+        _capi.check(L.ceres_scene_f64_create(_p(nodes), nodes.shape[0], _p(idx), _p(tris), _p(norms), tris.shape[0], int(device), C.byref(h)))
+        self._h, self._L, self.device = h, L, int(device)
+        self.kernel_ms = 0.0
+
+    @classmethod
+    def from_pod(cls, pod, device=0):
+        return cls(pod["nodes"], pod["prim_indices"], pod["triangles"], pod.get("norms"), device=device)
+
+    def render(self, camera, sun_position, width, height, flags=0, want_ids=False):
+        """Returns (pixels float64[H, W, 3], ids uint32[H, W] or None, (rays, hits)); camera: Camera or 10 numbers."""
+        cam = _capi.CameraF64()
+        vals = (list(camera.eye) + list(camera.dir) + list(camera.up) + [camera.fov]) if hasattr(camera, "eye") else [float(x) for x in camera]
+        for k in range(3):
+            cam.eye[k], cam.dir[k], cam.up[k] = vals[k], vals[3 + k], vals[6 + k]
+        cam.fov = vals[9]
+        pixels = np.empty((height, width, 3), np.float64)
+        ids = np.empty((height, width), np.uint32) if want_ids else None
+        sun = np.ascontiguousarray(sun_position, np.float64)
+        cnt, ms = np.zeros(2, np.uint64), C.c_double(0.0)
+        _capi.check(self._L.ceres_render_f64(self._h, C.byref(cam), _p(sun), width, height, flags, _p(pixels), _p(ids), _p(cnt), C.byref(ms)))
+        self.kernel_ms = float(ms.value)
+        return pixels, ids, (int(cnt[0]), int(cnt[1]))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ceres_scene_f64_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    __del__ = close

@@ -127,6 +127,27 @@ int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes
  * rotate / transform / refit and download (reference node numbering: children of radix-tree node i at 1 + 2 i, 2 + 2 i). */
 int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_count, int device, ceres_scene** out, double* build_ms);
 
+/* ---- Scalar = double (`anim -d`, include/anim.cpp:154-155) -------------------------------------
+ * render<double>() (render.hpp:86-156) over the double-precision scene the reference holds: nodes = node_count x
+ * 64-byte bvh::Bvh<double>::Node {double bounds[6]; uint64 primitive_count; uint64 first_child_or_primitive}
+ * (bvh.hpp:20-28), tris = tri_count x 96-byte Triangle<double> (triangle.hpp:27), norms = tri_count x 72 bytes
+ * (obj_norms.hpp:113-115; nullable), prim_idx as for ceres_scene_create.  pixels: HOST 3 * width * height doubles,
+ * layout 3 * (width * j + i) (render.hpp:107); ids (nullable): HOST width * height primitive indices, CERES_MISS where
+ * nothing was hit; counters = the pair of render.hpp:155; flags: CERES_NO_SHADOWS.  kernel_ms (nullable): device time
+ * of the frame's kernel.  One kernel, one device, no sharding: a completeness path next to the float one. */
+typedef struct ceres_scene_f64 ceres_scene_f64;
+typedef struct ceres_camera_f64 {   /* Camera<double>, include/render.hpp:16-22 (fov in degrees) */
+    double eye[3];
+    double dir[3];
+    double up[3];
+    double fov;
+} ceres_camera_f64;
+int ceres_scene_f64_create(const void* nodes, size_t node_count, const size_t* prim_idx, const void* tris, const void* norms,
+                           size_t tri_count, int device, ceres_scene_f64** out);
+void ceres_scene_f64_destroy(ceres_scene_f64* scene);
+int ceres_render_f64(ceres_scene_f64* scene, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height,
+                     unsigned flags, double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms);
+
 /* ---- render: host buffers (the drop-in for render.hpp:86-156) ------------------------------------------------ */
 
 /* pixels: caller-owned HOST buffer of 3*width*height floats, layout pixels[3*(width*j+i)+c], row j=0 is v=-1,
