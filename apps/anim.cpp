@@ -7,7 +7,8 @@
 //                               (anim.cpp:27-35,62-65,77-89,140-143).
 //
 // Written fresh.  What differs from upstream, and why:
-//   * -d (Scalar = double) is refused: there is no double GPU path and no CPU fallback.
+//   * -d (Scalar = double, anim.cpp:154-155) loads, builds and renders in double through ceres_render_f64 (one kernel per
+//     frame, no host-frame pipeline); the colours of render<double>() are float-valued, so the writers take them narrowed.
 //   * upstream encodes the frames with ImageMagick 7 Magick++ (anim.cpp:112-127) -- unavailable on this box.  Frames
 //     are written as <out_file stem>_NNNN.ppm instead (16-bit P6 with --ppm16, matching the x65535 quantum scaling of
 //     anim.cpp:117-119; 8-bit static.cpp-style by default).
@@ -37,14 +38,16 @@
 #include "obj_norms.hpp"
 #include "ppm.hpp"
 
-using Scalar = float;
-using Vector3 = bvh::Vector3<Scalar>;
-using Bvh = bvh::Bvh<Scalar>;
-using Triangle = bvh::Triangle<Scalar>;
-
 namespace {
 
-struct FramePose { Camera<Scalar> camera; Vector3 sun; };
+template <typename Scalar> struct FramePose { Camera<Scalar> camera; bvh::Vector3<Scalar> sun; };
+
+struct Options {
+    std::string out_file = "render.mp4", input_file = "../../waahh_smoothed.obj";
+    size_t width = 1242 / 2, height = 2688 / 2;
+    int n_frames = 60, gpus = 1;
+    bool ppm16 = false, no_output = false, dragon = false;
+};
 
 double seconds_since(std::chrono::high_resolution_clock::time_point t0) {
     return std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::high_resolution_clock::now() - t0).count() / 1e6;
@@ -61,32 +64,40 @@ std::string frame_name(const std::string& out_file, int i) {
 
 }  // namespace
 
+template <typename Scalar> int scene(const Options& opt);
+
 int main(int argc, char** argv) {
-    std::string out_file = "render.mp4", input_file = "../../waahh_smoothed.obj";
-    size_t width = 1242 / 2, height = 2688 / 2;
-    int n_frames = 60, gpus = 1;
-    bool ppm16 = false, no_output = false, dragon = false;
+    Options o;
+    bool use_double = false;
     std::vector<std::string> positional;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto val = [&]() -> const char* { if (i + 1 >= argc) { std::cerr << "anim: missing value after " << a << std::endl; std::exit(2); } return argv[++i]; };
-        if (a == "-d") {
-            std::cerr << "anim: -d (double precision, anim.cpp:154-155) is not available: the B200 path renders float only "
-                         "and has no CPU fallback" << std::endl;
-            return 2;
-        }
-        else if (a == "--input") input_file = val();
-        else if (a == "--frames") n_frames = std::atoi(val());
-        else if (a == "--width") width = std::strtoull(val(), nullptr, 10);
-        else if (a == "--height") height = std::strtoull(val(), nullptr, 10);
-        else if (a == "--gpus") gpus = std::atoi(val());
-        else if (a == "--ppm16") ppm16 = true;
-        else if (a == "--no-output") no_output = true;
-        else if (a == "--scene") { dragon = std::string(val()) == "dragon"; }
+        if (a == "-d") use_double = true;                        // anim.cpp:146-148
+        else if (a == "--input") o.input_file = val();
+        else if (a == "--frames") o.n_frames = std::atoi(val());
+        else if (a == "--width") o.width = std::strtoull(val(), nullptr, 10);
+        else if (a == "--height") o.height = std::strtoull(val(), nullptr, 10);
+        else if (a == "--gpus") o.gpus = std::atoi(val());
+        else if (a == "--ppm16") o.ppm16 = true;
+        else if (a == "--no-output") o.no_output = true;
+        else if (a == "--scene") { o.dragon = std::string(val()) == "dragon"; }
         else positional.push_back(a);
     }
-    if (!positional.empty()) out_file = positional.back();     // anim.cpp:145-152
-    if (n_frames < 1 || gpus < 1 || !width || !height) { std::cerr << "anim: bad --frames/--gpus/--width/--height" << std::endl; return 2; }
+    if (!positional.empty()) o.out_file = positional.back();     // anim.cpp:145-152
+    if (o.n_frames < 1 || o.gpus < 1 || !o.width || !o.height) { std::cerr << "anim: bad --frames/--gpus/--width/--height" << std::endl; return 2; }
+    return use_double ? scene<double>(o) : scene<float>(o);      // anim.cpp:154-155
+}
+
+template <typename Scalar>
+int scene(const Options& opt) {
+    using Vector3 = bvh::Vector3<Scalar>;
+    using Bvh = bvh::Bvh<Scalar>;
+    const std::string out_file = opt.out_file;
+    std::string input_file = opt.input_file;
+    const size_t width = opt.width, height = opt.height;
+    const int n_frames = opt.n_frames, gpus = opt.gpus;
+    const bool ppm16 = opt.ppm16, no_output = opt.no_output, dragon = opt.dragon;
 
     constexpr Scalar pi = Scalar(3.14159265359);
     Camera<Scalar> camera = {Vector3(-150.0, -20.0, 0.0), Vector3(1, -0.1, 0), Vector3(0, -1, 0), 60};
@@ -127,12 +138,12 @@ int main(int argc, char** argv) {
     // the camera path, serially (each pose is the previous one rotated, anim.cpp:77-89)
     const auto t_cam = Transform<Scalar>().rotate(axis, rotation_step_degrees / 180.0f * pi);
     const auto t_sun = Transform<Scalar>().rotate(axis, rotation_step_degrees / 180.0f * pi);
-    std::vector<FramePose> path(n_frames);
+    std::vector<FramePose<Scalar>> path(n_frames);
     for (int i = 0; i < n_frames; ++i) {
         camera.eye = t_cam(camera.eye);
         camera.dir = t_cam(camera.dir);
         sun_position = t_sun(sun_position);
-        path[i] = FramePose{camera, sun_position};
+        path[i] = FramePose<Scalar>{camera, sun_position};
     }
 
     const int ndev = ceres_device_count();
@@ -143,14 +154,14 @@ int main(int argc, char** argv) {
     std::vector<long> frame_rays(n_frames, 0);
     std::vector<std::string> errors(gpus);
     auto wall = std::chrono::high_resolution_clock::now();
-    auto worker = [&](int g) {
+    auto worker_f32 = [&](int g) {
         ceres_scene* scene = nullptr;
         if (ceres_scene_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
                                tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
         // two page-locked frames per GPU: frame k is quantised and written by a writer thread while frame k+1 renders
         // (upstream encodes synchronously inside the frame loop, anim.cpp:112-127)
-        Scalar* buffers[2] = {static_cast<Scalar*>(ceres_host_alloc(3 * width * height * sizeof(Scalar))),
-                              static_cast<Scalar*>(ceres_host_alloc(3 * width * height * sizeof(Scalar)))};
+        float* buffers[2] = {static_cast<float*>(ceres_host_alloc(3 * width * height * sizeof(float))),
+                             static_cast<float*>(ceres_host_alloc(3 * width * height * sizeof(float)))};
         if (!buffers[0] || !buffers[1]) {
             errors[g] = ceres_last_error(); ceres_host_free(buffers[0]); ceres_host_free(buffers[1]); ceres_scene_destroy(scene); return;
         }
@@ -164,11 +175,11 @@ int main(int argc, char** argv) {
         int turn = 0;
         for (int i = g; i < n_frames; i += gpus, turn ^= 1) {
             if (!drain(turn)) break;
-            Scalar* pixels = buffers[turn];
+            float* pixels = buffers[turn];
             ceres_camera cam;
-            for (int k = 0; k < 3; ++k) { cam.eye[k] = path[i].camera.eye[k]; cam.dir[k] = path[i].camera.dir[k]; cam.up[k] = path[i].camera.up[k]; }
-            cam.fov = path[i].camera.fov;
-            const float sun[3] = {path[i].sun[0], path[i].sun[1], path[i].sun[2]};
+            for (int k = 0; k < 3; ++k) { cam.eye[k] = (float)path[i].camera.eye[k]; cam.dir[k] = (float)path[i].camera.dir[k]; cam.up[k] = (float)path[i].camera.up[k]; }
+            cam.fov = (float)path[i].camera.fov;
+            const float sun[3] = {(float)path[i].sun[0], (float)path[i].sun[1], (float)path[i].sun[2]};
             uint64_t cnt[2] = {0, 0};
             auto t0 = std::chrono::high_resolution_clock::now();
             if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, cnt) != CERES_OK) { errors[g] = ceres_last_error(); break; }
@@ -189,6 +200,53 @@ int main(int argc, char** argv) {
         drain(0); drain(1);
         ceres_host_free(buffers[0]); ceres_host_free(buffers[1]);
         ceres_scene_destroy(scene);
+    };
+    // Scalar = double: ceres_render_f64 fills a double frame; its colours are float-valued (render.hpp:56-84 accumulates
+    // in float), so they are narrowed without loss for the same writers.
+    auto worker_f64 = [&](int g) {
+        ceres_scene_f64* scene = nullptr;
+        if (ceres_scene_f64_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
+                                   tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
+        std::vector<double> frame(3 * width * height);
+        std::vector<float> narrow[2] = {std::vector<float>(3 * width * height), std::vector<float>(3 * width * height)};
+        std::future<std::string> writing[2];
+        auto drain = [&](int b) {
+            if (!writing[b].valid()) return true;
+            const std::string err = writing[b].get();
+            if (!err.empty() && errors[g].empty()) errors[g] = err;
+            return err.empty();
+        };
+        int turn = 0;
+        for (int i = g; i < n_frames; i += gpus, turn ^= 1) {
+            if (!drain(turn)) break;
+            ceres_camera_f64 cam;
+            for (int k = 0; k < 3; ++k) { cam.eye[k] = path[i].camera.eye[k]; cam.dir[k] = path[i].camera.dir[k]; cam.up[k] = path[i].camera.up[k]; }
+            cam.fov = path[i].camera.fov;
+            const double sun[3] = {(double)path[i].sun[0], (double)path[i].sun[1], (double)path[i].sun[2]};
+            uint64_t cnt[2] = {0, 0};
+            auto t0 = std::chrono::high_resolution_clock::now();
+            if (ceres_render_f64(scene, &cam, sun, width, height, 0u, frame.data(), nullptr, cnt, nullptr) != CERES_OK) { errors[g] = ceres_last_error(); break; }
+            const double s = seconds_since(t0);
+            std::ostringstream os;
+            os << "Rendering image " << i << " (" << width << "x" << height << ") on GPU " << g << "...\n"
+               << "Rays: " << (int)cnt[0] << "\tHits: " << (int)cnt[1] << "\n" << "Tracing took " << s << " s\n";
+            log[i] = os.str();
+            frame_rays[i] = (long)(int)cnt[0];
+            if (!no_output) {
+                float* pixels = narrow[turn].data();
+                for (size_t k = 0; k < frame.size(); ++k) pixels[k] = (float)frame[k];
+                const std::string name = frame_name(out_file, i);
+                writing[turn] = std::async(std::launch::async, [=]() -> std::string {
+                    const bool ok = ppm16 ? ceres_apps::write_ppm16(name, pixels, width, height) : ceres_apps::write_ppm(name, pixels, width, height);
+                    return ok ? std::string() : "cannot write " + name;
+                });
+            }
+        }
+        drain(0); drain(1);
+        ceres_scene_f64_destroy(scene);
+    };
+    auto worker = [&](int g) {
+        if constexpr (std::is_same<Scalar, float>::value) worker_f32(g); else worker_f64(g);
     };
     std::vector<std::thread> threads;
     for (int g = 1; g < gpus; ++g) threads.emplace_back(worker, g);

@@ -17,8 +17,8 @@
 // only reference code this header needs is the lib/bvh type definitions of the caller's own tree.
 //
 // Differences a caller can observe:
-//   * Scalar = float only.  render<double> (anim -d, anim.cpp:154-155) fails to compile with a static_assert: the
-//     GPU path has no double variant and there is NO CPU fallback.
+//   * Scalar = double (anim -d, anim.cpp:154-155) renders through ceres_render_f64: one kernel on one GPU, same
+//     results as the reference's double build (hit ids bit for bit), without the float path's host-frame pipeline.
 //   * tri_norms may be nullptr (static.cpp:130 passes nullptr, which does not even deduce against the reference
 //     signature): normals are then taken as zero, as the reference would read them if it could.
 //   * errors (no GPU, CUDA failure, malformed BVH) throw std::runtime_error; the reference has no error path.
@@ -157,21 +157,74 @@ inline ceres_scene* scene_for(const bvh::Bvh<float>& bvh, const bvh::Triangle<fl
 
 }  // namespace ceres
 
+namespace ceres {
+
+namespace detail {
+struct SceneCacheF64 {
+    ceres_scene_f64* scene = nullptr;
+    const void* nodes = nullptr; const void* tris = nullptr; const void* norms = nullptr;
+    size_t node_count = 0, tri_count = 0;
+    uint64_t fingerprint = 0;
+    ~SceneCacheF64() { if (scene) ceres_scene_f64_destroy(scene); }
+};
+inline SceneCacheF64& cache_f64() { static SceneCacheF64 c; return c; }
+}  // namespace detail
+
+// the double-precision scene on the GPU; same caching rule as scene_for above
+inline ceres_scene_f64* scene_for(const bvh::Bvh<double>& bvh, const bvh::Triangle<double>* triangles,
+                                  const std::array<bvh::Vector3<double>, 3>* tri_norms) {
+    static_assert(sizeof(bvh::Bvh<double>::Node) == 64, "lib/bvh/bvh.hpp:20-28");
+    static_assert(sizeof(bvh::Triangle<double>) == 96, "lib/bvh/triangle.hpp:27");
+    static_assert(sizeof(std::array<bvh::Vector3<double>, 3>) == 72, "lib/obj_norms.hpp:113-115");
+    auto& c = detail::cache_f64();
+    const void* nodes = bvh.nodes.get();
+    size_t tri_count = c.tri_count;
+    const bool same_arrays = c.scene && c.nodes == nodes && c.tris == triangles && c.norms == tri_norms && c.node_count == bvh.node_count;
+    if (!same_arrays) {
+        tri_count = 0;
+        for (size_t k = 0; k < bvh.node_count; ++k) tri_count += bvh.nodes[k].primitive_count;
+    }
+    uint64_t fp = 1469598103934665603ull;
+    fp = detail::sample(nodes, bvh.node_count * 64, fp);
+    fp = detail::sample(triangles, tri_count * 96, fp);
+    fp = detail::sample(tri_norms, tri_norms ? tri_count * 72 : 0, fp);
+    if (same_arrays && fp == c.fingerprint) return c.scene;
+    if (c.scene) ceres_scene_f64_destroy(c.scene);
+    c = detail::SceneCacheF64{};
+    ceres_scene_f64* s = nullptr;
+    if (ceres_scene_f64_create(nodes, bvh.node_count, bvh.primitive_indices.get(), triangles, tri_norms, tri_count, device(), &s) != CERES_OK)
+        detail::fail("ceres_scene_f64_create");
+    c.scene = s; c.nodes = nodes; c.tris = triangles; c.norms = tri_norms;
+    c.node_count = bvh.node_count; c.tri_count = tri_count; c.fingerprint = fp;
+    return s;
+}
+
+}  // namespace ceres
+
 template <typename Scalar>
 std::pair<int, int> render(const Camera<Scalar>& camera, const bvh::Vector3<Scalar>& sun_position,
                            const bvh::Bvh<Scalar>& bvh, const bvh::Triangle<Scalar>* triangles,
                            std::array<bvh::Vector3<Scalar>, 3>* tri_norms, Scalar* pixels,
                            size_t width, size_t height) {
-    static_assert(std::is_same<Scalar, float>::value,
-                  "ceres_b200 renders Scalar = float only; there is no double GPU path and no CPU fallback");
-    ceres_scene* scene = ceres::scene_for(bvh, triangles, tri_norms);
-    ceres_camera cam;
-    for (int k = 0; k < 3; ++k) { cam.eye[k] = camera.eye[k]; cam.dir[k] = camera.dir[k]; cam.up[k] = camera.up[k]; }
-    cam.fov = camera.fov;
-    const float sun[3] = {sun_position[0], sun_position[1], sun_position[2]};
+    static_assert(std::is_same<Scalar, float>::value || std::is_same<Scalar, double>::value, "Scalar is float or double");
     uint64_t counters[2] = {0, 0};
-    if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, counters) != CERES_OK)
-        ceres::detail::fail("ceres_render");
+    if constexpr (std::is_same<Scalar, float>::value) {
+        ceres_scene* scene = ceres::scene_for(bvh, triangles, tri_norms);
+        ceres_camera cam;
+        for (int k = 0; k < 3; ++k) { cam.eye[k] = camera.eye[k]; cam.dir[k] = camera.dir[k]; cam.up[k] = camera.up[k]; }
+        cam.fov = camera.fov;
+        const float sun[3] = {sun_position[0], sun_position[1], sun_position[2]};
+        if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, counters) != CERES_OK)
+            ceres::detail::fail("ceres_render");
+    } else {
+        ceres_scene_f64* scene = ceres::scene_for(bvh, triangles, tri_norms);
+        ceres_camera_f64 cam;
+        for (int k = 0; k < 3; ++k) { cam.eye[k] = camera.eye[k]; cam.dir[k] = camera.dir[k]; cam.up[k] = camera.up[k]; }
+        cam.fov = camera.fov;
+        const double sun[3] = {sun_position[0], sun_position[1], sun_position[2]};
+        if (ceres_render_f64(scene, &cam, sun, width, height, 0u, pixels, nullptr, counters, nullptr) != CERES_OK)
+            ceres::detail::fail("ceres_render_f64");
+    }
     return std::pair<int, int>(static_cast<int>(counters[0]), static_cast<int>(counters[1]));   // render.hpp:155
 }
 

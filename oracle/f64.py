@@ -100,8 +100,16 @@ def ref_lib():
         L.cref64_render.restype = C.c_double
         L.cref64_render.argtypes = [vp, vp, vp, vp, sz, sz, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.cref64_render_ex.argtypes = [vp, vp, vp, sz, sz, C.c_uint, vp, vp, vp, vp]
+        L.cref64_turntable.argtypes = [vp, vp, vp, C.c_int, vp]
         _ref = L
     return _ref
+
+
+def ref_turntable(cam, sun, axis, n_frames):
+    """n_frames x 13 doubles (eye, dir, up, fov, sun): the camera path of anim.cpp:77-89 computed by the reference in double."""
+    out = np.zeros((n_frames, 13), np.float64)
+    ref_lib().cref64_turntable(_p(_f64(cam)), _p(_f64(sun)), _p(_f64(axis)), n_frames, _p(out))
+    return out
 
 
 class RefScene64:

@@ -176,4 +176,23 @@ void cref64_render_ex(void* h, const double* cam, const double* sun, size_t widt
     if (counters) { counters[0] = n_rays; counters[1] = n_hits; }
 }
 
+// Turntable camera sequence in double: the statements of anim.cpp:77-89 with Scalar = double (Transform::rotate about
+// `axis`, applied to the PREVIOUS camera each frame).  cams_out: n_frames x 13 doubles (eye, dir, up, fov, sun).
+void cref64_turntable(const double* cam, const double* sun, const double* axis, int n_frames, double* cams_out) {
+    constexpr Scalar pi = Scalar(3.14159265359);
+    auto camera = make_camera(cam);
+    Vector3 sun_position(sun[0], sun[1], sun[2]);
+    Scalar rotation_step_degrees = 360.0f / n_frames;
+    auto t_cam = Transform<Scalar>().rotate(Vector3(axis[0], axis[1], axis[2]), rotation_step_degrees / 180.0f * pi);
+    auto t_sun = Transform<Scalar>().rotate(Vector3(axis[0], axis[1], axis[2]), rotation_step_degrees / 180.0f * pi);
+    for (int i = 0; i < n_frames; i++) {
+        camera.eye = t_cam(camera.eye);
+        camera.dir = t_cam(camera.dir);
+        sun_position = t_sun(sun_position);
+        double* o = cams_out + 13 * i;
+        for (int k = 0; k < 3; ++k) { o[k] = camera.eye[k]; o[3 + k] = camera.dir[k]; o[6 + k] = camera.up[k]; o[10 + k] = sun_position[k]; }
+        o[9] = camera.fov;
+    }
+}
+
 } // extern "C"

@@ -161,9 +161,24 @@ def test_anim_binary_matches_reference_turntable(tmp_path):
         assert (img != 0).any()
     assert f"Total Rays: {total}" in r.stdout
     s.close()
-    # -d is refused loudly
-    r = subprocess.run([ANIM, "-d", out], capture_output=True, text=True)
-    assert r.returncode != 0 and "double" in r.stderr
+    # -d (anim.cpp:154-155): loader, builder, camera path and render in double, against the reference's double build
+    from oracle import f64
+    if not f64.ref_available():
+        return
+    out = str(tmp_path / "turnd.mp4")
+    r = subprocess.run([ANIM, "-d", "--input", obj, "--frames", "3", "--width", str(W), "--height", str(H), out],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    s = f64.RefScene64.load_obj(obj)
+    cams = f64.ref_turntable(f64.cam_array((-150, -20, 0), (1, -0.1, 0), (0, -1, 0), 60), [-500, 300, 10], [0, 1, 0], 3)
+    for k in range(3):
+        px, (rays, hits), _ = s.render(cams[k, :10], cams[k, 10:13], W, H)
+        assert f"Rays: {rays}\tHits: {hits}" in r.stdout
+        img = read_ppm(str(tmp_path / f"turnd_{k:04d}.ppm"))
+        d = img.astype(np.int16) - quantise(px.astype(np.float32)).astype(np.int16)
+        assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-5
+        assert (img != 0).any()
+    s.close()
 
 
 @needs_binaries
