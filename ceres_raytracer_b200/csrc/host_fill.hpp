@@ -22,7 +22,18 @@
 
 namespace ceres_host {
 
-struct Segment { unsigned char* p; size_t n; unsigned char byte; };
+// src == nullptr: fill n bytes with `byte`; widen == false: copy n bytes from src; widen == true: n floats at src -> n doubles at p
+struct Segment { unsigned char* p; size_t n; unsigned char byte; const unsigned char* src = nullptr; bool widen = false; };
+
+// float -> double, exact (the double-precision path's colours are float-valued, render.hpp:56-84): the frame crosses PCIe
+// as floats and is widened into the caller's double buffer here
+inline void widen_f32(double* dst, const float* src, size_t n) {
+    size_t k = 0;
+#if defined(__AVX2__)
+    for (; k + 4 <= n; k += 4) _mm256_storeu_pd(dst + k, _mm256_cvtps_pd(_mm_loadu_ps(src + k)));
+#endif
+    for (; k < n; ++k) dst[k] = (double)src[k];
+}
 
 inline void fill_bytes(unsigned char* p, size_t n, unsigned char byte) {
 #if defined(__AVX2__)
@@ -61,10 +72,15 @@ struct Job {
         while (n > piece + piece / 2) { segs.push_back({b, piece, byte}); b += piece; n -= piece; }
         if (n) segs.push_back({b, n, byte});
     }
+    void add_copy(void* dst, const void* src, size_t bytes) { if (bytes) segs.push_back({static_cast<unsigned char*>(dst), bytes, 0, static_cast<const unsigned char*>(src), false}); }
+    void add_widen(double* dst, const float* src, size_t count) { if (count) segs.push_back({reinterpret_cast<unsigned char*>(dst), count, 0, reinterpret_cast<const unsigned char*>(src), true}); }
     bool work_one() {
         const size_t k = next.fetch_add(1, std::memory_order_relaxed);
         if (k >= segs.size()) return false;
-        fill_bytes(segs[k].p, segs[k].n, segs[k].byte);
+        const Segment& g = segs[k];
+        if (!g.src) fill_bytes(g.p, g.n, g.byte);
+        else if (g.widen) widen_f32(reinterpret_cast<double*>(g.p), reinterpret_cast<const float*>(g.src), g.n);
+        else std::memcpy(g.p, g.src, g.n);
         done.fetch_add(1, std::memory_order_release);
         return true;
     }

@@ -42,8 +42,9 @@ struct Scene64 {
 struct Frame64 {
     double eye[3], dir[3], iu[3], iv[3], sun[3];
     uint32_t width, height, flags;
-    double* pixels; uint32_t* ids;
+    float* rgb; uint32_t* ids;      // the colours are float-valued (render.hpp:56-84): 3 floats per pixel on the device
     unsigned long long* counters;   // rays beyond W*H (= primary hits), hits
+    int* rect;                      // min i, min j, max i, max j over the pixels whose primary ray hit
 };
 
 struct Ray64 { D3 o, d; double tmax; int oct[3]; double inv[3], so[3]; };
@@ -188,12 +189,19 @@ __global__ void __launch_bounds__(128) render_kernel(const Scene64 sc, const Fra
             if (!occluded) smooth_shading(sun_line, sc.norms + 9ull * hit.slot, view, hu, hv, rgb);
             else hits = 2;
         }
-        f.pixels[3 * pix] = (double)rgb[0]; f.pixels[3 * pix + 1] = (double)rgb[1]; f.pixels[3 * pix + 2] = (double)rgb[2];
+        f.rgb[3 * pix] = rgb[0]; f.rgb[3 * pix + 1] = rgb[1]; f.rgb[3 * pix + 2] = rgb[2];
         if (f.ids) f.ids[pix] = hit.hit ? sc.slot_id[hit.slot] : 0xFFFFFFFFu;
     }
     const unsigned int shadow_rays = (f.flags & CERES_NO_SHADOWS) ? 0u : primary_hit;
     const unsigned int r = __reduce_add_sync(0xFFFFFFFFu, shadow_rays), h = __reduce_add_sync(0xFFFFFFFFu, hits);
-    if (lane == 0 && (r | h)) { atomicAdd(&f.counters[0], (unsigned long long)r); atomicAdd(&f.counters[1], (unsigned long long)h); }
+    if (h) {        // warp-uniform: some lane hit -> widen the frame's hit rectangle
+        const int x0 = __reduce_min_sync(0xFFFFFFFFu, primary_hit ? (int)i : 0x7FFFFFFF), y0 = __reduce_min_sync(0xFFFFFFFFu, primary_hit ? (int)j : 0x7FFFFFFF);
+        const int x1 = __reduce_max_sync(0xFFFFFFFFu, primary_hit ? (int)i : -1), y1 = __reduce_max_sync(0xFFFFFFFFu, primary_hit ? (int)j : -1);
+        if (lane == 0) {
+            atomicAdd(&f.counters[0], (unsigned long long)r); atomicAdd(&f.counters[1], (unsigned long long)h);
+            atomicMin(&f.rect[0], x0); atomicMin(&f.rect[1], y0); atomicMax(&f.rect[2], x1); atomicMax(&f.rect[3], y1);
+        }
+    }
 }
 
 }  // namespace f64
@@ -203,9 +211,10 @@ struct ceres_scene_f64 {
     int device = 0;
     f64::Scene64 dev{};
     void* d_pairs = nullptr; double* d_tris = nullptr; double* d_norms = nullptr; uint32_t* d_slot_id = nullptr;
-    double* d_pixels = nullptr; size_t pixels_cap = 0;
+    float* d_rgb = nullptr; size_t pixels_cap = 0;
     uint32_t* d_ids = nullptr; size_t ids_cap = 0;
-    unsigned long long* d_counters = nullptr;
+    unsigned long long* d_counters = nullptr;           // 2 counters followed by the 4 ints of the hit rectangle
+    float* h_rgb = nullptr; uint32_t* h_ids = nullptr; size_t stage_cap = 0;      // page-locked staging of the hit rectangle
     size_t tri_count = 0, node_count = 0;
 };
 
@@ -295,7 +304,7 @@ int ceres_scene_f64_create(const void* nodes_v, size_t node_count, const size_t*
     TRY_D(cudaMalloc((void**)&s->d_tris, tri_slots.size() * 8));
     TRY_D(cudaMalloc((void**)&s->d_norms, norm_slots.size() * 8));
     TRY_D(cudaMalloc((void**)&s->d_slot_id, slot_id.size() * 4));
-    TRY_D(cudaMalloc((void**)&s->d_counters, 2 * sizeof(unsigned long long)));
+    TRY_D(cudaMalloc((void**)&s->d_counters, 4 * sizeof(unsigned long long)));
     TRY_D(cudaMemcpy(s->d_pairs, pairs.data(), pairs.size() * sizeof(f64::Child), cudaMemcpyHostToDevice));
     TRY_D(cudaMemcpy(s->d_tris, tri_slots.data(), tri_slots.size() * 8, cudaMemcpyHostToDevice));
     TRY_D(cudaMemcpy(s->d_norms, norm_slots.data(), norm_slots.size() * 8, cudaMemcpyHostToDevice));
@@ -311,7 +320,9 @@ void ceres_scene_f64_destroy(ceres_scene_f64* s) {
     if (!s) return;
     DeviceGuard guard(s->device);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
-    cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_counters);
+    cudaFree(s->d_rgb); cudaFree(s->d_ids); cudaFree(s->d_counters);
+    if (s->h_rgb) cudaFreeHost(s->h_rgb);
+    if (s->h_ids) cudaFreeHost(s->h_ids);
     delete s;
 }
 
@@ -323,8 +334,8 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
     if (s->pixels_cap < npix) {
-        cudaFree(s->d_pixels); s->d_pixels = nullptr; s->pixels_cap = 0;
-        CUDA_TRY(cudaMalloc((void**)&s->d_pixels, npix * 24));
+        cudaFree(s->d_rgb); s->d_rgb = nullptr; s->pixels_cap = 0;
+        CUDA_TRY(cudaMalloc((void**)&s->d_rgb, npix * 12));
         s->pixels_cap = npix;
     }
     if (ids && s->ids_cap < npix) {
@@ -350,22 +361,62 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
         }
     }
     f.width = (uint32_t)width; f.height = (uint32_t)height; f.flags = flags;
-    f.pixels = s->d_pixels; f.ids = ids ? s->d_ids : nullptr; f.counters = s->d_counters;
+    f.rgb = s->d_rgb; f.ids = ids ? s->d_ids : nullptr; f.counters = s->d_counters; f.rect = reinterpret_cast<int*>(s->d_counters + 2);
+    struct Out { unsigned long long c[2]; int rect[4]; } o = {{0, 0}, {0x7FFFFFFF, 0x7FFFFFFF, -1, -1}};
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    CUDA_TRY(cudaMemset(s->d_counters, 0, 2 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemcpy(s->d_counters, &o, sizeof o, cudaMemcpyHostToDevice));
     if (kernel_ms) { CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventRecord(e0, 0)); }
     f64::render_kernel<<<dim3((unsigned)((width + 15) / 16), (unsigned)((height + 7) / 8)), 128>>>(s->dev, f);
     g_launches++;
     if (kernel_ms) cudaEventRecord(e1, 0);
     cudaError_t err = cudaGetLastError();
-    if (err == cudaSuccess) err = cudaMemcpy(pixels, s->d_pixels, npix * 24, cudaMemcpyDeviceToHost);
-    if (err == cudaSuccess && ids) err = cudaMemcpy(ids, s->d_ids, npix * 4, cudaMemcpyDeviceToHost);
-    unsigned long long c[2] = {0, 0};
-    if (err == cudaSuccess) err = cudaMemcpy(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost);
+    if (err == cudaSuccess) err = cudaMemcpy(&o, s->d_counters, sizeof o, cudaMemcpyDeviceToHost);
     if (kernel_ms && err == cudaSuccess) { float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1); *kernel_ms = ms; }
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
+    // Only the rectangle of pixels that hit something crosses PCIe, as floats, into page-locked staging; host threads
+    // widen it into the caller's frame and write the zeros (ids: CERES_MISS) around it meanwhile.
+    const bool any = o.rect[2] >= o.rect[0] && o.rect[3] >= o.rect[1];
+    const size_t x0 = any ? (size_t)o.rect[0] : 0, y0 = any ? (size_t)o.rect[1] : 0;
+    const size_t rw = any ? (size_t)(o.rect[2] - o.rect[0] + 1) : 0, rh = any ? (size_t)(o.rect[3] - o.rect[1] + 1) : 0;
+    if (err == cudaSuccess && rw * rh > s->stage_cap) {
+        if (s->h_rgb) cudaFreeHost(s->h_rgb);
+        if (s->h_ids) cudaFreeHost(s->h_ids);
+        s->h_rgb = nullptr; s->h_ids = nullptr; s->stage_cap = 0;
+        err = cudaMallocHost((void**)&s->h_rgb, rw * rh * 12);
+        if (err == cudaSuccess) err = cudaMallocHost((void**)&s->h_ids, rw * rh * 4);
+        if (err == cudaSuccess) s->stage_cap = rw * rh;
+    }
+    if (err == cudaSuccess && any) {
+        err = cudaMemcpy2DAsync(s->h_rgb, rw * 12, s->d_rgb + 3 * (width * y0 + x0), width * 12, rw * 12, rh, cudaMemcpyDeviceToHost, 0);
+        if (err == cudaSuccess && ids) err = cudaMemcpy2DAsync(s->h_ids, rw * 4, s->d_ids + (width * y0 + x0), width * 4, rw * 4, rh, cudaMemcpyDeviceToHost, 0);
+    }
+    if (err == cudaSuccess) {
+        ceres_host::Job zeros, body;
+        auto outside = [&](unsigned char* base, size_t px_bytes, unsigned char byte) {
+            if (!any) { zeros.add(base, npix * px_bytes, byte); return; }
+            zeros.add(base, width * y0 * px_bytes, byte);
+            zeros.add(base + width * (y0 + rh) * px_bytes, width * (height - y0 - rh) * px_bytes, byte);
+            for (size_t j = y0; j < y0 + rh; ++j) {
+                unsigned char* row = base + width * j * px_bytes;
+                if (x0) zeros.segs.push_back({row, x0 * px_bytes, byte});
+                if (x0 + rw < width) zeros.segs.push_back({row + (x0 + rw) * px_bytes, (width - x0 - rw) * px_bytes, byte});
+            }
+        };
+        outside(reinterpret_cast<unsigned char*>(pixels), 24, 0x00);
+        if (ids) outside(reinterpret_cast<unsigned char*>(ids), 4, 0xFF);
+        ceres_host::Pool::instance().submit(&zeros);
+        err = cudaStreamSynchronize(0);
+        for (size_t j = 0; j < rh && err == cudaSuccess; ++j) {
+            body.add_widen(pixels + 3 * (width * (y0 + j) + x0), s->h_rgb + 3 * rw * j, 3 * rw);
+            if (ids) body.add_copy(ids + width * (y0 + j) + x0, s->h_ids + rw * j, rw * 4);
+        }
+        ceres_host::Pool::instance().submit(&body);
+        ceres_host::Pool::instance().wait(&zeros);
+        ceres_host::Pool::instance().wait(&body);
+    }
     if (err != cudaSuccess) return fail(CERES_ERR_CUDA, std::string("ceres_render_f64: ") + cudaGetErrorString(err));
+    const unsigned long long c[2] = {o.c[0], o.c[1]};
     if (counters) { counters[0] = (uint64_t)npix + c[0]; counters[1] = c[1]; }      // render.hpp:115,138 / :119,148
     return CERES_OK;
 }
