@@ -15,3 +15,5 @@ if [ -s gpurun_out/bench.json ]; then
 fi
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
 python bench.py --workload dragon_turntable_4k --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_seq4k_n1.json 2> gpurun_out/bench_seq4k_n1.err; tail -2 gpurun_out/bench_seq4k_n1.err
+python profiles/f64_probe.py > gpurun_out/f64_probe.log 2>&1; tail -2 gpurun_out/f64_probe.log
+python profiles/lbvh_probe.py grid448_4k_shadow > gpurun_out/lbvh_probe.log 2>&1; tail -7 gpurun_out/lbvh_probe.log
