@@ -155,6 +155,7 @@ int scene(const Options& opt) {
     std::vector<std::string> errors(gpus);
     auto wall = std::chrono::high_resolution_clock::now();
     auto worker_f32 = [&](int g) {
+      if constexpr (std::is_same<Scalar, float>::value) {      // the other instantiation never takes this branch
         ceres_scene* scene = nullptr;
         if (ceres_scene_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
                                tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
@@ -200,10 +201,12 @@ int scene(const Options& opt) {
         drain(0); drain(1);
         ceres_host_free(buffers[0]); ceres_host_free(buffers[1]);
         ceres_scene_destroy(scene);
+      }
     };
     // Scalar = double: ceres_render_f64 fills a double frame; its colours are float-valued (render.hpp:56-84 accumulates
     // in float), so they are narrowed without loss for the same writers.
     auto worker_f64 = [&](int g) {
+      if constexpr (std::is_same<Scalar, double>::value) {
         ceres_scene_f64* scene = nullptr;
         if (ceres_scene_f64_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
                                    tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
@@ -244,6 +247,7 @@ int scene(const Options& opt) {
         }
         drain(0); drain(1);
         ceres_scene_f64_destroy(scene);
+      }
     };
     auto worker = [&](int g) {
         if constexpr (std::is_same<Scalar, float>::value) worker_f32(g); else worker_f64(g);

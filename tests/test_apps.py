@@ -16,6 +16,7 @@ from oracle import ref
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 RENDER = os.path.join(ROOT, "apps", "_build", "render")
 ANIM = os.path.join(ROOT, "apps", "_build", "anim")
+SHIM_CHECK = os.path.join(ROOT, "apps", "_build", "shim_check")
 RGB_ATOL = 1e-6
 
 
@@ -179,6 +180,50 @@ def test_anim_binary_matches_reference_turntable(tmp_path):
         assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-5
         assert (img != 0).any()
     s.close()
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.skipif(not os.path.exists(SHIM_CHECK), reason="apps/_build/shim_check not built")
+def test_drop_in_header_renders_float_and_double_like_the_reference(tmp_path):
+    """render<float>() and render<double>() called through include/ceres/render.hpp by a caller that is otherwise the
+    reference's own code (loader, SweepSah builder): counters equal, frame sums equal to 1e-6 relative."""
+    import re
+    from oracle import f64
+    obj = str(tmp_path / "torus.obj")
+    write_torus_obj(obj, 64, 32)
+    with open(obj, "rb") as f:
+        txt = f.read().decode().replace("\r\n", "\n").split("\n")
+    with open(obj, "w") as f:
+        for line in txt:
+            if line.startswith("v "):
+                a, b, c = (float(t) * 40 for t in line.split()[1:4])
+                f.write(f"v {a:.5f} {b:.5f} {c:.5f}\n")
+            else:
+                f.write(line + "\n")
+    W, H = 200, 320
+    r = subprocess.run([SHIM_CHECK, obj, str(W), str(H)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    got = {}
+    for m in re.finditer(r"(float|double) pass (\d): rays (\d+) hits (\d+) lit (\d+) negative (\d+) sum (\S+)", r.stdout):
+        got[(m.group(1), int(m.group(2)))] = (int(m.group(3)), int(m.group(4)), int(m.group(5)), int(m.group(6)), float(m.group(7)))
+    assert len(got) == 4, r.stdout
+    s32 = ref.RefScene.load_obj(obj, builder=0)
+    s64 = f64.RefScene64.load_obj(obj) if f64.ref_available() else None
+    sun = [-500, 300, 10]
+    for k in range(2):
+        eye = (-150 + 5 * k, -20, 0)
+        px, rays, hits, _ = s32.render(ref.cam_array(eye, (1, -0.1, 0), (0, -1, 0), 60), sun, W, H)
+        g = got[("float", k)]
+        assert g[:2] == (rays, hits) and g[3] == 0 and g[2] == int((px > 0).sum())
+        assert abs(g[4] - float(px.astype(np.float64).sum())) <= 1e-6 * max(1.0, abs(g[4]))
+        if s64 is not None:
+            px, (rays, hits), _ = s64.render(f64.cam_array(eye, (1, -0.1, 0), (0, -1, 0), 60), np.array(sun, np.float64), W, H)
+            g = got[("double", k)]
+            assert g[:2] == (rays, hits) and g[3] == 0 and g[2] == int((px > 0).sum())
+            assert abs(g[4] - float(px.sum())) <= 1e-6 * max(1.0, abs(g[4]))
+    assert got[("float", 0)][1] > 0 and got[("float", 0)] != got[("float", 1)]
+    s32.close()
 
 
 @needs_binaries
