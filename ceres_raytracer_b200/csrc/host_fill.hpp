@@ -37,7 +37,8 @@ inline void widen_f32(double* dst, const float* src, size_t n) {
 
 inline void fill_bytes(unsigned char* p, size_t n, unsigned char byte) {
 #if defined(__AVX2__)
-    if (n >= 256) {
+    static const bool cached = std::getenv("CERES_HOST_FILL_CACHED") != nullptr;      // experiment switch: plain memset
+    if (n >= 256 && !cached) {
         // streaming stores: the framebuffer is write-only here, do not pull it through the caches
         size_t head = (32 - (reinterpret_cast<uintptr_t>(p) & 31)) & 31;
         std::memset(p, byte, head);
