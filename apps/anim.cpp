@@ -11,7 +11,7 @@
 //     frame, no host-frame pipeline); the colours of render<double>() are float-valued, so the writers take them narrowed.
 //   * upstream encodes the frames with ImageMagick 7 Magick++ (anim.cpp:112-127) -- unavailable on this box.  Frames
 //     are written as <out_file stem>_NNNN.ppm instead (16-bit P6 with --ppm16, matching the x65535 quantum scaling of
-//     anim.cpp:117-119; 8-bit static.cpp-style by default).
+//     anim.cpp:117-119; 8-bit static.cpp-style by default), quantised and flipped on the GPU.
 //   * frames are independent once the camera path is known; the path is iterative (each frame transforms the previous
 //     camera, anim.cpp:87-89), so it is computed serially on the host first and the frames are then dealt round-robin
 //     to the GPUs (--gpus N), one host thread per GPU, scene replicated.
@@ -159,10 +159,13 @@ int scene(const Options& opt) {
         ceres_scene* scene = nullptr;
         if (ceres_scene_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
                                tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
-        // two page-locked frames per GPU: frame k is quantised and written by a writer thread while frame k+1 renders
-        // (upstream encodes synchronously inside the frame loop, anim.cpp:112-127)
-        float* buffers[2] = {static_cast<float*>(ceres_host_alloc(3 * width * height * sizeof(float))),
-                             static_cast<float*>(ceres_host_alloc(3 * width * height * sizeof(float)))};
+        // The frames leave the GPU as the file's payload: quantised and flipped on the device (ceres_render_ppm8 /
+        // ceres_render_ppm16), so a quarter / half of the float frame's bytes cross PCIe.  Two page-locked payload
+        // buffers per GPU: frame k is written by a writer thread while frame k+1 renders (SURVEY.md 8(f) N1 + N4;
+        // upstream encodes synchronously inside the frame loop, anim.cpp:112-127).
+        const int bpc = ppm16 ? 2 : 1;
+        const size_t payload = 3 * width * height * (size_t)bpc;
+        uint8_t* buffers[2] = {static_cast<uint8_t*>(ceres_host_alloc(payload)), static_cast<uint8_t*>(ceres_host_alloc(payload))};
         if (!buffers[0] || !buffers[1]) {
             errors[g] = ceres_last_error(); ceres_host_free(buffers[0]); ceres_host_free(buffers[1]); ceres_scene_destroy(scene); return;
         }
@@ -176,14 +179,16 @@ int scene(const Options& opt) {
         int turn = 0;
         for (int i = g; i < n_frames; i += gpus, turn ^= 1) {
             if (!drain(turn)) break;
-            float* pixels = buffers[turn];
+            uint8_t* bytes = buffers[turn];
             ceres_camera cam;
             for (int k = 0; k < 3; ++k) { cam.eye[k] = (float)path[i].camera.eye[k]; cam.dir[k] = (float)path[i].camera.dir[k]; cam.up[k] = (float)path[i].camera.up[k]; }
             cam.fov = (float)path[i].camera.fov;
             const float sun[3] = {(float)path[i].sun[0], (float)path[i].sun[1], (float)path[i].sun[2]};
             uint64_t cnt[2] = {0, 0};
             auto t0 = std::chrono::high_resolution_clock::now();
-            if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, cnt) != CERES_OK) { errors[g] = ceres_last_error(); break; }
+            const int rc = ppm16 ? ceres_render_ppm16(scene, &cam, sun, width, height, 0u, bytes, cnt)
+                                 : ceres_render_ppm8(scene, &cam, sun, width, height, 0u, bytes, cnt);
+            if (rc != CERES_OK) { errors[g] = ceres_last_error(); break; }
             const double s = seconds_since(t0);
             std::ostringstream os;
             os << "Rendering image " << i << " (" << width << "x" << height << ") on GPU " << g << "...\n"
@@ -193,8 +198,7 @@ int scene(const Options& opt) {
             if (!no_output) {
                 const std::string name = frame_name(out_file, i);
                 writing[turn] = std::async(std::launch::async, [=]() -> std::string {
-                    const bool ok = ppm16 ? ceres_apps::write_ppm16(name, pixels, width, height) : ceres_apps::write_ppm(name, pixels, width, height);
-                    return ok ? std::string() : "cannot write " + name;
+                    return ceres_apps::write_ppm_bytes(name, bytes, width, height, bpc) ? std::string() : "cannot write " + name;
                 });
             }
         }

@@ -37,11 +37,13 @@ inline bool write_ppm(const std::string& path, const float* pixels, size_t width
 }
 
 // P6 payload that is already quantised and flipped (ceres_render_ppm8)
-inline bool write_ppm_bytes(const std::string& path, const uint8_t* bytes, size_t width, size_t height) {
+// (bytes_per_channel 1: ceres_render_ppm8, maxval 255; 2: ceres_render_ppm16, maxval 65535, big-endian)
+inline bool write_ppm_bytes(const std::string& path, const uint8_t* bytes, size_t width, size_t height, int bytes_per_channel = 1) {
     std::FILE* f = std::fopen(path.c_str(), "wb");
     if (!f) return false;
-    std::fprintf(f, "P6 %zu %zu 255\n", width, height);
-    const bool ok = std::fwrite(bytes, 1, 3 * width * height, f) == 3 * width * height;
+    std::fprintf(f, "P6 %zu %zu %d\n", width, height, bytes_per_channel == 2 ? 65535 : 255);
+    const size_t n = 3 * width * height * (size_t)bytes_per_channel;
+    const bool ok = std::fwrite(bytes, 1, n, f) == n;
     return std::fclose(f) == 0 && ok;
 }
 

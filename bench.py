@@ -497,6 +497,20 @@ def main():
         ppm8 = {"value": rays_frame / (t_ppm8 / steps_e2e) / 1e6, "unit": UNIT, "ms_per_step": 1e3 * t_ppm8 / steps_e2e,
                 "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm8() -> page-locked 8-bit P6 payload"}
         hb8.close()
+        # and as 16-bit payload (the x 65535 scaling of anim.cpp:117-119 on the device): half of the bytes
+        hb16 = cr.PinnedBuffer((H, W, 3), np.uint16)
+        for _ in range(2):
+            scene.render_ppm16(cam, sun, W, H, flags=flags, out=hb16.array)
+        t_ppm16 = 0.0
+        for _ in range(steps_e2e):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            scene.render_ppm16(cam, sun, W, H, flags=flags, out=hb16.array)
+            t_ppm16 += time.perf_counter() - t0
+        ppm8["ppm16"] = {"value": rays_frame / (t_ppm16 / steps_e2e) / 1e6, "unit": UNIT, "ms_per_step": 1e3 * t_ppm16 / steps_e2e,
+                         "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm16() -> page-locked 16-bit P6 payload"}
+        hb16.close()
         scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)      # last_d2h_bytes of the float path again
         d2h = scene.last_d2h_bytes        # the screen rectangle of the scene + counters; the rest of the frame is host-filled zeros
     else:

@@ -48,7 +48,7 @@ SYMBOLS = [
     "ceres_peer_frame_create", "ceres_peer_frame_open", "ceres_peer_frame_alias", "ceres_peer_frame_destroy",
     "ceres_peer_frame_pixels", "ceres_peer_frame_ids", "ceres_render_peer", "ceres_peer_frame_error",
 ]
-SYMBOLS += ["ceres_render_ppm8", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download"]
+SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -106,6 +106,7 @@ def lib():
     L.ceres_render_peer.argtypes = [vp, camp, vp, C.c_uint, vp, vp, vp]
     L.ceres_peer_frame_error.argtypes = [vp]
     L.ceres_render_ppm8.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp]
+    L.ceres_render_ppm16.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp]
     L.ceres_probe_read_bandwidth.argtypes = [C.c_int, sz, C.c_int, vp]
     L.ceres_build_lbvh.argtypes = [vp, sz, C.c_int, vp, vp, vp]
     L.ceres_scene_create_lbvh.argtypes = [vp, vp, sz, C.c_int, vp, vp]

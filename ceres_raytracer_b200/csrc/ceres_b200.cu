@@ -563,21 +563,25 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 
 // Same quantisation restricted to frame rows [j0, j1) x columns [i0, i1) (the screen rectangle of the scene): the
 // host-frame P6 path copies only that rectangle and fills the rest with zeros on the host.
+template <int BPC>       // bytes per channel: 1 = static.cpp:135-147 (x 255), 2 = the x 65535 quantum scaling of anim.cpp:117-119, big-endian
 __global__ void __launch_bounds__(256) quantize_rect_kernel(const float* __restrict__ px, uint32_t W, uint32_t H, uint32_t i0, uint32_t i1,
                                                             uint32_t j0, uint32_t j1, uint8_t* __restrict__ out) {
     const uint32_t rw = i1 - i0;
     const size_t n = (size_t)rw * (j1 - j0);
+    const float top = BPC == 1 ? 255.0f : 65535.0f;
     for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < n; k += (size_t)gridDim.x * 256u) {
         const uint32_t rj = (uint32_t)(k / rw), i = i0 + (uint32_t)(k - (size_t)rj * rw);
         const uint32_t j = j0 + rj, row_out = H - 1u - j;
         const float* p = px + 3 * ((size_t)j * W + i);
-        uint8_t* o = out + 3 * ((size_t)row_out * W + i);
+        uint8_t* o = out + 3 * BPC * ((size_t)row_out * W + i);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            float x = mul(p[c], 255.0f);
-            float y = (255.0f < x) ? 255.0f : x;
+            float x = mul(p[c], top);
+            float y = (top < x) ? top : x;
             float z = (y < 0.0f) ? 0.0f : y;
-            o[c] = (uint8_t)(int)z;
+            const unsigned q = (unsigned)(int)z;
+            if (BPC == 1) o[c] = (uint8_t)q;
+            else { o[2 * c] = (uint8_t)(q >> 8); o[2 * c + 1] = (uint8_t)(q & 0xFFu); }
         }
     }
 }
@@ -1928,9 +1932,13 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
 // The frame as the payload of the reference's P6 file (static.cpp:135-147): render, quantise on the device, and move
 // only the 8-bit screen rectangle over PCIe (a quarter of the float path's bytes); the rest of the image is zero-filled
 // by the host pool.  rgb8: HOST 3*width*height bytes, row 0 = frame row height-1.
-int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
-                      uint8_t* rgb8, uint64_t counters[2]) {
-    if (!s || !rgb8) return fail(CERES_ERR_INVALID, "ceres_render_ppm8: null argument");
+}  // extern "C"
+
+// The host-frame path for an already quantised, vertically flipped P6 payload with BPC bytes per channel.
+template <int BPC>
+static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
+                            uint8_t* rgb8, uint64_t counters[2]) {
+    if (!s || !rgb8) return fail(CERES_ERR_INVALID, "ceres_render_ppm8/16: null argument");
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
     Frame f; uint32_t rows = 0;
@@ -1939,7 +1947,7 @@ int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3
         if (int rc = prepare_frame(s, cam, sun, width, height, flags & ~CERES_COMPACT_ROWS, nullptr, &dummy, nullptr, nullptr, f, rows)) return rc;
     }
     if (int rc = ensure(s->d_pixels, s->pixels_cap, npix * 3)) return rc;
-    if (int rc = ensure(s->d_rgb8, s->rgb8_cap, npix * 3)) return rc;
+    if (int rc = ensure(s->d_rgb8, s->rgb8_cap, npix * 3 * BPC)) return rc;
     f.pixels = s->d_pixels; f.ids = nullptr;
     const uint32_t l0 = std::min(f.cull_l0, rows), l1 = std::max(l0, std::min(f.cull_l1, rows));
     const uint32_t i0 = std::min<uint32_t>(f.cull_i0, (uint32_t)width), i1 = std::max(i0, std::min<uint32_t>(f.cull_i1, (uint32_t)width));
@@ -1947,15 +1955,15 @@ int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3
     // host fill of everything outside the rectangle (output rows are flipped: frame row j -> row height-1-j)
     ceres_host::Job job;
     {
-        const size_t rowb = width * 3;
+        const size_t rowb = width * 3 * BPC;
         if (empty) job.add(rgb8, rowb * height, 0x00);
         else {
             const size_t top = height - l1, bottom = height - l0;           // output rows [top, bottom) hold the rectangle
             if (top > 0) job.add(rgb8, rowb * top, 0x00);
             if (bottom < height) job.add(rgb8 + rowb * bottom, rowb * (height - bottom), 0x00);
             for (size_t r = top; r < bottom && (i0 > 0 || i1 < width); ++r) {
-                if (i0 > 0) job.add(rgb8 + rowb * r, (size_t)i0 * 3, 0x00);
-                if (i1 < width) job.add(rgb8 + rowb * r + (size_t)i1 * 3, (width - i1) * 3, 0x00);
+                if (i0 > 0) job.add(rgb8 + rowb * r, (size_t)i0 * 3 * BPC, 0x00);
+                if (i1 < width) job.add(rgb8 + rowb * r + (size_t)i1 * 3 * BPC, (width - i1) * 3 * BPC, 0x00);
             }
         }
     }
@@ -1963,7 +1971,7 @@ int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3
     pool.submit(&job);
     struct Waiter { ceres_host::Pool& p; ceres_host::Job* j; ~Waiter() { p.wait(j); } } waiter{pool, &job};
     const uint64_t prim_outside = (uint64_t)width * (rows - (empty ? 0 : l1 - l0));
-    s->last_d2h_bytes = empty ? 0 : (uint64_t)(l1 - l0) * (i1 - i0) * 3u + 2 * sizeof(unsigned long long);
+    s->last_d2h_bytes = empty ? 0 : (uint64_t)(l1 - l0) * (i1 - i0) * 3u * BPC + 2 * sizeof(unsigned long long);
     if (empty) {
         if (counters) { counters[0] = (uint64_t)width * rows; counters[1] = 0; }
         return CERES_OK;
@@ -1971,11 +1979,11 @@ int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3
     s->rays_outside = prim_outside;
     const uint32_t W32 = (uint32_t)width, H32 = (uint32_t)height;
     auto quantize_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
-        quantize_rect_kernel<<<(unsigned)(s->sm_count * 4), 256, 0, bs>>>(s->d_pixels, W32, H32, i0, i1, r0, r1, s->d_rgb8);
+        quantize_rect_kernel<BPC><<<(unsigned)(s->sm_count * 4), 256, 0, bs>>>(s->d_pixels, W32, H32, i0, i1, r0, r1, s->d_rgb8);
         g_launches++;
         const size_t out_row = height - r1;                                   // first output row of this band
-        const size_t off = (out_row * width + i0) * 3;
-        CUDA_TRY(cudaMemcpy2DAsync(rgb8 + off, width * 3, s->d_rgb8 + off, width * 3, (size_t)(i1 - i0) * 3, r1 - r0, cudaMemcpyDeviceToHost, bs));
+        const size_t off = (out_row * width + i0) * 3 * BPC;
+        CUDA_TRY(cudaMemcpy2DAsync(rgb8 + off, width * 3 * BPC, s->d_rgb8 + off, width * 3 * BPC, (size_t)(i1 - i0) * 3 * BPC, r1 - r0, cudaMemcpyDeviceToHost, bs));
         return CERES_OK;
     };
     if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, quantize_band)) return rc;
@@ -1984,6 +1992,18 @@ int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
     return CERES_OK;
+}
+
+extern "C" {
+
+int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
+                      uint8_t* rgb8, uint64_t counters[2]) {
+    return render_quantized<1>(s, cam, sun, width, height, flags, rgb8, counters);
+}
+
+int ceres_render_ppm16(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
+                       uint8_t* rgb16, uint64_t counters[2]) {
+    return render_quantized<2>(s, cam, sun, width, height, flags, rgb16, counters);
 }
 
 int ceres_render(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,

@@ -237,6 +237,16 @@ class Scene:
         _capi.check(self._L.ceres_render_ppm8(self._h, C.byref(camera.c()), _p(sun), width, height, flags, _p(out), _p(cnt)))
         return out, (int(cnt[0]), int(cnt[1]))
 
+    def render_ppm16(self, camera, sun_position, width, height, flags=0, out=None):
+        """The frame as 16-bit P6 payload (maxval 65535, big-endian; the x 65535 scaling of anim.cpp:117-119), quantised and
+        flipped on the device: (uint16 big-endian [H,W,3], (rays, hits))."""
+        if out is None:
+            out = np.empty((height, width, 3), ">u2")
+        sun = np.asarray(sun_position, np.float32)
+        cnt = np.zeros(2, np.uint64)
+        _capi.check(self._L.ceres_render_ppm16(self._h, C.byref(camera.c()), _p(sun), width, height, flags, _p(out), _p(cnt)))
+        return out, (int(cnt[0]), int(cnt[1]))
+
     def render_sequence(self, cams, width, height, flags=0, pixels_all=None):
         """cams: (n,13) float32 rows of eye,dir,up,fov,sun.  Returns (pixels[n,H,W,3], counters[n,2])."""
         cams = np.ascontiguousarray(cams, np.float32).reshape(-1, 13)

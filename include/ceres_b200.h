@@ -164,6 +164,12 @@ int ceres_render(ceres_scene* scene, const ceres_camera* camera, const float sun
 int ceres_render_ppm8(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                       size_t width, size_t height, unsigned flags, uint8_t* rgb8, uint64_t counters[2]);
 
+/* The 16-bit counterpart for `anim` frames: channel = uint16(max(min(p*65535,65535),0)) -- the x 65535 quantum scaling
+ * of anim.cpp:117-119 -- big-endian as a P6 file with maxval 65535 stores it, rows flipped like ceres_render_ppm8.
+ * rgb16: HOST 6*width*height bytes; half of the float path's PCIe and host-memory bytes. */
+int ceres_render_ppm16(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
+                       size_t width, size_t height, unsigned flags, uint8_t* rgb16, uint64_t counters[2]);
+
 /* Same, one shard of the frame.  Without CERES_COMPACT_ROWS only the shard's rows of pixels/ids are written. */
 int ceres_render_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                        size_t width, size_t height, unsigned flags, const ceres_shard* shard,

@@ -162,6 +162,22 @@ def test_anim_binary_matches_reference_turntable(tmp_path):
         assert (img != 0).any()
     assert f"Total Rays: {total}" in r.stdout
     s.close()
+    # --ppm16: the x 65535 scaling of anim.cpp:117-119, quantised on the GPU, big-endian P6 with maxval 65535
+    out16 = str(tmp_path / "turn16.mp4")
+    r16 = subprocess.run([ANIM, "--input", obj, "--frames", "2", "--width", str(W), "--height", str(H), "--ppm16", out16],
+                         capture_output=True, text=True, timeout=300)
+    assert r16.returncode == 0, r16.stdout + r16.stderr
+    s = ref.RefScene.load_obj(obj, builder=0)
+    cams2 = ref.turntable(ref.cam_array((-150, -20, 0), (1, -0.1, 0), (0, -1, 0), 60), [-500, 300, 10], [0, 1, 0], 2)
+    for k in range(2):
+        px, rays, hits, _ = s.render(cams2[k, :10], cams2[k, 10:13], W, H)
+        x = px.astype(np.float32) * np.float32(65535)
+        x = np.where(np.float32(65535) < x, np.float32(65535), x)
+        want = np.where(x < 0, np.float32(0), x).astype(np.uint16)[::-1]
+        img = read_ppm(str(tmp_path / f"turn16_{k:04d}.ppm")).astype(np.int32)
+        d = img - want.astype(np.int32)
+        assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-4 and img.max() > 255
+    s.close()
     # -d (anim.cpp:154-155): loader, builder, camera path and render in double, against the reference's double build
     from oracle import f64
     if not f64.ref_available():

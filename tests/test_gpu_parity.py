@@ -333,3 +333,21 @@ def test_ppm8_host_path_equals_quantised_float_frame(cr, dragon, bunny, W, H):
             assert np.array_equal(got, want) and cnt8 == cnt
         got2, _ = scene.render_ppm8(cam, SUN, W, H)               # pageable destination
         assert np.array_equal(got2, want)
+
+
+@pytest.mark.parametrize("W,H", [(1280, 720), (333, 217)])
+def test_ppm16_host_path_equals_quantised_float_frame(cr, dragon, W, H):
+    """ceres_render_ppm16 against the float frame pushed through the 16-bit arithmetic on the host
+    (x 65535 as anim.cpp:117-119, clamped, truncated, rows flipped, big-endian): byte-identical."""
+    cam = cr.configs.DRAGON_CAMERA
+    px, _, cnt = dragon.render(cam, SUN, W, H)
+    x = px.astype(np.float32) * np.float32(65535)
+    x = np.where(np.float32(65535) < x, np.float32(65535), x)
+    x = np.where(x < 0, np.float32(0), x)
+    want = x.astype(np.uint16)[::-1].astype(">u2")
+    got, cnt16 = dragon.render_ppm16(cam, SUN, W, H)
+    assert cnt16 == cnt and np.array_equal(got.view(np.uint8), want.view(np.uint8))
+    assert (got != 0).any() and dragon.last_d2h_bytes < got.nbytes
+    # and the 8-bit path still agrees with its own definition after sharing the kernel
+    got8, _ = dragon.render_ppm8(cam, SUN, W, H)
+    assert np.array_equal(got8, cr.write_ppm(os.devnull, px))
