@@ -351,3 +351,43 @@ def test_ppm16_host_path_equals_quantised_float_frame(cr, dragon, W, H):
     # and the 8-bit path still agrees with its own definition after sharing the kernel
     got8, _ = dragon.render_ppm8(cam, SUN, W, H)
     assert np.array_equal(got8, cr.write_ppm(os.devnull, px))
+
+
+def _random_rays(rng, n, lo, hi):
+    """Same recipe as tests/golden/make_golden.py: origins around the scene box, directions on the sphere plus
+    axis-aligned, signed-zero and tiny components (safe_inverse / signbit, vector.hpp:69-74), half of them aimed at
+    the scene; some finite tmax and some tmin > 0."""
+    ext = hi - lo
+    o = (lo - ext) + rng.random((n, 3)) * (3 * ext)
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    k = n // 8
+    d[:k, 0] = 0.0
+    d[k:2 * k, 1] = -0.0
+    d[2 * k:3 * k, 2] = 1e-9 * rng.choice([-1, 1], size=k)
+    c = (lo + hi) / 2 + (rng.random((n, 3)) - 0.5) * ext * 0.8
+    aim = rng.random(n) < 0.5
+    v = c - o
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    d[aim] = v[aim]
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3], rays[:, 3:6] = o, d
+    rays[:, 7] = np.finfo(np.float32).max
+    rays[::7, 7] = (rng.random(len(rays[::7])) * np.linalg.norm(ext) * 2).astype(np.float32)
+    rays[::11, 6] = (rng.random(len(rays[::11])) * np.linalg.norm(ext) * 0.5).astype(np.float32)
+    return rays
+
+
+@pytest.mark.parametrize("which", ["bunny", "dragon"])
+def test_trace_rays_2p20_random_rays_bit_exact(cr, bunny, bunny_pod, dragon, dragon_pod, which):
+    """SURVEY.md 8(d) unit KATs at full size: 2^20 seeded random rays through the slab test, the ordered traversal and
+    the triangle test; hit primitive and the raw bit patterns of (t, u, v) against the strict C restatement."""
+    scene, pod = (bunny, bunny_pod) if which == "bunny" else (dragon, dragon_pod)
+    b = pod["nodes"][0]["bounds"].astype(np.float64)
+    rays = _random_rays(np.random.default_rng(12345), 1 << 20, b[0::2], b[1::2])
+    ids, tuv = scene.trace_rays(rays)
+    want_ids, want_tuv = port.trace_rays(pod, rays)
+    assert np.array_equal(ids, want_ids)
+    assert np.array_equal(tuv.view(np.uint32), want_tuv.view(np.uint32))
+    hit = ids != cr.MISS
+    assert 0.2 < hit.mean() < 0.9
