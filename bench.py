@@ -175,7 +175,7 @@ def run_reference_arm(args):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def algorithmic_bytes(st, W, rows, lit):
@@ -319,12 +319,31 @@ def run_sequence(args):
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT = sys.stdout
+
+
+def keep_stdout_for_the_result():
+    """The contract is ONE JSON line on stdout.  Libraries write banners to file descriptor 1 from C (NCCL prints
+    "NCCL version ..." when the box sets NCCL_DEBUG): point fd 1 at stderr for everything else and keep a private
+    handle on the real stdout for the result line."""
+    global _RESULT
+    sys.stdout.flush()
+    _RESULT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    _RESULT.write(json.dumps(line) + "\n")
+    _RESULT.flush()
+
+
 def main():
+    keep_stdout_for_the_result()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -597,7 +616,7 @@ def main():
             line["verified"] = verified
         if args.workload != WORKLOAD:
             line["data"] = f"synthetic: {cfg.WORKLOADS[args.workload][0]} (ceres_raytracer_b200.scenes.instanced_grid of the reference-built dragon scene, boxes by device refit)"
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
