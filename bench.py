@@ -129,9 +129,23 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is the reference with all the host threads it can
+    use (its `#pragma omp parallel for`, render.hpp:104), so give libgomp the box's cores back."""
+    import ctypes
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(n)
+    except OSError:
+        pass
+    return n
+
+
 def cpu_reference_frames(pod, cam, sun, W, H, frames, warmup=1, budget_s=None):
     """Times the reference's own render() on the host cores.  Returns (seconds per frame list, kind, cores, rays)."""
     from oracle import ref, port
+    use_all_host_threads()
     if ref.available("fast"):
         s = ref.RefScene.from_pod(pod, "fast")       # the reference's own flags (CMakeLists.txt:5,11-13)
         for _ in range(warmup):
