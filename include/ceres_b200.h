@@ -19,7 +19,7 @@
  *   tri_norms  std::array<Vector3<float>,3>, 36 B                                    (lib/obj_norms.hpp:113-115)
  *
  * There is NO CPU fallback: every entry point that computes fails with CERES_ERR_NO_DEVICE / CERES_ERR_CUDA when
- * no sm_100 device is usable.  Scalar = double (anim -d, include/anim.cpp:154-155) is not provided.
+ * no sm_100 device is usable.  Scalar = double (anim -d, include/anim.cpp:154-155): see ceres_render_f64 below.
  * A ceres_scene is not thread-safe; use one per host thread / per GPU.
  */
 #ifndef CERES_B200_H
