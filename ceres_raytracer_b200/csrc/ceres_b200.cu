@@ -25,6 +25,8 @@
 #include <string>
 #include <vector>
 #include <atomic>
+#include <memory>
+#include <immintrin.h>
 #include <chrono>
 #include <new>
 #include <algorithm>
@@ -71,6 +73,7 @@ struct FrameCounters {
     uint32_t occluded;      // shadow rays that hit something
     uint32_t done_blocks;   // shade kernel: blocks finished (last one publishes the counters)
     uint32_t primary_next;  // work-stealing cursor of the persistent primary wave
+    uint32_t ext[4];        // shade kernel: min column, max column, min local row, max local row over the band's hit pixels
     uint32_t pad_[3];
     unsigned long long stats[6];  // S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow (statistics mode only)
 };
@@ -110,6 +113,10 @@ struct Frame {
     PeerCtl* peer;
     uint32_t peer_epoch, peer_rank;
     uint32_t skip_clear;       // the rows were zeroed by somebody else (rank 0 in peer mode)
+    // host-frame path: where the band's last shade CTA publishes the extents of its hit pixels (mapped page-locked host
+    // memory, 8 words per band: ext[4], then the frame's epoch as the ready flag); null = not wanted
+    uint32_t* host_ext;
+    uint32_t ext_epoch;
 };
 
 // ------------------------------------------------------------------------------------------------ device math
@@ -426,9 +433,11 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
         __syncthreads();
     }
     const V3 sun = mk(f.sun[0], f.sun[1], f.sun[2]);
+    uint32_t e_i0 = 0xFFFFFFFFu, e_i1 = 0u, e_r0 = 0xFFFFFFFFu, e_r1 = 0u;
     for (uint32_t r = blockIdx.x * SHADE_THREADS + threadIdx.x; r < total; r += gridDim.x * SHADE_THREADS) {
         const uint4 rec = f.queue[r];
         const uint32_t lrow = rec.x / f.W, i = rec.x - lrow * f.W;
+        e_i0 = min(e_i0, i); e_i1 = max(e_i1, i); e_r0 = min(e_r0, lrow); e_r1 = max(e_r1, lrow);
         const uint32_t j = frame_row(f, lrow);
         const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
         const uint32_t slot = rec.y & ~OCCLUDED_BIT;
@@ -461,6 +470,13 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
         p[0] = c0; p[1] = c1; p[2] = c2;
         if (f.ids) f.ids[opix] = __ldg(sc.slot_id + slot);
     }
+    if (f.host_ext) {        // uniform branch: extents of the hit pixels this warp wrote
+        e_i0 = __reduce_min_sync(0xFFFFFFFFu, e_i0); e_i1 = __reduce_max_sync(0xFFFFFFFFu, e_i1);
+        e_r0 = __reduce_min_sync(0xFFFFFFFFu, e_r0); e_r1 = __reduce_max_sync(0xFFFFFFFFu, e_r1);
+        if ((threadIdx.x & 31u) == 0u && e_i0 <= e_i1) {
+            atomicMin(&f.ctr->ext[0], e_i0); atomicMax(&f.ctr->ext[1], e_i1); atomicMin(&f.ctr->ext[2], e_r0); atomicMax(&f.ctr->ext[3], e_r1);
+        }
+    }
     // the last CTA publishes the frame counters and re-arms the per-frame state for the next frame
     __shared__ bool last;
     if (f.peer) __threadfence_system();     // my pixel stores (NVLink) are performed before the CTA is counted done
@@ -485,6 +501,15 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
         }
         f.ctr->qcount = 0; f.ctr->shadow_next = 0; f.ctr->occluded = 0; f.ctr->done_blocks = 0; f.ctr->primary_next = 0;
         for (int k = 0; k < 6; ++k) f.ctr->stats[k] = 0;
+        if (f.host_ext) {
+            // every CTA fenced its pixel stores and its extent atomics before it was counted: tell the host which
+            // rectangle of this band holds anything but zeros, then raise the flag it is polling
+            volatile uint32_t* e = f.ctr->ext;
+            for (int k = 0; k < 4; ++k) f.host_ext[k] = e[k];
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(f.host_ext + 4), "r"(f.ext_epoch) : "memory");
+        }
+        f.ctr->ext[0] = 0xFFFFFFFFu; f.ctr->ext[1] = 0u; f.ctr->ext[2] = 0xFFFFFFFFu; f.ctr->ext[3] = 0u;
         __threadfence();
         if (f.peer) {
             // every CTA fenced its stores at system scope before it was counted; publish counters, then the flag
@@ -634,6 +659,8 @@ struct ceres_scene {
     int trace_blocks_per_sm[4] = {0, 0, 0, 0};              // [wave*2 + stats]
     float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
     uint64_t last_d2h_bytes = 0;                            // bytes DMA-copied to the host by the last host-frame render
+    uint32_t* h_ext = nullptr;                              // mapped page-locked: 8 words per band (Frame::host_ext)
+    uint32_t ext_epoch = 0;
     uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
 };
 
@@ -763,7 +790,13 @@ static int scene_new(int device, int sm_count, ceres_scene** out) {
     TRY_S(cudaMalloc((void**)&s->d_ctr, CERES_MAX_SUB * sizeof(FrameCounters)));
     TRY_S(cudaMalloc((void**)&s->d_out, 10 * sizeof(unsigned long long)));
     TRY_S(cudaMallocHost((void**)&s->h_out, 10 * sizeof(unsigned long long)));
-    TRY_S(cudaMemset(s->d_ctr, 0, CERES_MAX_SUB * sizeof(FrameCounters)));
+    {
+        FrameCounters init[CERES_MAX_SUB] = {};
+        for (auto& c : init) { c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu; }
+        TRY_S(cudaMemcpy(s->d_ctr, init, sizeof init, cudaMemcpyHostToDevice));
+    }
+    TRY_S(cudaHostAlloc((void**)&s->h_ext, CERES_MAX_SUB * 8 * sizeof(uint32_t), cudaHostAllocMapped));
+    std::memset(s->h_ext, 0, CERES_MAX_SUB * 8 * sizeof(uint32_t));
     TRY_S(cudaMemset(s->d_out, 0, 10 * sizeof(unsigned long long)));
 #undef TRY_S
     *out = s;
@@ -901,6 +934,7 @@ void ceres_scene_destroy(ceres_scene* s) {
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_rgb8); cudaFree(s->d_out);
     if (s->h_out) cudaFreeHost(s->h_out);
+    if (s->h_ext) cudaFreeHost(s->h_ext);
     for (cudaEvent_t e : s->prof_events) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
@@ -1412,6 +1446,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
     if ((size_t)row_end * f.W > s->queue_cap) return fail(CERES_ERR_INVALID, "internal: queue not sized for the frame");
     f.queue = s->d_queue + (size_t)row_begin * f.W;
     f.ctr = s->d_ctr + sub;
+    if (f.host_ext) f.host_ext += 8 * sub;
 
     const size_t smem_p = (size_t)s->dev.stack_depth * 4 * PRIMARY_THREADS;
     const size_t smem_s = (size_t)s->dev.stack_depth * 4 * SHADOW_THREADS;
@@ -1914,10 +1949,76 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
         return copy_run(b1 * br, r1, bs);
     };
     s->rays_outside = prim_outside;
-    if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, copy_band)) return rc;
+    // Tight band copies (rows contiguous in the caller's frame only): the band's last shade CTA publishes the extents of
+    // its hit pixels into mapped host memory; this thread, which has nothing else to do once the frame is enqueued,
+    // polls the flags band by band, copies only that sub-rectangle (everything else inside the conservative rectangle is
+    // zero / CERES_MISS by construction) and hands the strips around it to the fill pool.  For the dragon the bands'
+    // own rectangles hold ~2/3 of the conservative rectangle's bytes, and the copy engine is the serial resource.
+    static const bool tight_off = std::getenv("CERES_NO_TIGHT_COPY") != nullptr;
+    const bool tight = !scatter && !tight_off && s->tune.variant != 1;
+    struct Band { uint32_t k, r0, r1; cudaStream_t bs; };
+    std::vector<Band> bands;
+    std::vector<std::unique_ptr<ceres_host::Job>> gap_jobs;
+    struct GapWaiter { ceres_host::Pool& p; std::vector<std::unique_ptr<ceres_host::Job>>& v; ~GapWaiter() { for (auto& j : v) p.wait(j.get()); } } gap_waiter{pool, gap_jobs};
+    if (tight) {
+        f.host_ext = s->h_ext;
+        f.ext_epoch = ++s->ext_epoch;
+        if (f.ext_epoch == 0u) f.ext_epoch = ++s->ext_epoch;      // 0 is the value of a never-written flag
+        auto note_band = [&](uint32_t k, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int { bands.push_back({k, r0, r1, bs}); return CERES_OK; };
+        if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, note_band)) return rc;
+    } else {
+        if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, copy_band)) return rc;
+    }
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
     const double t_launched = trace_timing ? now_us() : 0.0;
+    if (tight) {
+        uint64_t copied = 0;
+        for (const Band& b : bands) {
+            volatile uint32_t* e = s->h_ext + 8 * b.k;
+            // wait for the band; the copy engine is the serial resource, so this thread does nothing else meanwhile (the
+            // pool fills without it) -- and a failed launch must not hang the caller
+            for (uint64_t spins = 0; e[4] != f.ext_epoch; ++spins) {
+                _mm_pause();
+                if ((spins & 0x3FFu) == 0x3FFu) {
+                    const cudaError_t q = cudaStreamQuery(b.bs);
+                    if (q != cudaErrorNotReady && e[4] != f.ext_epoch)
+                        return fail(CERES_ERR_CUDA, std::string("ceres_render: band did not complete: ") + cudaGetErrorString(q == cudaSuccess ? cudaErrorUnknown : q));
+                }
+            }
+            std::atomic_thread_fence(std::memory_order_acquire);
+            const uint32_t ci0 = e[0], ci1 = e[1], cr0 = e[2], cr1 = e[3];
+            const bool any = ci0 <= ci1 && cr0 <= cr1 && ci0 >= i0 && ci1 < i1 && cr0 >= b.r0 && cr1 < b.r1;
+            if (!(ci0 > ci1) && !any) return fail(CERES_ERR_CUDA, "ceres_render: band extents outside the band (internal error)");
+            auto gaps = std::make_unique<ceres_host::Job>();
+            auto strip = [&](uint32_t row, uint32_t a, uint32_t c) {      // columns [a, c) of local row `row`
+                if (c <= a) return;
+                const size_t o = out_row(row) * width + a;
+                gaps->segs.push_back({reinterpret_cast<unsigned char*>(pixels + 3 * o), (size_t)(c - a) * 12, 0x00});
+                if (ids) gaps->segs.push_back({reinterpret_cast<unsigned char*>(ids + o), (size_t)(c - a) * 4, 0xFF});
+            };
+            if (!any) {
+                for (uint32_t r = b.r0; r < b.r1; ++r) strip(r, i0, i1);
+            } else {
+                const size_t src = (size_t)cr0 * width + ci0, dst = out_row(cr0) * width + ci0;
+                const size_t cols = ci1 - ci0 + 1, nrows = cr1 - cr0 + 1;
+                CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, cols * 12, nrows, cudaMemcpyDeviceToHost, s->copy_stream));
+                if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, cols * 4, nrows, cudaMemcpyDeviceToHost, s->copy_stream));
+                copied += (uint64_t)cols * nrows * (ids ? 16u : 12u);
+                for (uint32_t r = b.r0; r < b.r1; ++r) {
+                    if (r < cr0 || r > cr1) strip(r, i0, i1);
+                    else { strip(r, i0, ci0); strip(r, ci1 + 1, i1); }
+                }
+            }
+            pool.submit(gaps.get());
+            gap_jobs.push_back(std::move(gaps));
+        }
+        s->last_d2h_bytes = copied + 2 * sizeof(unsigned long long);
+    }
     pool.wait(&job);                                      // this thread helps with the fill while the GPU works
+    if (tight) {
+        for (auto& j : gap_jobs) pool.wait(j.get());
+        CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
+    }
     const double t_filled = trace_timing ? now_us() : 0.0;
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     const double t_kernels = trace_timing ? now_us() : 0.0;
