@@ -1905,7 +1905,6 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
 
     // ---- GPU: concurrent row bands of the rectangle; each band is copied as soon as its own kernels are done ---------
     const uint32_t rcols = i1 - i0;
-    const size_t nb = 0;
     // rows [a, b) that are contiguous in the caller's frame: one pitched DMA
     auto copy_run = [&](uint32_t a, uint32_t b, cudaStream_t bs) -> int {
         if (b <= a) return CERES_OK;
@@ -2024,7 +2023,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     const double t_kernels = trace_timing ? now_us() : 0.0;
     if (trace_timing)
         std::fprintf(stderr, "ceres_render timing [us]: segments %zu bands %zu | job built+submitted %.0f, launches issued %.0f, fill done %.0f, "
-                     "kernels done %.0f, copies done %.0f\n", job.segs.size(), nb, t_submit - t_begin, t_launched - t_begin,
+                     "kernels done %.0f, copies done %.0f\n", job.segs.size(), bands.size(), t_submit - t_begin, t_launched - t_begin,
                      t_filled - t_begin, t_kernels - t_begin, now_us() - t_begin);
     if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
     return CERES_OK;
