@@ -660,6 +660,8 @@ struct ceres_scene {
     float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
     uint64_t last_d2h_bytes = 0;                            // bytes DMA-copied to the host by the last host-frame render
     uint32_t* h_ext = nullptr;                              // mapped page-locked: 8 words per band (Frame::host_ext)
+    ceres_scene* seq_view = nullptr;                        // second set of per-frame resources over the same geometry (sequences)
+    bool borrowed = false;                                  // a view: the geometry belongs to the scene it was made from
     uint32_t ext_epoch = 0;
     uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
 };
@@ -929,6 +931,8 @@ void ceres_scene_destroy(ceres_scene* s) {
         if (s->sub_done[k]) cudaEventDestroy(s->sub_done[k]);
     }
     if (s->fork_ev) cudaEventDestroy(s->fork_ev);
+    if (s->seq_view) { ceres_scene_destroy(s->seq_view); s->seq_view = nullptr; }
+    if (s->borrowed) { s->d_pairs = s->d_tris = s->d_norms = s->d_slot_id = nullptr; s->d_parent = s->d_need = s->d_arrived = nullptr; s->d_root_bounds = nullptr; s->d_hist = nullptr; }
     cudaFree(s->d_hist);
     cudaFree(s->d_parent); cudaFree(s->d_need); cudaFree(s->d_arrived); cudaFree(s->d_root_bounds);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
@@ -2143,19 +2147,46 @@ int ceres_render_multi(ceres_scene* const* scenes, int n, const ceres_camera* ca
 int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height,
                           unsigned flags, float* pixels_all, uint64_t* counters_all) {
     if (!s || !cams || !pixels_all) return fail(CERES_ERR_INVALID, "ceres_render_sequence: null argument");
-    // Every frame goes through the host-frame path of ceres_render: only the screen rectangle of the scene crosses PCIe
-    // (row bands copied while later bands still render) and the zeros around it are written by the host-fill pool.
-    // That moves 3-4x fewer bytes per frame than a full-frame D2H overlapped with the next frame's render
-    // (dragon 4K: 29.6 MB instead of 99.5 MB; 0.9 ms instead of 1.9 ms per frame on a PCIe-bound sequence).
+    // Every frame goes through the host-frame path of ceres_render: only the rectangles that hold hit pixels cross PCIe
+    // (row bands copied while later bands still render) and the zeros around them are written by the host-fill pool.
+    // Two frames are in flight at a time: a second set of per-frame resources (streams, record queue, staging frame,
+    // band flags) over the SAME resident geometry renders the odd frames from a second host thread, so that one frame's
+    // drain (copies + zero fill) overlaps the other frame's kernels.  Frames are independent (anim.cpp:82-105).
     const size_t npix = width * height;
-    for (size_t k = 0; k < n_frames; ++k) {
+    auto frame = [&](ceres_scene* v, size_t k) -> int {
         const float* c = cams + 13 * k;
         ceres_camera cam;
         for (int q = 0; q < 3; ++q) { cam.eye[q] = c[q]; cam.dir[q] = c[3 + q]; cam.up[q] = c[6 + q]; }
         cam.fov = c[9];
-        if (int rc = ceres_render(s, &cam, c + 10, width, height, flags, pixels_all + k * npix * 3, nullptr,
-                                  counters_all ? counters_all + 2 * k : nullptr)) return rc;
+        return ceres_render(v, &cam, c + 10, width, height, flags, pixels_all + k * npix * 3, nullptr,
+                            counters_all ? counters_all + 2 * k : nullptr);
+    };
+    static const bool serial = std::getenv("CERES_SEQUENCE_SERIAL") != nullptr;
+    if (n_frames < 2 || s->stats || s->profile || serial) {
+        for (size_t k = 0; k < n_frames; ++k) if (int rc = frame(s, k)) return rc;
+        return CERES_OK;
     }
+    if (!s->seq_view) {
+        DeviceGuard guard(s->device);
+        if (int rc = scene_new(s->device, s->sm_count, &s->seq_view)) return rc;
+        s->seq_view->borrowed = true;
+    }
+    ceres_scene* v = s->seq_view;       // refreshed every call: a refit moves the boxes, set_tuning the knobs
+    v->dev = s->dev; v->d_pairs = s->d_pairs; v->d_tris = s->d_tris; v->d_norms = s->d_norms; v->d_slot_id = s->d_slot_id;
+    v->scene_bytes = s->scene_bytes; v->tri_count = s->tri_count; v->node_count = s->node_count; v->n_pairs = s->n_pairs;
+    v->tune = s->tune; v->shadow_blocks_per_sm = s->shadow_blocks_per_sm; v->shadow_blocks_per_sm_stats = s->shadow_blocks_per_sm_stats;
+    for (int k = 0; k < 4; ++k) v->trace_blocks_per_sm[k] = s->trace_blocks_per_sm[k];
+    for (int k = 0; k < 6; ++k) v->bounds[k] = s->bounds[k];
+    int rc_odd = CERES_OK; std::string err_odd;
+    std::thread odd([&] {
+        for (size_t k = 1; k < n_frames; k += 2) if ((rc_odd = frame(v, k)) != CERES_OK) { err_odd = g_err; break; }
+    });
+    int rc_even = CERES_OK;
+    for (size_t k = 0; k < n_frames; k += 2) if ((rc_even = frame(s, k)) != CERES_OK) break;
+    odd.join();
+    s->last_d2h_bytes = std::max(s->last_d2h_bytes, v->last_d2h_bytes);
+    if (rc_even) return rc_even;
+    if (rc_odd) return fail(rc_odd, err_odd);
     return CERES_OK;
 }
 

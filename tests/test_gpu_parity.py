@@ -391,3 +391,23 @@ def test_trace_rays_2p20_random_rays_bit_exact(cr, bunny, bunny_pod, dragon, dra
     assert np.array_equal(tuv.view(np.uint32), want_tuv.view(np.uint32))
     hit = ids != cr.MISS
     assert 0.2 < hit.mean() < 0.9
+
+
+def test_sequence_two_frames_in_flight_equals_single_frames(cr, dragon_pod, kat):
+    """ceres_render_sequence keeps two frames in flight (a second set of per-frame resources over the same geometry, odd
+    frames on a second host thread): every frame must equal the same frame rendered alone, also after the geometry was
+    moved and refitted (the second set is refreshed from the scene on every call), for an odd number of frames."""
+    W, H = 512, 288
+    cams = np.ascontiguousarray(kat["turntable"][:7, :])
+    with cr.Scene.from_pod(dragon_pod) as s:
+        for moved in (False, True):
+            if moved:
+                s.rotate(2, 11.0)
+                s.refit()
+            px_all, cnt = s.render_sequence(cams, W, H)
+            for k in range(cams.shape[0]):
+                c = cams[k]
+                px, _, counters = s.render(cr.Camera(c[0:3], c[3:6], c[6:9], float(c[9])), c[10:13], W, H)
+                assert np.array_equal(px.view(np.uint32), px_all[k].view(np.uint32)), (moved, k)
+                assert counters == (int(cnt[k, 0]), int(cnt[k, 1]))
+            assert (px_all != 0).any()
