@@ -192,15 +192,15 @@ def run_reference_arm(args):
     emit(line)
 
 
-def algorithmic_bytes(st, W, rows, lit):
-    """Per-kernel algorithmic bytes of one frame from the work the GPU executed (DESIGN.md 'roofline'):
-    64 B per node-pair step, 48 B per triangle test, 16 B per queue record, 12 B per pixel written."""
+def algorithmic_bytes(st, W, rows, lit, traced_px):
+    """Algorithmic bytes of one frame from the work the GPU executed (DESIGN.md 'roofline'): 64 B per node-pair step,
+    48 B per triangle test, 16 B per queue record written and read, 48 B triangle re-read per shadow record, 36 B normals
+    per lit pixel, 12 B per pixel written (frame kernel: the traced rectangle; clear_outside_kernel: everything else)."""
     P, Hh = W * rows, st["hits_primary"]
     return {
-        # clear pass (12 B per pixel of the launch) + primary wave: node pairs, triangles, one queue record per hit
-        "primary": 64 * (st["S_miss"] + st["S_hit"]) + 48 * (st["T_miss"] + st["T_hit"]) + 12 * P + 16 * Hh,
-        "shadow": 64 * st["S_shadow"] + 48 * st["T_shadow"] + 16 * Hh + 48 * Hh + 4 * st["occluded"],
-        "shade": 16 * Hh + (48 + 36) * lit + 12 * Hh,
+        "clear": 12 * (P - traced_px),
+        "frame": 64 * (st["S_miss"] + st["S_hit"] + st["S_shadow"]) + 48 * (st["T_miss"] + st["T_hit"] + st["T_shadow"])
+                 + 2 * 16 * Hh + 48 * Hh + 36 * lit + 12 * traced_px,
     }
 
 

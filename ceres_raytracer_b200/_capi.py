@@ -34,7 +34,7 @@ class Shard(C.Structure):
 
 class Tuning(C.Structure):
     _fields_ = [("variant", C.c_uint32), ("primary_block", C.c_uint32), ("shadow_block", C.c_uint32),
-                ("ctas_per_sm", C.c_uint32), ("band_bytes", C.c_uint32), ("reserved", C.c_uint32 * 3)]
+                ("ctas_per_sm", C.c_uint32), ("shadow_order", C.c_uint32), ("reserved", C.c_uint32 * 3)]
 
 
 # every symbol include/ceres_b200.h declares (tests/test_capi_symbols.py checks the header against this list)
@@ -47,6 +47,7 @@ SYMBOLS = [
     "ceres_kernel_launch_count", "ceres_last_error",
     "ceres_peer_frame_create", "ceres_peer_frame_open", "ceres_peer_frame_alias", "ceres_peer_frame_destroy",
     "ceres_peer_frame_pixels", "ceres_peer_frame_ids", "ceres_render_peer", "ceres_peer_frame_error",
+    "ceres_peer_frame_invalidate",
 ]
 SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download"]
 PEER_HANDLE_BYTES = 64
@@ -58,13 +59,15 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB
-    if _build.needs_build():
+    # CERES_B200_EXPERIMENTS=1 (profiles/kbench.py, tests/test_gpu_experiments.py): the -DCERES_EXPERIMENTS build
+    experiments = os.environ.get("CERES_B200_EXPERIMENTS", "") not in ("", "0")
+    path = _build.LIB_EXP if experiments else _build.LIB
+    if _build.needs_build(path):
         try:
-            _build.build()
+            _build.build(experiments=experiments)
         except Exception as e:  # no nvcc on the box and no prebuilt library: fail loudly, never fall back
             if not os.path.exists(path):
-                raise RuntimeError(f"libceres_b200.so is missing and could not be built ({e}); "
+                raise RuntimeError(f"{os.path.basename(path)} is missing and could not be built ({e}); "
                                    "ceres_raytracer_b200 has no CPU fallback") from e
     L = C.CDLL(path)
     vp, sz, u32, u64 = C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint64
@@ -105,6 +108,7 @@ def lib():
     L.ceres_peer_frame_ids.restype = vp
     L.ceres_render_peer.argtypes = [vp, camp, vp, C.c_uint, vp, vp, vp]
     L.ceres_peer_frame_error.argtypes = [vp]
+    L.ceres_peer_frame_invalidate.argtypes = [vp]
     L.ceres_render_ppm8.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp]
     L.ceres_render_ppm16.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp]
     L.ceres_probe_read_bandwidth.argtypes = [C.c_int, sz, C.c_int, vp]

@@ -7,6 +7,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 SRC = os.path.join(HERE, "csrc", "ceres_b200.cu")
 LIB = os.path.join(HERE, "libceres_b200.so")
+# The same sources with -DCERES_EXPERIMENTS: the product plus the wave pipelines of round 1 (ceres_tuning.variant 1-6),
+# kept for A/B measurements (profiles/kbench.py).  Loaded only when CERES_B200_EXPERIMENTS=1 is set; never shipped as
+# the product library.
+LIB_EXP = os.path.join(HERE, "libceres_b200_exp.so")
 HEADER = os.path.join(ROOT, "include", "ceres_b200.h")
 
 # sm_100a only.  -fmad=false: belt and braces -- the kernels already issue every operation of the path through
@@ -25,23 +29,30 @@ def nvcc():
     return exe
 
 
-def needs_build():
-    if not os.path.exists(LIB):
+def _deps():
+    out = [SRC, HEADER]
+    for d, _, names in os.walk(os.path.join(HERE, "csrc")):
+        out += [os.path.join(d, n) for n in names]
+    return out
+
+
+def needs_build(lib=LIB):
+    if not os.path.exists(lib):
         return True
-    t = os.path.getmtime(LIB)
-    deps = [SRC, HEADER] + [os.path.join(HERE, 'csrc', n) for n in os.listdir(os.path.join(HERE, 'csrc'))]
-    return any(os.path.getmtime(p) > t for p in deps)
+    t = os.path.getmtime(lib)
+    return any(os.path.getmtime(p) > t for p in _deps())
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
-        return LIB
-    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, SRC]
-    env = dict(os.environ)
-    subprocess.check_call(cmd, env=env)
-    return LIB
+def build(force=False, verbose=False, experiments=False):
+    lib = LIB_EXP if experiments else LIB
+    if not force and not needs_build(lib):
+        return lib
+    cmd = [nvcc()] + NVCC_FLAGS + (["-DCERES_EXPERIMENTS", "-diag-suppress", "177"] if experiments else []) \
+        + (["-Xptxas", "-v"] if verbose else []) + ["-o", lib, SRC]
+    subprocess.check_call(cmd, env=dict(os.environ))
+    return lib
 
 
 if __name__ == "__main__":
     import sys
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, experiments="--experiments" in sys.argv))

@@ -2,14 +2,13 @@
 // include/ceres_b200.h.  Written from scratch; citations are to the reference behaviour each piece reproduces
 // (paths relative to the upstream repository).
 //
-// Pipeline per frame (all on one stream, 3 launches, no host synchronisation inside):
-//   primary_kernel  camera ray generation (render.hpp:105-113) + ordered eager-leaf closest-hit BVH traversal
-//                   (single_ray_traverser.hpp:65-126) + Moeller-Trumbore (triangle.hpp:95-115).  Miss pixels are
-//                   zeroed in place; hits are ballot-compacted into a 16-byte record queue.
-//   shadow_kernel   persistent warps steal 32-record chunks from the queue, rebuild the shadow ray
-//                   (render.hpp:120-136) and run an any-hit traversal (only bool(hit) is used, render.hpp:137-150).
-//   shade_kernel    coalesced pass over the queue: smooth_shading (render.hpp:56-84) for lit records, zeros for
-//                   occluded ones, framebuffer + id writes, frame counters (render.hpp:115,119,138,148,155).
+// Pipeline per frame: ONE persistent kernel (frame_fused.cuh) whose warps first trace 8x4-pixel tiles of the scene's
+// conservative screen rectangle -- camera ray generation (render.hpp:105-113), ordered eager-leaf closest-hit BVH
+// traversal (single_ray_traverser.hpp:65-126), Moeller-Trumbore (triangle.hpp:95-115); misses store their zeros, hits
+// are ballot-compacted into a 16-byte record queue -- and then, 32 queue records at a time, rebuild the shadow rays
+// (render.hpp:120-136), run the any-hit traversal (only bool(hit) is used, render.hpp:137-150) and shade + store the
+// pixels (render.hpp:56-84) together with the frame counters (render.hpp:115,119,138,148,155).  Pixels outside the
+// rectangle are zeroed by clear_outside_kernel where the output buffer is not known to hold zeros there already.
 //
 // Arithmetic: every floating-point operation of the path is issued through the round-to-nearest intrinsics
 // (__fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn/__fsqrt_rn never contract), the slab test uses __fmaf_rn exactly where
@@ -73,14 +72,16 @@ struct FrameCounters {
     uint32_t occluded;      // shadow rays that hit something
     uint32_t done_blocks;   // shade kernel: blocks finished (last one publishes the counters)
     uint32_t primary_next;  // work-stealing cursor of the persistent primary wave
-    uint32_t ext[4];        // shade kernel: min column, max column, min local row, max local row over the band's hit pixels
-    uint32_t pad_[3];
+    uint32_t ext[4];        // min column, max column, min local row, max local row over the band's hit pixels
+    uint32_t primary_done;  // frame kernel: primary tiles retired (the warp that retires the last one closes the queue)
+    uint32_t error;         // frame kernel: FRAME_ERR_* bits (a bounded wait expired)
+    uint32_t pad_[1];
     unsigned long long stats[6];  // S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow (statistics mode only)
 };
 
 // Control block of a peer frame (lives in rank 0's device memory, mapped by every rank; include/ceres_b200.h).
 struct PeerCtl {
-    uint32_t cleared_epoch;                          // rank 0: the frame has been zeroed for this epoch
+    uint32_t cleared_epoch;                          // rank 0: my kernels of this epoch have begun (the other ranks may store)
     uint32_t clear_blocks;                           // rank 0: CTAs of the clear pass that have finished
     uint32_t error;                                  // a bounded wait expired (1 = cleared wait, 2 = done wait)
     uint32_t pad_;
@@ -112,7 +113,11 @@ struct Frame {
     // peer-frame mode (ceres_render_peer): pixels/ids point into rank 0's memory
     PeerCtl* peer;
     uint32_t peer_epoch, peer_rank;
-    uint32_t skip_clear;       // the rows were zeroed by somebody else (rank 0 in peer mode)
+    uint32_t skip_clear;       // experiment kernels: the rows were zeroed by somebody else (rank 0 in peer mode)
+    uint32_t peer_wait_world;  // frame kernel, rank 0 of a peer frame: wait for this many ranks' done flags at the end (0 = no)
+    unsigned long long* peer_out;   // ... and put the frame's summed (rays, hits) here (nullable)
+    uint32_t* ready;           // frame kernel: per-32-record-chunk fill counters of this launch's queue region (frame_fused.cuh)
+    unsigned long long* out_error;  // frame kernel: FRAME_ERR_* bits are ORed in here (nullable)
     // host-frame path: where the band's last shade CTA publishes the extents of its hit pixels (mapped page-locked host
     // memory, 8 words per band: ext[4], then the frame's epoch as the ready flag); null = not wanted
     uint32_t* host_ext;
@@ -300,6 +305,7 @@ __device__ __forceinline__ void shadow_setup(const Tri& tr, float u, float v, V3
 #define PRIMARY_THREADS 256
 #define OCCLUDED_BIT 0x80000000u
 
+#ifdef CERES_EXPERIMENTS   // tuning variant 1: the first kernels of round 1 (one thread per pixel, separate waves)
 // One thread per pixel; a warp covers an 8x4 pixel tile, a CTA 32x8 pixels.
 template <bool STATS>
 __global__ void __launch_bounds__(PRIMARY_THREADS) primary_kernel(const DevScene sc, const Frame f) {
@@ -390,6 +396,8 @@ __global__ void __launch_bounds__(SHADOW_THREADS) shadow_kernel(const DevScene s
     }
 }
 
+#endif  // CERES_EXPERIMENTS
+
 // render.hpp:46-54,56-84.  pow(double(x), 24) by repeated squaring in double (5 roundings, relative error
 // < 3e-16, then narrowed to float like the reference's `return std::pow(...)` in a float function).
 __device__ __forceinline__ float spec_pow24(float x) {
@@ -424,6 +432,7 @@ __device__ __forceinline__ bool peer_wait_flag(const uint32_t* flag, uint32_t ep
     return true;
 }
 
+#ifdef CERES_EXPERIMENTS   // separate shade pass + rank-0 clear / wait kernels of the wave pipelines (variants 1-6)
 #define SHADE_THREADS 256
 __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc, const Frame f) {
     const uint32_t total = f.ctr->qcount;
@@ -521,35 +530,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) shade_kernel(const DevScene sc,
     }
 }
 
-// Peer-frame mode, rank 0: zero the whole frame (ids: CERES_MISS), then publish cleared_epoch.
-__global__ void __launch_bounds__(256) peer_clear_kernel(float4* __restrict__ px4, size_t n4, uint4* __restrict__ id4, size_t ni4,
-                                                         PeerCtl* ctl, uint32_t epoch) {
-    const size_t stride = (size_t)gridDim.x * 256u;
-    for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < n4; k += stride) px4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < ni4; k += stride) id4[k] = make_uint4(CERES_MISS, CERES_MISS, CERES_MISS, CERES_MISS);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence_system();
-        if (atomicAdd(&ctl->clear_blocks, 1u) == gridDim.x - 1) {
-            ctl->clear_blocks = 0;
-            __threadfence_system();
-            st_release_sys(&ctl->cleared_epoch, epoch);
-        }
-    }
-}
-
-// Peer-frame mode, rank 0, last kernel of the frame: wait for every rank's done flag, sum the counters.
-__global__ void __launch_bounds__(32) peer_wait_kernel(PeerCtl* ctl, uint32_t epoch, uint32_t world, unsigned long long* out_counters) {
-    const uint32_t r = threadIdx.x;
-    unsigned long long rays = 0, hits = 0;
-    if (r < world) {
-        if (!peer_wait_flag(&ctl->done_epoch[r], epoch)) ctl->error = 2u;
-        const volatile unsigned long long* c = ctl->counters[r];
-        rays = c[0]; hits = c[1];
-    }
-    for (int o = 16; o; o >>= 1) { rays += __shfl_xor_sync(0xFFFFFFFFu, rays, o); hits += __shfl_xor_sync(0xFFFFFFFFu, hits, o); }
-    if (r == 0 && out_counters) { out_counters[0] = rays; out_counters[1] = hits; }
-}
+#endif  // CERES_EXPERIMENTS
 
 // Known-answer kernel: closest-hit traversal of caller-supplied rays.
 __global__ void __launch_bounds__(256) trace_rays_kernel(const DevScene sc, const float* __restrict__ rays, uint32_t n,
@@ -611,10 +592,16 @@ __global__ void __launch_bounds__(256) quantize_rect_kernel(const float* __restr
     }
 }
 
-#include "trace_persistent.cuh"
-#include "trace_batched.cuh"
-#include "trace_repack.cuh"
-#include "trace_shadow_spec.cuh"
+#include "ray_step.cuh"
+#include "frame_fused.cuh"
+#ifdef CERES_EXPERIMENTS
+// Wave pipelines kept for A/B measurements (profiles/kbench.py against libceres_b200_exp.so); none of them is in the
+// product library.  See DESIGN.md "kernel variants" and profiles/r1/sweeps.md for what each one lost by.
+#include "experiments/trace_waves.cuh"
+#include "experiments/trace_batched.cuh"
+#include "experiments/trace_repack.cuh"
+#include "experiments/trace_shadow_spec.cuh"
+#endif
 #include "scene_prep.cuh"
 #include "lbvh_build.cuh"
 
@@ -644,10 +631,12 @@ struct ceres_scene {
     unsigned long long* d_hist = nullptr;                   // step histogram (ceres_scene_get_step_histogram)
     FrameCounters* d_ctr = nullptr;
     uint4* d_queue = nullptr; size_t queue_cap = 0;
+    uint32_t* d_ready = nullptr; size_t ready_cap = 0;     // per-chunk fill counters of the queue (frame_fused.cuh), all-zero between launches
+    cudaEvent_t frame_done = nullptr; cudaStream_t last_stream = nullptr;   // stream order between the frames of this scene
     float* d_pixels = nullptr; size_t pixels_cap = 0;      // staging for the host-buffer API
     uint32_t* d_ids = nullptr; size_t ids_cap = 0;
     uint8_t* d_rgb8 = nullptr; size_t rgb8_cap = 0;        // staging of the 8-bit host-frame path (ceres_render_ppm8)
-    unsigned long long* d_out = nullptr;                    // 2 counters + 8 stats
+    unsigned long long* d_out = nullptr;                    // 2 counters + 8 stats + 1 error word (FRAME_ERR_* bits)
     unsigned long long* h_out = nullptr;                    // pinned mirror
     bool stats = false;
     bool profile = false;                                   // CUDA events around each kernel of every frame
@@ -733,6 +722,13 @@ bool host_is_pinned(const void* p) {
 
 }  // namespace
 
+// Dynamic shared memory above the 48 KB default needs an opt-in per kernel (a 64-deep stack x 256 threads = 64 KB).
+template <class K>
+static int smem_opt_in(K kernel, size_t bytes) {
+    if (bytes > 48u * 1024u) CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return CERES_OK;
+}
+
 extern "C" {
 
 int ceres_abi_version(void) { return CERES_B200_ABI_VERSION; }
@@ -789,9 +785,10 @@ static int scene_new(int device, int sm_count, ceres_scene** out) {
         TRY_S(cudaEventCreateWithFlags(&s->sub_done[k], cudaEventDisableTiming));
     }
     TRY_S(cudaEventCreateWithFlags(&s->fork_ev, cudaEventDisableTiming));
+    TRY_S(cudaEventCreateWithFlags(&s->frame_done, cudaEventDisableTiming));
     TRY_S(cudaMalloc((void**)&s->d_ctr, CERES_MAX_SUB * sizeof(FrameCounters)));
-    TRY_S(cudaMalloc((void**)&s->d_out, 10 * sizeof(unsigned long long)));
-    TRY_S(cudaMallocHost((void**)&s->h_out, 10 * sizeof(unsigned long long)));
+    TRY_S(cudaMalloc((void**)&s->d_out, 11 * sizeof(unsigned long long)));
+    TRY_S(cudaMallocHost((void**)&s->h_out, 11 * sizeof(unsigned long long)));
     {
         FrameCounters init[CERES_MAX_SUB] = {};
         for (auto& c : init) { c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu; }
@@ -799,7 +796,7 @@ static int scene_new(int device, int sm_count, ceres_scene** out) {
     }
     TRY_S(cudaHostAlloc((void**)&s->h_ext, CERES_MAX_SUB * 8 * sizeof(uint32_t), cudaHostAllocMapped));
     std::memset(s->h_ext, 0, CERES_MAX_SUB * 8 * sizeof(uint32_t));
-    TRY_S(cudaMemset(s->d_out, 0, 10 * sizeof(unsigned long long)));
+    TRY_S(cudaMemset(s->d_out, 0, 11 * sizeof(unsigned long long)));
 #undef TRY_S
     *out = s;
     return CERES_OK;
@@ -931,12 +928,13 @@ void ceres_scene_destroy(ceres_scene* s) {
         if (s->sub_done[k]) cudaEventDestroy(s->sub_done[k]);
     }
     if (s->fork_ev) cudaEventDestroy(s->fork_ev);
+    if (s->frame_done) cudaEventDestroy(s->frame_done);
     if (s->seq_view) { ceres_scene_destroy(s->seq_view); s->seq_view = nullptr; }
     if (s->borrowed) { s->d_pairs = s->d_tris = s->d_norms = s->d_slot_id = nullptr; s->d_parent = s->d_need = s->d_arrived = nullptr; s->d_root_bounds = nullptr; s->d_hist = nullptr; }
     cudaFree(s->d_hist);
     cudaFree(s->d_parent); cudaFree(s->d_need); cudaFree(s->d_arrived); cudaFree(s->d_root_bounds);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
-    cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_rgb8); cudaFree(s->d_out);
+    cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_ready); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_rgb8); cudaFree(s->d_out);
     if (s->h_out) cudaFreeHost(s->h_out);
     if (s->h_ext) cudaFreeHost(s->h_ext);
     for (cudaEvent_t e : s->prof_events) cudaEventDestroy(e);
@@ -1440,22 +1438,30 @@ static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float su
     return CERES_OK;
 }
 
-// Enqueues the three kernels for local rows [row_begin, row_end) of the frame on `st`.
-static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row_end, cudaStream_t st, int sub) {
+// What has to be zeroed around the rectangle the frame kernel writes.
+enum { CLEAR_NONE = 0,       // nothing: the caller never reads outside the rectangle (host-frame staging), or clears itself
+       CLEAR_OUTSIDE = 1 };  // every pixel of the launch's rows outside the rectangle (caller-owned device frames)
+
+// ready[] entries (frame_fused.cuh) a launch over `records` queue slots can touch: its chunks + one terminating entry per warp
+static size_t ready_words(const ceres_scene* s, size_t records) { return records / 32 + 2 + (size_t)s->sm_count * 16 * (FRAME_THREADS / 32); }
+
+#ifdef CERES_EXPERIMENTS
+static int launch_rows_waves(ceres_scene* s, Frame& f, uint32_t row_begin, uint32_t row_end, cudaStream_t st, cudaEvent_t* pe);
+#endif
+
+// Enqueues the kernels for local rows [row_begin, row_end) of the frame on `st`.
+static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row_end, cudaStream_t st, int sub, int clear_mode) {
     if (row_end <= row_begin) return CERES_OK;
     f.row_begin = row_begin; f.row_end = row_end; f.accumulate = 1u;
-    const uint32_t rows = row_end - row_begin;
     // every launch owns the queue region of its rows and one FrameCounters slot, so that bands of one frame can run
     // concurrently on different streams (the caller has sized the queue for the whole shard)
     if ((size_t)row_end * f.W > s->queue_cap) return fail(CERES_ERR_INVALID, "internal: queue not sized for the frame");
     f.queue = s->d_queue + (size_t)row_begin * f.W;
+    f.ready = s->d_ready + ((size_t)row_begin * f.W) / 32 + (size_t)sub * ready_words(s, 0);
     f.ctr = s->d_ctr + sub;
+    f.out_error = s->d_out + 10;
     if (f.host_ext) f.host_ext += 8 * sub;
 
-    const size_t smem_p = (size_t)s->dev.stack_depth * 4 * PRIMARY_THREADS;
-    const size_t smem_s = (size_t)s->dev.stack_depth * 4 * SHADOW_THREADS;
-    dim3 grid((unsigned)((f.W + 31) / 32), (unsigned)((rows + 7) / 8));
-    if (grid.y > 65535u) return fail(CERES_ERR_INVALID, "ceres_render: image too tall");
     cudaEvent_t* pe = nullptr;
     if (s->profile && s->profile_kernels) {
         if (s->prof_events.size() < 4 * (s->prof_frames + 1)) {
@@ -1464,8 +1470,69 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         pe = &s->prof_events[4 * s->prof_frames++];
         CUDA_TRY(cudaEventRecord(pe[0], st));
     }
+    // the conservative screen rectangle of the scene within this launch's rows, cut into 8x4-pixel tiles
+    {
+        const uint32_t r0 = std::max(row_begin, f.cull_l0), r1 = std::min(row_end, f.cull_l1);
+        f.rect_x0 = f.cull_i0; f.rect_x1 = f.cull_i1; f.rect_row0 = r0; f.rect_row1 = r1 > r0 ? r1 : r0;
+        f.tiles_x = (f.rect_x1 - f.rect_x0 + 7u) / 8u;
+        const uint64_t tiles = (uint64_t)f.tiles_x * ((f.rect_row1 - f.rect_row0 + 3u) / 4u);
+        if (tiles * 32u >= (1ull << 32)) return fail(CERES_ERR_INVALID, "ceres_render: image too large");
+        f.work_items = (uint32_t)(tiles * 32u);
+    }
+    if (s->tune.variant != 0) {
+#ifdef CERES_EXPERIMENTS
+        // (the wave pipelines always clear their own rows: their misses store nothing)
+        return launch_rows_waves(s, f, row_begin, row_end, st, pe);
+#else
+        return fail(CERES_ERR_UNSUPPORTED, "ceres_tuning.variant != 0 needs the experiments build (libceres_b200_exp.so, -DCERES_EXPERIMENTS)");
+#endif
+    }
+    if (clear_mode == CLEAR_OUTSIDE) {
+        const ClearRegion q{row_begin, row_end, 0u, f.W, f.rect_row0, f.rect_row1, f.rect_x0, f.rect_x1};
+        clear_outside_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(f, q);
+        g_launches++;
+        CUDA_TRY(cudaGetLastError());
+    }
+    if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
+    {
+        const size_t smem = (size_t)s->dev.stack_depth * 4 * FRAME_THREADS;          // <= 32 KB: depth <= 64
+        const int order = s->tune.shadow_order == 1 ? ORDER_NEAR : s->tune.shadow_order == 2 ? ORDER_LEFT : FRAME_DEFAULT_SHADOW_ORDER;
+        auto go = [&](auto kernel, int slot) -> int {
+            int& bps = s->trace_blocks_per_sm[slot];
+            if (bps == 0) {
+                if (s->tune.ctas_per_sm) bps = (int)std::min(16u, s->tune.ctas_per_sm);
+                else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, FRAME_THREADS, smem));
+                if (bps < 1) bps = 1;
+                if (bps > 16) bps = 16;             // ready_words() reserves one terminating entry per warp of 16 CTAs per SM
+            }
+            kernel<<<(unsigned)(s->sm_count * bps), FRAME_THREADS, smem, st>>>(s->dev, f);
+            g_launches++;
+            CUDA_TRY(cudaGetLastError());
+            return CERES_OK;
+        };
+        int rc;
+        if (s->stats) rc = order == ORDER_NEAR ? go(frame_kernel<true, ORDER_NEAR>, 1) : go(frame_kernel<true, ORDER_LEFT>, 3);
+        else rc = order == ORDER_NEAR ? go(frame_kernel<false, ORDER_NEAR>, 0) : go(frame_kernel<false, ORDER_LEFT>, 2);
+        if (rc) return rc;
+    }
+    if (pe) { CUDA_TRY(cudaEventRecord(pe[2], st)); CUDA_TRY(cudaEventRecord(pe[3], st)); }
+    return CERES_OK;
+}
+
+#ifdef CERES_EXPERIMENTS
+// The wave pipelines of round 1 (tuning variants 1-6): clear -> primary wave -> shadow wave -> shade pass.
+static int launch_rows_waves(ceres_scene* s, Frame& f, uint32_t row_begin, uint32_t row_end, cudaStream_t st, cudaEvent_t* pe) {
+    const uint32_t rows = row_end - row_begin;
+    const size_t smem_p = (size_t)s->dev.stack_depth * 4 * PRIMARY_THREADS;
+    const size_t smem_s = (size_t)s->dev.stack_depth * 4 * SHADOW_THREADS;
+    dim3 grid((unsigned)((f.W + 31) / 32), (unsigned)((rows + 7) / 8));
+    if (grid.y > 65535u) return fail(CERES_ERR_INVALID, "ceres_render: image too tall");
     if (s->tune.variant == 1) {
         // legacy wave kernels: one thread per pixel, no culling, no refill (kept for A/B measurements)
+        if (int rc = smem_opt_in(primary_kernel<true>, smem_p)) return rc;
+        if (int rc = smem_opt_in(primary_kernel<false>, smem_p)) return rc;
+        if (int rc = smem_opt_in(shadow_kernel<true>, smem_s)) return rc;
+        if (int rc = smem_opt_in(shadow_kernel<false>, smem_s)) return rc;
         if (s->stats) primary_kernel<true><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
         else primary_kernel<false><<<grid, PRIMARY_THREADS, smem_p, st>>>(s->dev, f);
         g_launches++;
@@ -1500,6 +1567,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         // launch helper: persistent grid = SMs x resident CTAs of this instantiation
         auto launch_wave = [&](int wave, auto kernel, int threads) -> int {
             const size_t smem_t = (size_t)s->dev.stack_depth * 4 * threads;
+            if (int rc = smem_opt_in(kernel, smem_t)) return rc;
             int& bps = s->trace_blocks_per_sm[wave * 2 + (s->stats ? 1 : 0)];
             if (bps == 0) {
                 if (s->tune.ctas_per_sm) bps = (int)s->tune.ctas_per_sm;
@@ -1564,6 +1632,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         }
         }
     }
+    CUDA_TRY(cudaGetLastError());            // a failed wave launch must not be followed by the shade pass (it re-arms the counters)
     if (pe) CUDA_TRY(cudaEventRecord(pe[2], st));
     shade_kernel<<<(unsigned)(s->sm_count * 4), SHADE_THREADS, 0, st>>>(s->dev, f);
     g_launches++;
@@ -1571,6 +1640,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
     CUDA_TRY(cudaGetLastError());
     return CERES_OK;
 }
+#endif  // CERES_EXPERIMENTS
 
 }  // extern "C" (a C++ template follows)
 
@@ -1586,14 +1656,42 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
 // node steps while the rest of the GPU idles, ~30-50 us per wave on the dragon); with concurrent bands the tail of one
 // band's wave is filled by the next band's bulk, and in the host path a finished band is copied while others render.
 // hook(band, r0, r1, stream) may enqueue follow-up work (the D2H copies) behind a band's kernels.
-template <class Hook>
-static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, cudaStream_t st, uint32_t default_sub, Hook&& hook) {
-    if (b <= a) return CERES_OK;
-    const size_t need = (size_t)b * f.W;
-    if (need > s->queue_cap) {
-        CUDA_TRY(cudaDeviceSynchronize());      // growing the queue frees the old one: wait for frames still using it
-        if (int rc = ensure(s->d_queue, s->queue_cap, need)) return rc;
+// After a host-path frame has been synchronised: h_out[10] holds the FRAME_ERR_* bits of its launches.  On error the
+// queue bookkeeping may be inconsistent: re-arm it so that the next frame starts clean.
+static int frame_error_check(ceres_scene* s) {
+    if (!s->h_out[10]) return CERES_OK;
+    const unsigned long long bits = s->h_out[10];
+    s->h_out[10] = 0;
+    cudaDeviceSynchronize();
+    cudaMemset(s->d_out + 10, 0, sizeof(unsigned long long));
+    if (s->d_ready) cudaMemset(s->d_ready, 0, s->ready_cap * sizeof(uint32_t));
+    FrameCounters init[CERES_MAX_SUB] = {};
+    for (auto& c : init) { c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu; }
+    cudaMemcpy(s->d_ctr, init, sizeof init, cudaMemcpyHostToDevice);
+    return fail(CERES_ERR_CUDA, "frame kernel: a bounded device-side wait expired (error bits " + std::to_string(bits) + ")");
+}
+
+// Sizes the record queue and its ready[] array for `records` queue slots.
+static int size_queue(ceres_scene* s, size_t records) {
+    const size_t need_ready = records / 32 + (size_t)CERES_MAX_SUB * ready_words(s, 0) + 2;
+    if (records <= s->queue_cap && need_ready <= s->ready_cap) return CERES_OK;
+    CUDA_TRY(cudaDeviceSynchronize());      // growing the queue frees the old one: wait for frames still using it
+    if (int rc = ensure(s->d_queue, s->queue_cap, records)) return rc;
+    if (need_ready > s->ready_cap) {
+        if (int rc = ensure(s->d_ready, s->ready_cap, need_ready)) return rc;
+        CUDA_TRY(cudaMemset(s->d_ready, 0, s->ready_cap * sizeof(uint32_t)));      // the frame kernel keeps it all-zero between launches
     }
+    return CERES_OK;
+}
+
+template <class Hook>
+static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, cudaStream_t st, uint32_t default_sub, int clear_mode, Hook&& hook) {
+    if (b <= a) return CERES_OK;
+    if (int rc = size_queue(s, (size_t)b * f.W)) return rc;
+    // the frames of one scene share the record queue, ready[] and the counter slots: a frame enqueued on another stream
+    // than the previous one waits for it
+    if (s->last_stream && s->last_stream != st) CUDA_TRY(cudaStreamWaitEvent(st, s->frame_done, 0));
+    struct Done { ceres_scene* s; cudaStream_t st; ~Done() { if (cudaEventRecord(s->frame_done, st) == cudaSuccess) s->last_stream = st; else cudaGetLastError(); } } done{s, st};
     CUDA_TRY(cudaMemsetAsync(f.out_counters, 0, 2 * sizeof(unsigned long long), st));
     if (f.out_stats) CUDA_TRY(cudaMemsetAsync(f.out_stats, 0, 8 * sizeof(unsigned long long), st));
     const uint32_t rows = b - a;
@@ -1604,7 +1702,7 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
     nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (uint32_t)std::max<uint64_t>(1u, rect_px >> 18));
     if (nsub <= 1) {
         s->profile_kernels = true;
-        if (int rc = launch_rows(s, f, a, b, st, 0)) return rc;
+        if (int rc = launch_rows(s, f, a, b, st, 0, clear_mode)) return rc;
         return hook(0u, a, b, st);
     }
     cudaEvent_t* pe = nullptr;
@@ -1627,7 +1725,7 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
         const uint32_t r1 = std::min(b, r0 + band_rows);
         cudaStream_t bs = s->sub_stream[k];
         CUDA_TRY(cudaStreamWaitEvent(bs, s->fork_ev, 0));
-        if (int rc = launch_rows(s, f, r0, r1, bs, (int)k)) return rc;
+        if (int rc = launch_rows(s, f, r0, r1, bs, (int)k, clear_mode)) return rc;
         if (dbg) CUDA_TRY(cudaEventRecord(dbg_ev[1 + 2 * k], bs));
         if (int rc = hook(k, r0, r1, bs)) return rc;
         if (dbg) CUDA_TRY(cudaEventRecord(dbg_ev[2 + 2 * k], bs));
@@ -1663,7 +1761,7 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
         return CERES_OK;
     }
     s->rays_outside = 0;
-    return render_rows(s, f, 0, rows_local, st, CERES_SUBFRAMES_DEVICE, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; });
+    return render_rows(s, f, 0, rows_local, st, CERES_SUBFRAMES_DEVICE, CLEAR_OUTSIDE, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; });
 }
 
 // ---- peer frame (include/ceres_b200.h: "one frame on N GPUs, fused with its gather over NVLink peer memory") ----
@@ -1678,6 +1776,10 @@ struct ceres_peer_frame {
     float* pixels = nullptr;
     uint32_t* ids = nullptr;
     size_t n4 = 0, ni4 = 0;
+    // Dirty-rectangle bookkeeping of THIS rank's rows.  Invariant between frames: the rank's rows hold the last frame's
+    // values inside `prev` (columns [i0, i1) x local rows [l0, l1)) and zeros / CERES_MISS everywhere else.
+    uint32_t prev_i0 = 0, prev_i1 = 0, prev_l0 = 0, prev_l1 = 0;
+    bool dirty_all = false;        // somebody else wrote into the frame (ceres_peer_frame_invalidate): clear all my rows once
 };
 
 static size_t peer_layout(ceres_peer_frame* pf) {
@@ -1703,11 +1805,7 @@ static int peer_size_queue(ceres_scene* s, size_t width, size_t height, int worl
     ceres_shard sh{CERES_TILE_BLOCK_ROWS, (uint32_t)rank, (uint32_t)world};
     const size_t rows = shard_rows(height, world > 1 ? &sh : nullptr);
     DeviceGuard guard(s->device);
-    if (rows * width > s->queue_cap) {
-        CUDA_TRY(cudaDeviceSynchronize());
-        if (int rc = ensure(s->d_queue, s->queue_cap, rows * width)) return rc;
-    }
-    return CERES_OK;
+    return size_queue(s, rows * width);
 }
 
 static int peer_args_ok(ceres_scene* s, size_t width, size_t height, int world, int rank) {
@@ -1729,7 +1827,8 @@ int ceres_peer_frame_create(ceres_scene* s, size_t width, size_t height, int wan
     pf->owner = true; pf->device = s->device; pf->world = world; pf->rank = 0; pf->W = width; pf->H = height; pf->with_ids = want_ids != 0;
     const size_t bytes = peer_layout(pf);      // base is null: only the size is meaningful here
     cudaError_t e = cudaMalloc(&pf->base, bytes);
-    if (e == cudaSuccess) e = cudaMemset(pf->base, 0, bytes);
+    if (e == cudaSuccess) e = cudaMemset(pf->base, 0, bytes);                       // pixels: zeros
+    if (e == cudaSuccess && pf->with_ids) { peer_layout(pf); e = cudaMemset(pf->ids, 0xFF, pf->ni4 * 16); }    // ids: CERES_MISS
     if (e == cudaSuccess && handle_out) {
         cudaIpcMemHandle_t h;
         e = cudaIpcGetMemHandle(&h, pf->base);
@@ -1801,11 +1900,17 @@ int ceres_peer_frame_error(ceres_peer_frame* pf) {
     return (int)e;
 }
 
+int ceres_peer_frame_invalidate(ceres_peer_frame* pf) {
+    if (!pf) return fail(CERES_ERR_INVALID, "ceres_peer_frame_invalidate: null frame");
+    pf->dirty_all = true;
+    return CERES_OK;
+}
+
 int ceres_render_peer(ceres_scene* s, const ceres_camera* cam, const float sun[3], unsigned flags, void* stream_v,
                       ceres_peer_frame* pf, uint64_t* d_counters) {
     if (!s || !pf) return fail(CERES_ERR_INVALID, "ceres_render_peer: null argument");
     if (s->device != pf->device) return fail(CERES_ERR_INVALID, "ceres_render_peer: scene and frame handle belong to different devices");
-    if (s->tune.variant == 1) return fail(CERES_ERR_UNSUPPORTED, "ceres_render_peer: needs the clear-pass kernels (any variant but 1)");
+    if (s->tune.variant != 0) return fail(CERES_ERR_UNSUPPORTED, "ceres_render_peer: needs the frame kernel (tuning variant 0)");
     ceres_shard sh{CERES_TILE_BLOCK_ROWS, (uint32_t)pf->rank, (uint32_t)pf->world};
     Frame f; uint32_t rows_local = 0;
     if (int rc = prepare_frame(s, cam, sun, pf->W, pf->H, flags & ~CERES_COMPACT_ROWS, pf->world > 1 ? &sh : nullptr, pf->pixels,
@@ -1813,24 +1918,36 @@ int ceres_render_peer(ceres_scene* s, const ceres_camera* cam, const float sun[3
     DeviceGuard guard(s->device);
     cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
     const uint32_t epoch = ++pf->epoch;
-    f.peer = pf->ctl; f.peer_epoch = epoch; f.peer_rank = (uint32_t)pf->rank; f.skip_clear = 1u;
-    if (pf->rank == 0) {
-        peer_clear_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>((float4*)pf->pixels, pf->n4, (uint4*)pf->ids, pf->ni4, pf->ctl, epoch);
-        g_launches++;
-    }
+    f.peer = pf->ctl; f.peer_epoch = epoch; f.peer_rank = (uint32_t)pf->rank;
+    if (pf->rank == 0) { f.peer_wait_world = (uint32_t)pf->world; f.peer_out = (unsigned long long*)d_counters; }
     s->rays_outside = 0;
     if (rows_local == 0) {
         peer_publish_kernel<<<1, 1, 0, st>>>(pf->ctl, (uint32_t)pf->rank, epoch);
         g_launches++;
-    } else if (int rc = render_rows(s, f, 0, rows_local, st, 1u, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; })) {
-        return rc;
+        CUDA_TRY(cudaGetLastError());
+        return CERES_OK;
     }
-    if (pf->rank == 0) {
-        peer_wait_kernel<<<1, 32, 0, st>>>(pf->ctl, epoch, (uint32_t)pf->world, (unsigned long long*)d_counters);
+    // Dirty-rectangle clear of MY rows: the frame kernel writes every pixel of the current rectangle; outside it my rows
+    // already hold zeros except where the previous frame's rectangle sticks out (a moving camera), or everywhere after
+    // ceres_peer_frame_invalidate.  Nothing to do for a repeated or growing rectangle -- no clear pass, no cross-rank wait.
+    const uint32_t l0 = std::min(f.cull_l0, rows_local), l1 = std::max(l0, std::min(f.cull_l1, rows_local));
+    const uint32_t i0 = std::min(f.cull_i0, f.W), i1 = std::max(i0, std::min(f.cull_i1, f.W));
+    const bool cur_empty = l1 == l0 || i1 == i0;
+    ClearRegion q{0, 0, 0, 0, l0, l1, i0, i1};
+    if (pf->dirty_all) { q.row_a = 0; q.row_b = rows_local; q.x_a = 0; q.x_b = f.W; }
+    else if (pf->prev_l1 > pf->prev_l0 && pf->prev_i1 > pf->prev_i0 &&
+             (cur_empty || pf->prev_l0 < l0 || pf->prev_l1 > l1 || pf->prev_i0 < i0 || pf->prev_i1 > i1)) {
+        q.row_a = pf->prev_l0; q.row_b = pf->prev_l1; q.x_a = pf->prev_i0; q.x_b = pf->prev_i1;
+    }
+    if (q.row_b > q.row_a) {
+        const unsigned grid = (unsigned)std::min<uint32_t>(q.row_b - q.row_a, (uint32_t)s->sm_count * 8u);
+        clear_outside_kernel<<<grid, 256, 0, st>>>(f, q);
         g_launches++;
+        CUDA_TRY(cudaGetLastError());
     }
-    CUDA_TRY(cudaGetLastError());
-    return CERES_OK;
+    pf->dirty_all = false;
+    pf->prev_l0 = l0; pf->prev_l1 = l1; pf->prev_i0 = i0; pf->prev_i1 = i1;
+    return render_rows(s, f, 0, rows_local, st, 1u, CLEAR_NONE, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; });
 }
 
 // Host-framebuffer render (the drop-in for render.hpp:86-156).
@@ -1968,11 +2085,12 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
         f.ext_epoch = ++s->ext_epoch;
         if (f.ext_epoch == 0u) f.ext_epoch = ++s->ext_epoch;      // 0 is the value of a never-written flag
         auto note_band = [&](uint32_t k, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int { bands.push_back({k, r0, r1, bs}); return CERES_OK; };
-        if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, note_band)) return rc;
+        if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, CLEAR_NONE, note_band)) return rc;
     } else {
-        if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, copy_band)) return rc;
+        if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, CLEAR_NONE, copy_band)) return rc;
     }
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->h_out + 10, s->d_out + 10, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
     const double t_launched = trace_timing ? now_us() : 0.0;
     if (tight) {
         uint64_t copied = 0;
@@ -2029,6 +2147,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
         std::fprintf(stderr, "ceres_render timing [us]: segments %zu bands %zu | job built+submitted %.0f, launches issued %.0f, fill done %.0f, "
                      "kernels done %.0f, copies done %.0f\n", job.segs.size(), bands.size(), t_submit - t_begin, t_launched - t_begin,
                      t_filled - t_begin, t_kernels - t_begin, now_us() - t_begin);
+    if (int rc = frame_error_check(s)) return rc;
     if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
     return CERES_OK;
 }
@@ -2090,10 +2209,12 @@ static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float
         CUDA_TRY(cudaMemcpy2DAsync(rgb8 + off, width * 3 * BPC, s->d_rgb8 + off, width * 3 * BPC, (size_t)(i1 - i0) * 3 * BPC, r1 - r0, cudaMemcpyDeviceToHost, bs));
         return CERES_OK;
     };
-    if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, quantize_band)) return rc;
+    if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, CLEAR_NONE, quantize_band)) return rc;
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->h_out + 10, s->d_out + 10, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
     pool.wait(&job);
     CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (int rc = frame_error_check(s)) return rc;
     if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
     return CERES_OK;
 }

@@ -160,9 +160,12 @@ class Scene:
         """Bytes the last host-frame render moved over PCIe (the scene's screen rectangle + counters)."""
         return int(self._L.ceres_scene_last_d2h_bytes(self._h))
 
-    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, band_bytes=0, refill_min=0, subframes=0, chunk=0):
-        t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm, band_bytes, (C.c_uint32 * 3)(refill_min, subframes, chunk))
+    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, shadow_order=0, refill_min=0, subframes=0, chunk=0):
+        """variant 0 = the frame kernel; 1-6 = the wave pipelines (experiments build only).  shadow_order: 0 default,
+        1 nearer child first, 2 left child first.  subframes = row bands per frame."""
+        t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm, shadow_order, (C.c_uint32 * 3)(refill_min, subframes, chunk))
         _capi.check(self._L.ceres_scene_set_tuning(self._h, C.byref(t)))
+        self._variant = int(variant)
 
     # ---- scene preparation on the device (SURVEY.md 8(f) N2) ---------------------------------------------------
     def rotate(self, axis, degrees):
@@ -206,10 +209,13 @@ class Scene:
         _capi.check(self._L.ceres_scene_set_profiling(self._h, int(bool(enable))))
 
     def kernel_ms(self):
-        """Sums over the frames recorded since set_profiling(True): ({primary,shadow,shade,total} ms, frames)."""
+        """Sums over the frames recorded since set_profiling(True): ({clear, frame, total} ms, frames) for the frame
+        kernel; ({primary, shadow, shade, total} ms, frames) for the wave pipelines of the experiments build."""
         ms = np.zeros(4, np.float64)
         n = C.c_uint64(0)
         _capi.check(self._L.ceres_scene_get_kernel_ms(self._h, _p(ms), C.byref(n)))
+        if getattr(self, "_variant", 0) == 0:
+            return {"clear": float(ms[0]), "frame": float(ms[1]), "total": float(ms[3])}, int(n.value)
         return dict(zip(["primary", "shadow", "shade", "total"], ms.tolist())), int(n.value)
 
     # ---- host buffers ---------------------------------------------------------------------------------------

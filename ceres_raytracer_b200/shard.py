@@ -126,6 +126,11 @@ class PeerFrame:
     def error(self):
         return int(self._L.ceres_peer_frame_error(self._h))
 
+    def invalidate(self):
+        """Somebody wrote into the frame (through .pixels / .ids): this rank's next render() re-clears all of its rows."""
+        from . import _capi
+        _capi.check(self._L.ceres_peer_frame_invalidate(self._h))
+
     def close(self):
         if getattr(self, "_h", None):
             self._L.ceres_peer_frame_destroy(self._h)

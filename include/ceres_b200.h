@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define CERES_B200_ABI_VERSION 1
+#define CERES_B200_ABI_VERSION 2
 
 enum {
     CERES_OK = 0,
@@ -70,12 +70,14 @@ typedef struct ceres_shard {
 /* Kernel tuning knobs (0 = library default).  Exposed so bench.py/tests can sweep them; results never depend
  * on them. */
 typedef struct ceres_tuning {
-    uint32_t variant;            /* 0 default; see DESIGN.md "kernel variants" */
-    uint32_t primary_block;      /* threads per CTA, primary kernel */
-    uint32_t shadow_block;       /* threads per CTA, shadow kernel */
+    uint32_t variant;            /* 0 = the frame kernel (the product).  1-6 = the wave pipelines of round 1, present only in
+                                    the experiments build (libceres_b200_exp.so, -DCERES_EXPERIMENTS); see DESIGN.md */
+    uint32_t primary_block;      /* experiments: threads per CTA, primary wave */
+    uint32_t shadow_block;       /* experiments: threads per CTA, shadow wave */
     uint32_t ctas_per_sm;        /* persistent CTAs per SM */
-    uint32_t band_bytes;         /* host-framebuffer calls: float RGB bytes per pipelined row band */
-    uint32_t reserved[3];
+    uint32_t shadow_order;       /* frame kernel, any-hit shadow rays: 0 default, 1 nearer child first (the reference's
+                                    order), 2 left child first (no ordering work; the boolean cannot depend on it) */
+    uint32_t reserved[3];        /* [0] experiments: lane-refill threshold, [1] row bands per frame, [2] experiments: chunk */
 } ceres_tuning;
 
 /* ---- scene ------------------------------------------------------------------------------------------------- */
@@ -201,14 +203,19 @@ int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const fl
  * One process per GPU.  Rank 0 owns the frame: a device allocation holding the float RGB frame (+ optional ids) and
  * a small control block; the other ranks map it (CUDA IPC) and their kernels store the pixels of their row blocks
  * STRAIGHT INTO rank 0's memory while they shade -- there is no separate gather pass and no collective call.
- * Per frame ("epoch" e, counted by every rank in lockstep):
- *   rank 0   clears the whole frame (render.hpp:116-117: everything that is not a lit hit is 0), publishes
- *            cleared_epoch = e, renders its own row blocks, then a one-warp kernel waits until done_epoch[r] >= e for
- *            every rank and sums the ranks' counters into d_counters;
- *   rank r   traces its row blocks; its shade kernel waits for cleared_epoch >= e, stores its pixels over NVLink,
- *            fences at system scope and publishes done_epoch[r] = e together with its (rays, hits).
- * Waits are bounded (about 4 s): on expiry the control block's error word is set and ceres_peer_frame_error reports
- * it; the GPU is never left spinning.  All ranks must call ceres_render_peer the same number of times. */
+ * Per frame ("epoch" e, counted by every rank in lockstep) every rank -- rank 0 included -- launches ONE kernel: its frame
+ * kernel writes EVERY pixel of its row blocks that lies inside the scene's conservative screen rectangle (zeros for misses and
+ * shadowed hits, colours for lit hits) over NVLink into rank 0's memory, fences at system scope and publishes
+ * done_epoch[r] = e with its (rays, hits).  The frame is library-owned, so outside the rectangle it already holds zeros:
+ * a rank clears only what the PREVIOUS epoch's rectangle left outside the current one (a moving camera; nothing for a
+ * repeated view) -- there is no whole-frame clear and no rank waits for another rank's clear.  Rank 0's kernel ends by waiting
+ * until done_epoch[r] >= e for every rank and sums the counters into d_counters.  The only cross-rank gate at the start: a
+ * rank's first store of epoch e waits until rank 0's kernels of epoch e have begun, so a rank that runs ahead cannot write
+ * into a frame rank 0's process is still reading (stream order on rank 0).  When several ranks share ONE GPU (tests), enqueue
+ * rank 0 first.  Waits are bounded (about 4 s): on expiry the control block's error word is set and ceres_peer_frame_error
+ * reports it; the GPU is never left spinning.  All ranks must call ceres_render_peer the same number of times.
+ * Whoever writes into the frame through ceres_peer_frame_pixels/_ids must call ceres_peer_frame_invalidate on every rank
+ * before the next ceres_render_peer (the next frame then clears all of the rank's rows once). */
 typedef struct ceres_peer_frame ceres_peer_frame;
 #define CERES_PEER_HANDLE_BYTES 64
 #define CERES_PEER_MAX_RANKS 16
@@ -231,6 +238,8 @@ int ceres_render_peer(ceres_scene* scene, const ceres_camera* camera, const floa
                       void* stream, ceres_peer_frame* frame, uint64_t* d_counters);
 /* after the stream has been synchronised: 0 = no wait of any rank expired so far */
 int ceres_peer_frame_error(ceres_peer_frame* frame);
+/* the frame's memory was written by somebody else: this rank's next frame re-establishes zeros outside its rectangle */
+int ceres_peer_frame_invalidate(ceres_peer_frame* frame);
 
 /* Per-frame work statistics of the LAST ceres_render_device call on this scene, read back after the stream has
  * been synchronised: stats[0..7] = {S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow,rays,hits} where S = node-pair
@@ -245,8 +254,9 @@ int ceres_scene_get_step_histogram(ceres_scene* scene, uint64_t hist[128]);
 
 /* Per-kernel timing.  While enabled, every ceres_render_device call records CUDA events on its launch stream
  * before/after each of its kernels.  ceres_scene_get_kernel_ms waits for the recorded frames and returns the SUMS
- * over the frames recorded since the last ceres_scene_set_profiling call: ms[0] primary, ms[1] shadow, ms[2] shade,
- * ms[3] first-to-last event; *frames (nullable) = number of frames summed. */
+ * over the frames recorded since the last ceres_scene_set_profiling call: ms[0] clear_outside_kernel, ms[1] frame_kernel,
+ * ms[2] 0 (experiments build, variants 1-6: primary wave incl. clear, shadow wave, shade pass), ms[3] first-to-last
+ * event; *frames (nullable) = number of frames summed. */
 int ceres_scene_set_profiling(ceres_scene* scene, int enable);
 int ceres_scene_get_kernel_ms(ceres_scene* scene, double ms[4], uint64_t* frames);
 

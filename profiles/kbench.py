@@ -19,13 +19,14 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="dragon_4k_shadow")
-    ap.add_argument("--variants", default="0,1,2")
+    ap.add_argument("--variants", default="0")
     ap.add_argument("--frames", type=int, default=20)
     ap.add_argument("--ctas", default="0")
     ap.add_argument("--refill", default="0")
     ap.add_argument("--block", type=int, default=0)
     ap.add_argument("--sub", default="1")
     ap.add_argument("--chunk", default="0")
+    ap.add_argument("--order", default="0", help="frame kernel: shadow child order(s), 0 default / 1 near-first / 2 left-first")
     args = ap.parse_args()
     import torch
     import ceres_raytracer_b200 as cr
@@ -43,9 +44,12 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     ref_px = None
     ref_ids = None
-    for ctas, refill, sub, chunk in [(int(c), int(r), int(q), int(h)) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",") for h in args.chunk.split(",")]:
+    for ctas, refill, sub, chunk, order in [(int(c), int(r), int(q), int(h), int(o)) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",") for h in args.chunk.split(",") for o in args.order.split(",")]:
         for v in [int(x) for x in args.variants.split(",")]:
-            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block, subframes=sub, chunk=chunk)
+            if v != 0 and os.environ.get("CERES_B200_EXPERIMENTS", "") in ("", "0"):
+                print(f"variant {v}: skipped (wave pipelines need CERES_B200_EXPERIMENTS=1)", flush=True)
+                continue
+            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block, subframes=sub, chunk=chunk, shadow_order=order)
             d_px.fill_(float("nan"))
             scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, ids=d_ids, counters=d_cnt)
             torch.cuda.synchronize()
@@ -71,8 +75,8 @@ def main():
             torch.cuda.synchronize()
             ms, n = scene.kernel_ms()
             scene.set_profiling(False)
-            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub} chunk {chunk}: primary {ms['primary']/n*1e3:7.1f} us  shadow {ms['shadow']/n*1e3:7.1f} us  "
-                  f"shade {ms['shade']/n*1e3:6.1f} us  total {ms['total']/n*1e3:7.1f} us   ids_ok={ok} counters_ok={cnt_ok} "
+            parts = "  ".join(f"{k} {ms[k]/n*1e3:7.1f} us" for k in ms)
+            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub} chunk {chunk} order {order}: {parts}   ids_ok={ok} counters_ok={cnt_ok} "
                   f"pixels_same_as_first={same_px}", flush=True)
     scene.set_tuning()
 

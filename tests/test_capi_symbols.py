@@ -24,7 +24,7 @@ def test_header_symbols_exported():
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/ceres_b200.h but not exported"
     assert sorted(_capi.SYMBOLS) == names
-    assert L.ceres_abi_version() == 1
+    assert L.ceres_abi_version() == 2
 
 
 def test_frame_setup_is_host_only_and_matches_oracle():

@@ -35,20 +35,31 @@ def test_peer_frame_same_process(cr, dragon_pod, world, flags):
     streams = [torch.cuda.Stream(device=s.device) for s in scenes]
     owner = PeerFrame(scenes[0], W, H, 0, world, want_ids=True)
     frames = [owner] + [PeerFrame(scenes[r], W, H, r, world, want_ids=True, owner=owner) for r in range(1, world)]
+    # a second view whose screen rectangle neither contains nor is contained in the first one's: the dirty-rectangle clear
+    # has to wipe what the previous epoch left outside the new rectangle
+    cam2 = cr.Camera((3.0, -15.0, 2.5), (-0.1, 1.0, 0.0), (0.0, 0.0, 1.0), 45.0)
+    ref2 = scenes[0].render(cam2, SUN, W, H, flags=flags, want_ids=True)
     try:
-        for it in range(3):           # several epochs: the flags must carry over from frame to frame
-            owner.pixels.fill_(float("nan"))
+        # epochs 0-2: the frame is poisoned by the caller, who says so (invalidate): every pixel must be rewritten;
+        # epochs 3-4: untouched frame, same view (no clear at all); 5: other view; 6: back; 7: poisoned again
+        for it, (view, poison) in enumerate([(cam, True)] * 3 + [(cam, False)] * 2 + [(cam2, False), (cam, False), (cam2, True)]):
+            want = (ref_px, ref_ids, ref_cnt) if view is cam else ref2
+            if poison:
+                owner.pixels.fill_(float("nan"))
+                owner.ids.fill_(12345)
+                for f in frames:
+                    f.invalidate()
             torch.cuda.synchronize(scenes[0].device)
-            for r in range(world):
-                frames[r].render(cam, SUN, flags=flags, stream=streams[r].cuda_stream)
+            for r in range(world):        # rank 0 first: the ranks may share one GPU (include/ceres_b200.h)
+                frames[r].render(view, SUN, flags=flags, stream=streams[r].cuda_stream)
             for s in streams:
                 s.synchronize()
             assert owner.error() == 0
             px = owner.pixels.cpu().numpy()
             ids = owner.ids.cpu().numpy().view(np.uint32)
-            assert np.array_equal(px.view(np.uint32), ref_px.view(np.uint32)), f"epoch {it}"
-            assert np.array_equal(ids, ref_ids)
-            assert tuple(owner.counters.cpu().tolist()) == ref_cnt
+            assert np.array_equal(px.view(np.uint32), want[0].view(np.uint32)), f"epoch {it}"
+            assert np.array_equal(ids, want[1]), f"epoch {it}"
+            assert tuple(owner.counters.cpu().tolist()) == want[2]
     finally:
         for f in frames[1:] + [owner]:
             f.close()
