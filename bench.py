@@ -4,15 +4,22 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
 One "step" = one frame of the hot path (render.hpp:86-156) over the reference-built dragon scene.  Rays are the
-reference's own counter: W*H + primary hits (render.hpp:115,138) = 9 450 006 per frame.
-  value        device-resident throughput: scene in HBM, frame left in HBM (CUDA events on the launch stream; L2 is
-               flushed before every timed frame)
-  e2e          the same frame through the reference-facing C-ABI call ceres_render() with a HOST framebuffer: the
-               device->host copy of the float RGB frame and of the counters is inside the timed region
-  roofline     dominant kernel: algorithmic bytes / its CUDA-event duration vs the measured HBM peak
-  cpu_baseline the reference's own render() (oracle/_ref, its flags, all host threads) on the same frame
-N > 1 (torchrun): the frame is split in interleaved 16-row blocks, one shard per GPU, scene replicated, finished
-blocks gathered on rank 0 with NCCL; time = max over ranks; scaling is strong (one frame, more GPUs).
+reference's own counter: W*H + primary hits (render.hpp:115,138) = 9 450 006 per frame; `rays_traced` is the number of
+rays the GPU actually walks through the BVH (pixels of the scene's conservative screen rectangle + shadow rays).
+  value          device-resident throughput: scene in HBM, frame left in HBM (CUDA events on the launch stream; L2 is
+                 flushed before every timed frame)
+  sustained      >= 2 s of back-to-back frames (no flush; every frame rewrites the 99.5 MB frame buffer) with the SM
+                 clock sampled in-process (NVML) every 10 ms
+  e2e            the same frame through the reference-facing C-ABI call ceres_render() with a page-locked HOST frame:
+                 the device->host copy of the float RGB frame and of the counters is inside the timed region;
+                 e2e.floor_ms = host frame bytes / host store bandwidth measured in this run
+  e2e_pageable   the same call into plain malloc'ed memory, i.e. what anim.cpp:76 / static.cpp:117 pass
+  roofline       the frame kernel: warp instructions (committed ncu capture) against the SMs' issue slots at the
+                 measured SM clock, next to its algorithmic bytes against the measured HBM and L2 peaks
+  cpu_baseline   the reference's own render() (oracle/_ref, its flags, all host threads) on the same frame
+N > 1 (torchrun): the frame is split in interleaved 16-row blocks, one shard per GPU, scene replicated; every rank's
+frame kernel stores its pixels straight into rank 0's frame over NVLink (no collective on the data path); time = max
+over ranks; scaling is strong (one frame, more GPUs).
 """
 import argparse
 import json
@@ -83,50 +90,94 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + clock-event reasons sampled every `period` seconds from a thread of this process through NVML (the
+    nvidia-smi -lms recipe of B200_PROFILING.md misses regions of a few ms); falls back to nvidia-smi when NVML is not
+    importable.  mark(tag) labels the samples that follow, so that the summary can tell the timed regions from the rest."""
+    NAMES = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, index, period=0.01):
+        self.index, self.period, self.rows, self.tag, self.stop, self.proc, self.h = index, period, [], "idle", False, None, None
+        self.max_mhz = None
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
         except Exception:
-            self.proc = None
+            self.h = None
+            try:
+                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                              "--format=csv,noheader,nounits", "-lms", "20"],
+                                             stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                self.t = threading.Thread(target=self._read, daemon=True)
+                self.t.start()
+            except Exception:
+                self.proc = None
         return self
+
+    def mark(self, tag):
+        self.tag = tag
+
+    def _poll(self):
+        nv = self.nv
+        while not self.stop:
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    bits = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    bits = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((self.tag, mhz, bits))
+            except Exception:
+                pass
+            time.sleep(self.period)
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            r = [x.strip() for x in line.split(",")]
+            try:
+                bits = sum(v for (n, v), x in zip(self.NAMES.items(), r[2:6]) if x.lower().startswith("active"))
+                self.max_mhz = max(self.max_mhz or 0.0, float(r[1]))
+                self.rows.append((self.tag, float(r[0]), bits))
+            except Exception:
+                continue
 
     def __exit__(self, *a):
+        self.stop = True
         if self.proc:
-            time.sleep(0.15)
+            time.sleep(0.05)
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
             except Exception:
                 self.proc.kill()
 
-    def summary(self):
-        sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx = max(mx, float(r[1]))
-                for n, v in zip(names, r[2:6]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                continue
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+    def summary(self, tags=("timed", "sustained")):
+        rows = [r for r in self.rows if r[0] in tags] or self.rows
+        sm = [r[1] for r in rows]
+        bits = 0
+        for r in rows:
+            bits |= r[2]
+        per_tag = {}
+        for t in sorted({r[0] for r in self.rows}):
+            v = [r[1] for r in self.rows if r[0] == t]
+            per_tag[t] = {"samples": len(v), "sm_mhz": float(np.median(v))}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(n for n, v in self.NAMES.items() if bits & v), "samples": len(sm),
+                "source": "NVML in-process, every %d ms" % int(self.period * 1e3) if self.h is not None else "nvidia-smi -lms 20",
+                "regions": per_tag}
 
 
 def use_all_host_threads():
@@ -143,7 +194,7 @@ def use_all_host_threads():
 
 
 def cpu_reference_frames(pod, cam, sun, W, H, frames, warmup=1, budget_s=None):
-    """Times the reference's own render() on the host cores.  Returns (seconds per frame list, kind, cores, rays)."""
+    """Times the reference's own render() on the host cores.  Returns (seconds per frame list, kind, cores, rays, hits)."""
     from oracle import ref, port
     use_all_host_threads()
     if ref.available("fast"):
@@ -152,21 +203,36 @@ def cpu_reference_frames(pod, cam, sun, W, H, frames, warmup=1, budget_s=None):
             _, _, _, sec0 = s.render(cam, sun, W, H)
             if budget_s:
                 frames = int(min(frames, max(2, budget_s / max(sec0, 1e-3))))
-        secs, rays = [], 0
+        secs, rays, hits = [], 0, 0
         for _ in range(frames):
-            _, rays, _, sec = s.render(cam, sun, W, H)
+            _, rays, hits, sec = s.render(cam, sun, W, H)
             secs.append(sec)
         cores = ref.threads("fast")
         s.close()
-        return secs, "reference", cores, rays
-    secs, rays = [], 0
+        return secs, "reference", cores, rays, hits
+    secs, rays, hits = [], 0, 0
     for k in range(warmup + frames):
         t0 = time.perf_counter()
         r = port.render(pod, cam, sun, W, H, 0, want_pixels=True)
         if k >= warmup:
             secs.append(time.perf_counter() - t0)
-        rays = r["stats"]["rays"]
-    return secs, "port", port.threads(), rays
+        rays, hits = r["stats"]["rays"], r["stats"]["hits"]
+    return secs, "port", port.threads(), rays, hits
+
+
+def scene_device_bytes(pod):
+    """Bytes of the flattened scene as ceres_scene_create lays it out (64 B per node pair, 48 B triangle + 48 B normals +
+    4 B slot id per triangle): computed from the arrays, so the CPU arm can name the same config without a GPU."""
+    n_nodes, n_tris = int(len(pod["nodes"])), int(len(pod["triangles"]))
+    return max(1, (n_nodes - 1) // 2) * 64 + n_tris * (48 + 48 + 4)
+
+
+def frame_config(workload, W, H, rays, scene_bytes, sharding, l2):
+    """The `config` object of the JSON line; both arms build it here so that their keys AND values agree (the `hits`
+    counter is not part of it: the reference's shipped -ffp-contract=fast build counts 1-2 more or fewer than the strict
+    arithmetic the GPU reproduces)."""
+    return {"workload": workload, "width": W, "height": H, "rays_per_frame": rays,
+            "scene_device_bytes": scene_bytes, "sharding": sharding, "l2": l2}
 
 
 def run_reference_arm(args):
@@ -175,14 +241,15 @@ def run_reference_arm(args):
     if rank != 0:
         return
     pod, cam, sun, W, H, flags, _ = load_workload(args.workload)
-    secs, kind, cores, rays = cpu_reference_frames(pod, cam.as_array(), sun, W, H, frames=args.steps, warmup=args.warmup)
+    secs, kind, cores, rays, hits = cpu_reference_frames(pod, cam.as_array(), sun, W, H, frames=args.steps, warmup=args.warmup)
     ms = 1e3 * float(np.sum(secs)) / len(secs)
     val = rays / (ms * 1e-3) / 1e6
     line = {
         "impl": "reference", "metric": metric_name(args.workload, W, H, flags), "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": DATA,
-        "config": {"workload": args.workload, "width": W, "height": H, "rays_per_frame": rays, "l2": "n/a (CPU)"},
+        "config": frame_config(args.workload, W, H, rays, scene_device_bytes(pod), sharding_text(args.gpus), L2_TEXT),
+        "counters": {"rays": rays, "hits": hits},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                          "sample": f"{len(secs)} full {W}x{H} frames, unmodified render() (render.hpp:86-156), "
                                    f"best {min(secs)*1e3:.1f} ms, median {np.median(secs)*1e3:.1f} ms"},
@@ -190,6 +257,17 @@ def run_reference_arm(args):
         "gpu_launches": 0,
     }
     emit(line)
+
+
+L2_TEXT = "flushed (256 MiB fill) before every timed frame"
+
+
+def sharding_text(world, peer=True):
+    if world <= 1:
+        return "none"
+    import ceres_raytracer_b200.configs as cfg
+    return (f"{world} x interleaved {cfg.TILE_BLOCK_ROWS}-row blocks, " +
+            ("kernels store into rank 0's frame over NVLink peer memory (no collective)" if peer else "NCCL gather to rank 0"))
 
 
 def algorithmic_bytes(st, W, rows, lit, traced_px):
@@ -253,12 +331,14 @@ def run_sequence(args):
     scene.set_profiling(True)
     with ClockSampler(local) as clocks:
         barrier()
+        clocks.mark("timed")
         for a, b in ev:
             flush.fill_(1)
             a.record()
             one_pass()
             b.record()
         barrier()
+        clocks.mark("between")
     launches = cr.kernel_launch_count() - launches0
     kms, kframes = scene.kernel_ms()
     scene.set_profiling(False)
@@ -270,17 +350,20 @@ def run_sequence(args):
     # ---- work executed by this rank (statistics build, untimed), summed over its frames --------------------------
     scene.set_stats(True)
     st = {k: 0 for k in ("S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "rays", "hits")}
+    traced_px = 0
     for f in mine:
         scene.render_device(cams[f][0], cams[f][1], W, H, flags=flags, pixels=d_fb, counters=d_cnt[f])
         torch.cuda.synchronize()
         for k, v in scene.get_stats().items():
             st[k] += v
+        r_ = scene.last_rectangle
+        traced_px += (r_[1] - r_[0]) * (r_[3] - r_[2])
     scene.set_stats(False)
     st["hits_primary"] = st["rays"] - W * H * len(mine)
     st["occluded"] = st["hits"] - st["hits_primary"]
-    abytes = algorithmic_bytes(st, W, H * len(mine), st["hits_primary"] - st["occluded"])
-    per_pass = {k: kms[k] / max(args.steps, 1) for k in ("primary", "shadow", "shade", "total")}
-    dominant = max(("primary", "shadow", "shade"), key=lambda k: per_pass[k])
+    abytes = algorithmic_bytes(st, W, H * len(mine), st["hits_primary"] - st["occluded"], traced_px)
+    per_pass = {k: kms[k] / max(args.steps, 1) for k in ("clear", "frame", "total")}
+    dominant = "frame"
     peak, peak_src = measured_peak()
     achieved = abytes[dominant] / (per_pass[dominant] * 1e-3) / 1e9 if per_pass[dominant] > 0 else 0.0
 
@@ -308,7 +391,7 @@ def run_sequence(args):
         secs, rays_cpu = [], 0
         sample = list(range(0, n_frames, max(1, n_frames // 4)))[:4]
         for f in sample:
-            s_, kind, cores, r_ = cpu_reference_frames(pod, path[f, :10], path[f, 10:13], W, H, frames=1, warmup=1 if f == sample[0] else 0)
+            s_, kind, cores, r_, _h = cpu_reference_frames(pod, path[f, :10], path[f, 10:13], W, H, frames=1, warmup=1 if f == sample[0] else 0)
             secs += s_
             rays_cpu += r_
         cpu = {"value": rays_cpu / sum(secs) / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
@@ -325,10 +408,11 @@ def run_sequence(args):
             "e2e": {"value": rays_total / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 13 * 4 * len(mine),
                     "d2h_bytes_per_step": d2h_seq, "host_frame_bytes": 3 * W * H * 4 * len(mine), "path": "ceres_render_sequence() -> page-locked host frames"},
             "gpu_launches": launches, "kernels_ms": per_pass,
-            "roofline": {"bound": "hbm", "kernel": dominant + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "issue", "kernel": "frame_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": abytes[dominant] // max(1, len(mine)),
-                         "note": "summed over this rank's frames; scene (3 MB) is L1/L2-resident"},
+                         "note": "summed over this rank's frames; the 3 MB scene is L1/L2-resident, so the HBM figure is context only: "
+                                 "the kernel is bound by instruction issue (see the single-frame bench line's roofline.issue)"},
             "clocks": clocks.summary(),
         }
         if cpu is not None:
@@ -365,6 +449,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="length of the sustained block (seconds of back-to-back frames)")
     ap.add_argument("--verify", action="store_true",
                     help="after the measurement, render the same frame with the oracle (CPU) and compare hit ids, "
                          "counters and RGB at the full size (N=1)")
@@ -414,7 +499,7 @@ def main():
 
     def frame():
         if pf is not None:
-            pf.render(cam, sun, flags=flags)        # clear (rank 0) + trace + shade-into-rank-0 + wait (rank 0): no collective
+            pf.render(cam, sun, flags=flags)        # ONE kernel per rank: trace + shade-into-rank-0 (+ rank 0 waits inside it)
             return
         scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
         fg.assemble()               # N > 1: NCCL gather to rank 0 + row scatter, counters summed over shards
@@ -430,150 +515,180 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    for _ in range(warmup):
-        flush.fill_(1)
-        frame()
-    barrier()
-    counters = (pf.counters if pf is not None and rank == 0 else d_cnt).cpu().tolist()
-    rays_frame, hits_frame = int(counters[0]), int(counters[1])
-    if pf is not None and rank == 0 and pf.error():
-        raise SystemExit("peer frame: a rank did not deliver within the wait bound")
+    def allgather(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world == 1:
+            return [float(x)]
+        out = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [float(o.item()) for o in out]
 
-    # ---- timed region: K frames, each preceded by an L2 flush that is outside its event pair ------------------
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    launches0 = cr.kernel_launch_count()
-    scene.set_profiling(True)            # per-kernel CUDA events on the launch stream, inside the timed region
-    with ClockSampler(local) as clocks:
+    with ClockSampler(local) as clocks:          # samples from here to the end; the regions are tagged below
+        clocks.mark("warmup")
+        for _ in range(warmup):
+            flush.fill_(1)
+            frame()
         barrier()
+        counters = (pf.counters if pf is not None and rank == 0 else d_cnt).cpu().tolist()
+        rays_frame, hits_frame = int(counters[0]), int(counters[1])
+        if pf is not None and rank == 0 and pf.error():
+            raise SystemExit("peer frame: a rank did not deliver within the wait bound")
+
+        # ---- timed region: K frames, each preceded by an L2 flush that is outside its event pair ------------------
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        launches0 = cr.kernel_launch_count()
+        scene.set_profiling(True)            # per-kernel CUDA events on the launch stream, inside the timed region
+        barrier()
+        clocks.mark("timed")
         for a, b in ev:
             flush.fill_(1)
             a.record()
             frame()
             b.record()
         barrier()
-    launches = cr.kernel_launch_count() - launches0
-    kms, kframes = scene.kernel_ms()
-    scene.set_profiling(False)
-    ms_step = allmax(sum(a.elapsed_time(b) for a, b in ev) / args.steps)
+        clocks.mark("between")
+        launches = cr.kernel_launch_count() - launches0
+        kms, kframes = scene.kernel_ms()
+        scene.set_profiling(False)
+        ms_step = allmax(sum(a.elapsed_time(b) for a, b in ev) / args.steps)
+        kavg = {k: kms[k] / max(kframes, 1) for k in ("clear", "frame", "total")}
+        per_rank_kernel_ms = allgather(kavg["total"])
 
-    # back-to-back frames without flush (warm L2), for context
-    barrier()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(args.steps):
-        frame()
-    b.record()
-    barrier()
-    ms_warm = allmax(a.elapsed_time(b) / args.steps)
+        # ---- sustained: >= args.sustain_s of back-to-back frames, clock sampled throughout (warm L2: no flush) -------
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(args.steps):
+            frame()
+        b.record()
+        barrier()
+        ms_warm = allmax(a.elapsed_time(b) / args.steps)
+        n_sus = int(max(args.steps, min(200000, args.sustain_s * 1e3 / max(ms_warm, 1e-3))))
+        n_sus = int(allmax(n_sus))
+        barrier()
+        clocks.mark("sustained")
+        a.record()
+        done = 0
+        while done < n_sus:                     # in slices, so that the host never runs far ahead of the device queue
+            for _ in range(min(500, n_sus - done)):
+                frame()
+            done += min(500, n_sus - done)
+            torch.cuda.current_stream().synchronize()
+        b.record()
+        barrier()
+        clocks.mark("between")
+        ms_sus = allmax(a.elapsed_time(b) / n_sus)
+        if pf is not None and rank == 0 and pf.error():
+            raise SystemExit("peer frame: a rank did not deliver within the wait bound")
 
-    # ---- work actually executed by this rank's kernels (statistics build of the same kernels, untimed) ----------
-    scene.set_stats(True)
-    scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
-    torch.cuda.synchronize()
-    st = scene.get_stats()
-    scene.set_stats(False)
-    local_rays, local_hits = st["rays"], st["hits"]
-    st["hits_primary"] = local_rays - W * n_rows if not (flags & cr.NO_SHADOWS) else None
-    if st["hits_primary"] is None:      # primary-only: every hit is lit, hits counter = primary hits
-        st["hits_primary"] = local_hits
-        st["occluded"] = 0
-    else:
-        st["occluded"] = local_hits - st["hits_primary"]
-    lit = st["hits_primary"] - st["occluded"]
-    abytes = algorithmic_bytes(st, W, n_rows, lit)
-    kavg = {k: kms[k] / max(kframes, 1) for k in ("primary", "shadow", "shade", "total")}
-    dominant = max(("primary", "shadow", "shade"), key=lambda k: kavg[k])
-    peak, peak_src = measured_peak()
-    achieved = abytes[dominant] / (kavg[dominant] * 1e-3) / 1e9 if kavg[dominant] > 0 else 0.0
-    whole = sum(abytes.values()) / (kavg["total"] * 1e-3) / 1e9 if kavg["total"] > 0 else 0.0
-    # second denominator: read bandwidth of an L2-resident working set, measured on this GPU
-    try:
-        l2_peak = cr.probe_read_bandwidth(48 << 20, repeats=20, device=local)
-    except Exception:
-        l2_peak = None
-    ncu_traffic = None
-    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")     # dram bytes per launch from the committed ncu --set full capture
-    if os.path.exists(tp) and args.workload == WORKLOAD:
-        try:
-            ncu_traffic = json.load(open(tp)).get(dominant)
-        except Exception:
-            pass
-
-    # ---- end to end through the reference-facing call with a HOST framebuffer ------------------------------------
-    # N = 1: ceres_render() (the drop-in for render.hpp:86-156) into a page-locked host buffer: launch + D2H of the
-    # float frame + counters inside the timed region.  N > 1: shard render + NCCL gather + D2H of the frame on rank 0.
-    steps_e2e = args.steps
-    if world == 1:
-        hb = cr.PinnedBuffer((H, W, 3), np.float32)
-        for _ in range(2):
-            scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)
+        # ---- work actually executed by this rank's kernels (statistics build of the same kernel, untimed) ----------
+        scene.set_stats(True)
+        scene.render_device(cam, sun, W, H, flags=rflags, shard=shard, pixels=d_band, counters=d_cnt)
         torch.cuda.synchronize()
-        t_e2e = 0.0
-        for _ in range(steps_e2e):
-            flush.fill_(1)
+        st = scene.get_stats()
+        scene.set_stats(False)
+        rect = scene.last_rectangle
+        traced_px = (rect[1] - rect[0]) * (rect[3] - rect[2])
+        local_rays, local_hits = st["rays"], st["hits"]
+        if flags & cr.NO_SHADOWS:      # primary-only: every hit is lit, hits counter = primary hits
+            st["hits_primary"], st["occluded"] = local_hits, 0
+        else:
+            st["hits_primary"] = local_rays - W * n_rows
+            st["occluded"] = local_hits - st["hits_primary"]
+        lit = st["hits_primary"] - st["occluded"]
+        rays_traced_local = traced_px + (0 if flags & cr.NO_SHADOWS else st["hits_primary"])
+        t = torch.tensor([rays_traced_local], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(t)
+        rays_traced = int(t.item())
+        abytes = algorithmic_bytes(st, W, n_rows, lit, traced_px)
+        peak, peak_src = measured_peak()
+        achieved = abytes["frame"] / (kavg["frame"] * 1e-3) / 1e9 if kavg["frame"] > 0 else 0.0
+        whole = sum(abytes.values()) / (kavg["total"] * 1e-3) / 1e9 if kavg["total"] > 0 else 0.0
+        # second denominator: read bandwidth of an L2-resident working set, measured on this GPU
+        try:
+            l2_peak = cr.probe_read_bandwidth(48 << 20, repeats=20, device=local)
+        except Exception:
+            l2_peak = None
+
+        # ---- end to end through the reference-facing call with a HOST framebuffer ------------------------------------
+        clocks.mark("e2e")
+        steps_e2e = args.steps
+        extra = {}
+
+        def time_host_call(fn, n=steps_e2e, pre=2):
+            for _ in range(pre):
+                fn()
             torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            _, _, cnt_e2e = scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)
-            t_e2e += time.perf_counter() - t0
-        assert cnt_e2e == (rays_frame, hits_frame)
-        # the same frame as 8-bit P6 payload (static.cpp:135-147 on the device; N1): a quarter of the PCIe bytes
-        hb8 = cr.PinnedBuffer((H, W, 3), np.uint8)
-        for _ in range(2):
-            scene.render_ppm8(cam, sun, W, H, flags=flags, out=hb8.array)
-        t_ppm8 = 0.0
-        for _ in range(steps_e2e):
-            flush.fill_(1)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            scene.render_ppm8(cam, sun, W, H, flags=flags, out=hb8.array)
-            t_ppm8 += time.perf_counter() - t0
-        ppm8 = {"value": rays_frame / (t_ppm8 / steps_e2e) / 1e6, "unit": UNIT, "ms_per_step": 1e3 * t_ppm8 / steps_e2e,
-                "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm8() -> page-locked 8-bit P6 payload"}
-        hb8.close()
-        # and as 16-bit payload (the x 65535 scaling of anim.cpp:117-119 on the device): half of the bytes
-        hb16 = cr.PinnedBuffer((H, W, 3), np.uint16)
-        for _ in range(2):
-            scene.render_ppm16(cam, sun, W, H, flags=flags, out=hb16.array)
-        t_ppm16 = 0.0
-        for _ in range(steps_e2e):
-            flush.fill_(1)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            scene.render_ppm16(cam, sun, W, H, flags=flags, out=hb16.array)
-            t_ppm16 += time.perf_counter() - t0
-        ppm8["ppm16"] = {"value": rays_frame / (t_ppm16 / steps_e2e) / 1e6, "unit": UNIT, "ms_per_step": 1e3 * t_ppm16 / steps_e2e,
-                         "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm16() -> page-locked 16-bit P6 payload"}
-        hb16.close()
-        scene.render(cam, sun, W, H, flags=flags, pixels=hb.array)      # last_d2h_bytes of the float path again
-        d2h = scene.last_d2h_bytes        # the screen rectangle of the scene + counters; the rest of the frame is host-filled zeros
-    else:
-        # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
-        # DMA-writes them in place over its own PCIe link; the counter all-reduce is the completion barrier.
-        from ceres_raytracer_b200.shard import SharedHostFrame
-        hf = SharedHostFrame(f"ceres_bench_{os.environ.get('MASTER_PORT', '0')}", (H, W, 3), rank, world)
-        t_e2e = 0.0
-        for k in range(steps_e2e + 2):
-            flush.fill_(1)
-            barrier()
-            t0 = time.perf_counter()
-            cnt_e2e = hf.render(scene, cam, sun, W, H, flags=flags)
-            if k >= 2:
-                t_e2e += time.perf_counter() - t0
-        if rank == 0:
-            assert tuple(cnt_e2e) == (rays_frame, hits_frame)
-        hf.close()
-        t = torch.tensor([scene.last_d2h_bytes], dtype=torch.int64, device=dev)
-        dist.all_reduce(t)
-        d2h = int(t.item())
-    if world != 1:
-        ppm8 = None
-    ms_e2e = allmax(1e3 * t_e2e / steps_e2e)
+            tot = 0.0
+            for _ in range(n):
+                flush.fill_(1)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                out = fn()
+                tot += time.perf_counter() - t0
+            return 1e3 * tot / n, out
+
+        if world == 1:
+            # N = 1: ceres_render() (the drop-in for render.hpp:86-156): launch + D2H of the frame + counters inside the timed region
+            hb = cr.PinnedBuffer((H, W, 3), np.float32)
+            ms_e2e, r = time_host_call(lambda: scene.render(cam, sun, W, H, flags=flags, pixels=hb.array))
+            assert r[2] == (rays_frame, hits_frame)
+            d2h = scene.last_d2h_bytes        # the rectangles that hold hit pixels + counters; the rest of the frame is host-filled zeros
+            hb.close()
+            # the same call into a plain malloc'ed frame -- what anim.cpp:76 / static.cpp:117 hand to render()
+            plain = np.empty((H, W, 3), np.float32)
+            ms_pg, r = time_host_call(lambda: scene.render(cam, sun, W, H, flags=flags, pixels=plain))
+            assert r[2] == (rays_frame, hits_frame)
+            extra["e2e_pageable"] = {"value": rays_frame / (ms_pg * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_pg,
+                                     "d2h_bytes_per_step": scene.last_d2h_bytes,
+                                     "path": "ceres_render() -> plain malloc'ed (pageable) frame, the buffer anim.cpp:76 / static.cpp:117 pass"}
+            del plain
+            # the same frame as 8-bit P6 payload (static.cpp:135-147 on the device; N1): a quarter of the bytes
+            hb8 = cr.PinnedBuffer((H, W, 3), np.uint8)
+            ms8, _ = time_host_call(lambda: scene.render_ppm8(cam, sun, W, H, flags=flags, out=hb8.array))
+            ppm8 = {"value": rays_frame / (ms8 * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms8,
+                    "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm8() -> page-locked 8-bit P6 payload"}
+            hb8.close()
+            # and as 16-bit payload (the x 65535 scaling of anim.cpp:117-119 on the device): half of the bytes
+            hb16 = cr.PinnedBuffer((H, W, 3), np.uint16)
+            ms16, _ = time_host_call(lambda: scene.render_ppm16(cam, sun, W, H, flags=flags, out=hb16.array))
+            ppm8["ppm16"] = {"value": rays_frame / (ms16 * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms16,
+                             "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm16() -> page-locked 16-bit P6 payload"}
+            hb16.close()
+            extra["e2e_ppm8"] = ppm8
+        else:
+            # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
+            # DMA-writes them in place over its own PCIe link; the counter barrier in the shared control page completes it.
+            from ceres_raytracer_b200.shard import SharedHostFrame
+            hf = SharedHostFrame(f"ceres_bench_{os.environ.get('MASTER_PORT', '0')}", (H, W, 3), rank, world)
+            t_e2e = 0.0
+            for k in range(steps_e2e + 2):
+                flush.fill_(1)
+                barrier()
+                t0 = time.perf_counter()
+                cnt_e2e = hf.render(scene, cam, sun, W, H, flags=flags)
+                if k >= 2:
+                    t_e2e += time.perf_counter() - t0
+            if rank == 0:
+                assert tuple(cnt_e2e) == (rays_frame, hits_frame)
+            hf.close()
+            t = torch.tensor([scene.last_d2h_bytes], dtype=torch.int64, device=dev)
+            dist.all_reduce(t)
+            d2h = int(t.item())
+            ms_e2e = allmax(1e3 * t_e2e / steps_e2e)
+        # host-side floor of a float host frame: every byte of it is written into host DRAM by somebody
+        try:
+            fill_gbs = cr.probe_host_fill_bandwidth(256 << 20, 3) if rank == 0 else 0.0
+        except Exception:
+            fill_gbs = 0.0
+        clocks.mark("between")
 
     # ---- CPU baseline: the reference's own render() on this box's host cores (rank 0, N = 1 only) ------------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         try:
-            secs, kind, cores, rays_cpu = cpu_reference_frames(pod, cam.as_array(), sun, W, H, frames=8, warmup=1, budget_s=12.0)
+            secs, kind, cores, rays_cpu, _h = cpu_reference_frames(pod, cam.as_array(), sun, W, H, frames=8, warmup=1, budget_s=12.0)
             ms_cpu = 1e3 * float(np.mean(secs))
             cpu = {"value": rays_cpu / (ms_cpu * 1e-3) / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
                    "ms_per_frame": ms_cpu,
@@ -596,36 +711,63 @@ def main():
         del px, ids, o
 
     if rank == 0:
+        ck = clocks.summary()
+        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+        # issue roofline: warp instructions of the frame kernel (deterministic for a workload; counted by the committed
+        # ncu capture) against the issue slots of the SMs -- 4 schedulers per SM, one warp instruction per cycle each
+        issue = None
+        ip = os.path.join(ROOT, "profiles", "ncu_frame_kernel.json")
+        if os.path.exists(ip) and args.workload == WORKLOAD and world == 1:
+            try:
+                cap = json.load(open(ip))
+                f_hz = (ck["sm_mhz"] or ck["sm_max_mhz"] or 1965.0) * 1e6
+                slots = sm_count * 4 * f_hz * kavg["frame"] * 1e-3
+                issue = {"warp_instructions": cap["warp_instructions"], "issue_slots": slots, "frac": cap["warp_instructions"] / slots,
+                         "lanes_per_instruction": cap.get("lanes_per_instruction"), "sm_mhz": f_hz / 1e6,
+                         "ncu_issue_active_pct": cap.get("issue_active_pct"), "source": cap.get("source")}
+            except Exception:
+                issue = None
+        host_bytes = 3 * W * H * 4
         line = {
             "metric": metric_name(args.workload, W, H, flags), "value": rays_frame / (ms_step * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": DATA,
-            "config": {"workload": args.workload, "width": W, "height": H, "rays_per_frame": rays_frame,
-                       "hits_counter": hits_frame, "scene_device_bytes": scene.device_bytes,
-                       "sharding": (f"{world} x interleaved {cfg.TILE_BLOCK_ROWS}-row blocks, " + ("kernels store into rank 0's frame over NVLink peer memory (no collective)" if pf is not None else "NCCL gather to rank 0")) if world > 1 else "none",
-                       "l2": "flushed (256 MiB fill) before every timed frame", "ms_per_step_warm_l2": ms_warm},
+            "config": frame_config(args.workload, W, H, rays_frame, scene_device_bytes(pod), sharding_text(world, pf is not None), L2_TEXT),
+            "counters": {"rays": rays_frame, "hits": hits_frame},
+            "rays_traced": {"per_frame": rays_traced, "value": rays_traced / (ms_step * 1e-3) / 1e6, "unit": "M traced rays/s",
+                            "note": "rays actually walked through the BVH: pixels of the scene's conservative screen rectangle + shadow rays; "
+                                    "`value` counts the reference's rays (W*H + primary hits), most of which miss the rectangle"},
+            "sustained": {"ms_per_step": ms_sus, "value": rays_frame / (ms_sus * 1e-3) / 1e6, "unit": UNIT, "frames": n_sus,
+                          "seconds": ms_sus * n_sus * 1e-3, "l2": "not flushed (back-to-back frames; every frame rewrites the frame buffer)",
+                          "ms_per_step_same_length_as_timed": ms_warm,
+                          "sm_mhz": ck["regions"].get("sustained", {}).get("sm_mhz"), "clock_samples": ck["regions"].get("sustained", {}).get("samples", 0)},
             "e2e": {"value": rays_frame / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": d2h, "host_frame_bytes": 3 * W * H * 4,
+                    "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": d2h, "host_frame_bytes": host_bytes,
+                    "floor_ms": (host_bytes / (fill_gbs * 1e9) * 1e3) if fill_gbs else None, "host_fill_gbs": fill_gbs or None,
+                    "floor_note": "host_frame_bytes / streaming-store bandwidth of the host-fill pool measured in this run: every byte of the "
+                                  "frame is written into host DRAM by somebody (DMA for the hit rectangles, the pool for the zeros)",
                     "path": "ceres_render() -> page-locked host framebuffer" if world == 1 else
                             "ceres_render_shard() per rank -> one shared page-locked host frame, each GPU drains its rows over its own PCIe link"},
             "gpu_launches": launches,
-            "kernels_ms": kavg,
-            "roofline": {"bound": "hbm", "kernel": dominant + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": abytes[dominant],
+            "kernels_ms": kavg, "kernels_ms_per_rank": per_rank_kernel_ms,
+            "roofline": {"bound": "issue", "kernel": "frame_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": ncu_dram_traffic(args.workload), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": abytes["frame"],
+                         "issue": issue,
                          "l2": {"peak": l2_peak, "frac": (achieved / l2_peak) if l2_peak else None, "unit": "GB/s",
                                 "peak_source": "measured here: ceres_probe_read_bandwidth, 48 MiB working set, 128-bit __ldg reads"},
                          "whole_frame": {"achieved": whole, "frac": whole / peak, "bytes": sum(abytes.values())},
                          "work": {k: st[k] for k in ("S_miss", "T_miss", "S_hit", "T_hit", "S_shadow", "T_shadow", "hits_primary", "occluded")},
-                         "note": ("scene (3 MB) is L1/L2-resident: the HBM peak is the conservative denominator SURVEY.md 8(d) asks for"
-                                  if scene.device_bytes < (64 << 20) else
-                                  f"scene ({scene.device_bytes / 1e9:.2f} GB) exceeds the 126 MB L2: node/triangle fetches are HBM/L2-miss traffic")},
-            "clocks": clocks.summary(),
+                         "note": ("the 3 MB scene is L1/L2-resident (ncu: DRAM traffic ~1 % of the algorithmic bytes), so achieved/peak/frac -- the "
+                                  "HBM-denominated figures SURVEY.md 8(d) prescribes -- exceed 1 and are context only; the kernel is bound by "
+                                  "instruction issue x SIMD efficiency: see `issue`"
+                                  if scene_device_bytes(pod) < (64 << 20) else
+                                  f"scene ({scene_device_bytes(pod) / 1e9:.2f} GB) exceeds the 126 MB L2: node/triangle fetches are HBM/L2-miss traffic")},
+            "clocks": ck,
         }
+        line.update(extra)
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        if ppm8 is not None:
-            line["e2e_ppm8"] = ppm8
         if verified is not None:
             line["verified"] = verified
         if args.workload != WORKLOAD:
@@ -633,6 +775,17 @@ def main():
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_dram_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the frame kernel, per launch, from the committed ncu --set full capture."""
+    tp = os.path.join(ROOT, "profiles", "ncu_frame_kernel.json")
+    if workload != WORKLOAD or not os.path.exists(tp):
+        return None
+    try:
+        return json.load(open(tp)).get("dram_bytes")
+    except Exception:
+        return None
 
 
 if __name__ == "__main__":

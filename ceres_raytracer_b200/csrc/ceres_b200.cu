@@ -653,6 +653,7 @@ struct ceres_scene {
     bool borrowed = false;                                  // a view: the geometry belongs to the scene it was made from
     uint32_t ext_epoch = 0;
     uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
+    uint32_t last_rect[4] = {0, 0, 0, 0};                   // conservative screen rectangle of the last frame: columns [0],[1]; local rows [2],[3]
 };
 
 namespace {
@@ -1296,6 +1297,34 @@ int ceres_probe_read_bandwidth(int device, size_t working_set_bytes, int repeats
     return CERES_OK;
 }
 
+int ceres_scene_last_rectangle(const ceres_scene* s, uint32_t rect[4]) {
+    if (!s || !rect) return fail(CERES_ERR_INVALID, "ceres_scene_last_rectangle: null argument");
+    for (int k = 0; k < 4; ++k) rect[k] = s->last_rect[k];
+    return CERES_OK;
+}
+
+// Streaming-store bandwidth of the host-fill pool into page-locked memory: the denominator of the host-frame floor
+// (every byte of a host frame is written into host DRAM by somebody: DMA for the rectangle, this pool for the zeros).
+int ceres_probe_host_fill_bandwidth(size_t bytes, int repeats, double* gb_per_s) {
+    if (!gb_per_s || bytes < (1u << 20) || repeats < 1) return fail(CERES_ERR_INVALID, "ceres_probe_host_fill_bandwidth: bad argument");
+    void* buf = nullptr;
+    CUDA_TRY(cudaMallocHost(&buf, bytes));
+    ceres_host::Pool& pool = ceres_host::Pool::instance();
+    double best = 0.0;
+    for (int r = 0; r < repeats + 1; ++r) {
+        ceres_host::Job job;
+        job.add(buf, bytes, 0x00);
+        const auto t0 = std::chrono::steady_clock::now();
+        pool.submit(&job);
+        pool.wait(&job);
+        const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (r > 0 && sec > 0.0) best = std::max(best, (double)bytes / sec / 1e9);       // r = 0 touches the pages
+    }
+    cudaFreeHost(buf);
+    *gb_per_s = best;
+    return CERES_OK;
+}
+
 int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");
     if (t) s->tune = *t; else s->tune = ceres_tuning{};
@@ -1435,6 +1464,7 @@ static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float su
     f.ctr = s->d_ctr;
     if (s->tune.variant != 2) cull_rectangle(s->bounds, f, rows_local);
     else { f.cull_i0 = 0; f.cull_i1 = f.W; f.cull_l0 = 0; f.cull_l1 = rows_local; }
+    s->last_rect[0] = f.cull_i0; s->last_rect[1] = f.cull_i1; s->last_rect[2] = f.cull_l0; s->last_rect[3] = f.cull_l1;
     return CERES_OK;
 }
 

@@ -86,6 +86,13 @@ def probe_read_bandwidth(working_set_bytes, repeats=20, device=0):
     return float(out.value)
 
 
+def probe_host_fill_bandwidth(nbytes=256 << 20, repeats=3):
+    """GB/s of the library's host-fill pool into page-locked memory (ceres_probe_host_fill_bandwidth)."""
+    out = C.c_double(0.0)
+    _capi.check(_capi.lib().ceres_probe_host_fill_bandwidth(int(nbytes), int(repeats), C.byref(out)))
+    return float(out.value)
+
+
 def build_lbvh(triangles, device=0):
     """GPU linear-BVH build (ceres_build_lbvh): returns (nodes NODE_DT[2n-1], prim_indices uint64[n], build_ms) in the
     reference's layout for `triangles` float32[n, 12]."""
@@ -159,6 +166,13 @@ class Scene:
     def last_d2h_bytes(self):
         """Bytes the last host-frame render moved over PCIe (the scene's screen rectangle + counters)."""
         return int(self._L.ceres_scene_last_d2h_bytes(self._h))
+
+    @property
+    def last_rectangle(self):
+        """(i0, i1, l0, l1): columns x local rows of the conservative screen rectangle traced for the last frame."""
+        out = np.zeros(4, np.uint32)
+        _capi.check(self._L.ceres_scene_last_rectangle(self._h, _p(out)))
+        return tuple(int(x) for x in out)
 
     def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, shadow_order=0, refill_min=0, subframes=0, chunk=0):
         """variant 0 = the frame kernel; 1-6 = the wave pipelines (experiments build only).  shadow_order: 0 default,

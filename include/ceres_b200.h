@@ -95,6 +95,9 @@ size_t ceres_scene_device_bytes(const ceres_scene* scene);
 /* bytes the last host-frame render (ceres_render / _shard / one frame of _sequence) moved over PCIe: the screen
  * rectangle of the scene's rows + the counters; everything else of the frame is zero-filled by host threads */
 uint64_t ceres_scene_last_d2h_bytes(const ceres_scene* scene);
+/* conservative screen rectangle of the scene in the last frame prepared on this scene: columns [rect[0], rect[1]) x LOCAL
+ * rows [rect[2], rect[3]) of the shard; only its pixels are traced (everything outside cannot hit anything) */
+int ceres_scene_last_rectangle(const ceres_scene* scene, uint32_t rect[4]);
 
 /* ---- scene preparation on the device (the step before the path) ------------------------------
  * For animated objects: move the triangles that already live on the GPU and refit the BVH there, instead of a host
@@ -291,6 +294,11 @@ int ceres_host_is_pinned(const void* p);
  * read kernel (best of 5): a few MB per SM-resident set -> L1, 16-64 MB -> L2, >= 1 GB -> HBM.  bench.py reports
  * the cache-resident scene's traffic against the L2 figure next to the HBM roofline. */
 int ceres_probe_read_bandwidth(int device, size_t working_set_bytes, int repeats, double* gb_per_s);
+
+/* Streaming-store bandwidth (GB/s, best of `repeats`) of the library's host-fill pool into `bytes` of page-locked memory.
+ * Every byte of a host frame has to be written into host DRAM by somebody -- DMA for the scene's rectangle, this pool
+ * for the zeros around it -- so host_frame_bytes / this figure is the floor of a host-frame call (bench.py e2e.floor_ms). */
+int ceres_probe_host_fill_bandwidth(size_t bytes, int repeats, double* gb_per_s);
 
 /* ---- misc --------------------------------------------------------------------------------------------------- */
 int ceres_abi_version(void);
