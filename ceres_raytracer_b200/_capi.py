@@ -50,7 +50,7 @@ SYMBOLS = [
     "ceres_peer_frame_invalidate",
 ]
 SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download",
-            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth"]
+            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -63,7 +63,13 @@ def lib():
     # CERES_B200_EXPERIMENTS=1 (profiles/kbench.py, tests/test_gpu_experiments.py): the -DCERES_EXPERIMENTS build
     experiments = os.environ.get("CERES_B200_EXPERIMENTS", "") not in ("", "0")
     path = _build.LIB_EXP if experiments else _build.LIB
-    if _build.needs_build(path):
+    # development aid (profiles/kbench.py A/B of compile-time options): a library built by `build.py --variant NAME -D...`
+    variant = os.environ.get("CERES_B200_VARIANT", "")
+    if variant:
+        path = _build.variant_path(variant)
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} is missing: build it with python -m ceres_raytracer_b200.build --variant {variant} [nvcc flags]")
+    elif _build.needs_build(path):
         try:
             _build.build(experiments=experiments)
         except Exception as e:  # no nvcc on the box and no prebuilt library: fail loudly, never fall back
@@ -128,6 +134,8 @@ def lib():
     L.ceres_scene_download.argtypes = [vp, vp, sz, vp, sz]
     L.ceres_scene_last_rectangle.argtypes = [vp, vp]
     L.ceres_probe_host_fill_bandwidth.argtypes = [sz, C.c_int, vp]
+    L.ceres_scene_get_timeline.argtypes = [vp, vp, sz, vp]
+    L.ceres_scene_set_timeline.argtypes = [vp, C.c_int]
     L.ceres_abi_version.restype = C.c_int
     L.ceres_device_count.restype = C.c_int
     L.ceres_kernel_launch_count.restype = u64

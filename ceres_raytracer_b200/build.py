@@ -43,16 +43,25 @@ def needs_build(lib=LIB):
     return any(os.path.getmtime(p) > t for p in _deps())
 
 
-def build(force=False, verbose=False, experiments=False):
-    lib = LIB_EXP if experiments else LIB
-    if not force and not needs_build(lib):
+def variant_path(name):
+    return os.path.join(HERE, f"libceres_b200_{name}.so")
+
+
+def build(force=False, verbose=False, experiments=False, variant=None, extra=()):
+    lib = variant_path(variant) if variant else LIB_EXP if experiments else LIB
+    if not force and not variant and not needs_build(lib):
         return lib
     cmd = [nvcc()] + NVCC_FLAGS + (["-DCERES_EXPERIMENTS", "-diag-suppress", "177"] if experiments else []) \
-        + (["-Xptxas", "-v"] if verbose else []) + ["-o", lib, SRC]
+        + (["-Xptxas", "-v"] if verbose else []) + list(extra) + ["-o", lib, SRC]
     subprocess.check_call(cmd, env=dict(os.environ))
     return lib
 
 
 if __name__ == "__main__":
     import sys
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, experiments="--experiments" in sys.argv))
+    # --variant NAME [nvcc flags...]: libceres_b200_NAME.so with extra compile-time options, loaded with CERES_B200_VARIANT=NAME
+    if "--variant" in sys.argv:
+        k = sys.argv.index("--variant")
+        print(build(variant=sys.argv[k + 1], extra=sys.argv[k + 2:]))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, experiments="--experiments" in sys.argv))

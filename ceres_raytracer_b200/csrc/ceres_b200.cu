@@ -64,6 +64,7 @@ struct DevScene {
     uint32_t root_leaf_count;  // != 0: the root itself is a leaf (single_ray_traverser.hpp:72-73)
     uint32_t stack_depth;      // entries of traversal stack needed (<= 64, single_ray_traverser.hpp:14)
     unsigned long long* hist;  // statistics mode: 2 x 64 bins of node-pair steps per ray (bin = steps / 4), primary then shadow; may be null
+    unsigned long long* timeline;  // CERES_TIMELINE_WORDS words per warp of the frame kernel (ceres_scene_set_timeline); null = off
 };
 
 struct FrameCounters {
@@ -100,7 +101,7 @@ struct Frame {
     uint32_t shadows;
     // persistent primary wave: conservative screen rectangle of the scene, in local rows / columns of this launch,
     // cut into 8x4-pixel tiles (work item = tile * 32 + pixel in tile)
-    uint32_t rect_x0, rect_x1, rect_row0, rect_row1, tiles_x, work_items;
+    uint32_t rect_x0, rect_x1, rect_row0, rect_row1, tiles_x, tiles_y, work_items;
     uint32_t refill_min;                            // refill a warp when at least this many ray slots are idle (1..32)
     uint32_t chunk;                                 // work items a warp takes from the global cursor at a time (multiple of 32)
     uint32_t cull_i0, cull_i1, cull_l0, cull_l1;   // host only: the rectangle for the whole frame (columns, LOCAL rows)
@@ -116,12 +117,16 @@ struct Frame {
     uint32_t skip_clear;       // experiment kernels: the rows were zeroed by somebody else (rank 0 in peer mode)
     uint32_t peer_wait_world;  // frame kernel, rank 0 of a peer frame: wait for this many ranks' done flags at the end (0 = no)
     unsigned long long* peer_out;   // ... and put the frame's summed (rays, hits) here (nullable)
+    uint32_t* gate;            // peer frames, ranks > 0: LOCAL relay of rank 0's cleared_epoch {flag, poller election} (frame_fused.cuh)
     uint32_t* ready;           // frame kernel: per-32-record-chunk fill counters of this launch's queue region (frame_fused.cuh)
     unsigned long long* out_error;  // frame kernel: FRAME_ERR_* bits are ORed in here (nullable)
     // host-frame path: where the band's last shade CTA publishes the extents of its hit pixels (mapped page-locked host
     // memory, 8 words per band: ext[4], then the frame's epoch as the ready flag); null = not wanted
     uint32_t* host_ext;
     uint32_t ext_epoch;
+    // frame kernel, shadow-subtree sharing (frame_fused.cuh): steps between two rounds of bookkeeping; idle lanes needed for a hand-over round
+    uint32_t share_period, share_min_idle;
+    uint32_t chunk_shift;      // frame kernel: a shadow work item is 1 << chunk_shift queue records (3..5)
 };
 
 // ------------------------------------------------------------------------------------------------ device math
@@ -629,6 +634,7 @@ struct ceres_scene {
     uint32_t* d_parent = nullptr; uint32_t* d_need = nullptr; uint32_t* d_arrived = nullptr;   // made by the first refit
     float* d_root_bounds = nullptr;
     unsigned long long* d_hist = nullptr;                   // step histogram (ceres_scene_get_step_histogram)
+    unsigned long long* d_timeline = nullptr; size_t timeline_warps = 0;   // per-warp timestamps of the last statistics frame (ceres_scene_get_timeline)
     FrameCounters* d_ctr = nullptr;
     uint4* d_queue = nullptr; size_t queue_cap = 0;
     uint32_t* d_ready = nullptr; size_t ready_cap = 0;     // per-chunk fill counters of the queue (frame_fused.cuh), all-zero between launches
@@ -645,7 +651,7 @@ struct ceres_scene {
     size_t prof_frames = 0;
     ceres_tuning tune{};
     int shadow_blocks_per_sm = 0, shadow_blocks_per_sm_stats = 0;
-    int trace_blocks_per_sm[4] = {0, 0, 0, 0};              // [wave*2 + stats]
+    int trace_blocks_per_sm[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // frame kernel: [stats + 2 * left-first + 4 * no-share], 8/9 timeline build; experiments: [wave*2 + stats]
     float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
     uint64_t last_d2h_bytes = 0;                            // bytes DMA-copied to the host by the last host-frame render
     uint32_t* h_ext = nullptr;                              // mapped page-locked: 8 words per band (Frame::host_ext)
@@ -653,6 +659,7 @@ struct ceres_scene {
     bool borrowed = false;                                  // a view: the geometry belongs to the scene it was made from
     uint32_t ext_epoch = 0;
     uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
+    uint32_t cur_nsub = 1;                                  // row bands of the frame being enqueued (render_rows)
     uint32_t last_rect[4] = {0, 0, 0, 0};                   // conservative screen rectangle of the last frame: columns [0],[1]; local rows [2],[3]
 };
 
@@ -932,7 +939,7 @@ void ceres_scene_destroy(ceres_scene* s) {
     if (s->frame_done) cudaEventDestroy(s->frame_done);
     if (s->seq_view) { ceres_scene_destroy(s->seq_view); s->seq_view = nullptr; }
     if (s->borrowed) { s->d_pairs = s->d_tris = s->d_norms = s->d_slot_id = nullptr; s->d_parent = s->d_need = s->d_arrived = nullptr; s->d_root_bounds = nullptr; s->d_hist = nullptr; }
-    cudaFree(s->d_hist);
+    cudaFree(s->d_hist); cudaFree(s->d_timeline);
     cudaFree(s->d_parent); cudaFree(s->d_need); cudaFree(s->d_arrived); cudaFree(s->d_root_bounds);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_ctr); cudaFree(s->d_queue); cudaFree(s->d_ready); cudaFree(s->d_pixels); cudaFree(s->d_ids); cudaFree(s->d_rgb8); cudaFree(s->d_out);
@@ -1329,7 +1336,7 @@ int ceres_scene_set_tuning(ceres_scene* s, const ceres_tuning* t) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");
     if (t) s->tune = *t; else s->tune = ceres_tuning{};
     s->shadow_blocks_per_sm = s->shadow_blocks_per_sm_stats = 0;
-    for (int k = 0; k < 4; ++k) s->trace_blocks_per_sm[k] = 0;
+    for (int k = 0; k < 10; ++k) s->trace_blocks_per_sm[k] = 0;
     return CERES_OK;
 }
 
@@ -1339,6 +1346,29 @@ int ceres_scene_get_step_histogram(ceres_scene* s, uint64_t hist[128]) {
     DeviceGuard guard(s->device);
     CUDA_TRY(cudaMemcpy(hist, s->d_hist, 128 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     CUDA_TRY(cudaMemset(s->d_hist, 0, 128 * sizeof(uint64_t)));
+    return CERES_OK;
+}
+
+int ceres_scene_set_timeline(ceres_scene* s, int enable) {
+    if (!s) return fail(CERES_ERR_INVALID, "null scene");
+    DeviceGuard guard(s->device);
+    if (enable && !s->d_timeline) {
+        s->timeline_warps = (size_t)s->sm_count * 16 * (FRAME_THREADS / 32);
+        CUDA_TRY(cudaMalloc((void**)&s->d_timeline, s->timeline_warps * CERES_TIMELINE_WORDS * sizeof(unsigned long long)));
+    }
+    CUDA_TRY(cudaDeviceSynchronize());
+    s->dev.timeline = enable ? s->d_timeline : nullptr;
+    return CERES_OK;
+}
+
+int ceres_scene_get_timeline(ceres_scene* s, uint64_t* out, size_t cap_warps, size_t* warps) {
+    if (!s || !out || !warps) return fail(CERES_ERR_INVALID, "null argument");
+    if (!s->d_timeline) return fail(CERES_ERR_INVALID, "ceres_scene_get_timeline: ceres_scene_set_timeline was never enabled");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaDeviceSynchronize());
+    const size_t n = std::min(cap_warps, s->timeline_warps);
+    CUDA_TRY(cudaMemcpy(out, s->d_timeline, n * CERES_TIMELINE_WORDS * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    *warps = n;
     return CERES_OK;
 }
 
@@ -1473,7 +1503,7 @@ enum { CLEAR_NONE = 0,       // nothing: the caller never reads outside the rect
        CLEAR_OUTSIDE = 1 };  // every pixel of the launch's rows outside the rectangle (caller-owned device frames)
 
 // ready[] entries (frame_fused.cuh) a launch over `records` queue slots can touch: its chunks + one terminating entry per warp
-static size_t ready_words(const ceres_scene* s, size_t records) { return records / 32 + 2 + (size_t)s->sm_count * 16 * (FRAME_THREADS / 32); }
+static size_t ready_words(const ceres_scene* s, size_t records) { return (records >> READY_MIN_SHIFT) + 2 + (size_t)s->sm_count * 16 * (FRAME_THREADS / 32); }
 
 #ifdef CERES_EXPERIMENTS
 static int launch_rows_waves(ceres_scene* s, Frame& f, uint32_t row_begin, uint32_t row_end, cudaStream_t st, cudaEvent_t* pe);
@@ -1487,7 +1517,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
     // concurrently on different streams (the caller has sized the queue for the whole shard)
     if ((size_t)row_end * f.W > s->queue_cap) return fail(CERES_ERR_INVALID, "internal: queue not sized for the frame");
     f.queue = s->d_queue + (size_t)row_begin * f.W;
-    f.ready = s->d_ready + ((size_t)row_begin * f.W) / 32 + (size_t)sub * ready_words(s, 0);
+    f.ready = s->d_ready + (((size_t)row_begin * f.W) >> READY_MIN_SHIFT) + (size_t)sub * ready_words(s, 0);
     f.ctr = s->d_ctr + sub;
     f.out_error = s->d_out + 10;
     if (f.host_ext) f.host_ext += 8 * sub;
@@ -1505,7 +1535,8 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         const uint32_t r0 = std::max(row_begin, f.cull_l0), r1 = std::min(row_end, f.cull_l1);
         f.rect_x0 = f.cull_i0; f.rect_x1 = f.cull_i1; f.rect_row0 = r0; f.rect_row1 = r1 > r0 ? r1 : r0;
         f.tiles_x = (f.rect_x1 - f.rect_x0 + 7u) / 8u;
-        const uint64_t tiles = (uint64_t)f.tiles_x * ((f.rect_row1 - f.rect_row0 + 3u) / 4u);
+        f.tiles_y = (f.rect_row1 - f.rect_row0 + 3u) / 4u;
+        const uint64_t tiles = (uint64_t)f.tiles_x * f.tiles_y;
         if (tiles * 32u >= (1ull << 32)) return fail(CERES_ERR_INVALID, "ceres_render: image too large");
         f.work_items = (uint32_t)(tiles * 32u);
     }
@@ -1540,9 +1571,31 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
             CUDA_TRY(cudaGetLastError());
             return CERES_OK;
         };
+        // reserved[0]: 0 default, 1 off, 2 on; reserved[2]: period | min_idle << 8 (0 = defaults).  Default: on when the launch is
+        // small enough for its tail to matter -- fewer than FRAME_SHARE_AUTO_PX rectangle pixels per resident warp (a rank's share
+        // of a frame at N >= 4, small images); a full 4K frame on one GPU is throughput-bound and runs 2 % faster without it
+        // (profiles/r2/sweeps.md).  Row bands of one frame overlap each other's tails instead.
+        const uint64_t warps_guess = (uint64_t)s->sm_count * 8u * (FRAME_THREADS / 32);
+        const bool share_auto = s->cur_nsub <= 1u && f.work_items / warps_guess < FRAME_SHARE_AUTO_PX;
+        const bool share = s->tune.reserved[0] ? s->tune.reserved[0] == 2u : share_auto;
+        f.share_period = (s->tune.reserved[2] & 0xFFu) ? (s->tune.reserved[2] & 0xFFu) : FRAME_SHARE_PERIOD;
+        f.share_min_idle = ((s->tune.reserved[2] >> 8) & 0xFFu) ? ((s->tune.reserved[2] >> 8) & 0xFFu) : FRAME_SHARE_MIN_IDLE;
+        if (s->dev.timeline) CUDA_TRY(cudaMemsetAsync(s->d_timeline, 0, s->timeline_warps * CERES_TIMELINE_WORDS * sizeof(unsigned long long), st));
+        {   // records per shadow work item: tune.shadow_block = 8 / 16 / 32, 0 = default
+            const uint32_t want = s->tune.shadow_block ? s->tune.shadow_block : FRAME_DEFAULT_CHUNK;
+            f.chunk_shift = want <= 8u ? 3u : want <= 16u ? 4u : 5u;
+        }
         int rc;
-        if (s->stats) rc = order == ORDER_NEAR ? go(frame_kernel<true, ORDER_NEAR>, 1) : go(frame_kernel<true, ORDER_LEFT>, 3);
-        else rc = order == ORDER_NEAR ? go(frame_kernel<false, ORDER_NEAR>, 0) : go(frame_kernel<false, ORDER_LEFT>, 2);
+        const int near = order == ORDER_NEAR;
+        if (s->dev.timeline && !s->stats) {      // the timeline build: default child order only
+            rc = share ? go(frame_kernel<false, FRAME_DEFAULT_SHADOW_ORDER, true, true>, 8) : go(frame_kernel<false, FRAME_DEFAULT_SHADOW_ORDER, false, true>, 9);
+        } else if (s->stats) {
+            rc = share ? (near ? go(frame_kernel<true, ORDER_NEAR, true, false>, 1) : go(frame_kernel<true, ORDER_LEFT, true, false>, 3))
+                       : (near ? go(frame_kernel<true, ORDER_NEAR, false, false>, 5) : go(frame_kernel<true, ORDER_LEFT, false, false>, 7));
+        } else {
+            rc = share ? (near ? go(frame_kernel<false, ORDER_NEAR, true, false>, 0) : go(frame_kernel<false, ORDER_LEFT, true, false>, 2))
+                       : (near ? go(frame_kernel<false, ORDER_NEAR, false, false>, 4) : go(frame_kernel<false, ORDER_LEFT, false, false>, 6));
+        }
         if (rc) return rc;
     }
     if (pe) { CUDA_TRY(cudaEventRecord(pe[2], st)); CUDA_TRY(cudaEventRecord(pe[3], st)); }
@@ -1585,7 +1638,8 @@ static int launch_rows_waves(ceres_scene* s, Frame& f, uint32_t row_begin, uint3
         const uint32_t r0 = std::max(row_begin, f.cull_l0), r1 = std::min(row_end, f.cull_l1);
         f.rect_x0 = f.cull_i0; f.rect_x1 = f.cull_i1; f.rect_row0 = r0; f.rect_row1 = r1 > r0 ? r1 : r0;
         f.tiles_x = (f.rect_x1 - f.rect_x0 + 7u) / 8u;
-        const uint64_t tiles = (uint64_t)f.tiles_x * ((f.rect_row1 - f.rect_row0 + 3u) / 4u);
+        f.tiles_y = (f.rect_row1 - f.rect_row0 + 3u) / 4u;
+        const uint64_t tiles = (uint64_t)f.tiles_x * f.tiles_y;
         if (tiles * 32u >= (1ull << 32)) return fail(CERES_ERR_INVALID, "ceres_render: image too large");
         f.work_items = (uint32_t)(tiles * 32u);
         f.refill_min = s->tune.reserved[0] ? std::min(32u, s->tune.reserved[0]) : REFILL_MIN;
@@ -1703,7 +1757,7 @@ static int frame_error_check(ceres_scene* s) {
 
 // Sizes the record queue and its ready[] array for `records` queue slots.
 static int size_queue(ceres_scene* s, size_t records) {
-    const size_t need_ready = records / 32 + (size_t)CERES_MAX_SUB * ready_words(s, 0) + 2;
+    const size_t need_ready = (records >> READY_MIN_SHIFT) + (size_t)CERES_MAX_SUB * ready_words(s, 0) + 2;
     if (records <= s->queue_cap && need_ready <= s->ready_cap) return CERES_OK;
     CUDA_TRY(cudaDeviceSynchronize());      // growing the queue frees the old one: wait for frames still using it
     if (int rc = ensure(s->d_queue, s->queue_cap, records)) return rc;
@@ -1730,6 +1784,7 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
     // a band must be worth its four launches: at least 256 Ki pixels of the rectangle each
     const uint64_t rect_px = (uint64_t)rows * (f.cull_i1 > f.cull_i0 ? f.cull_i1 - f.cull_i0 : 1u);
     nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (uint32_t)std::max<uint64_t>(1u, rect_px >> 18));
+    s->cur_nsub = nsub;
     if (nsub <= 1) {
         s->profile_kernels = true;
         if (int rc = launch_rows(s, f, a, b, st, 0, clear_mode)) return rc;
@@ -1809,6 +1864,7 @@ struct ceres_peer_frame {
     // Dirty-rectangle bookkeeping of THIS rank's rows.  Invariant between frames: the rank's rows hold the last frame's
     // values inside `prev` (columns [i0, i1) x local rows [l0, l1)) and zeros / CERES_MISS everywhere else.
     uint32_t prev_i0 = 0, prev_i1 = 0, prev_l0 = 0, prev_l1 = 0;
+    uint32_t* d_gate = nullptr;    // ranks > 0: two words in THIS rank's memory, the local relay of rank 0's epoch flag (Frame::gate)
     bool dirty_all = false;        // somebody else wrote into the frame (ceres_peer_frame_invalidate): clear all my rows once
 };
 
@@ -1885,6 +1941,10 @@ int ceres_peer_frame_open(ceres_scene* s, const unsigned char* handle, size_t wi
     pf->base = base; pf->mapped = true; pf->device = s->device; pf->world = world; pf->rank = rank;
     pf->W = width; pf->H = height; pf->with_ids = want_ids != 0;
     peer_layout(pf);
+    if (cudaMalloc((void**)&pf->d_gate, 2 * sizeof(uint32_t)) != cudaSuccess || cudaMemset(pf->d_gate, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {
+        cudaIpcCloseMemHandle(base); cudaFree(pf->d_gate); delete pf;
+        return fail(CERES_ERR_CUDA, std::string("ceres_peer_frame_open: ") + cudaGetErrorString(cudaGetLastError()));
+    }
     *out = pf;
     return CERES_OK;
 }
@@ -1906,6 +1966,17 @@ int ceres_peer_frame_alias(ceres_peer_frame* owner, ceres_scene* s, int rank, ce
     ceres_peer_frame* pf = new (std::nothrow) ceres_peer_frame(*owner);
     if (!pf) return fail(CERES_ERR_INVALID, "out of host memory");
     pf->owner = false; pf->mapped = false; pf->device = s->device; pf->rank = rank; pf->epoch = owner->epoch;
+    pf->d_gate = nullptr;
+    {
+        DeviceGuard guard(s->device);
+        // the relay starts at the owner's current epoch: everything up to it has been announced
+        if (cudaMalloc((void**)&pf->d_gate, 2 * sizeof(uint32_t)) != cudaSuccess ||
+            cudaMemcpy(pf->d_gate, &pf->epoch, sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaMemcpy(pf->d_gate + 1, &pf->epoch, sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess) {
+            cudaFree(pf->d_gate); delete pf;
+            return fail(CERES_ERR_CUDA, std::string("ceres_peer_frame_alias: ") + cudaGetErrorString(cudaGetLastError()));
+        }
+    }
     *out = pf;
     return CERES_OK;
 }
@@ -1916,6 +1987,7 @@ void ceres_peer_frame_destroy(ceres_peer_frame* pf) {
     cudaDeviceSynchronize();
     if (pf->owner) cudaFree(pf->base);
     else if (pf->mapped) cudaIpcCloseMemHandle(pf->base);
+    cudaFree(pf->d_gate);
     delete pf;
 }
 
@@ -1948,7 +2020,7 @@ int ceres_render_peer(ceres_scene* s, const ceres_camera* cam, const float sun[3
     DeviceGuard guard(s->device);
     cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
     const uint32_t epoch = ++pf->epoch;
-    f.peer = pf->ctl; f.peer_epoch = epoch; f.peer_rank = (uint32_t)pf->rank;
+    f.peer = pf->ctl; f.peer_epoch = epoch; f.peer_rank = (uint32_t)pf->rank; f.gate = pf->d_gate;
     if (pf->rank == 0) { f.peer_wait_world = (uint32_t)pf->world; f.peer_out = (unsigned long long*)d_counters; }
     s->rays_outside = 0;
     if (rows_local == 0) {
@@ -2326,7 +2398,7 @@ int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, si
     v->dev = s->dev; v->d_pairs = s->d_pairs; v->d_tris = s->d_tris; v->d_norms = s->d_norms; v->d_slot_id = s->d_slot_id;
     v->scene_bytes = s->scene_bytes; v->tri_count = s->tri_count; v->node_count = s->node_count; v->n_pairs = s->n_pairs;
     v->tune = s->tune; v->shadow_blocks_per_sm = s->shadow_blocks_per_sm; v->shadow_blocks_per_sm_stats = s->shadow_blocks_per_sm_stats;
-    for (int k = 0; k < 4; ++k) v->trace_blocks_per_sm[k] = s->trace_blocks_per_sm[k];
+    for (int k = 0; k < 10; ++k) v->trace_blocks_per_sm[k] = s->trace_blocks_per_sm[k];
     for (int k = 0; k < 6; ++k) v->bounds[k] = s->bounds[k];
     int rc_odd = CERES_OK; std::string err_odd;
     std::thread odd([&] {

@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_repack
     const V3 eye = mk(f.eye[0], f.eye[1], f.eye[2]);
 
     RaySlot r;
-    r.found = false; r.item = 0; r.sp = tid; r.cur = 0; r.tmax = 0.0f; r.u = r.v = 0.0f; r.slot = 0;
+    r.found = false; r.item = 0; r.sp = tid; r.sb = tid; r.cur = 0; r.tmax = 0.0f; r.u = r.v = 0.0f; r.slot = 0;
     r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.ix = r.iy = r.iz = r.sx = r.sy = r.sz = 0.0f;
     uint32_t col = tid;             // stack column owned by this lane's ray (or free for the next ray of this lane)
     bool live = false, retire = false;
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_repack
         if (live) {
             const uint32_t* x = xchg + tid;
             int k = 0;
-            r.item = x[THREADS * k++]; r.cur = x[THREADS * k++]; r.sp = x[THREADS * k++]; col = x[THREADS * k++];
+            r.item = x[THREADS * k++]; r.cur = x[THREADS * k++]; r.sp = x[THREADS * k++]; col = x[THREADS * k++]; r.sb = col;
             r.ox = __uint_as_float(x[THREADS * k++]); r.oy = __uint_as_float(x[THREADS * k++]); r.oz = __uint_as_float(x[THREADS * k++]);
             r.dx = __uint_as_float(x[THREADS * k++]); r.dy = __uint_as_float(x[THREADS * k++]); r.dz = __uint_as_float(x[THREADS * k++]);
             r.ix = __uint_as_float(x[THREADS * k++]); r.iy = __uint_as_float(x[THREADS * k++]); r.iz = __uint_as_float(x[THREADS * k++]);

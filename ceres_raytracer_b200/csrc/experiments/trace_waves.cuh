@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_kernel
     const V3 eye = mk(f.eye[0], f.eye[1], f.eye[2]);
 
     RaySlot r;
-    r.found = false; r.item = 0; r.sp = tid; r.cur = 0; r.tmax = 0.0f; r.u = r.v = 0.0f; r.slot = 0;
+    r.found = false; r.item = 0; r.sp = tid; r.sb = tid; r.cur = 0; r.tmax = 0.0f; r.u = r.v = 0.0f; r.slot = 0;
     r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.ix = r.iy = r.iz = r.sx = r.sy = r.sz = 0.0f;
     bool active = false;        // this lane holds a ray in flight
     bool retire = false;        // this lane holds a finished ray whose result is not yet published

@@ -10,6 +10,13 @@
 //   phase 2  SHADOW    once the tile cursor has run out, take queue chunk c (one atomicAdd), wait until ready[c] says
 //            + SHADE   its 32 records are written, rebuild the shadow rays (render.hpp:120-136), run the any-hit
 //                      traversal, and shade + store the 32 pixels (render.hpp:56-84,140-150) from registers.
+//            SHARE: while the 32 shadow rays of a chunk are walked, lanes whose ray has ended take over the OLDEST pending
+//            subtree (the bottom entry of the traversal stack) of a lane that is still busy and walk it with a copy of
+//            that ray; a hit found by any lane settles the record for all of them.  Parity-safe for shadow rays only:
+//            `bool(hit)` (render.hpp:137-140) is "some leaf that passes all slab tests above it holds a triangle hit in
+//            [0, FLT_MAX]" -- tmax never shrinks before the first accepted triangle, so the set of reachable leaves does
+//            not depend on who walks which subtree in which order.  It turns the idle lanes of the shadow phase (14 of
+//            32 active per instruction without it) into helpers and cuts the longest chains -- the tail of a frame.
 // So warps that run out of tiles during the primary tail start on shadow rays while the last primary warps are still
 // walking their long rays: one latency tail per frame instead of three (primary wave, shadow wave, shade pass), one
 // launch instead of four, and the only pass over the framebuffer is the one that writes final values.
@@ -101,23 +108,55 @@ __device__ __forceinline__ void publish_frame(const Frame& f, unsigned long long
 }
 
 // Peer frames: rank 0 owns the frame and announces "epoch e has begun" when its own kernels of that epoch start --
-// stream order puts that after whatever its process did with frame e-1.  The other ranks hold back their first store
-// of epoch e until then, so a rank that runs ahead never writes into a frame the owner is still reading.
-__device__ __forceinline__ void peer_begin_gate(const Frame& f) {
-    if (f.peer_rank == 0u) {
-        if (blockIdx.x == 0 && threadIdx.x == 0 && (int32_t)(ld_acquire_sys(&f.peer->cleared_epoch) - f.peer_epoch) < 0)
-            st_release_sys(&f.peer->cleared_epoch, f.peer_epoch);
-    } else {
-        if (threadIdx.x == 0 && !peer_wait_flag(&f.peer->cleared_epoch, f.peer_epoch)) f.peer->error = 1u;
-        __syncthreads();
+// stream order puts that after whatever its process did with frame e-1.  The other ranks hold back their first STORE
+// of epoch e until then (they trace meanwhile), so a rank that runs ahead never writes into a frame the owner is still
+// reading.  Only ONE thread per GPU polls rank 0's flag over NVLink: the first warp that needs the gate elects itself
+// (f.gate[1]), waits for the remote flag and relays it into f.gate[0] in local memory, where everybody else looks.
+// (Every CTA polling the remote word -- 7 x 1184 pollers on one address at N = 8 -- delayed the flag by 20-90 us.)
+__device__ __forceinline__ void peer_announce(const Frame& f) {          // rank 0, once per kernel
+    if (blockIdx.x == 0 && threadIdx.x == 0 && (int32_t)(ld_acquire_sys(&f.peer->cleared_epoch) - f.peer_epoch) < 0)
+        st_release_sys(&f.peer->cleared_epoch, f.peer_epoch);
+}
+__device__ __forceinline__ void peer_gate_wait(const Frame& f) {         // ranks > 0, one thread on behalf of its warp / CTA
+    const uint32_t e = f.peer_epoch;
+    if ((int32_t)(ld_acquire_gpu(&f.gate[0]) - e) >= 0) return;
+    uint32_t seen = *(volatile uint32_t*)&f.gate[1];
+    bool poller = false;
+    while ((int32_t)(seen - e) < 0) {
+        const uint32_t old = atomicCAS(&f.gate[1], seen, e);
+        if (old == seen) { poller = true; break; }
+        seen = old;
+    }
+    if (poller) {
+        if (!peer_wait_flag(&f.peer->cleared_epoch, e)) f.peer->error = 1u;
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(&f.gate[0]), "r"(e) : "memory");
+        return;
+    }
+    const unsigned long long t0 = global_ns();
+    while ((int32_t)(ld_acquire_gpu(&f.gate[0]) - e) < 0) {
+        __nanosleep(100);
+        if (global_ns() - t0 > PEER_WAIT_NS + 1000000000ull) { f.peer->error = 1u; return; }
     }
 }
 
+#ifndef FRAME_DEFAULT_CHUNK
+#define FRAME_DEFAULT_CHUNK 32u
+#endif
+#define READY_MIN_SHIFT 3               // ready[] is sized for the smallest work item (8 records)
+#ifndef FRAME_SHARE_AUTO_PX
+#define FRAME_SHARE_AUTO_PX 200u        // shadow-subtree sharing is on by default below this many rectangle pixels per resident warp
+#endif
+#ifndef FRAME_SHARE_PERIOD
+#define FRAME_SHARE_PERIOD 4u
+#endif
+#ifndef FRAME_SHARE_MIN_IDLE
+#define FRAME_SHARE_MIN_IDLE 6u
+#endif
 #ifndef FRAME_DEFAULT_SHADOW_ORDER
 #define FRAME_DEFAULT_SHADOW_ORDER ORDER_NEAR
 #endif
 
-template <bool STATS, int ORDER>
+template <bool STATS, int ORDER, bool SHARE, bool TL>
 __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(const DevScene sc, const Frame f) {
     extern __shared__ uint32_t smem_stack[];
     const uint32_t FULL = 0xFFFFFFFFu;
@@ -129,7 +168,14 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
     const V3 sun = mk(f.sun[0], f.sun[1], f.sun[2]);
     const V3 eye = mk(f.eye[0], f.eye[1], f.eye[2]);
     unsigned long long st[6] = {0, 0, 0, 0, 0, 0};   // STATS: S_miss,T_miss,S_hit,T_hit,S_shadow,T_shadow
-    if (f.peer) peer_begin_gate(f);
+    unsigned long long tl_begin = 0, tl_primary = 0;  // sc.timeline: per-warp timestamps
+    unsigned long long tl_tile_max = 0, tl_tile_last = 0, tl_chunk_max = 0, tl_wait = 0, tl_t = 0;
+    uint32_t tl_tile_max_base = 0, tl_chunk_max_id = 0;
+    uint32_t my_chunks = 0;
+    if (TL) tl_begin = global_ns();
+    unsigned long long tl_gate = 0;
+    bool gated = f.peer != nullptr && f.peer_rank != 0u;      // a peer's first store of the epoch waits for rank 0's announcement
+    if (f.peer && f.peer_rank == 0u) peer_announce(f);
 
     // =================================================================== phase 1: primary tiles
     const uint32_t total = f.work_items;            // 32 per tile
@@ -140,6 +186,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
         base = __shfl_sync(FULL, base, 0);
         if (base >= total) break;
         ++my_tiles;
+        if (TL) tl_t = tl_tile_last = global_ns();
         uint32_t i, lrow, n_steps = 0, n_tests = 0;
         const bool have = item_pixel(f, base + lane, i, lrow);
         const uint32_t j = frame_row(f, lrow);
@@ -163,6 +210,12 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
         __syncwarp();
         const bool found = have && r.found;
         const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
+        if (gated) {
+            if (lane == 0) peer_gate_wait(f);
+            __syncwarp();
+            gated = false;
+            if (TL) tl_gate = global_ns();
+        }
         if (have && !found) {   // render.hpp:116-117
             float* p = f.pixels + 3 * opix;
             p[0] = 0.0f; p[1] = 0.0f; p[2] = 0.0f;
@@ -180,12 +233,13 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
                 __threadfence();
             }
             __syncwarp();
-            if (lane == 0) {
-                const uint32_t n0 = min(n, 32u - (qb & 31u));
-                atomicAdd(&f.ready[qb >> 5], n0);
-                if (n > n0) atomicAdd(&f.ready[(qb >> 5) + 1u], n - n0);
+            {   // credit the work items (1 << chunk_shift records each) these n records fall into: one lane per item
+                const uint32_t sh = f.chunk_shift, e = (qb >> sh) + lane;
+                const uint32_t lo = max(qb, e << sh), hi = min(qb + n, (e + 1u) << sh);
+                if (hi > lo) atomicAdd(&f.ready[e], hi - lo);
             }
         }
+        if (TL) { const unsigned long long d = global_ns() - tl_t; if (d > tl_tile_max) { tl_tile_max = d; tl_tile_max_base = base; } }
         if (STATS && have) {
             st[found ? 2 : 0] += n_steps; st[found ? 3 : 1] += n_tests;
             if (sc.hist) atomicAdd(&sc.hist[min(n_steps >> 2, 63u)], 1ull);
@@ -205,25 +259,28 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             uint32_t q = 0;
             if (lane == 0) q = atomicAdd(&ctr->qcount, 0u);
             q = __shfl_sync(FULL, q, 0);
-            const uint32_t c_full = q >> 5, rem = q & 31u, c_tot = c_full + (rem ? 1u : 0u);
+            const uint32_t c_full = q >> f.chunk_shift, rem = q & ((1u << f.chunk_shift) - 1u), c_tot = c_full + (rem ? 1u : 0u);
             const uint32_t n_warps = gridDim.x * (FRAME_THREADS / 32);
             if (rem && lane == 0) atomicOr(&f.ready[c_full], READY_FINAL);
             for (uint32_t k = lane; k < n_warps; k += 32u) atomicExch(&f.ready[c_tot + k], READY_FINAL);
         }
     }
 
+    if (TL) tl_primary = global_ns();
+
     // =================================================================== phase 2: shadow rays + shading, 32 records at a time
     uint32_t occl = 0;
     uint32_t e_i0 = 0xFFFFFFFFu, e_i1 = 0u, e_r0 = 0xFFFFFFFFu, e_r1 = 0u;
     for (;;) {
         uint32_t c = 0, v = 0;
+        if (TL) tl_t = global_ns();
         if (lane == 0) {
             c = atomicAdd(&ctr->shadow_next, 1u);
             unsigned ns = 32;
             unsigned long long t0 = 0;
             for (;;) {
                 v = ld_acquire_gpu(&f.ready[c]);
-                if (v == 32u || (v & READY_FINAL)) break;
+                if (v == (1u << f.chunk_shift) || (v & READY_FINAL)) break;
                 __nanosleep(ns);
                 if (ns < 1024u) ns <<= 1;
                 else if (t0 == 0) t0 = global_ns();
@@ -234,9 +291,85 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
         c = __shfl_sync(FULL, c, 0);
         v = __shfl_sync(FULL, v, 0);
         const uint32_t n = v & READY_COUNT;
+        if (TL) { const unsigned long long t = global_ns(); tl_wait += t - tl_t; tl_t = t; }
         if (n == 0u) break;
-        if (lane < n) {
-            const uint4 rec = __ldcg(f.queue + (size_t)c * 32u + lane);
+        if (gated) {
+            if (lane == 0) peer_gate_wait(f);
+            __syncwarp();
+            gated = false;
+            if (TL) tl_gate = global_ns();
+        }
+        ++my_chunks;
+        if (SHARE && f.shadows && !sc.root_leaf_count) {
+            // ---- the chunk's shadow rays, walked by all 32 lanes together (see SHARE above)
+            uint32_t my_rec = lane;             // the record whose ray this lane is walking
+            uint32_t occ_mask = 0;              // warp-uniform: records known to be occluded
+            uint32_t n_steps = 0, n_tests = 0;
+            RaySlot r;
+            bool active = lane < n;
+            if (active) {
+                const uint4 rec = __ldcg(f.queue + ((size_t)c << f.chunk_shift) + lane);
+                V3 P, sun_line;
+                shadow_setup(load_tri(tris, rec.y), __uint_as_float(rec.z), __uint_as_float(rec.w), sun, P, sun_line);
+                ray_begin(r, P, sun_line, tid);
+            } else {
+                r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.ix = r.iy = r.iz = r.sx = r.sy = r.sz = 0.0f;
+                r.tmax = FLT_MAX; r.u = r.v = 0.0f; r.slot = 0; r.cur = 0; r.sp = r.sb = tid; r.found = false;
+            }
+            const uint32_t period = f.share_period, min_idle = f.share_min_idle;
+            for (;;) {
+                for (uint32_t k = 0; k < period && active; ++k)
+                    active = ray_step<true, STATS, FRAME_THREADS, ORDER>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                // a lane that ended on a hit settles its record for every lane working on it
+                occ_mask |= __reduce_or_sync(FULL, (!active && r.found) ? 1u << my_rec : 0u);
+                if ((occ_mask >> my_rec) & 1u) active = false;
+                const unsigned act = __ballot_sync(FULL, active);
+                if (!act) break;
+                if ((uint32_t)__popc(~act) < min_idle) continue;
+                const unsigned donors = __ballot_sync(FULL, active && r.sp != r.sb);
+                if (!donors) continue;
+                // k-th idle lane <- oldest pending subtree of the k-th donor
+                const uint32_t n_idle = (uint32_t)__popc(~act), n_don = (uint32_t)__popc(donors);
+                const bool thief = !active && (uint32_t)__popc(~act & lt_mask) < n_don;
+                const bool donor = active && r.sp != r.sb && (uint32_t)__popc(donors & lt_mask) < n_idle;
+                uint32_t give = 0;
+                if (donor) { give = smem_stack[r.sb]; r.sb += FRAME_THREADS; }
+                const uint32_t src = thief ? __fns(donors, 0u, __popc(~act & lt_mask) + 1) : lane;
+                give = __shfl_sync(FULL, give, src);
+                const uint32_t rec_src = __shfl_sync(FULL, my_rec, src);
+                const float ox = __shfl_sync(FULL, r.ox, src), oy = __shfl_sync(FULL, r.oy, src), oz = __shfl_sync(FULL, r.oz, src);
+                const float dx = __shfl_sync(FULL, r.dx, src), dy = __shfl_sync(FULL, r.dy, src), dz = __shfl_sync(FULL, r.dz, src);
+                const float ix = __shfl_sync(FULL, r.ix, src), iy = __shfl_sync(FULL, r.iy, src), iz = __shfl_sync(FULL, r.iz, src);
+                const float sx = __shfl_sync(FULL, r.sx, src), sy = __shfl_sync(FULL, r.sy, src), sz = __shfl_sync(FULL, r.sz, src);
+                if (thief) {
+                    r.ox = ox; r.oy = oy; r.oz = oz; r.dx = dx; r.dy = dy; r.dz = dz;
+                    r.ix = ix; r.iy = iy; r.iz = iz; r.sx = sx; r.sy = sy; r.sz = sz;
+                    r.cur = give; r.sp = r.sb = tid; r.found = false; r.tmax = FLT_MAX;
+                    my_rec = rec_src; active = true;
+                }
+            }
+            if (STATS) { st[4] += n_steps; st[5] += n_tests; }
+            if (lane < n) {
+                const uint4 rec = __ldcg(f.queue + ((size_t)c << f.chunk_shift) + lane);
+                const uint32_t lrow = rec.x / f.W, i = rec.x - lrow * f.W;
+                const uint32_t j = frame_row(f, lrow);
+                const uint32_t slot = rec.y;
+                float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+                if ((occ_mask >> lane) & 1u) occl++;
+                else {
+                    const float hu = __uint_as_float(rec.z), hv = __uint_as_float(rec.w);
+                    V3 P, sun_line;
+                    shadow_setup(load_tri(tris, slot), hu, hv, sun, P, sun_line);
+                    shade_lit(sc, f, sun_line, i, j, slot, hu, hv, c0, c1, c2);
+                }
+                const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
+                float* p = f.pixels + 3 * opix;
+                p[0] = c0; p[1] = c1; p[2] = c2;
+                if (f.ids) f.ids[opix] = __ldg(sc.slot_id + slot);
+                e_i0 = min(e_i0, i); e_i1 = max(e_i1, i); e_r0 = min(e_r0, lrow); e_r1 = max(e_r1, lrow);
+            }
+        } else if (lane < n) {
+            const uint4 rec = __ldcg(f.queue + ((size_t)c << f.chunk_shift) + lane);
             const uint32_t lrow = rec.x / f.W, i = rec.x - lrow * f.W;
             const uint32_t j = frame_row(f, lrow);
             const uint32_t slot = rec.y;
@@ -274,6 +407,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             e_i0 = min(e_i0, i); e_i1 = max(e_i1, i); e_r0 = min(e_r0, lrow); e_r1 = max(e_r1, lrow);
         }
         __syncwarp();
+        if (TL) { const unsigned long long d = global_ns() - tl_t; if (d > tl_chunk_max) { tl_chunk_max = d; tl_chunk_max_id = c; } }
         // no early exit after the partial last chunk: every warp consumes exactly one terminating entry, which is what
         // leaves ready[] all-zero for the next launch
     }
@@ -285,6 +419,11 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
         for (int k = 0; k < 6; ++k)
             for (int o = 16; o; o >>= 1) st[k] += __shfl_xor_sync(FULL, st[k], o);
         if (lane == 0) for (int k = 0; k < 6; ++k) if (st[k]) atomicAdd(&ctr->stats[k], st[k]);
+    }
+    if (TL && lane == 0) {
+        unsigned long long* t = sc.timeline + (unsigned long long)CERES_TIMELINE_WORDS * (blockIdx.x * (FRAME_THREADS / 32) + (tid >> 5));
+        t[0] = tl_begin; t[1] = tl_primary; t[2] = global_ns(); t[3] = my_tiles; t[4] = my_chunks;
+        t[5] = tl_tile_max; t[6] = tl_tile_max_base; t[7] = tl_tile_last; t[8] = tl_chunk_max; t[9] = tl_chunk_max_id; t[10] = tl_wait; t[11] = tl_gate;
     }
     if (f.host_ext) {        // uniform branch: extents of the hit pixels this warp wrote
         e_i0 = __reduce_min_sync(FULL, e_i0); e_i1 = __reduce_max_sync(FULL, e_i1);
@@ -337,7 +476,10 @@ __device__ __forceinline__ void clear_span(float* __restrict__ p, size_t n) {   
 }
 
 __global__ void __launch_bounds__(256) clear_outside_kernel(const Frame f, const ClearRegion q) {
-    if (f.peer) peer_begin_gate(f);
+    if (f.peer) {
+        if (f.peer_rank == 0u) peer_announce(f);
+        else { if (threadIdx.x == 0) peer_gate_wait(f); __syncthreads(); }
+    }
     for (uint32_t lr = q.row_a + blockIdx.x; lr < q.row_b; lr += gridDim.x) {
         const size_t orow = f.compact ? lr : frame_row(f, lr);
         float* px = f.pixels + orow * 3ull * f.W;

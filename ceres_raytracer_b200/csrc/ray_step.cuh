@@ -12,6 +12,7 @@ struct RaySlot {
     uint32_t slot;                      // leaf slot of the best hit
     uint32_t cur;                       // node pair to test next
     uint32_t sp;                        // word offset of the next free stack entry in this thread's column
+    uint32_t sb;                        // word offset of the column's oldest live entry (= tid unless entries were given away)
     uint32_t item;                      // work item being traced
     bool found;
 };
@@ -23,7 +24,7 @@ __device__ __forceinline__ void ray_begin(RaySlot& r, V3 o, V3 d, uint32_t tid) 
     r.iy = rcp(fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y);
     r.iz = rcp(fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z);
     r.sx = mul(-o.x, r.ix); r.sy = mul(-o.y, r.iy); r.sz = mul(-o.z, r.iz);
-    r.tmax = FLT_MAX; r.u = 0.0f; r.v = 0.0f; r.slot = 0; r.cur = 0; r.sp = tid; r.found = false;
+    r.tmax = FLT_MAX; r.u = 0.0f; r.v = 0.0f; r.slot = 0; r.cur = 0; r.sp = tid; r.sb = tid; r.found = false;
 }
 
 // Child order of a step whose two children are both inner nodes and both hit.
@@ -97,7 +98,7 @@ __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const
         r.cur = right_first ? fR : fL;
         return true;
     }
-    if (r.sp == tid) return false;
+    if (r.sp == r.sb) return false;
     r.sp -= STRIDE;
     r.cur = stack[r.sp];
     return true;

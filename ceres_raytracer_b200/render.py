@@ -174,9 +174,13 @@ class Scene:
         _capi.check(self._L.ceres_scene_last_rectangle(self._h, _p(out)))
         return tuple(int(x) for x in out)
 
-    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, shadow_order=0, refill_min=0, subframes=0, chunk=0):
+    def set_tuning(self, variant=0, primary_block=0, shadow_block=0, ctas_per_sm=0, shadow_order=0, refill_min=0, subframes=0, chunk=0,
+                   share=0, share_period=0, share_min_idle=0):
         """variant 0 = the frame kernel; 1-6 = the wave pipelines (experiments build only).  shadow_order: 0 default,
-        1 nearer child first, 2 left child first.  subframes = row bands per frame."""
+        1 nearer child first, 2 left child first.  subframes = row bands per frame.  share (frame kernel): shadow-subtree
+        sharing between the lanes of a warp, 0 default / 1 off / 2 on, with its period (steps) and idle-lane threshold."""
+        if variant == 0:
+            refill_min, chunk = share, (share_period & 0xFF) | ((share_min_idle & 0xFF) << 8)
         t = _capi.Tuning(variant, primary_block, shadow_block, ctas_per_sm, shadow_order, (C.c_uint32 * 3)(refill_min, subframes, chunk))
         _capi.check(self._L.ceres_scene_set_tuning(self._h, C.byref(t)))
         self._variant = int(variant)
@@ -217,6 +221,17 @@ class Scene:
         out = np.zeros(128, np.uint64)
         _capi.check(self._L.ceres_scene_get_step_histogram(self._h, _p(out)))
         return out[:64].copy(), out[64:].copy()
+
+    def set_timeline(self, enable):
+        _capi.check(self._L.ceres_scene_set_timeline(self._h, int(bool(enable))))
+
+    def timeline(self):
+        """uint64 [warps, 12] per warp of the last frame kernel (set_timeline(True)); columns: include/ceres_b200.h."""
+        out = np.zeros((16 * 4 * 256, 12), np.uint64)
+        n = C.c_size_t(0)
+        _capi.check(self._L.ceres_scene_get_timeline(self._h, _p(out), out.shape[0], C.byref(n)))
+        out = out[:n.value]
+        return out[out[:, 2] != 0]
 
     def set_profiling(self, enable):
         """Per-kernel CUDA-event timing of every render_device call (see kernel_ms)."""

@@ -77,7 +77,9 @@ typedef struct ceres_tuning {
     uint32_t ctas_per_sm;        /* persistent CTAs per SM */
     uint32_t shadow_order;       /* frame kernel, any-hit shadow rays: 0 default, 1 nearer child first (the reference's
                                     order), 2 left child first (no ordering work; the boolean cannot depend on it) */
-    uint32_t reserved[3];        /* [0] experiments: lane-refill threshold, [1] row bands per frame, [2] experiments: chunk */
+    uint32_t reserved[3];        /* [0] frame kernel: shadow-subtree sharing between the lanes of a warp, 0 default / 1 off /
+                                    2 on (experiments, variant != 0: lane-refill threshold); [1] row bands per frame;
+                                    [2] frame kernel: sharing period | min idle lanes << 8 (experiments: chunk) */
 } ceres_tuning;
 
 /* ---- scene ------------------------------------------------------------------------------------------------- */
@@ -254,6 +256,14 @@ int ceres_scene_get_stats(ceres_scene* scene, uint64_t stats[8]);
 /* Statistics mode also fills a histogram of node-pair steps per ray, accumulated over the frames rendered since the
  * last call (the call resets it): hist[b] = primary rays with b = min(steps / 4, 63), hist[64 + b] = shadow rays. */
 int ceres_scene_get_step_histogram(ceres_scene* scene, uint64_t hist[128]);
+/* Per-warp timeline of the frame kernel (development aid for the per-rank timelines of DESIGN.md).  While enabled, every
+ * warp w of the LAST frame kernel launched on this scene leaves CERES_TIMELINE_WORDS words at out[CERES_TIMELINE_WORDS w]:
+ * {t_begin, t_primary_end, t_end (globaltimer ns), primary tiles, shadow chunks, longest tile [ns], its first work item,
+ * claim time of the last tile, longest chunk [ns], its index, total wait for queue chunks [ns], time the peer gate was passed}; *warps = number of
+ * entries written (<= cap_warps; warps that never ran are all-zero).  Costs a few uniform branches per tile / chunk. */
+#define CERES_TIMELINE_WORDS 12
+int ceres_scene_set_timeline(ceres_scene* scene, int enable);
+int ceres_scene_get_timeline(ceres_scene* scene, uint64_t* out, size_t cap_warps, size_t* warps);
 
 /* Per-kernel timing.  While enabled, every ceres_render_device call records CUDA events on its launch stream
  * before/after each of its kernels.  ceres_scene_get_kernel_ms waits for the recorded frames and returns the SUMS

@@ -24,9 +24,11 @@ def main():
     ap.add_argument("--ctas", default="0")
     ap.add_argument("--refill", default="0")
     ap.add_argument("--block", type=int, default=0)
+    ap.add_argument("--records", default="0", help="frame kernel: records per shadow work item (8/16/32)")
     ap.add_argument("--sub", default="1")
     ap.add_argument("--chunk", default="0")
     ap.add_argument("--order", default="0", help="frame kernel: shadow child order(s), 0 default / 1 near-first / 2 left-first")
+    ap.add_argument("--share", default="0", help="frame kernel: shadow-subtree sharing, 0 default / 1 off / 2 on; 2:P:M = on with period P, min idle lanes M")
     args = ap.parse_args()
     import torch
     import ceres_raytracer_b200 as cr
@@ -44,12 +46,14 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     ref_px = None
     ref_ids = None
-    for ctas, refill, sub, chunk, order in [(int(c), int(r), int(q), int(h), int(o)) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",") for h in args.chunk.split(",") for o in args.order.split(",")]:
+    for ctas, refill, sub, chunk, order, share in [(int(c), int(r), int(q), int(h), int(o), sh) for c in args.ctas.split(",") for r in args.refill.split(",") for q in args.sub.split(",") for h in args.chunk.split(",") for o in args.order.split(",") for sh in args.share.split(",")]:
+      for recs in [int(a) for a in args.records.split(",")]:
+        shp = [int(x) for x in share.split(":")] + [0, 0]
         for v in [int(x) for x in args.variants.split(",")]:
             if v != 0 and os.environ.get("CERES_B200_EXPERIMENTS", "") in ("", "0"):
                 print(f"variant {v}: skipped (wave pipelines need CERES_B200_EXPERIMENTS=1)", flush=True)
                 continue
-            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block, subframes=sub, chunk=chunk, shadow_order=order)
+            scene.set_tuning(variant=v, ctas_per_sm=ctas, refill_min=refill, primary_block=args.block, shadow_block=args.block if v else recs, subframes=sub, chunk=chunk, shadow_order=order, share=shp[0], share_period=shp[1], share_min_idle=shp[2])
             d_px.fill_(float("nan"))
             scene.render_device(cam, sun, W, H, flags=flags, pixels=d_px, ids=d_ids, counters=d_cnt)
             torch.cuda.synchronize()
@@ -76,7 +80,7 @@ def main():
             ms, n = scene.kernel_ms()
             scene.set_profiling(False)
             parts = "  ".join(f"{k} {ms[k]/n*1e3:7.1f} us" for k in ms)
-            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub} chunk {chunk} order {order}: {parts}   ids_ok={ok} counters_ok={cnt_ok} "
+            print(f"variant {v} ctas/SM {ctas} refill {refill} subframes {sub} chunk {chunk} order {order} share {share} records {recs}: {parts}   ids_ok={ok} counters_ok={cnt_ok} "
                   f"pixels_same_as_first={same_px}", flush=True)
     scene.set_tuning()
 

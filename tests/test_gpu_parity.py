@@ -214,7 +214,7 @@ def test_gpu_statistics_match_oracle_for_primary_rays(cr, dragon, dragon_pod):
     o = port.render(dragon_pod, cr.configs.DRAGON_CAMERA.as_array(), SUN, W, H, 0, want_pixels=False)["stats"]
     got = {}
     for order in (1, 2):       # any-hit shadow rays: nearer child first (the reference's order) / left child first
-        dragon.set_tuning(shadow_order=order)
+        dragon.set_tuning(shadow_order=order, share=1)      # sharing off: a shared walk may look into subtrees a closest-hit walk prunes
         dragon.set_stats(True)
         try:
             dragon.render(cr.configs.DRAGON_CAMERA, SUN, W, H)
@@ -246,6 +246,52 @@ def test_shadow_order_and_grid_size_do_not_change_the_frame(cr, dragon, dragon_p
         check_frame(cr, dragon, dragon_pod, cam, SUN, 640, 360, 0)
     finally:
         dragon.set_tuning()
+
+
+@pytest.mark.parametrize("share,period,min_idle", [(1, 0, 0), (2, 0, 0), (2, 1, 1), (2, 2, 31), (2, 7, 12)])
+def test_shadow_subtree_sharing_does_not_change_the_frame(cr, dragon, dragon_pod, bunny, bunny_pod, share, period, min_idle):
+    """Idle lanes of a shadow chunk walk subtrees taken from the busy lanes' stacks (frame_fused.cuh, SHARE): the boolean
+    of render.hpp:137-140 cannot depend on who walks what, so frames, ids and counters are those of the unshared walk
+    and of the oracle, whatever the hand-over period and threshold."""
+    cam, W, H = cr.configs.DRAGON_CAMERA, 1280, 720
+    dragon.set_tuning(share=1)
+    ref = dragon.render(cam, SUN, W, H, want_ids=True)
+    dragon.set_tuning(share=share, share_period=period, share_min_idle=min_idle)
+    bunny.set_tuning(share=share, share_period=period, share_min_idle=min_idle)
+    try:
+        px, ids, cnt = dragon.render(cam, SUN, W, H, want_ids=True)
+        assert np.array_equal(px.view(np.uint32), ref[0].view(np.uint32)) and np.array_equal(ids, ref[1]) and cnt == ref[2]
+        check_frame(cr, dragon, dragon_pod, cam, SUN, 640, 360, 0)
+        check_frame(cr, bunny, bunny_pod, cr.configs.BUNNY_CAMERA, np.array(cr.configs.BUNNY_SUN, np.float32), 480, 270, 0)
+    finally:
+        dragon.set_tuning()
+        bunny.set_tuning()
+
+
+def test_shared_shadow_walk_statistics(cr, dragon):
+    """Statistics of the shared walk: it does at least the unshared walk's node steps for the rays that reach the sun (every
+    reachable node is visited exactly once by somebody) and its counters are the same."""
+    cam, W, H = cr.configs.DRAGON_CAMERA, 960, 540
+    got = {}
+    for share in (1, 2):
+        dragon.set_tuning(share=share, subframes=1)
+        dragon.set_stats(True)
+        try:
+            dragon.render(cam, SUN, W, H)
+            got[share] = dragon.get_stats()
+            dragon.set_stats(False)
+            dragon.set_timeline(True)
+            dragon.render(cam, SUN, W, H)
+            tl = dragon.timeline()
+        finally:
+            dragon.set_stats(False)
+            dragon.set_timeline(False)
+            dragon.set_tuning()
+        assert tl.shape[1] == 12 and len(tl) > 0 and (tl[:, 2] >= tl[:, 1]).all() and (tl[:, 1] >= tl[:, 0]).all()
+        assert int(tl[:, 4].sum()) == (got[share]["rays"] - W * H + 31) // 32       # every queue chunk was taken by one warp
+    for k in ("S_miss", "T_miss", "S_hit", "T_hit", "rays", "hits"):
+        assert got[1][k] == got[2][k], k
+    assert got[2]["S_shadow"] > 0 and got[2]["T_shadow"] > 0
 
 
 def test_wave_pipeline_variants_are_not_in_the_product_library(cr, dragon):
