@@ -127,6 +127,7 @@ struct Frame {
     // frame kernel, shadow-subtree sharing (frame_fused.cuh): steps between two rounds of bookkeeping; idle lanes needed for a hand-over round
     uint32_t share_period, share_min_idle;
     uint32_t chunk_shift;      // frame kernel: a shadow work item is 1 << chunk_shift queue records (3..5)
+    uint32_t clear_rows;       // frame kernel: zero the pixels of rows [row_begin, row_end) outside the rectangle itself
 };
 
 // ------------------------------------------------------------------------------------------------ device math
@@ -1548,12 +1549,7 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
         return fail(CERES_ERR_UNSUPPORTED, "ceres_tuning.variant != 0 needs the experiments build (libceres_b200_exp.so, -DCERES_EXPERIMENTS)");
 #endif
     }
-    if (clear_mode == CLEAR_OUTSIDE) {
-        const ClearRegion q{row_begin, row_end, 0u, f.W, f.rect_row0, f.rect_row1, f.rect_x0, f.rect_x1};
-        clear_outside_kernel<<<(unsigned)(s->sm_count * 8), 256, 0, st>>>(f, q);
-        g_launches++;
-        CUDA_TRY(cudaGetLastError());
-    }
+    f.clear_rows = clear_mode == CLEAR_OUTSIDE ? 1u : 0u;        // done by the frame kernel's own warps (phase 0)
     if (pe) CUDA_TRY(cudaEventRecord(pe[1], st));
     {
         const size_t smem = (size_t)s->dev.stack_depth * 4 * FRAME_THREADS;          // <= 32 KB: depth <= 64

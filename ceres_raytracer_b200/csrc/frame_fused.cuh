@@ -38,6 +38,35 @@
 #define FRAME_WAIT_NS 2000000000ull
 #define FRAME_ERR_READY_TIMEOUT 1u
 
+// Zeroes columns [a, b) of local row lr (pixels: 0, ids: CERES_MISS) with the 32 lanes of one warp, 16-byte stores where the
+// alignment allows.  Used by the frame kernel for the pixels of its rows that lie outside the traced rectangle.
+__device__ __forceinline__ void warp_zero_cols(const Frame& f, uint32_t lr, uint32_t a, uint32_t b, uint32_t lane) {
+    if (b <= a) return;
+    const size_t orow = f.compact ? lr : frame_row(f, lr);
+    {
+        float* p = f.pixels + (orow * f.W + a) * 3ull;
+        const size_t n = 3ull * (b - a);
+        const size_t head = min(n, (size_t)((16u - ((uintptr_t)p & 15u)) / 4u % 4u));
+        const size_t nv = (n - head) / 4;
+        float4* v = reinterpret_cast<float4*>(p + head);
+        for (size_t k = lane; k < nv; k += 32u) v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (lane < head) p[lane] = 0.0f;
+        const size_t t0 = head + nv * 4;
+        if (t0 + lane < n) p[t0 + lane] = 0.0f;
+    }
+    if (f.ids) {
+        uint32_t* p = f.ids + orow * f.W + a;
+        const size_t n = b - a;
+        const size_t head = min(n, (size_t)((16u - ((uintptr_t)p & 15u)) / 4u % 4u));
+        const size_t nv = (n - head) / 4;
+        uint4* v = reinterpret_cast<uint4*>(p + head);
+        for (size_t k = lane; k < nv; k += 32u) v[k] = make_uint4(CERES_MISS, CERES_MISS, CERES_MISS, CERES_MISS);
+        if (lane < head) p[lane] = CERES_MISS;
+        const size_t t0 = head + nv * 4;
+        if (t0 + lane < n) p[t0 + lane] = CERES_MISS;
+    }
+}
+
 __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
     uint32_t v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -176,6 +205,21 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
     unsigned long long tl_gate = 0;
     bool gated = f.peer != nullptr && f.peer_rank != 0u;      // a peer's first store of the epoch waits for rank 0's announcement
     if (f.peer && f.peer_rank == 0u) peer_announce(f);
+
+    // =================================================================== phase 0: zeros outside the rectangle
+    // (render.hpp:116-117 for the pixels that are never traced.)  Quarter rows are dealt out to the warps of the grid; the stores
+    // are fire-and-forget, so the memory system drains them while the same warps start tracing.
+    if (f.clear_rows) {
+        const uint32_t n_warps = gridDim.x * (FRAME_THREADS / 32), w = blockIdx.x * (FRAME_THREADS / 32) + (tid >> 5);
+        const uint32_t n_items = (f.row_end - f.row_begin) * 4u, q = (f.W + 3u) / 4u;
+        for (uint32_t it = w; it < n_items; it += n_warps) {
+            const uint32_t lr = f.row_begin + (it >> 2), a = (it & 3u) * q, b = min(f.W, a + q);
+            if (lr >= f.rect_row0 && lr < f.rect_row1 && f.rect_x0 < f.rect_x1) {
+                warp_zero_cols(f, lr, a, min(b, max(a, f.rect_x0)), lane);
+                warp_zero_cols(f, lr, max(a, min(b, f.rect_x1)), b, lane);
+            } else warp_zero_cols(f, lr, a, b, lane);
+        }
+    }
 
     // =================================================================== phase 1: primary tiles
     const uint32_t total = f.work_items;            // 32 per tile
