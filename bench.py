@@ -657,6 +657,7 @@ def main():
                              "d2h_bytes_per_step": scene.last_d2h_bytes, "path": "ceres_render_ppm16() -> page-locked 16-bit P6 payload"}
             hb16.close()
             extra["e2e_ppm8"] = ppm8
+            extra["e2e_shim"] = shim_bench(pod, cam, sun, W, H, steps_e2e, rays_frame, hits_frame)
         else:
             # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
             # DMA-writes them in place over its own PCIe link; the counter barrier in the shared control page completes it.
@@ -775,6 +776,44 @@ def main():
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def shim_bench(pod, cam, sun, W, H, frames, rays, hits):
+    """The drop-in C++ call -- render<float>() of include/ceres/render.hpp, apps/shim_bench.cpp -- into the frame the reference's
+    callers allocate (std::make_unique<float[]>, anim.cpp:76 / static.cpp:117): the shim page-locks it on first sight."""
+    exe = os.path.join(ROOT, "apps", "_build", "shim_bench")
+    if not os.path.exists(exe):
+        return {"unavailable": "apps/_build/shim_bench not built (needs the reference's lib/bvh headers at build time)"}
+    import subprocess
+    import tempfile
+    out = {"path": "apps/shim_bench: render<float>() of include/ceres/render.hpp, C++ caller, same scene arrays and camera", "unit": UNIT}
+    try:
+        with tempfile.TemporaryDirectory() as d:
+            p = os.path.join(d, "scene.bin")
+            with open(p, "wb") as f:
+                f.write(np.array([len(pod["nodes"]), len(pod["triangles"])], np.uint64).tobytes())
+                f.write(np.ascontiguousarray(pod["nodes"]).tobytes())
+                f.write(np.ascontiguousarray(pod["prim_indices"], np.uint64).tobytes())
+                f.write(np.ascontiguousarray(pod["triangles"], np.float32).tobytes())
+                f.write(np.ascontiguousarray(pod["norms"], np.float32).tobytes())
+            c = cam.as_array()
+            argv = [exe, p, str(W), str(H), str(frames)] + [repr(float(x)) for x in list(c[:10]) + list(np.asarray(sun, np.float32))]
+            for key, env in (("autopin", {}), ("no_autopin", {"CERES_NO_AUTOPIN": "1"})):
+                r = subprocess.run(argv, env=dict(os.environ, **env), capture_output=True, text=True, timeout=120)
+                if r.returncode != 0:
+                    return {"unavailable": f"shim_bench exit {r.returncode}: {r.stderr[-200:]}"}
+                for ln in r.stdout.splitlines():
+                    q = json.loads(ln)
+                    if (q["rays"], q["hits"]) != (rays, hits):
+                        return {"unavailable": f"shim_bench counters {q['rays']}, {q['hits']} differ from the GPU arm's"}
+                    tag = "make_unique" if q["frame"].startswith("make_unique") else "host_alloc"
+                    if key == "no_autopin" and tag == "host_alloc":
+                        continue
+                    name = tag if key == "autopin" else "make_unique_no_autopin"
+                    out[name] = {"ms_per_step": q["ms_mean"], "ms_best": q["ms_best"], "value": rays / (q["ms_mean"] * 1e-3) / 1e6, "frame": q["frame"]}
+    except Exception as e:
+        return {"unavailable": str(e)[:200]}
+    return out
 
 
 def ncu_dram_traffic(workload):

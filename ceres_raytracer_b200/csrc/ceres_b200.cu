@@ -1724,11 +1724,12 @@ static int launch_rows_waves(ceres_scene* s, Frame& f, uint32_t row_begin, uint3
 
 }  // extern "C" (a C++ template follows)
 
-// defaults from the sweeps in profiles/r1/: device-resident frames gain only ~2 % from 2-3 bands and lose beyond 4 (so
-// they stay serial, which also keeps the per-kernel event timing meaningful); host frames
-// want many bands so that the first copy starts early
+// defaults from the sweeps in profiles/r1/ and profiles/r2/sweeps.md: device-resident frames stay serial; host frames want
+// bands so that the first copy starts early, but every band is a persistent launch of its own with its own tail (a band of
+// 1/8 of the rectangle is as latency-bound as one rank of eight): 3-4 bands are the optimum with the frame kernel
+// (0.78 ms per 4K float frame against 0.86 ms with 8 bands and 0.98 ms with one)
 #define CERES_SUBFRAMES_DEVICE 1u
-#define CERES_SUBFRAMES_HOST 8u
+#define CERES_SUBFRAMES_HOST 4u
 
 // Renders local rows [a, b) of the frame, forked from and joined back to stream `st`.
 // The rows are cut into up to CERES_MAX_SUB row bands ("sub-frames"), each enqueued on its own stream with its own

@@ -17,11 +17,22 @@
 // only reference code this header needs is the lib/bvh type definitions of the caller's own tree.
 //
 // Differences a caller can observe:
+//   * STALE GEOMETRY IS POSSIBLE: the GPU copy of (bvh, triangles, tri_norms) is re-used while the same pointers, counts and
+//     a SAMPLED fingerprint (root node, 64 windows of 32 bytes and the tail of each array) repeat; the reference reads the live
+//     arrays every call.  A caller that edits a few triangles or nodes in place between calls must call
+//     ceres::invalidate_scene() -- see the last item.
 //   * Scalar = double (anim -d, anim.cpp:154-155) renders through ceres_render_f64: one kernel on one GPU, same
 //     results as the reference's double build (hit ids bit for bit), without the float path's host-frame pipeline.
 //   * tri_norms may be nullptr (static.cpp:130 passes nullptr, which does not even deduce against the reference
 //     signature): normals are then taken as zero, as the reference would read them if it could.
 //   * errors (no GPU, CUDA failure, malformed BVH) throw std::runtime_error; the reference has no error path.
+//   * the caller's `pixels` buffer is page-locked (ceres_host_register) the first time it is seen and stays so while the
+//     same (pointer, size) is passed again, so that the GPU writes the frame into it by DMA -- a plain make_unique /
+//     malloc frame (anim.cpp:76, static.cpp:117) then costs the same per frame as a cudaHostAlloc'ed one (the first call pays
+//     the registration, ~0.3 ms per MB).  A new (pointer, size) drops the old registration.  HAZARD: a caller that frees the
+//     frame and gets the SAME address back from the allocator for a new one between two calls keeps a registration of
+//     pages that no longer back the buffer; such callers set CERES_NO_AUTOPIN=1 (pageable path, ~2x slower at 4K) or call
+//     ceres::release_frame() before freeing.  Float frames only.
 //   * the scene (bvh, triangles, tri_norms) is flattened and uploaded on the first call and re-used while the same
 //     arrays are passed again (the reference builds them once, outside the frame loop, anim.cpp:46-65).  The cache
 //     key is the three pointers + counts + a sampled fingerprint of the contents; call ceres::invalidate_scene()
@@ -102,6 +113,7 @@ inline uint64_t sample(const void* p, size_t bytes, uint64_t h) {
     const size_t step = bytes > windows * span ? (bytes - span) / (windows - 1) : span;
     for (size_t off = 0; off + span <= bytes; off += step)
         for (size_t k = 0; k < span; ++k) { h ^= b[off + k]; h *= 1099511628211ull; }
+    for (size_t k = bytes > span ? bytes - span : 0; k < bytes; ++k) { h ^= b[k]; h *= 1099511628211ull; }     // always the tail
     return h;
 }
 
@@ -110,6 +122,29 @@ inline uint64_t sample(const void* p, size_t bytes, uint64_t h) {
 }
 
 }  // namespace detail
+
+namespace detail {
+struct FramePin { void* p = nullptr; size_t bytes = 0; bool ours = false; };
+inline FramePin& frame_pin() { static FramePin f; return f; }     // never unregistered at exit: the frame may be gone by then
+}  // namespace detail
+
+// Forget (and un-page-lock) the frame render() saw last; call before freeing a frame whose address may be reused.
+inline void release_frame() {
+    auto& f = detail::frame_pin();
+    if (f.ours) ceres_host_unregister(f.p);
+    f = detail::FramePin{};
+}
+
+// Page-lock the caller's frame while the same (pointer, size) keeps coming (see the header comment).
+inline void autopin_frame(void* pixels, size_t bytes) {
+    static const bool off = std::getenv("CERES_NO_AUTOPIN") != nullptr;
+    auto& f = detail::frame_pin();
+    if (f.p == pixels && f.bytes == bytes) return;
+    release_frame();
+    f.p = pixels; f.bytes = bytes;
+    if (off || !pixels || !bytes || ceres_host_is_pinned(pixels)) return;
+    f.ours = ceres_host_register(pixels, bytes) == CERES_OK;        // on failure: the pageable path still works
+}
 
 inline void invalidate_scene() {
     auto& c = detail::cache();
@@ -214,6 +249,7 @@ std::pair<int, int> render(const Camera<Scalar>& camera, const bvh::Vector3<Scal
         for (int k = 0; k < 3; ++k) { cam.eye[k] = camera.eye[k]; cam.dir[k] = camera.dir[k]; cam.up[k] = camera.up[k]; }
         cam.fov = camera.fov;
         const float sun[3] = {sun_position[0], sun_position[1], sun_position[2]};
+        ceres::autopin_frame(pixels, 3 * width * height * sizeof(float));
         if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, counters) != CERES_OK)
             ceres::detail::fail("ceres_render");
     } else {
