@@ -33,6 +33,7 @@
 
 #include "../../include/ceres_b200.h"
 #include "host_fill.hpp"
+#include "checked.cuh"
 
 // ------------------------------------------------------------------------------------------------ errors
 static thread_local std::string g_err;
@@ -64,6 +65,8 @@ struct DevScene {
     uint32_t root_leaf_count;  // != 0: the root itself is a leaf (single_ray_traverser.hpp:72-73)
     uint32_t stack_depth;      // entries of traversal stack needed (<= 64, single_ray_traverser.hpp:14)
     unsigned long long* hist;  // statistics mode: 2 x 64 bins of node-pair steps per ray (bin = steps / 4), primary then shadow; may be null
+    uint32_t n_pairs, n_slots;     // bounds of pairs[] / tris[] (checked build)
+    unsigned long long* check;     // checked build: CHECK_* bits are ORed in here (the scene's error word); null otherwise
     unsigned long long* timeline;  // CERES_TIMELINE_WORDS words per warp of the frame kernel (ceres_scene_set_timeline); null = off
 };
 
@@ -93,6 +96,7 @@ struct PeerCtl {
 struct Frame {
     float eye[3], dir[3], iu[3], iv[3], sun[3];
     uint32_t W, H;             // full frame
+    uint32_t rows_local;       // rows of this shard
     uint32_t row_begin;        // first local row of this launch (a frame may be rendered in several row bands)
     uint32_t row_end;          // one past the last local row of this launch
     uint32_t accumulate;       // add this launch's counters to out_counters instead of overwriting them
@@ -128,6 +132,7 @@ struct Frame {
     uint32_t share_period, share_min_idle;
     uint32_t chunk_shift;      // frame kernel: a shadow work item is 1 << chunk_shift queue records (3..5)
     uint32_t clear_rows;       // frame kernel: zero the pixels of rows [row_begin, row_end) outside the rectangle itself
+    uint32_t queue_cap, ready_cap, pix_rows;   // checked build: records / ready[] words of this launch's regions, rows of the output buffer
 };
 
 // ------------------------------------------------------------------------------------------------ device math
@@ -224,6 +229,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, V3 o, V3 d, float t
     uint32_t sp = 0;
     for (;;) {
         if (STATS) n_steps++;
+        CERES_CLAMP(cur, sc.n_pairs, CHECK_PAIR_INDEX, sc);
         const float4* pp = pairs + 4ull * cur;
         const float4 q0 = __ldg(pp), q1 = __ldg(pp + 1), q2 = __ldg(pp + 2), q3 = __ldg(pp + 3);
         float le, lx, re, rx;
@@ -252,7 +258,8 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, V3 o, V3 d, float t
         if (s == e) { s = s2; e = e2; s2 = e2; }
         while (s < e) {
             if (STATS) n_tests++;
-            Tri tr = load_tri(tris, s);
+            CERES_CK(s < sc.n_slots, CHECK_SLOT_INDEX, sc);
+            Tri tr = load_tri(tris, s < sc.n_slots ? s : 0u);
             float t, u, v;
             if (tri_test(tr, o, d, tmin, tmax, t, u, v)) {
                 best.slot = s; best.t = t; best.u = u; best.v = v; found = true; tmax = t;
@@ -266,6 +273,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, V3 o, V3 d, float t
         if (goL && goR) {
             const bool swap = le > re;  // ties keep left first
             const uint32_t nearc = swap ? fR : fL, farc = swap ? fL : fR;
+            CERES_CK(sp < sc.stack_depth, CHECK_STACK_DEPTH, sc);
             stack[sp * stride] = farc;
             ++sp;
             cur = nearc;
@@ -807,6 +815,9 @@ static int scene_new(int device, int sm_count, ceres_scene** out) {
     std::memset(s->h_ext, 0, CERES_MAX_SUB * 8 * sizeof(uint32_t));
     TRY_S(cudaMemset(s->d_out, 0, 11 * sizeof(unsigned long long)));
 #undef TRY_S
+#ifdef CERES_CHECKED
+    s->dev.check = s->d_out + 10;
+#endif
     *out = s;
     return CERES_OK;
 }
@@ -918,6 +929,10 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     s->dev.slot_id = (const uint32_t*)s->d_slot_id;
     s->dev.root_leaf_count = root_leaf_count;
     s->dev.stack_depth = depth_max;
+    s->dev.n_pairs = (uint32_t)(pairs.size() / 16); s->dev.n_slots = (uint32_t)tri_count;
+#ifdef CERES_CHECKED
+    if (std::getenv("CERES_CHECK_SELFTEST")) s->dev.n_slots = (uint32_t)(tri_count / 2);    // the checks must fire: proves they are live
+#endif
     s->node_count = node_count;
     s->n_pairs = root_leaf_count ? 0u : (uint32_t)(pairs.size() / 16);
     s->h_pair_first_child = std::move(pair_first_child);
@@ -1247,6 +1262,7 @@ int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_coun
     s->dev.norms = (const float4*)s->d_norms;
     s->dev.slot_id = (const uint32_t*)s->d_slot_id;
     s->dev.root_leaf_count = 0;
+    s->dev.n_pairs = (uint32_t)(tri_count - 1); s->dev.n_slots = (uint32_t)tri_count;
     s->node_count = 2 * tri_count - 1;
     s->n_pairs = (uint32_t)(tri_count - 1);
     s->h_pair_first_child.resize(tri_count - 1);
@@ -1373,6 +1389,40 @@ int ceres_scene_get_timeline(ceres_scene* s, uint64_t* out, size_t cap_warps, si
     return CERES_OK;
 }
 
+int ceres_scene_frame_error(ceres_scene* s, uint64_t* bits) {
+    if (!s || !bits) return fail(CERES_ERR_INVALID, "null argument");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaDeviceSynchronize());
+    unsigned long long w = 0;
+    CUDA_TRY(cudaMemcpy(&w, s->d_out + 10, sizeof w, cudaMemcpyDeviceToHost));
+#ifdef CERES_CHECKED
+    // protocol invariants between frames: ready[] all-zero, every counter slot re-armed (frame_fused.cuh)
+    if (s->d_ready && s->ready_cap) {
+        std::vector<uint32_t> r(s->ready_cap);
+        CUDA_TRY(cudaMemcpy(r.data(), s->d_ready, r.size() * 4, cudaMemcpyDeviceToHost));
+        for (uint32_t x : r) if (x) { w |= 0x10000ull; break; }
+    }
+    {
+        FrameCounters c[CERES_MAX_SUB];
+        CUDA_TRY(cudaMemcpy(c, s->d_ctr, sizeof c, cudaMemcpyDeviceToHost));
+        for (const auto& k : c)
+            if (k.qcount || k.shadow_next || k.occluded || k.done_blocks || k.primary_next || k.primary_done || k.error || k.ext[0] != 0xFFFFFFFFu || k.ext[1] || k.ext[2] != 0xFFFFFFFFu || k.ext[3])
+                w |= 0x20000ull;
+    }
+#endif
+    if (w) CUDA_TRY(cudaMemset(s->d_out + 10, 0, sizeof w));
+    *bits = w;
+    return CERES_OK;
+}
+
+int ceres_build_is_checked(void) {
+#ifdef CERES_CHECKED
+    return 1;
+#else
+    return 0;
+#endif
+}
+
 int ceres_scene_set_stats(ceres_scene* s, int enable) {
     if (!s) return fail(CERES_ERR_INVALID, "null scene");
     if (enable && !s->d_hist) {
@@ -1483,6 +1533,7 @@ static int prepare_frame(ceres_scene* s, const ceres_camera* cam, const float su
     frame_setup_host(cam, width, height, f.dir, f.iu, f.iv);
     f.W = (uint32_t)width; f.H = (uint32_t)height;
     rows_local = shard_rows(height, shard);
+    f.rows_local = rows_local;
     const bool sharded = shard && shard->count > 1;
     f.block_rows = sharded ? shard->block_rows : (uint32_t)height;
     f.shard_index = sharded ? shard->index : 0;
@@ -1521,6 +1572,9 @@ static int launch_rows(ceres_scene* s, Frame f, uint32_t row_begin, uint32_t row
     f.ready = s->d_ready + (((size_t)row_begin * f.W) >> READY_MIN_SHIFT) + (size_t)sub * ready_words(s, 0);
     f.ctr = s->d_ctr + sub;
     f.out_error = s->d_out + 10;
+    f.queue_cap = (row_end - row_begin) * f.W;
+    f.ready_cap = (uint32_t)ready_words(s, f.queue_cap);
+    f.pix_rows = f.compact ? f.rows_local : f.H;
     if (f.host_ext) f.host_ext += 8 * sub;
 
     cudaEvent_t* pe = nullptr;
@@ -1749,7 +1803,8 @@ static int frame_error_check(ceres_scene* s) {
     FrameCounters init[CERES_MAX_SUB] = {};
     for (auto& c : init) { c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu; }
     cudaMemcpy(s->d_ctr, init, sizeof init, cudaMemcpyHostToDevice);
-    return fail(CERES_ERR_CUDA, "frame kernel: a bounded device-side wait expired (error bits " + std::to_string(bits) + ")");
+    return fail(CERES_ERR_CUDA, std::string("frame kernel: ") + ((bits & 1u) ? "a bounded device-side wait expired" : "an index left its bound (checked build)") +
+                                " (error bits " + std::to_string(bits) + ", include/ceres_b200.h: ceres_scene_frame_error)");
 }
 
 // Sizes the record queue and its ready[] array for `records` queue slots.
@@ -2392,7 +2447,8 @@ int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, si
         s->seq_view->borrowed = true;
     }
     ceres_scene* v = s->seq_view;       // refreshed every call: a refit moves the boxes, set_tuning the knobs
-    v->dev = s->dev; v->d_pairs = s->d_pairs; v->d_tris = s->d_tris; v->d_norms = s->d_norms; v->d_slot_id = s->d_slot_id;
+    { unsigned long long* own = v->dev.check; v->dev = s->dev; v->dev.check = own; v->dev.timeline = nullptr; }
+    v->d_pairs = s->d_pairs; v->d_tris = s->d_tris; v->d_norms = s->d_norms; v->d_slot_id = s->d_slot_id;
     v->scene_bytes = s->scene_bytes; v->tri_count = s->tri_count; v->node_count = s->node_count; v->n_pairs = s->n_pairs;
     v->tune = s->tune; v->shadow_blocks_per_sm = s->shadow_blocks_per_sm; v->shadow_blocks_per_sm_stats = s->shadow_blocks_per_sm_stats;
     for (int k = 0; k < 10; ++k) v->trace_blocks_per_sm[k] = s->trace_blocks_per_sm[k];

@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_repack
         // ---- one slice: K step iterations per warp; a warp whose rays have all finished refills itself at once ---------
         for (uint32_t it = 0; it < REPACK_K; ++it) {
             if (live) {
-                live = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, stack, col, n_steps, n_tests);
+                live = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, stack, col, n_steps, n_tests, sc);
                 if (!live) {
                     retire = true;
                     if (WAVE == WAVE_SHADOW && r.found) { atomicOr(&f.queue[r.item].y, OCCLUDED_BIT); occl++; }

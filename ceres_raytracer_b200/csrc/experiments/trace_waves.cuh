@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_kernel
             // whole-warp refill: every lane runs its ray to the end, the warp reconverges after the loop
             const bool had_ray = active;
             while (active) {
-                active = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                active = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, smem_stack, tid, n_steps, n_tests, sc);
             }
             if (had_ray) {
                 retire = true;
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(THREADS, TRACE_MIN_CTAS(THREADS)) trace_kernel
             const uint32_t keep_going = 32u - f.refill_min;    // leave the loop when active lanes <= this
             for (;;) {
                 if (active) {
-                    active = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                    active = ray_step<WAVE == WAVE_SHADOW, STATS, THREADS>(pairs, tris, r, smem_stack, tid, n_steps, n_tests, sc);
                     if (!active) {
                         retire = true;
                         if (WAVE == WAVE_SHADOW && r.found) { atomicOr(&f.queue[r.item].y, OCCLUDED_BIT); occl++; }

@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
                 }
             } else {
                 bool active = true;
-                while (active) active = ray_step<false, STATS, FRAME_THREADS, ORDER_NEAR>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                while (active) active = ray_step<false, STATS, FRAME_THREADS, ORDER_NEAR>(pairs, tris, r, smem_stack, tid, n_steps, n_tests, sc);
             }
         }
         __syncwarp();
@@ -261,6 +261,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             if (TL) tl_gate = global_ns();
         }
         if (have && !found) {   // render.hpp:116-117
+            CERES_CK((f.compact ? lrow : j) < f.pix_rows && i < f.W, CHECK_PIXEL_INDEX, sc);
             float* p = f.pixels + 3 * opix;
             p[0] = 0.0f; p[1] = 0.0f; p[2] = 0.0f;
             if (f.ids) f.ids[opix] = CERES_MISS;
@@ -273,14 +274,16 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             qb = __shfl_sync(FULL, qb, 0);
             if (found) {
                 // pixel is stored as (local row, column): the shade step rebuilds both the frame row and the output position
-                f.queue[qb + __popc(m & lt_mask)] = make_uint4(lrow * f.W + i, r.slot, __float_as_uint(r.u), __float_as_uint(r.v));
+                uint32_t at = qb + __popc(m & lt_mask);
+                CERES_CLAMP(at, f.queue_cap, CHECK_QUEUE_INDEX, sc);
+                f.queue[at] = make_uint4(lrow * f.W + i, r.slot, __float_as_uint(r.u), __float_as_uint(r.v));
                 __threadfence();
             }
             __syncwarp();
             {   // credit the work items (1 << chunk_shift records each) these n records fall into: one lane per item
                 const uint32_t sh = f.chunk_shift, e = (qb >> sh) + lane;
                 const uint32_t lo = max(qb, e << sh), hi = min(qb + n, (e + 1u) << sh);
-                if (hi > lo) atomicAdd(&f.ready[e], hi - lo);
+                if (hi > lo) { CERES_CK(e < f.ready_cap, CHECK_READY_INDEX, sc); atomicAdd(&f.ready[e], hi - lo); }
             }
         }
         if (TL) { const unsigned long long d = global_ns() - tl_t; if (d > tl_tile_max) { tl_tile_max = d; tl_tile_max_base = base; } }
@@ -305,6 +308,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             q = __shfl_sync(FULL, q, 0);
             const uint32_t c_full = q >> f.chunk_shift, rem = q & ((1u << f.chunk_shift) - 1u), c_tot = c_full + (rem ? 1u : 0u);
             const uint32_t n_warps = gridDim.x * (FRAME_THREADS / 32);
+            CERES_CK(c_tot + n_warps <= f.ready_cap, CHECK_READY_INDEX, sc);
             if (rem && lane == 0) atomicOr(&f.ready[c_full], READY_FINAL);
             for (uint32_t k = lane; k < n_warps; k += 32u) atomicExch(&f.ready[c_tot + k], READY_FINAL);
         }
@@ -320,6 +324,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
         if (TL) tl_t = global_ns();
         if (lane == 0) {
             c = atomicAdd(&ctr->shadow_next, 1u);
+            CERES_CLAMP(c, f.ready_cap, CHECK_READY_INDEX, sc);
             unsigned ns = 32;
             unsigned long long t0 = 0;
             for (;;) {
@@ -352,7 +357,9 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             RaySlot r;
             bool active = lane < n;
             if (active) {
+                CERES_CK(((size_t)c << f.chunk_shift) + lane < f.queue_cap, CHECK_QUEUE_INDEX, sc);
                 const uint4 rec = __ldcg(f.queue + ((size_t)c << f.chunk_shift) + lane);
+                CERES_CK(rec.y < sc.n_slots, CHECK_SLOT_INDEX, sc);
                 V3 P, sun_line;
                 shadow_setup(load_tri(tris, rec.y), __uint_as_float(rec.z), __uint_as_float(rec.w), sun, P, sun_line);
                 ray_begin(r, P, sun_line, tid);
@@ -363,7 +370,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             const uint32_t period = f.share_period, min_idle = f.share_min_idle;
             for (;;) {
                 for (uint32_t k = 0; k < period && active; ++k)
-                    active = ray_step<true, STATS, FRAME_THREADS, ORDER>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                    active = ray_step<true, STATS, FRAME_THREADS, ORDER>(pairs, tris, r, smem_stack, tid, n_steps, n_tests, sc);
                 // a lane that ended on a hit settles its record for every lane working on it
                 occ_mask |= __reduce_or_sync(FULL, (!active && r.found) ? 1u << my_rec : 0u);
                 if ((occ_mask >> my_rec) & 1u) active = false;
@@ -377,7 +384,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
                 const bool thief = !active && (uint32_t)__popc(~act & lt_mask) < n_don;
                 const bool donor = active && r.sp != r.sb && (uint32_t)__popc(donors & lt_mask) < n_idle;
                 uint32_t give = 0;
-                if (donor) { give = smem_stack[r.sb]; r.sb += FRAME_THREADS; }
+                if (donor) { CERES_CK(r.sb >= tid && r.sb < r.sp, CHECK_STACK_UNDER, sc); give = smem_stack[r.sb]; r.sb += FRAME_THREADS; }
                 const uint32_t src = thief ? __fns(donors, 0u, __popc(~act & lt_mask) + 1) : lane;
                 give = __shfl_sync(FULL, give, src);
                 const uint32_t rec_src = __shfl_sync(FULL, my_rec, src);
@@ -407,6 +414,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
                     shade_lit(sc, f, sun_line, i, j, slot, hu, hv, c0, c1, c2);
                 }
                 const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
+                CERES_CK((f.compact ? lrow : j) < f.pix_rows && i < f.W && slot < sc.n_slots, CHECK_PIXEL_INDEX, sc);
                 float* p = f.pixels + 3 * opix;
                 p[0] = c0; p[1] = c1; p[2] = c2;
                 if (f.ids) f.ids[opix] = __ldg(sc.slot_id + slot);
@@ -433,7 +441,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
                     }
                 } else {
                     bool active = true;
-                    while (active) active = ray_step<true, STATS, FRAME_THREADS, ORDER>(pairs, tris, r, smem_stack, tid, n_steps, n_tests);
+                    while (active) active = ray_step<true, STATS, FRAME_THREADS, ORDER>(pairs, tris, r, smem_stack, tid, n_steps, n_tests, sc);
                 }
                 occluded = r.found;
                 if (occluded) occl++;
@@ -445,6 +453,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, FRAME_MIN_CTAS) frame_kernel(co
             float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
             if (!occluded) shade_lit(sc, f, sun_line, i, j, slot, hu, hv, c0, c1, c2);
             const size_t opix = (size_t)(f.compact ? lrow : j) * f.W + i;
+            CERES_CK((f.compact ? lrow : j) < f.pix_rows && i < f.W && slot < sc.n_slots, CHECK_PIXEL_INDEX, sc);
             float* p = f.pixels + 3 * opix;
             p[0] = c0; p[1] = c1; p[2] = c2;
             if (f.ids) f.ids[opix] = __ldg(sc.slot_id + slot);

@@ -40,8 +40,10 @@ __device__ __forceinline__ void ray_begin(RaySlot& r, V3 o, V3 d, uint32_t tid) 
 // Returns false when the traversal is over (stack empty, or first hit in ANY mode).
 template <bool ANY, bool STATS, int STRIDE, int ORDER = ORDER_NEAR>
 __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const float4* __restrict__ tris, RaySlot& r,
-                                         uint32_t* __restrict__ stack, uint32_t tid, uint32_t& n_steps, uint32_t& n_tests) {
+                                         uint32_t* __restrict__ stack, uint32_t tid, uint32_t& n_steps, uint32_t& n_tests,
+                                         const DevScene& sc) {
     if (STATS) n_steps++;
+    CERES_CLAMP(r.cur, sc.n_pairs, CHECK_PAIR_INDEX, sc);
     const float4* pp = pairs + 4ull * r.cur;
     const float4 q0 = __ldg(pp), q1 = __ldg(pp + 1), q2 = __ldg(pp + 2), q3 = __ldg(pp + 3);
     // octant = signbit(direction) = signbit(inverse) (safe_inverse keeps the sign, -0 included)
@@ -72,7 +74,8 @@ __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const
     if (nT) {
         const V3 o = mk(r.ox, r.oy, r.oz), d = mk(r.dx, r.dy, r.dz);
         for (uint32_t k = 0; k < nT; ++k) {
-            const uint32_t s = k < nL ? fL + k : fR + (k - nL);
+            uint32_t s = k < nL ? fL + k : fR + (k - nL);
+            CERES_CLAMP(s, sc.n_slots, CHECK_SLOT_INDEX, sc);
             if (STATS) n_tests++;
             const Tri tr = load_tri(tris, s);
             float t, u, v;
@@ -89,6 +92,7 @@ __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const
         const bool right_first = ORDER == ORDER_NEAR ? goR && (!goL || le > re) : !goL;
         if (goL && goR) {
             const uint32_t far_pair = right_first ? fL : fR;
+            CERES_CK(r.sp < tid + sc.stack_depth * STRIDE, CHECK_STACK_DEPTH, sc);
             stack[r.sp] = far_pair;
             r.sp += STRIDE;
 #ifdef CERES_PREFETCH_PUSH
@@ -99,6 +103,7 @@ __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const
         return true;
     }
     if (r.sp == r.sb) return false;
+    CERES_CK(r.sp >= r.sb + STRIDE && r.sb >= tid, CHECK_STACK_UNDER, sc);
     r.sp -= STRIDE;
     r.cur = stack[r.sp];
     return true;

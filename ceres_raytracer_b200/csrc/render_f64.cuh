@@ -37,6 +37,8 @@ struct Scene64 {
     const double* norms;          // 9 per slot
     const uint32_t* slot_id;
     uint32_t root_leaf_count;
+    uint32_t n_pairs, n_slots;    // bounds (checked build)
+    unsigned long long* check;    // checked build: CHECK_* bits; null otherwise
 };
 
 struct Frame64 {
@@ -76,7 +78,9 @@ struct Hit64 { uint32_t slot; double u, v; bool hit; };
 // triangle.hpp:95-115 for the slots [first, first + count), ascending (single_ray_traverser.hpp:41-63)
 template <bool ANY>
 __device__ __forceinline__ void leaf(const Scene64& sc, Ray64& r, uint32_t first, uint32_t count, Hit64& best) {
-    for (uint32_t s = first; s < first + count; ++s) {
+    for (uint32_t s0 = first; s0 < first + count; ++s0) {
+        uint32_t s = s0;
+        CERES_CLAMP(s, sc.n_slots, CHECK_SLOT_INDEX, sc);
         const double* t = sc.tris + 12ull * s;
         const double cx = sub(t[0], r.o.x), cy = sub(t[1], r.o.y), cz = sub(t[2], r.o.z);
         const double rx = sub(mul(r.d.y, cz), mul(r.d.z, cy)), ry = sub(mul(r.d.z, cx), mul(r.d.x, cz)), rz = sub(mul(r.d.x, cy), mul(r.d.y, cx));
@@ -106,6 +110,7 @@ __device__ Hit64 traverse(const Scene64& sc, Ray64& r) {
     uint32_t pair = 0;
     const uint32_t NONE = 0xFFFFFFFFu;
     for (;;) {
+        CERES_CLAMP(pair, sc.n_pairs, CHECK_PAIR_INDEX, sc);
         const Child& l = sc.pairs[2ull * pair];
         const Child& rt = sc.pairs[2ull * pair + 1];
         double le, lx, re, rx;
@@ -119,6 +124,7 @@ __device__ Hit64 traverse(const Scene64& sc, Ray64& r) {
         if (nl != NONE) {
             if (nr != NONE) {
                 if (le > re) { const uint32_t t = nl; nl = nr; nr = t; }
+                CERES_CK(sp < 64, CHECK_STACK_DEPTH, sc);
                 stack[sp++] = nr;
             }
             pair = nl;
@@ -304,7 +310,8 @@ int ceres_scene_f64_create(const void* nodes_v, size_t node_count, const size_t*
     TRY_D(cudaMalloc((void**)&s->d_tris, tri_slots.size() * 8));
     TRY_D(cudaMalloc((void**)&s->d_norms, norm_slots.size() * 8));
     TRY_D(cudaMalloc((void**)&s->d_slot_id, slot_id.size() * 4));
-    TRY_D(cudaMalloc((void**)&s->d_counters, 4 * sizeof(unsigned long long)));
+    TRY_D(cudaMalloc((void**)&s->d_counters, 5 * sizeof(unsigned long long)));
+    TRY_D(cudaMemset(s->d_counters, 0, 5 * sizeof(unsigned long long)));
     TRY_D(cudaMemcpy(s->d_pairs, pairs.data(), pairs.size() * sizeof(f64::Child), cudaMemcpyHostToDevice));
     TRY_D(cudaMemcpy(s->d_tris, tri_slots.data(), tri_slots.size() * 8, cudaMemcpyHostToDevice));
     TRY_D(cudaMemcpy(s->d_norms, norm_slots.data(), norm_slots.size() * 8, cudaMemcpyHostToDevice));
@@ -312,6 +319,10 @@ int ceres_scene_f64_create(const void* nodes_v, size_t node_count, const size_t*
 #undef TRY_D
     s->dev.pairs = (const f64::Child*)s->d_pairs; s->dev.tris = s->d_tris; s->dev.norms = s->d_norms; s->dev.slot_id = s->d_slot_id;
     s->dev.root_leaf_count = root_leaf_count;
+    s->dev.n_pairs = (uint32_t)(pairs.size() / 2); s->dev.n_slots = (uint32_t)tri_count;
+#ifdef CERES_CHECKED
+    s->dev.check = s->d_counters + 4;
+#endif
     *out = s;
     return CERES_OK;
 }
@@ -371,6 +382,18 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
     if (kernel_ms) cudaEventRecord(e1, 0);
     cudaError_t err = cudaGetLastError();
     if (err == cudaSuccess) err = cudaMemcpy(&o, s->d_counters, sizeof o, cudaMemcpyDeviceToHost);
+#ifdef CERES_CHECKED
+    if (err == cudaSuccess) {
+        unsigned long long w = 0;
+        err = cudaMemcpy(&w, s->d_counters + 4, sizeof w, cudaMemcpyDeviceToHost);
+        if (err == cudaSuccess && w) {
+            cudaMemset(s->d_counters + 4, 0, sizeof w);
+            if (e0) cudaEventDestroy(e0);
+            if (e1) cudaEventDestroy(e1);
+            return fail(CERES_ERR_CUDA, "ceres_render_f64: checked build: an index left its bound (bits " + std::to_string(w) + ")");
+        }
+    }
+#endif
     if (kernel_ms && err == cudaSuccess) { float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1); *kernel_ms = ms; }
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);

@@ -222,6 +222,12 @@ class Scene:
         _capi.check(self._L.ceres_scene_get_step_histogram(self._h, _p(out)))
         return out[:64].copy(), out[64:].copy()
 
+    def frame_error(self):
+        """Device-side error bits of the frames enqueued so far (synchronises; 0 = none; include/ceres_b200.h)."""
+        w = C.c_uint64(0)
+        _capi.check(self._L.ceres_scene_frame_error(self._h, C.byref(w)))
+        return int(w.value)
+
     def set_timeline(self, enable):
         _capi.check(self._L.ceres_scene_set_timeline(self._h, int(bool(enable))))
 

@@ -256,6 +256,14 @@ int ceres_scene_get_stats(ceres_scene* scene, uint64_t stats[8]);
 /* Statistics mode also fills a histogram of node-pair steps per ray, accumulated over the frames rendered since the
  * last call (the call resets it): hist[b] = primary rays with b = min(steps / 4, 63), hist[64 + b] = shadow rays. */
 int ceres_scene_get_step_histogram(ceres_scene* scene, uint64_t hist[128]);
+/* Device-side errors of the frames enqueued so far on this scene (synchronises the device): *bits = 0 when none.
+ * Bit 0: a bounded wait on the record queue expired.  Checked build only (-DCERES_CHECKED, ceres_build_is_checked()):
+ * 0x0100 node-pair index, 0x0200 triangle slot, 0x0400 stack overflow, 0x0800 record queue, 0x1000 ready[], 0x2000 pixel
+ * store, 0x4000 stack underflow -- an index was outside its bound (it was replaced by 0 and the run continued);
+ * 0x10000 / 0x20000: the per-frame queue state was not re-armed between frames.  Reading clears the word. */
+int ceres_scene_frame_error(ceres_scene* scene, uint64_t* bits);
+int ceres_build_is_checked(void);
+
 /* Per-warp timeline of the frame kernel (development aid for the per-rank timelines of DESIGN.md).  While enabled, every
  * warp w of the LAST frame kernel launched on this scene leaves CERES_TIMELINE_WORDS words at out[CERES_TIMELINE_WORDS w]:
  * {t_begin, t_primary_end, t_end (globaltimer ns), primary tiles, shadow chunks, longest tile [ns], its first work item,
