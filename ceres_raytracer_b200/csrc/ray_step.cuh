@@ -95,9 +95,6 @@ __device__ __forceinline__ bool ray_step(const float4* __restrict__ pairs, const
             CERES_CK(r.sp < tid + sc.stack_depth * STRIDE, CHECK_STACK_DEPTH, sc);
             stack[r.sp] = far_pair;
             r.sp += STRIDE;
-#ifdef CERES_PREFETCH_PUSH
-            asm volatile("prefetch.global.L1 [%0];" :: "l"(pairs + 4ull * far_pair));
-#endif
         }
         r.cur = right_first ? fR : fL;
         return true;

@@ -77,6 +77,23 @@ def main():
         traffic[k] = int(float(r[ir]) * mult[units[ir]] + float(r[iw]) * mult[units[iw]])
     lines += ["", "dram read+write bytes per launch: " + json.dumps(traffic)]
     open(out, "w").write("\n".join(lines) + "\n")
+    if "--frame-json" in sys.argv:
+        # profiles/ncu_frame_kernel.json: what bench.py's roofline.issue / roofline.traffic read (LAST frame_kernel row = warm launch)
+        want = sys.argv[sys.argv.index("--frame-json") + 1] if len(sys.argv) > sys.argv.index("--frame-json") + 1 and not sys.argv[sys.argv.index("--frame-json") + 1].startswith("--") else "frame_kernel"
+        rows_f = [r for r in data if want in r[name_i].replace("(bool)", "").replace("(int)", "")]
+        if rows_f:
+            r = rows_f[-1]
+            g = lambda key: float(r[hdr.index(key)].replace(",", ""))
+            dur_mult = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}
+            di = hdr.index("gpu__time_duration.sum")
+            frame = {"warp_instructions": int(g("smsp__inst_executed.sum")),
+                     "lanes_per_instruction": g("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                     "issue_active_pct": g("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                     "dram_bytes": int(float(r[ir]) * mult[units[ir]] + float(r[iw]) * mult[units[iw]]),
+                     "duration_us_under_ncu": float(r[di]) * dur_mult.get(units[di], 1.0),
+                     "kernel": r[name_i].split("(")[0].replace("void ", ""),
+                     "source": os.path.relpath(out, os.path.dirname(os.path.abspath(__file__)))}
+            json.dump(frame, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_frame_kernel.json"), "w"), indent=1)
     if "--traffic" in sys.argv:
         p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_traffic.json")
         traffic["_source"] = os.path.relpath(out, os.path.dirname(p))
