@@ -635,6 +635,14 @@ def main():
             ms_e2e, r = time_host_call(lambda: scene.render(cam, sun, W, H, flags=flags, pixels=hb.array))
             assert r[2] == (rays_frame, hits_frame)
             d2h = scene.last_d2h_bytes        # the rectangles that hold hit pixels + counters; the rest of the frame is host-filled zeros
+            # opt-in contract CERES_FRAME_RETAINED (include/ceres_b200.h): the caller passes the buffer of the previous call,
+            # untouched -- what anim.cpp does -- so the ~70 % of the frame outside the scene's rectangle is not zero-filled again
+            ms_ret, r = time_host_call(lambda: scene.render(cam, sun, W, H, flags=flags | cr.FRAME_RETAINED, pixels=hb.array))
+            assert r[2] == (rays_frame, hits_frame)
+            extra["e2e_retained"] = {"value": rays_frame / (ms_ret * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_ret,
+                                     "d2h_bytes_per_step": scene.last_d2h_bytes,
+                                     "path": "ceres_render(CERES_FRAME_RETAINED) -> the same page-locked frame as in the previous call (opt-in: "
+                                             "the caller promises not to write into it between calls); same frame, no host zero fill"}
             hb.close()
             # the same call into a plain malloc'ed frame -- what anim.cpp:76 / static.cpp:117 hand to render()
             plain = np.empty((H, W, 3), np.float32)

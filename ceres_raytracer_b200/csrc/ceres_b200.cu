@@ -664,6 +664,15 @@ struct ceres_scene {
     float bounds[6] = {0, 0, 0, 0, 0, 0};                   // root bounding box (nodes[0].bounds)
     uint64_t last_d2h_bytes = 0;                            // bytes DMA-copied to the host by the last host-frame render
     uint32_t* h_ext = nullptr;                              // mapped page-locked: 8 words per band (Frame::host_ext)
+    // CERES_FRAME_RETAINED: what the last host frame left in the caller's buffers (rectangles per band; zeros elsewhere)
+    struct Retained {
+        bool valid = false;
+        const void* px = nullptr; const void* ids = nullptr;
+        size_t W = 0, H = 0;
+        uint32_t sh[3] = {0, 0, 0}; bool compact = false;
+        uint32_t i0 = 0, i1 = 0, l0 = 0, l1 = 0, nb = 0, trpb = 0;
+        uint32_t ext[CERES_MAX_BANDS][4] = {};              // ci0, ci1, cr0, cr1 (inclusive) of band b; ci0 > ci1: nothing written
+    } kept;
     ceres_scene* seq_view = nullptr;                        // second set of per-frame resources over the same geometry (sequences)
     bool borrowed = false;                                  // a view: the geometry belongs to the scene it was made from
     uint32_t ext_epoch = 0;
@@ -811,8 +820,8 @@ static int scene_new(int device, int sm_count, ceres_scene** out) {
         for (auto& c : init) { c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu; }
         TRY_S(cudaMemcpy(s->d_ctr, init, sizeof init, cudaMemcpyHostToDevice));
     }
-    TRY_S(cudaHostAlloc((void**)&s->h_ext, CERES_MAX_SUB * 8 * sizeof(uint32_t), cudaHostAllocMapped));
-    std::memset(s->h_ext, 0, CERES_MAX_SUB * 8 * sizeof(uint32_t));
+    TRY_S(cudaHostAlloc((void**)&s->h_ext, CERES_MAX_BANDS * 8 * sizeof(uint32_t), cudaHostAllocMapped));
+    std::memset(s->h_ext, 0, CERES_MAX_BANDS * 8 * sizeof(uint32_t));
     TRY_S(cudaMemset(s->d_out, 0, 11 * sizeof(unsigned long long)));
 #undef TRY_S
 #ifdef CERES_CHECKED
@@ -1820,6 +1829,18 @@ static int size_queue(ceres_scene* s, size_t records) {
     return CERES_OK;
 }
 
+// How local rows [a, b) of a frame are cut into row bands: nsub launches of band_rows rows (the last one may be shorter).
+static void band_split(const ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, uint32_t default_sub, uint32_t& nsub, uint32_t& band_rows) {
+    const uint32_t rows = b - a;
+    nsub = s->tune.reserved[1] ? s->tune.reserved[1] : default_sub;
+    if (f.peer) nsub = 1;      // one done flag per rank and frame
+    // a band must be worth its launch: at least 256 Ki pixels of the rectangle each
+    const uint64_t rect_px = (uint64_t)rows * (f.cull_i1 > f.cull_i0 ? f.cull_i1 - f.cull_i0 : 1u);
+    nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (uint32_t)std::max<uint64_t>(1u, rect_px >> 18));
+    if (nsub < 1) nsub = 1;
+    band_rows = ((rows + nsub - 1) / nsub + 3u) / 4u * 4u;
+}
+
 template <class Hook>
 static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, cudaStream_t st, uint32_t default_sub, int clear_mode, Hook&& hook) {
     if (b <= a) return CERES_OK;
@@ -1830,12 +1851,8 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
     struct Done { ceres_scene* s; cudaStream_t st; ~Done() { if (cudaEventRecord(s->frame_done, st) == cudaSuccess) s->last_stream = st; else cudaGetLastError(); } } done{s, st};
     CUDA_TRY(cudaMemsetAsync(f.out_counters, 0, 2 * sizeof(unsigned long long), st));
     if (f.out_stats) CUDA_TRY(cudaMemsetAsync(f.out_stats, 0, 8 * sizeof(unsigned long long), st));
-    const uint32_t rows = b - a;
-    uint32_t nsub = s->tune.reserved[1] ? s->tune.reserved[1] : default_sub;
-    if (f.peer) nsub = 1;      // one done flag per rank and frame
-    // a band must be worth its four launches: at least 256 Ki pixels of the rectangle each
-    const uint64_t rect_px = (uint64_t)rows * (f.cull_i1 > f.cull_i0 ? f.cull_i1 - f.cull_i0 : 1u);
-    nsub = std::min<uint32_t>(std::min<uint32_t>(nsub, CERES_MAX_SUB), (uint32_t)std::max<uint64_t>(1u, rect_px >> 18));
+    uint32_t nsub = 1, band_rows = b - a;
+    band_split(s, f, a, b, default_sub, nsub, band_rows);
     s->cur_nsub = nsub;
     if (nsub <= 1) {
         s->profile_kernels = true;
@@ -1856,7 +1873,6 @@ static int render_rows(ceres_scene* s, const Frame& f, uint32_t a, uint32_t b, c
     if (dbg && !dbg_ev[0]) for (auto& e : dbg_ev) CUDA_TRY(cudaEventCreate(&e));
     if (dbg) CUDA_TRY(cudaEventRecord(dbg_ev[0], st));
     CUDA_TRY(cudaEventRecord(s->fork_ev, st));
-    uint32_t band_rows = ((rows + nsub - 1) / nsub + 3u) / 4u * 4u;
     uint32_t k = 0;
     for (uint32_t r0 = a; r0 < b; r0 += band_rows, ++k) {
         const uint32_t r1 = std::min(b, r0 + band_rows);
@@ -2137,9 +2153,36 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     const uint32_t i0 = std::min<uint32_t>(f.cull_i0, (uint32_t)width), i1 = std::max(i0, std::min<uint32_t>(f.cull_i1, (uint32_t)width));
     const bool empty = l1 == l0 || i1 == i0;
 
+    // ---- which path: tight band copies with in-kernel bands, and the CERES_FRAME_RETAINED contract on top of them -----------
+    static const bool tight_off = std::getenv("CERES_NO_TIGHT_COPY") != nullptr;
+    const bool tight = !scatter && !tight_off && s->tune.variant != 1;
+    uint32_t nb = 1, trpb = 0;                               // band layout of the tight path: nb launches of trpb rows
+    if (tight && !empty) band_split(s, f, l0, l1, CERES_SUBFRAMES_HOST, nb, trpb);
+    const ceres_scene::Retained old = s->kept;
+    s->kept.valid = false;                                   // re-established at the end of a successful retained call
+    const bool retained_req = (flags & CERES_FRAME_RETAINED) != 0 && tight;
+    const uint32_t sh3[3] = {sharded ? shard->block_rows : 0u, sharded ? shard->index : 0u, sharded ? shard->count : 0u};
+    const bool kept_ok = retained_req && old.valid && old.px == pixels && old.ids == ids && old.W == width && old.H == height &&
+                         old.compact == want_compact && old.sh[0] == sh3[0] && old.sh[1] == sh3[1] && old.sh[2] == sh3[2];
+    const bool same_layout = kept_ok && !empty && old.nb == nb && old.trpb == trpb && old.i0 == i0 && old.i1 == i1 && old.l0 == l0 && old.l1 == l1;
+
     // ---- host fill of everything outside the rectangle ---------------------------------------------------------
     ceres_host::Job job;
-    {
+    if (kept_ok) {
+        // the buffers still hold the previous frame: zeros / CERES_MISS everywhere but inside its bands' rectangles.  Same band
+        // layout: every band zeroes what its old rectangle leaves uncovered once its new one is known (below).  Otherwise all
+        // old rectangles are wiped here, before the first copy of the new frame lands.
+        if (!same_layout)
+            for (uint32_t b = 0; b < old.nb; ++b) {
+                const uint32_t* e = old.ext[b];
+                if (e[0] > e[1]) continue;
+                for (uint32_t r = e[2]; r <= e[3]; ++r) {
+                    const size_t o = out_row(r) * width + e[0];
+                    job.segs.push_back({reinterpret_cast<unsigned char*>(pixels + 3 * o), (size_t)(e[1] - e[0] + 1) * 12, 0x00});
+                    if (ids) job.segs.push_back({reinterpret_cast<unsigned char*>(ids + o), (size_t)(e[1] - e[0] + 1) * 4, 0xFF});
+                }
+            }
+    } else {
         auto fill_rows = [&](uint32_t a, uint32_t b) {       // local rows [a, b), full width; merge rows contiguous in the output
             uint32_t r = a;
             while (r < b) {
@@ -2175,6 +2218,12 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     s->last_d2h_bytes = empty ? 0 : (uint64_t)(l1 - l0) * (i1 - i0) * (ids ? 16u : 12u) + 2 * sizeof(unsigned long long);
     if (empty) {
         if (counters) { counters[0] = (uint64_t)width * rows; counters[1] = 0; }
+        pool.wait(&job);
+        if (retained_req) {
+            s->kept = ceres_scene::Retained{};
+            s->kept.valid = true; s->kept.px = pixels; s->kept.ids = ids; s->kept.W = width; s->kept.H = height; s->kept.compact = want_compact;
+            for (int k = 0; k < 3; ++k) s->kept.sh[k] = sh3[k];
+        }
         return CERES_OK;
     }
 
@@ -2228,8 +2277,6 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     // polls the flags band by band, copies only that sub-rectangle (everything else inside the conservative rectangle is
     // zero / CERES_MISS by construction) and hands the strips around it to the fill pool.  For the dragon the bands'
     // own rectangles hold ~2/3 of the conservative rectangle's bytes, and the copy engine is the serial resource.
-    static const bool tight_off = std::getenv("CERES_NO_TIGHT_COPY") != nullptr;
-    const bool tight = !scatter && !tight_off && s->tune.variant != 1;
     struct Band { uint32_t k, r0, r1; cudaStream_t bs; };
     std::vector<Band> bands;
     std::vector<std::unique_ptr<ceres_host::Job>> gap_jobs;
@@ -2261,6 +2308,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
                 }
             }
             std::atomic_thread_fence(std::memory_order_acquire);
+            if (trace_timing) std::fprintf(stderr, "  band %u flag at %.0f us\n", b.k, now_us() - t_begin);
             const uint32_t ci0 = e[0], ci1 = e[1], cr0 = e[2], cr1 = e[3];
             const bool any = ci0 <= ci1 && cr0 <= cr1 && ci0 >= i0 && ci1 < i1 && cr0 >= b.r0 && cr1 < b.r1;
             if (!(ci0 > ci1) && !any) return fail(CERES_ERR_CUDA, "ceres_render: band extents outside the band (internal error)");
@@ -2271,18 +2319,33 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
                 gaps->segs.push_back({reinterpret_cast<unsigned char*>(pixels + 3 * o), (size_t)(c - a) * 12, 0x00});
                 if (ids) gaps->segs.push_back({reinterpret_cast<unsigned char*>(ids + o), (size_t)(c - a) * 4, 0xFF});
             };
-            if (!any) {
-                for (uint32_t r = b.r0; r < b.r1; ++r) strip(r, i0, i1);
-            } else {
+            // what this band has to zero around its new rectangle: everything else of the band's part of the conservative
+            // rectangle -- or, under CERES_FRAME_RETAINED with an unchanged band layout, only what the OLD rectangle of the band
+            // leaves uncovered (the rest still holds the zeros of the previous call)
+            uint32_t zi0 = i0, zi1 = i1, zr0 = b.r0, zr1 = b.r1;        // region to reconcile: columns [zi0, zi1) x rows [zr0, zr1)
+            if (same_layout) {
+                const uint32_t* o = old.ext[b.k];
+                if (o[0] > o[1]) { zr1 = zr0; }                          // the old frame left nothing in this band
+                else { zi0 = o[0]; zi1 = o[1] + 1u; zr0 = o[2]; zr1 = o[3] + 1u; }
+            } else if (kept_ok && !job.segs.empty()) {
+                pool.wait(&job);                                         // every old rectangle is wiped before a new one lands
+                job.segs.clear();
+            }
+            if (kept_ok && !same_layout) zr1 = zr0;                      // already wiped above: nothing to reconcile per band
+            if (any) {
                 const size_t src = (size_t)cr0 * width + ci0, dst = out_row(cr0) * width + ci0;
                 const size_t cols = ci1 - ci0 + 1, nrows = cr1 - cr0 + 1;
                 CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, cols * 12, nrows, cudaMemcpyDeviceToHost, s->copy_stream));
                 if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, cols * 4, nrows, cudaMemcpyDeviceToHost, s->copy_stream));
                 copied += (uint64_t)cols * nrows * (ids ? 16u : 12u);
-                for (uint32_t r = b.r0; r < b.r1; ++r) {
-                    if (r < cr0 || r > cr1) strip(r, i0, i1);
-                    else { strip(r, i0, ci0); strip(r, ci1 + 1, i1); }
-                }
+            }
+            for (uint32_t r = zr0; r < zr1; ++r) {
+                if (!any || r < cr0 || r > cr1) strip(r, zi0, zi1);
+                else { strip(r, zi0, std::min(zi1, ci0)); strip(r, std::max(zi0, ci1 + 1u), zi1); }
+            }
+            if (retained_req) {
+                uint32_t* k = s->kept.ext[b.k];
+                if (any) { k[0] = ci0; k[1] = ci1; k[2] = cr0; k[3] = cr1; } else { k[0] = 1u; k[1] = 0u; k[2] = 1u; k[3] = 0u; }
             }
             pool.submit(gaps.get());
             gap_jobs.push_back(std::move(gaps));
@@ -2303,6 +2366,11 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
                      t_filled - t_begin, t_kernels - t_begin, now_us() - t_begin);
     if (int rc = frame_error_check(s)) return rc;
     if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
+    if (retained_req) {       // the bands' rectangles were noted above
+        s->kept.valid = true; s->kept.px = pixels; s->kept.ids = ids; s->kept.W = width; s->kept.H = height; s->kept.compact = want_compact;
+        for (int k = 0; k < 3; ++k) s->kept.sh[k] = sh3[k];
+        s->kept.i0 = i0; s->kept.i1 = i1; s->kept.l0 = l0; s->kept.l1 = l1; s->kept.nb = nb; s->kept.trpb = trpb;
+    }
     return CERES_OK;
 }
 

@@ -14,7 +14,7 @@ from typing import Sequence
 import numpy as np
 
 from . import _capi
-from ._capi import NO_SHADOWS, COMPACT_ROWS, MISS, CeresError  # noqa: F401
+from ._capi import NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, MISS, CeresError  # noqa: F401
 
 NODE_DT = np.dtype([("bounds", "<f4", (6,)), ("primitive_count", "<u4"), ("first_child_or_primitive", "<u4")])
 NODE64_DT = np.dtype([("bounds", "<f8", (6,)), ("primitive_count", "<u8"), ("first_child_or_primitive", "<u8")])   # Bvh<double>::Node
@@ -254,14 +254,18 @@ class Scene:
         return dict(zip(["primary", "shadow", "shade", "total"], ms.tolist())), int(n.value)
 
     # ---- host buffers ---------------------------------------------------------------------------------------
-    def render(self, camera, sun_position, width, height, flags=0, pixels=None, want_ids=False, shard=None):
-        """Returns (pixels[H,W,3] float32, ids[H,W] uint32 or None, (rays, hits))."""
+    def render(self, camera, sun_position, width, height, flags=0, pixels=None, want_ids=False, shard=None, ids=None):
+        """Returns (pixels[H,W,3] float32, ids[H,W] uint32 or None, (rays, hits)).  flags may carry FRAME_RETAINED (the same
+        pixels / ids buffers as in the previous call, untouched since: include/ceres_b200.h)."""
         rows = len(shard_rows(height, shard)) if (shard is not None and flags & COMPACT_ROWS) else height
         if pixels is None:
             pixels = np.zeros((rows, width, 3), np.float32) if shard is not None else np.empty((rows, width, 3), np.float32)
         if pixels.dtype != np.float32 or not pixels.flags.c_contiguous or pixels.size != rows * width * 3:
             raise ValueError("pixels must be a C-contiguous float32 buffer of 3*width*height")
-        ids = (np.full((rows, width), MISS, np.uint32) if shard is not None else np.empty((rows, width), np.uint32)) if want_ids else None
+        if ids is None:
+            ids = (np.full((rows, width), MISS, np.uint32) if shard is not None else np.empty((rows, width), np.uint32)) if want_ids else None
+        elif ids.dtype != np.uint32 or not ids.flags.c_contiguous or ids.size != rows * width:
+            raise ValueError("ids must be a C-contiguous uint32 buffer of width*height")
         sun = np.asarray(sun_position, np.float32)
         cnt = np.zeros(2, np.uint64)
         sh = _shard(shard)

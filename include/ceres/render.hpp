@@ -33,6 +33,10 @@
 //     frame and gets the SAME address back from the allocator for a new one between two calls keeps a registration of
 //     pages that no longer back the buffer; such callers set CERES_NO_AUTOPIN=1 (pageable path, ~2x slower at 4K) or call
 //     ceres::release_frame() before freeing.  Float frames only.
+//   * opt-in, CERES_FRAME_RETAINED=1 in the environment: render() stops zero-filling the ~70 % of the frame outside the scene's
+//     screen rectangle on every call, on the caller's word that the frame is not written between calls (the reference's
+//     anim.cpp only reads it).  Same frames; 0.84 -> 0.6 ms per 4K frame.  Off by default: render() then overwrites every pixel
+//     whatever the buffer held, exactly as render.hpp:107,117 do.
 //   * the scene (bvh, triangles, tri_norms) is flattened and uploaded on the first call and re-used while the same
 //     arrays are passed again (the reference builds them once, outside the frame loop, anim.cpp:46-65).  The cache
 //     key is the three pointers + counts + a sampled fingerprint of the contents; call ceres::invalidate_scene()
@@ -250,7 +254,10 @@ std::pair<int, int> render(const Camera<Scalar>& camera, const bvh::Vector3<Scal
         cam.fov = camera.fov;
         const float sun[3] = {sun_position[0], sun_position[1], sun_position[2]};
         ceres::autopin_frame(pixels, 3 * width * height * sizeof(float));
-        if (ceres_render(scene, &cam, sun, width, height, 0u, pixels, nullptr, counters) != CERES_OK)
+        // CERES_FRAME_RETAINED=1 in the environment: the caller states that nobody writes into `pixels` between two render()
+        // calls (true for anim.cpp:76-127, which only reads the frame) -- see CERES_FRAME_RETAINED in ceres_b200.h
+        static const unsigned retained = std::getenv("CERES_FRAME_RETAINED") ? CERES_FRAME_RETAINED : 0u;
+        if (ceres_render(scene, &cam, sun, width, height, retained, pixels, nullptr, counters) != CERES_OK)
             ceres::detail::fail("ceres_render");
     } else {
         ceres_scene_f64* scene = ceres::scene_for(bvh, triangles, tri_norms);

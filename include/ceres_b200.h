@@ -45,6 +45,14 @@ enum {
 /* flags for the render calls */
 #define CERES_NO_SHADOWS   1u  /* skip the sun shadow ray (render.hpp:135-137) and shade every primary hit
                                   ("primary rays only", BASELINE.json configs 1-2; not a mode of the reference) */
+#define CERES_FRAME_RETAINED 4u /* host frames (ceres_render / ceres_render_shard), OPT-IN contract: "the pixels / ids buffers I pass
+                                   are the ones I passed to the previous call with this flag on this scene, and nobody has written
+                                   into them since".  The library then knows that everything outside the rectangles it wrote
+                                   last time is still zero / CERES_MISS and only zeroes what the previous frame's rectangles
+                                   leave uncovered by the new ones, instead of zero-filling ~70 % of a 4K frame from the host on
+                                   every call (render.hpp:107,117 overwrite every pixel; the result is the same frame).  The
+                                   first call with the flag, a different buffer / size / shard, or a call without the flag in
+                                   between re-establishes the whole frame.  Ignored by the paths that do not use it. */
 #define CERES_COMPACT_ROWS 2u  /* sharded render: write the shard's rows packed, not at their frame position */
 
 #define CERES_MISS 0xFFFFFFFFu /* value of ids[] where the primary ray hit nothing */

@@ -460,3 +460,52 @@ def test_sequence_two_frames_in_flight_equals_single_frames(cr, dragon_pod, kat)
                 assert np.array_equal(px.view(np.uint32), px_all[k].view(np.uint32)), (moved, k)
                 assert counters == (int(cnt[k, 0]), int(cnt[k, 1]))
             assert (px_all != 0).any()
+
+
+def test_retained_frame_contract(cr, dragon):
+    """CERES_FRAME_RETAINED (opt-in): the caller hands in the buffers of the previous call, untouched; the library zeroes only
+    what the previous frame's rectangles leave uncovered.  Every frame of a sequence with moving, shrinking, growing and
+    disappearing rectangles must equal the frame rendered into a NaN-poisoned buffer WITHOUT the flag; the default path
+    never trusts the buffer's contents."""
+    W, H = 1280, 720
+    cams = [cr.configs.DRAGON_CAMERA, cr.configs.DRAGON_CAMERA,
+            cr.Camera((3.0, -15.0, 2.5), (-0.1, 1.0, 0.0), (0.0, 0.0, 1.0), 45.0),          # other rectangle, other band layout
+            cr.Camera((0.5, -15.0, 2.0), (0.0, 1.0, 0.0), (0.0, 0.0, 1.0), 60.0),           # shifted by a few pixels
+            cr.Camera((0.0, -40.0, 2.0), (0.0, 1.0, 0.0), (0.0, 0.0, 1.0), 60.0),           # far away: small rectangle
+            cr.Camera((0.0, -15.0, 2.0), (0.0, -1.0, 0.0), (0.0, 0.0, 1.0), 60.0),          # looking away: no rectangle at all
+            cr.configs.DRAGON_CAMERA,
+            cr.Camera((0.0, -6.0, 2.0), (0.0, 1.0, 0.0), (0.0, 0.0, 1.0), 60.0)]            # close up: the rectangle is the frame
+    hb = cr.PinnedBuffer((H, W, 3), np.float32)
+    hi = cr.PinnedBuffer((H, W), np.uint32)
+    try:
+        hb.array.fill(np.nan)
+        hi.array.fill(7)
+        for k, cam in enumerate(cams):
+            for flags in (0, cr.NO_SHADOWS):
+                fresh = np.full((H, W, 3), np.nan, np.float32)
+                want = dragon.render(cam, SUN, W, H, flags=flags, pixels=fresh, want_ids=True)
+                got = dragon.render(cam, SUN, W, H, flags=flags | cr.FRAME_RETAINED, pixels=hb.array, ids=hi.array)
+                assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), (k, flags)
+                assert np.array_equal(got[1], want[1]) and got[2] == want[2], (k, flags)
+        # the flag is a promise: a caller who breaks it gets his own scribbling back (outside the rectangles) ...
+        dragon.render(cams[0], SUN, W, H, flags=cr.FRAME_RETAINED, pixels=hb.array, ids=hi.array)
+        hb.array[0, 0, :] = 5.0
+        dragon.render(cams[0], SUN, W, H, flags=cr.FRAME_RETAINED, pixels=hb.array, ids=hi.array)
+        assert hb.array[0, 0, 0] == 5.0
+        # ... and the default call, which promises nothing, overwrites every pixel (render.hpp:107,117)
+        dragon.render(cams[0], SUN, W, H, pixels=hb.array, ids=hi.array)
+        assert hb.array[0, 0, 0] == 0.0
+        # a call without the flag forgets the retained state: the next retained call re-establishes the whole frame
+        hb.array[1, 1, :] = 9.0
+        got = dragon.render(cams[0], SUN, W, H, flags=cr.FRAME_RETAINED, pixels=hb.array, ids=hi.array)
+        assert hb.array[1, 1, 0] == 0.0
+        # another size in the same memory: re-established as well
+        small = hb.array.reshape(-1)[:3 * 640 * 360].reshape(360, 640, 3)
+        small_ids = hi.array.reshape(-1)[:640 * 360].reshape(360, 640)
+        small.fill(np.nan)
+        got = dragon.render(cams[0], SUN, 640, 360, flags=cr.FRAME_RETAINED, pixels=small, ids=small_ids)
+        want = dragon.render(cams[0], SUN, 640, 360, want_ids=True)
+        assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)) and np.array_equal(got[1], want[1])
+    finally:
+        hb.close()
+        hi.close()
