@@ -2549,7 +2549,12 @@ int ceres_trace_rays(ceres_scene* s, const float* rays, size_t n, uint32_t* out_
     TRY_T(cudaMalloc((void**)&d_id, n * sizeof(uint32_t)));
     TRY_T(cudaMalloc((void**)&d_tuv, n * 3 * sizeof(float)));
     TRY_T(cudaMemcpyAsync(d_rays, rays, n * 8 * sizeof(float), cudaMemcpyHostToDevice, s->stream));
-    trace_rays_kernel<<<(unsigned)((n + 255) / 256), 256, (size_t)s->dev.stack_depth * 4 * 256, s->stream>>>(s->dev, d_rays, (uint32_t)n, d_id, d_tuv);
+    {
+        // a 64-deep stack x 256 threads = 64 KB of dynamic shared memory: above the 48 KB default, needs the opt-in
+        const size_t smem = (size_t)s->dev.stack_depth * 4 * 256;
+        if (int rc = smem_opt_in(trace_rays_kernel, smem)) { cleanup(); return rc; }
+        trace_rays_kernel<<<(unsigned)((n + 255) / 256), 256, smem, s->stream>>>(s->dev, d_rays, (uint32_t)n, d_id, d_tuv);
+    }
     g_launches++;
     TRY_T(cudaGetLastError());
     TRY_T(cudaMemcpyAsync(out_id, d_id, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));

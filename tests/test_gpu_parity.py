@@ -509,3 +509,116 @@ def test_retained_frame_contract(cr, dragon):
     finally:
         hb.close()
         hi.close()
+
+
+def chain_scene(cr, depth):
+    """A degenerate BVH of `depth` + 1 triangles: every inner node has a leaf (left) and another inner node (right), so the
+    traversal stack of a ray that enters every box grows to `depth` entries (single_ray_traverser.hpp:14: 64 at most).  The
+    triangles overlap along z so that many rays pass through every box."""
+    n = depth + 1
+    v = np.zeros((n, 9), np.float32)
+    for k in range(n):
+        z, s = 5.0 + 0.25 * k, 1.0 + 0.05 * k
+        v[k] = [-s, -s, z, s, -s, z, 0.0, s, z + 0.1]
+    tri = port.make_triangles(v)
+    lo = v.reshape(n, 3, 3).min(axis=1)
+    hi = v.reshape(n, 3, 3).max(axis=1)
+    nodes = np.zeros(2 * n - 1, cr.NODE_DT)
+
+    def box(a, b):      # union of triangles a..b-1
+        l, h = lo[a:b].min(axis=0), hi[a:b].max(axis=0)
+        return [l[0], h[0], l[1], h[1], l[2], h[2]]
+
+    # node 0 = root over all; inner node k (index idx) has children idx' (leaf: triangle k) and idx'+1 (rest)
+    idx = 0
+    for k in range(n - 1):
+        nodes[idx]["bounds"] = box(k, n)
+        nodes[idx]["primitive_count"] = 0
+        child = 2 * k + 1
+        nodes[idx]["first_child_or_primitive"] = child
+        nodes[child]["bounds"] = box(k, k + 1); nodes[child]["primitive_count"] = 1; nodes[child]["first_child_or_primitive"] = k
+        idx = child + 1
+    nodes[idx]["bounds"] = box(n - 1, n); nodes[idx]["primitive_count"] = 1; nodes[idx]["first_child_or_primitive"] = n - 1
+    return {"nodes": nodes, "prim_indices": np.arange(n, dtype=np.uint64), "triangles": tri,
+            "norms": np.tile(np.array([0, 0, -1], np.float32), (n, 3))}
+
+
+@pytest.mark.parametrize("depth", [20, 49, 63])
+def test_deep_trees_up_to_the_reference_stack(cr, depth):
+    """Trees deeper than 48 need more than the default 48 KB of dynamic shared memory in the 256-thread kernels
+    (ceres_trace_rays: 64 entries x 4 B x 256 threads = 64 KB); every kernel opts in or sizes its CTA accordingly."""
+    pod = chain_scene(cr, depth)
+    cam = cr.Camera((0, 0, 0), (0, 0, 1), (0, 1, 0), 60)
+    rng = np.random.default_rng(depth)
+    rays = np.zeros((4096, 8), np.float32)
+    rays[:, :3] = rng.uniform(-0.5, 0.5, (4096, 3)) * [1, 1, 0]
+    d = rng.normal(size=(4096, 3)) * [0.08, 0.08, 0] + [0, 0, 1]
+    rays[:, 3:6] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays[:, 7] = np.finfo(np.float32).max
+    with cr.Scene.from_pod(pod) as s:
+        ids, tuv = s.trace_rays(rays)
+        o_ids, o_tuv = port.trace_rays(pod, rays)
+        assert np.array_equal(ids, o_ids) and np.array_equal(tuv.view(np.uint32), o_tuv.view(np.uint32))
+        assert (ids != cr.MISS).sum() > 1000
+        check_frame(cr, s, pod, cam, np.array([0, 0, -10], np.float32), 320, 240, 0)
+        check_frame(cr, s, pod, cr.Camera((0.3, 0.2, 40), (0, 0, -1), (0, 1, 0), 30), np.array([5, 5, 100], np.float32), 320, 240, 0)
+        for share in (1, 2):
+            s.set_tuning(share=share)
+            check_frame(cr, s, pod, cam, np.array([3, 0, -10], np.float32), 160, 120, 0)
+        assert s.frame_error() == 0
+    too_deep = chain_scene(cr, 65)
+    with pytest.raises(cr.CeresError):
+        cr.Scene.from_pod(too_deep)
+
+
+def test_culling_rectangle_adversarial(cr, bunny, bunny_pod):
+    """The conservative screen rectangle (cull_rectangle): pixels outside it are never traced, so it must contain every pixel
+    whose ray can hit.  (a) cameras placed so that the scene's root box ends within a fraction of a pixel of a pixel centre
+    row / column, from both sides; (b) the whole scene scaled by 1e4 (coordinates ~1e4, the margins are relative); (c) the eye
+    inside the root box (culling must switch itself off).  Every frame is compared with the oracle, which traces every pixel."""
+    W, H = 640, 360
+    b = bunny_pod["nodes"][0]["bounds"].astype(np.float64)
+    cx, cy = 0.5 * (b[0] + b[1]), 0.5 * (b[2] + b[3])
+    tan_h = np.tan(np.radians(30.0))
+    for k, frac in enumerate([0.0, 0.02, -0.02, 0.1, -0.1, 0.49, -0.49, 0.5]):
+        # distance d such that the box's right edge (front face) projects exactly frac pixels off the centre of column 500
+        u = 2.0 * (500 + 0.5 + frac) / W - 1.0
+        d = (b[1] - cx) / (u * tan_h)
+        cam = cr.Camera((cx, cy, b[4] - d), (0, 0, 1), (0, 1, 0), 60.0)
+        check_frame(cr, bunny, bunny_pod, cam, np.array([-50, -20, 0], np.float32), W, H, 0)
+        # and the top edge against a pixel row
+        v = 2.0 * (300 + 0.5 + frac) / H - 1.0
+        d = (b[3] - cy) / (v * tan_h * H / W)
+        cam = cr.Camera((cx, cy, b[4] - d), (0, 0, 1), (0, 1, 0), 60.0)
+        check_frame(cr, bunny, bunny_pod, cam, np.array([-50, -20, 0], np.float32), W, H, cr.NO_SHADOWS)
+    # (b) the scene 1e4 times larger (rebuilt boxes: scale is exact for powers of two only, so refit the boxes on the oracle side)
+    big = {k: v.copy() for k, v in bunny_pod.items()}
+    big["triangles"] = (bunny_pod["triangles"].astype(np.float32) * np.float32(8192.0)).astype(np.float32)       # p0, e1, e2, n all scale
+    big["triangles"][:, 9:12] = bunny_pod["triangles"][:, 9:12] * np.float32(8192.0 * 8192.0)                  # n = e1 x e2
+    big["nodes"] = bunny_pod["nodes"].copy()
+    big["nodes"]["bounds"] = bunny_pod["nodes"]["bounds"] * np.float32(8192.0)
+    with cr.Scene.from_pod(big) as s:
+        for eye in ((0.0, 0.1 * 8192, -0.3 * 8192), (0.02 * 8192, 0.1 * 8192, -0.12 * 8192), (0.0, 0.1 * 8192, -3.0 * 8192)):
+            check_frame(cr, s, big, cr.Camera(eye, (0, 0, 1), (0, 1, 0), 60.0), np.array([-50 * 8192, -20 * 8192, 0], np.float32), W, H, 0)
+    # (c) eye inside the root box, looking along each axis
+    for dirv, up in (((0, 0, 1), (0, 1, 0)), ((1, 0, 0), (0, 1, 0)), ((0, -1, 0), (0, 0, 1))):
+        cam = cr.Camera((cx, cy, 0.5 * (b[4] + b[5])), dirv, up, 90.0)
+        check_frame(cr, bunny, bunny_pod, cam, np.array([-50, -20, 0], np.float32), W, H, 0)
+
+
+def test_config5_full_size_against_the_oracle(cr, dragon_pod):
+    """BASELINE config 5 at its FULL size: the 10.5 M-triangle instanced-dragon scene (8 x 8 x 7 copies, one flat tree, boxes by
+    the device refit) at 7680 x 4320 with shadow rays; hit ids, counters and RGB against the oracle's render of the same
+    33 M pixels (~1 minute of host work)."""
+    import bench
+    pod, cam, sun, W, H, flags, scene = bench.load_workload("grid448_8k_shadow", device=0)
+    try:
+        assert len(pod["triangles"]) == 448 * len(dragon_pod["triangles"]) >= 10_000_000 and (W, H) == (7680, 4320)
+        px, ids, cnt = scene.render(cam, sun, W, H, flags=flags, want_ids=True)
+        o = port.render(pod, cam.as_array(), sun, W, H, flags)
+        assert int((ids != o["ids"]).sum()) == 0
+        assert cnt == (o["stats"]["rays"], o["stats"]["hits"])
+        assert float(np.abs(px - o["pixels"]).max()) <= RGB_ATOL
+        assert cnt[0] > 50_000_000
+    finally:
+        scene.close()
