@@ -50,7 +50,7 @@ SYMBOLS = [
     "ceres_peer_frame_invalidate",
 ]
 SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download",
-            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked"]
+            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -118,6 +118,8 @@ def lib():
     L.ceres_peer_frame_invalidate.argtypes = [vp]
     L.ceres_render_ppm8.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp]
     L.ceres_render_ppm16.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp]
+    L.ceres_render_ppm8_shard.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp]
+    L.ceres_render_ppm16_shard.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp]
     L.ceres_probe_read_bandwidth.argtypes = [C.c_int, sz, C.c_int, vp]
     L.ceres_build_lbvh.argtypes = [vp, sz, C.c_int, vp, vp, vp]
     L.ceres_scene_create_lbvh.argtypes = [vp, vp, sz, C.c_int, vp, vp]

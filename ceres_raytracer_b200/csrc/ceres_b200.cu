@@ -584,16 +584,17 @@ __global__ void __launch_bounds__(256) quantize_kernel(const float* __restrict__
 // Same quantisation restricted to frame rows [j0, j1) x columns [i0, i1) (the screen rectangle of the scene): the
 // host-frame P6 path copies only that rectangle and fills the rest with zeros on the host.
 template <int BPC>       // bytes per channel: 1 = static.cpp:135-147 (x 255), 2 = the x 65535 quantum scaling of anim.cpp:117-119, big-endian
-__global__ void __launch_bounds__(256) quantize_rect_kernel(const float* __restrict__ px, uint32_t W, uint32_t H, uint32_t i0, uint32_t i1,
-                                                            uint32_t j0, uint32_t j1, uint8_t* __restrict__ out) {
+__global__ void __launch_bounds__(256) quantize_rect_kernel(const float* __restrict__ px, const Frame f, uint32_t i0, uint32_t i1,
+                                                            uint32_t r0, uint32_t r1, uint8_t* __restrict__ out) {
+    // local rows [r0, r1) x columns [i0, i1) of the (possibly packed) float staging -> their place in the flipped full-size payload
     const uint32_t rw = i1 - i0;
-    const size_t n = (size_t)rw * (j1 - j0);
+    const size_t n = (size_t)rw * (r1 - r0);
     const float top = BPC == 1 ? 255.0f : 65535.0f;
     for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < n; k += (size_t)gridDim.x * 256u) {
         const uint32_t rj = (uint32_t)(k / rw), i = i0 + (uint32_t)(k - (size_t)rj * rw);
-        const uint32_t j = j0 + rj, row_out = H - 1u - j;
-        const float* p = px + 3 * ((size_t)j * W + i);
-        uint8_t* o = out + 3 * BPC * ((size_t)row_out * W + i);
+        const uint32_t lr = r0 + rj, j = frame_row(f, lr), row_out = f.H - 1u - j;
+        const float* p = px + 3 * ((size_t)(f.compact ? lr : j) * f.W + i);
+        uint8_t* o = out + 3 * BPC * ((size_t)row_out * f.W + i);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             float x = mul(p[c], top);
@@ -2155,7 +2156,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
 
     // ---- which path: tight band copies with in-kernel bands, and the CERES_FRAME_RETAINED contract on top of them -----------
     static const bool tight_off = std::getenv("CERES_NO_TIGHT_COPY") != nullptr;
-    const bool tight = !scatter && !tight_off && s->tune.variant != 1;
+    const bool tight = !tight_off && s->tune.variant != 1;
     uint32_t nb = 1, trpb = 0;                               // band layout of the tight path: nb launches of trpb rows
     if (tight && !empty) band_split(s, f, l0, l1, CERES_SUBFRAMES_HOST, nb, trpb);
     const ceres_scene::Retained old = s->kept;
@@ -2228,51 +2229,52 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     }
 
     // ---- GPU: concurrent row bands of the rectangle; each band is copied as soon as its own kernels are done ---------
-    const uint32_t rcols = i1 - i0;
-    // rows [a, b) that are contiguous in the caller's frame: one pitched DMA
-    auto copy_run = [&](uint32_t a, uint32_t b, cudaStream_t bs) -> int {
-        if (b <= a) return CERES_OK;
-        const size_t src = (size_t)a * width + i0, dst = out_row(a) * width + i0;
-        CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, (size_t)rcols * 12, b - a,
+    // local rows [a, b) x columns [x0, x1), rows contiguous in the caller's frame: one pitched DMA
+    auto copy_run = [&](uint32_t a, uint32_t b, uint32_t x0, uint32_t x1, cudaStream_t bs) -> int {
+        if (b <= a || x1 <= x0) return CERES_OK;
+        const size_t src = (size_t)a * width + x0, dst = out_row(a) * width + x0;
+        CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, (size_t)(x1 - x0) * 12, b - a,
                                    cudaMemcpyDeviceToHost, bs));
-        if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, (size_t)rcols * 4, b - a,
+        if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, (size_t)(x1 - x0) * 4, b - a,
                                             cudaMemcpyDeviceToHost, bs));
         return CERES_OK;
     };
-    auto copy_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
-        if (!scatter) return copy_run(r0, r1, bs);
+    // local rows [r0, r1) x columns [x0, x1) to their place in the caller's frame
+    auto copy_rect = [&](uint32_t r0, uint32_t r1, uint32_t x0, uint32_t x1, cudaStream_t bs) -> int {
+        if (!scatter) return copy_run(r0, r1, x0, x1, bs);
         // scattered shard: local block lb (block_rows packed rows) lands at frame block lb * count + index.  The whole
-        // blocks of the band go in ONE strided 3-D DMA (slice = one block; source slices are adjacent, destination
-        // slices are `count` blocks apart); a partial block at either end of the band is a 2-D copy.
+        // blocks of the range go in ONE strided 3-D DMA (slice = one block; source slices are adjacent, destination
+        // slices are `count` blocks apart); a partial block at either end of the range is a 2-D copy.
         const uint32_t br = f.block_rows;
         const uint32_t b0 = (r0 + br - 1) / br, b1 = r1 / br;              // whole local blocks [b0, b1)
-        if (b1 <= b0) {                                                   // the band lies inside one or two blocks
+        if (b1 <= b0) {                                                   // the range lies inside one or two blocks
             const uint32_t mid = std::min(r1, (r0 / br + 1) * br);
-            if (int rc = copy_run(r0, mid, bs)) return rc;
-            return copy_run(mid, r1, bs);
+            if (int rc = copy_run(r0, mid, x0, x1, bs)) return rc;
+            return copy_run(mid, r1, x0, x1, bs);
         }
-        if (int rc = copy_run(r0, b0 * br, bs)) return rc;
-        {
-            const size_t src = (size_t)b0 * br * width + i0, dst = out_row(b0 * br) * width + i0;
+        if (int rc = copy_run(r0, b0 * br, x0, x1, bs)) return rc;
+        if (x1 > x0) {
+            const size_t src = (size_t)b0 * br * width + x0, dst = out_row(b0 * br) * width + x0;
             cudaMemcpy3DParms p3 = {};
             p3.srcPtr = make_cudaPitchedPtr(s->d_pixels + 3 * src, width * 12, width * 12, br);
             p3.dstPtr = make_cudaPitchedPtr(pixels + 3 * dst, width * 12, width * 12, (size_t)br * f.shard_count);
-            p3.extent = make_cudaExtent((size_t)rcols * 12, br, b1 - b0);
+            p3.extent = make_cudaExtent((size_t)(x1 - x0) * 12, br, b1 - b0);
             p3.kind = cudaMemcpyDeviceToHost;
             CUDA_TRY(cudaMemcpy3DAsync(&p3, bs));
             if (ids) {
                 cudaMemcpy3DParms q3 = {};
                 q3.srcPtr = make_cudaPitchedPtr(s->d_ids + src, width * 4, width * 4, br);
                 q3.dstPtr = make_cudaPitchedPtr(ids + dst, width * 4, width * 4, (size_t)br * f.shard_count);
-                q3.extent = make_cudaExtent((size_t)rcols * 4, br, b1 - b0);
+                q3.extent = make_cudaExtent((size_t)(x1 - x0) * 4, br, b1 - b0);
                 q3.kind = cudaMemcpyDeviceToHost;
                 CUDA_TRY(cudaMemcpy3DAsync(&q3, bs));
             }
         }
-        return copy_run(b1 * br, r1, bs);
+        return copy_run(b1 * br, r1, x0, x1, bs);
     };
+    auto copy_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int { return copy_rect(r0, r1, i0, i1, bs); };
     s->rays_outside = prim_outside;
-    // Tight band copies (rows contiguous in the caller's frame only): the band's last shade CTA publishes the extents of
+    // Tight band copies: the band's last CTA publishes the extents of
     // its hit pixels into mapped host memory; this thread, which has nothing else to do once the frame is enqueued,
     // polls the flags band by band, copies only that sub-rectangle (everything else inside the conservative rectangle is
     // zero / CERES_MISS by construction) and hands the strips around it to the fill pool.  For the dragon the bands'
@@ -2333,11 +2335,8 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
             }
             if (kept_ok && !same_layout) zr1 = zr0;                      // already wiped above: nothing to reconcile per band
             if (any) {
-                const size_t src = (size_t)cr0 * width + ci0, dst = out_row(cr0) * width + ci0;
-                const size_t cols = ci1 - ci0 + 1, nrows = cr1 - cr0 + 1;
-                CUDA_TRY(cudaMemcpy2DAsync(pixels + 3 * dst, width * 12, s->d_pixels + 3 * src, width * 12, cols * 12, nrows, cudaMemcpyDeviceToHost, s->copy_stream));
-                if (ids) CUDA_TRY(cudaMemcpy2DAsync(ids + dst, width * 4, s->d_ids + src, width * 4, cols * 4, nrows, cudaMemcpyDeviceToHost, s->copy_stream));
-                copied += (uint64_t)cols * nrows * (ids ? 16u : 12u);
+                if (int rc = copy_rect(cr0, cr1 + 1u, ci0, ci1 + 1u, s->copy_stream)) return rc;
+                copied += (uint64_t)(ci1 - ci0 + 1u) * (cr1 - cr0 + 1u) * (ids ? 16u : 12u);
             }
             for (uint32_t r = zr0; r < zr1; ++r) {
                 if (!any || r < cr0 || r > cr1) strip(r, zi0, zi1);
@@ -2379,36 +2378,50 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
 // by the host pool.  rgb8: HOST 3*width*height bytes, row 0 = frame row height-1.
 }  // extern "C"
 
-// The host-frame path for an already quantised, vertically flipped P6 payload with BPC bytes per channel.
+// The host-frame path for an already quantised, vertically flipped P6 payload with BPC bytes per channel.  With a shard only
+// the shard's rows of the full-size payload are written (output row height-1-j for frame row j): the ranks of a box fill one
+// shared payload, each over its own PCIe link.
 template <int BPC>
 static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
-                            uint8_t* rgb8, uint64_t counters[2]) {
+                            const ceres_shard* shard, uint8_t* rgb8, uint64_t counters[2]) {
     if (!s || !rgb8) return fail(CERES_ERR_INVALID, "ceres_render_ppm8/16: null argument");
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
+    const bool sharded = shard && shard->count > 1;
     Frame f; uint32_t rows = 0;
     {
         float dummy;
-        if (int rc = prepare_frame(s, cam, sun, width, height, flags & ~CERES_COMPACT_ROWS, nullptr, &dummy, nullptr, nullptr, f, rows)) return rc;
+        const unsigned dev_flags = (flags & ~CERES_COMPACT_ROWS) | (sharded ? CERES_COMPACT_ROWS : 0u);      // packed float staging
+        if (int rc = prepare_frame(s, cam, sun, width, height, dev_flags, shard, &dummy, nullptr, nullptr, f, rows)) return rc;
     }
+    if (rows == 0) { if (counters) counters[0] = counters[1] = 0; return CERES_OK; }
     if (int rc = ensure(s->d_pixels, s->pixels_cap, npix * 3)) return rc;
     if (int rc = ensure(s->d_rgb8, s->rgb8_cap, npix * 3 * BPC)) return rc;
     f.pixels = s->d_pixels; f.ids = nullptr;
     const uint32_t l0 = std::min(f.cull_l0, rows), l1 = std::max(l0, std::min(f.cull_l1, rows));
     const uint32_t i0 = std::min<uint32_t>(f.cull_i0, (uint32_t)width), i1 = std::max(i0, std::min<uint32_t>(f.cull_i1, (uint32_t)width));
     const bool empty = l1 == l0 || i1 == i0;
-    // host fill of everything outside the rectangle (output rows are flipped: frame row j -> row height-1-j)
+    const size_t rowb = width * 3 * BPC;
+    auto out_row = [&](uint32_t lrow) -> size_t { return height - 1 - (size_t)frame_row_host(f, lrow); };
+    // host fill of everything outside the rectangle: local rows are ascending frame rows = DESCENDING output rows
     ceres_host::Job job;
     {
-        const size_t rowb = width * 3 * BPC;
-        if (empty) job.add(rgb8, rowb * height, 0x00);
+        auto fill_rows = [&](uint32_t a, uint32_t b) {       // local rows [a, b), full width; merge rows contiguous in the output
+            uint32_t r = a;
+            while (r < b) {
+                uint32_t e = r + 1;
+                while (e < b && out_row(e) + 1 == out_row(e - 1)) ++e;
+                job.add(rgb8 + rowb * out_row(e - 1), rowb * (e - r), 0x00);
+                r = e;
+            }
+        };
+        if (empty) fill_rows(0, rows);
         else {
-            const size_t top = height - l1, bottom = height - l0;           // output rows [top, bottom) hold the rectangle
-            if (top > 0) job.add(rgb8, rowb * top, 0x00);
-            if (bottom < height) job.add(rgb8 + rowb * bottom, rowb * (height - bottom), 0x00);
-            for (size_t r = top; r < bottom && (i0 > 0 || i1 < width); ++r) {
-                if (i0 > 0) job.add(rgb8 + rowb * r, (size_t)i0 * 3 * BPC, 0x00);
-                if (i1 < width) job.add(rgb8 + rowb * r + (size_t)i1 * 3 * BPC, (width - i1) * 3 * BPC, 0x00);
+            fill_rows(0, l0);
+            fill_rows(l1, rows);
+            for (uint32_t r = l0; r < l1 && (i0 > 0 || i1 < width); ++r) {
+                if (i0 > 0) job.add(rgb8 + rowb * out_row(r), (size_t)i0 * 3 * BPC, 0x00);
+                if (i1 < width) job.add(rgb8 + rowb * out_row(r) + (size_t)i1 * 3 * BPC, (width - i1) * 3 * BPC, 0x00);
             }
         }
     }
@@ -2422,14 +2435,38 @@ static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float
         return CERES_OK;
     }
     s->rays_outside = prim_outside;
-    const uint32_t W32 = (uint32_t)width, H32 = (uint32_t)height;
-    auto quantize_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
-        quantize_rect_kernel<BPC><<<(unsigned)(s->sm_count * 4), 256, 0, bs>>>(s->d_pixels, W32, H32, i0, i1, r0, r1, s->d_rgb8);
-        g_launches++;
-        const size_t out_row = height - r1;                                   // first output row of this band
-        const size_t off = (out_row * width + i0) * 3 * BPC;
-        CUDA_TRY(cudaMemcpy2DAsync(rgb8 + off, width * 3 * BPC, s->d_rgb8 + off, width * 3 * BPC, (size_t)(i1 - i0) * 3 * BPC, r1 - r0, cudaMemcpyDeviceToHost, bs));
+    // device payload and host payload have the same geometry: a run of local rows that is contiguous in the output is one 2-D copy
+    auto copy_rows = [&](uint32_t a, uint32_t b, cudaStream_t bs) -> int {      // local rows [a, b), contiguous in the output
+        if (b <= a) return CERES_OK;
+        const size_t off = (out_row(b - 1) * width + i0) * 3 * BPC;
+        CUDA_TRY(cudaMemcpy2DAsync(rgb8 + off, rowb, s->d_rgb8 + off, rowb, (size_t)(i1 - i0) * 3 * BPC, b - a, cudaMemcpyDeviceToHost, bs));
         return CERES_OK;
+    };
+    auto quantize_band = [&](uint32_t, uint32_t r0, uint32_t r1, cudaStream_t bs) -> int {
+        quantize_rect_kernel<BPC><<<(unsigned)(s->sm_count * 4), 256, 0, bs>>>(s->d_pixels, f, i0, i1, r0, r1, s->d_rgb8);
+        g_launches++;
+        CUDA_TRY(cudaGetLastError());
+        if (!sharded) return copy_rows(r0, r1, bs);
+        // scattered: the whole blocks of the band in ONE strided 3-D copy, enumerated from the LAST local block backwards
+        // (output rows grow as frame rows fall); partial blocks at the band's ends as 2-D copies
+        const uint32_t br = f.block_rows;
+        const uint32_t b0 = (r0 + br - 1) / br, b1 = r1 / br;
+        if (b1 <= b0) {
+            const uint32_t mid = std::min(r1, (r0 / br + 1) * br);
+            if (int rc = copy_rows(r0, mid, bs)) return rc;
+            return copy_rows(mid, r1, bs);
+        }
+        if (int rc = copy_rows(r0, b0 * br, bs)) return rc;
+        {
+            const size_t off = (out_row(b1 * br - 1) * width + i0) * 3 * BPC;        // first output row of the last whole block
+            cudaMemcpy3DParms p3 = {};
+            p3.srcPtr = make_cudaPitchedPtr(s->d_rgb8 + off, rowb, rowb, (size_t)br * f.shard_count);
+            p3.dstPtr = make_cudaPitchedPtr(rgb8 + off, rowb, rowb, (size_t)br * f.shard_count);
+            p3.extent = make_cudaExtent((size_t)(i1 - i0) * 3 * BPC, br, b1 - b0);
+            p3.kind = cudaMemcpyDeviceToHost;
+            CUDA_TRY(cudaMemcpy3DAsync(&p3, bs));
+        }
+        return copy_rows(b1 * br, r1, bs);
     };
     if (int rc = render_rows(s, f, l0, l1, s->stream, CERES_SUBFRAMES_HOST, CLEAR_NONE, quantize_band)) return rc;
     CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
@@ -2445,12 +2482,22 @@ extern "C" {
 
 int ceres_render_ppm8(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
                       uint8_t* rgb8, uint64_t counters[2]) {
-    return render_quantized<1>(s, cam, sun, width, height, flags, rgb8, counters);
+    return render_quantized<1>(s, cam, sun, width, height, flags, nullptr, rgb8, counters);
 }
 
 int ceres_render_ppm16(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
                        uint8_t* rgb16, uint64_t counters[2]) {
-    return render_quantized<2>(s, cam, sun, width, height, flags, rgb16, counters);
+    return render_quantized<2>(s, cam, sun, width, height, flags, nullptr, rgb16, counters);
+}
+
+int ceres_render_ppm8_shard(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
+                            const ceres_shard* shard, uint8_t* rgb8, uint64_t counters[2]) {
+    return render_quantized<1>(s, cam, sun, width, height, flags, shard, rgb8, counters);
+}
+
+int ceres_render_ppm16_shard(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
+                             const ceres_shard* shard, uint8_t* rgb16, uint64_t counters[2]) {
+    return render_quantized<2>(s, cam, sun, width, height, flags, shard, rgb16, counters);
 }
 
 int ceres_render(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,

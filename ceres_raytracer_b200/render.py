@@ -273,23 +273,28 @@ class Scene:
                                                C.byref(sh) if sh is not None else None, _p(pixels), _p(ids), _p(cnt)))
         return pixels, ids, (int(cnt[0]), int(cnt[1]))
 
-    def render_ppm8(self, camera, sun_position, width, height, flags=0, out=None):
-        """The frame as P6 payload bytes (static.cpp:135-147), quantised and flipped on the device: (uint8[H,W,3], (rays, hits))."""
+    def render_ppm8(self, camera, sun_position, width, height, flags=0, out=None, shard=None):
+        """The frame as P6 payload bytes (static.cpp:135-147), quantised and flipped on the device: (uint8[H,W,3], (rays, hits)).
+        shard = (block_rows, index, count): only that shard's rows of the full-size payload are written."""
         if out is None:
-            out = np.empty((height, width, 3), np.uint8)
+            out = np.empty((height, width, 3), np.uint8) if shard is None else np.zeros((height, width, 3), np.uint8)
         sun = np.asarray(sun_position, np.float32)
         cnt = np.zeros(2, np.uint64)
-        _capi.check(self._L.ceres_render_ppm8(self._h, C.byref(camera.c()), _p(sun), width, height, flags, _p(out), _p(cnt)))
+        sh = _shard(shard)
+        _capi.check(self._L.ceres_render_ppm8_shard(self._h, C.byref(camera.c()), _p(sun), width, height, flags,
+                                                    C.byref(sh) if sh is not None else None, _p(out), _p(cnt)))
         return out, (int(cnt[0]), int(cnt[1]))
 
-    def render_ppm16(self, camera, sun_position, width, height, flags=0, out=None):
+    def render_ppm16(self, camera, sun_position, width, height, flags=0, out=None, shard=None):
         """The frame as 16-bit P6 payload (maxval 65535, big-endian; the x 65535 scaling of anim.cpp:117-119), quantised and
         flipped on the device: (uint16 big-endian [H,W,3], (rays, hits))."""
         if out is None:
-            out = np.empty((height, width, 3), ">u2")
+            out = np.empty((height, width, 3), ">u2") if shard is None else np.zeros((height, width, 3), ">u2")
         sun = np.asarray(sun_position, np.float32)
         cnt = np.zeros(2, np.uint64)
-        _capi.check(self._L.ceres_render_ppm16(self._h, C.byref(camera.c()), _p(sun), width, height, flags, _p(out), _p(cnt)))
+        sh = _shard(shard)
+        _capi.check(self._L.ceres_render_ppm16_shard(self._h, C.byref(camera.c()), _p(sun), width, height, flags,
+                                                     C.byref(sh) if sh is not None else None, _p(out), _p(cnt)))
         return out, (int(cnt[0]), int(cnt[1]))
 
     def render_sequence(self, cams, width, height, flags=0, pixels_all=None):

@@ -170,10 +170,16 @@ class SharedHostFrame:
     def render(self, scene, camera, sun_position, width, height, flags=0, timeout_s=30.0):
         """Collective: every rank renders + copies its rows; returns the frame's (rays, hits) on every rank.
         Completion is a barrier in the shared control page (no NCCL/gloo call on the data path): a rank publishes its
-        counters, then its epoch, and waits until every rank's epoch has reached the frame's."""
+        counters, then its epoch, and waits until every rank's epoch has reached the frame's.  A uint8 / big-endian uint16 frame
+        receives the quantised, flipped P6 payload (ceres_render_ppm8_shard / ppm16_shard) instead of floats."""
         import time
         shard = (self.block_rows, self.rank, self.world) if self.world > 1 else None
-        _, _, cnt = scene.render(camera, sun_position, width, height, flags=flags, pixels=self.array, shard=shard)
+        if self.array.dtype == np.uint8:
+            _, cnt = scene.render_ppm8(camera, sun_position, width, height, flags=flags, out=self.array, shard=shard)
+        elif self.array.dtype.itemsize == 2:
+            _, cnt = scene.render_ppm16(camera, sun_position, width, height, flags=flags, out=self.array, shard=shard)
+        else:
+            _, _, cnt = scene.render(camera, sun_position, width, height, flags=flags, pixels=self.array, shard=shard)
         if self.world <= 1:
             return cnt
         self._epoch += 1

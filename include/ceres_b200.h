@@ -185,6 +185,15 @@ int ceres_render_ppm8(ceres_scene* scene, const ceres_camera* camera, const floa
 int ceres_render_ppm16(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                        size_t width, size_t height, unsigned flags, uint8_t* rgb16, uint64_t counters[2]);
 
+/* One shard of either payload: only the shard's rows of the FULL-SIZE payload are written (output row height-1-j for frame
+ * row j), so the ranks of a box fill one shared payload, each over its own PCIe link, with no gather (counters: the shard's).
+ * This is the path on which more GPUs shorten a frame end to end: the 8-bit 4K payload is 24.9 MB of host memory instead of
+ * the float frame's 99.5 MB, which no number of GPUs can write faster than the host's DRAM takes it. */
+int ceres_render_ppm8_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3], size_t width, size_t height,
+                            unsigned flags, const ceres_shard* shard, uint8_t* rgb8, uint64_t counters[2]);
+int ceres_render_ppm16_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3], size_t width, size_t height,
+                             unsigned flags, const ceres_shard* shard, uint8_t* rgb16, uint64_t counters[2]);
+
 /* Same, one shard of the frame.  Without CERES_COMPACT_ROWS only the shard's rows of pixels/ids are written. */
 int ceres_render_shard(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                        size_t width, size_t height, unsigned flags, const ceres_shard* shard,

@@ -622,3 +622,56 @@ def test_config5_full_size_against_the_oracle(cr, dragon_pod):
         assert cnt[0] > 50_000_000
     finally:
         scene.close()
+
+
+@pytest.mark.parametrize("count", [2, 3, 8])
+@pytest.mark.parametrize("W,H", [(1280, 720), (333, 217)])
+def test_sharded_payloads_fill_one_shared_frame(cr, dragon, count, W, H):
+    """ceres_render_ppm8_shard / ppm16_shard: every shard writes only its rows of the full-size flipped payload; the shards of
+    one frame together give exactly the unsharded payload, bytes outside a shard's rows are left alone."""
+    cam = cr.configs.DRAGON_CAMERA
+    want8, cnt = dragon.render_ppm8(cam, SUN, W, H)
+    want16, _ = dragon.render_ppm16(cam, SUN, W, H)
+    with cr.PinnedBuffer((H, W, 3), np.uint8) as h8:
+        h8.array[:] = 0xAB
+        got16 = np.full((H, W, 3), 0xABAB, ">u2")
+        rays = hits = 0
+        for k in range(count):
+            before = h8.array.copy()
+            _, (r, h) = dragon.render_ppm8(cam, SUN, W, H, out=h8.array, shard=(16, k, count))
+            rays += r; hits += h
+            rows = H - 1 - cr.shard_rows(H, (16, k, count))            # output rows of this shard
+            other = np.ones(H, bool); other[rows] = False
+            assert np.array_equal(h8.array[other], before[other])
+            dragon.render_ppm16(cam, SUN, W, H, out=got16, shard=(16, k, count))
+        assert np.array_equal(h8.array, want8) and (rays, hits) == cnt
+        assert np.array_equal(got16.view(np.uint8), want16.view(np.uint8))
+
+
+@pytest.mark.parametrize("count", [2, 8])
+def test_scattered_shards_tight_copies_and_retained_frames(cr, dragon, count):
+    """Scattered shards (every rank writes its row blocks in place into one host frame) use the tight band copies too, and the
+    CERES_FRAME_RETAINED contract holds per shard: a sequence of views into the same frame equals the unsharded frames."""
+    W, H = 1280, 720
+    cams = [cr.configs.DRAGON_CAMERA, cr.Camera((3.0, -15.0, 2.5), (-0.1, 1.0, 0.0), (0.0, 0.0, 1.0), 45.0),
+            cr.Camera((0.0, -15.0, 2.0), (0.0, -1.0, 0.0), (0.0, 0.0, 1.0), 60.0), cr.configs.DRAGON_CAMERA, cr.configs.DRAGON_CAMERA]
+    scenes = [dragon] + [cr.Scene.from_pod(scene_pod("dragon")) for _ in range(count - 1)]     # one scene per shard keeps its own state
+    hb = cr.PinnedBuffer((H, W, 3), np.float32)
+    hi = cr.PinnedBuffer((H, W), np.uint32)
+    try:
+        hb.array.fill(np.nan); hi.array.fill(7)
+        for k, cam in enumerate(cams):
+            want = dragon.render(cam, SUN, W, H, want_ids=True)
+            rays = hits = 0
+            for r in range(count):
+                _, _, (a, b) = scenes[r].render(cam, SUN, W, H, flags=cr.FRAME_RETAINED, pixels=hb.array, ids=hi.array, shard=(16, r, count))
+                rays += a; hits += b
+            assert np.array_equal(hb.array.view(np.uint32), want[0].view(np.uint32)), k
+            assert np.array_equal(hi.array, want[1]) and (rays, hits) == want[2], k
+            if k == 0:      # tight copies: fewer bytes than the conservative rectangles of the shards (pixels + ids)
+                conservative = sum((r[1] - r[0]) * (r[3] - r[2]) * 16 for r in (s.last_rectangle for s in scenes))
+                assert sum(s.last_d2h_bytes for s in scenes) < 0.85 * conservative
+    finally:
+        hb.close(); hi.close()
+        for s in scenes[1:]:
+            s.close()
