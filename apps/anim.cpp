@@ -11,7 +11,7 @@
 //     frame, no host-frame pipeline); the colours of render<double>() are float-valued, so the writers take them narrowed.
 //   * upstream encodes the frames with ImageMagick 7 Magick++ (anim.cpp:112-127) -- unavailable on this box.  Frames
 //     are written as <out_file stem>_NNNN.ppm instead (16-bit P6 with --ppm16, matching the x65535 quantum scaling of
-//     anim.cpp:117-119; 8-bit static.cpp-style by default), quantised and flipped on the GPU.
+//     anim.cpp:117-119; 8-bit static.cpp-style by default), quantised on the GPU, image row = frame row as in anim.cpp:117-119.
 //   * frames are independent once the camera path is known; the path is iterative (each frame transforms the previous
 //     camera, anim.cpp:87-89), so it is computed serially on the host first and the frames are then dealt round-robin
 //     to the GPUs (--gpus N), one host thread per GPU, scene replicated.
@@ -159,7 +159,7 @@ int scene(const Options& opt) {
         ceres_scene* scene = nullptr;
         if (ceres_scene_create(bvh.nodes.get(), bvh.node_count, bvh.primitive_indices.get(), triangles.data(),
                                tri_norms.data(), reference_count, g, &scene) != CERES_OK) { errors[g] = ceres_last_error(); return; }
-        // The frames leave the GPU as the file's payload: quantised and flipped on the device (ceres_render_ppm8 /
+        // The frames leave the GPU as the file's payload: quantised on the device (ceres_render_ppm8 /
         // ceres_render_ppm16), so a quarter / half of the float frame's bytes cross PCIe.  Two page-locked payload
         // buffers per GPU: frame k is written by a writer thread while frame k+1 renders (SURVEY.md 8(f) N1 + N4;
         // upstream encodes synchronously inside the frame loop, anim.cpp:112-127).
@@ -186,8 +186,9 @@ int scene(const Options& opt) {
             const float sun[3] = {(float)path[i].sun[0], (float)path[i].sun[1], (float)path[i].sun[2]};
             uint64_t cnt[2] = {0, 0};
             auto t0 = std::chrono::high_resolution_clock::now();
-            const int rc = ppm16 ? ceres_render_ppm16(scene, &cam, sun, width, height, 0u, bytes, cnt)
-                                 : ceres_render_ppm8(scene, &cam, sun, width, height, 0u, bytes, cnt);
+            // image row = frame row, as anim.cpp:117-119 fills its Magick image (static.cpp flips, anim.cpp does not)
+            const int rc = ppm16 ? ceres_render_ppm16(scene, &cam, sun, width, height, CERES_PAYLOAD_NO_FLIP, bytes, cnt)
+                                 : ceres_render_ppm8(scene, &cam, sun, width, height, CERES_PAYLOAD_NO_FLIP, bytes, cnt);
             if (rc != CERES_OK) { errors[g] = ceres_last_error(); break; }
             const double s = seconds_since(t0);
             std::ostringstream os;
@@ -244,7 +245,7 @@ int scene(const Options& opt) {
                 for (size_t k = 0; k < frame.size(); ++k) pixels[k] = (float)frame[k];
                 const std::string name = frame_name(out_file, i);
                 writing[turn] = std::async(std::launch::async, [=]() -> std::string {
-                    const bool ok = ppm16 ? ceres_apps::write_ppm16(name, pixels, width, height) : ceres_apps::write_ppm(name, pixels, width, height);
+                    const bool ok = ppm16 ? ceres_apps::write_ppm16(name, pixels, width, height, false) : ceres_apps::write_ppm(name, pixels, width, height, false);
                     return ok ? std::string() : "cannot write " + name;
                 });
             }

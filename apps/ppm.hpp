@@ -21,11 +21,12 @@ inline uint8_t to_u8(float p) {
     return x == x ? static_cast<uint8_t>(x) : 0;
 }
 
-inline bool write_ppm(const std::string& path, const float* pixels, size_t width, size_t height) {
+// flip = true: static.cpp:135-147 (rows from j = height-1 down); false: anim.cpp:117-119 (image row = frame row)
+inline bool write_ppm(const std::string& path, const float* pixels, size_t width, size_t height, bool flip = true) {
     std::vector<uint8_t> bytes(3 * width * height);
     #pragma omp parallel for
     for (size_t row = 0; row < height; ++row) {
-        const float* src = pixels + 3 * width * (height - 1 - row);
+        const float* src = pixels + 3 * width * (flip ? height - 1 - row : row);
         uint8_t* dst = bytes.data() + 3 * width * row;
         for (size_t k = 0; k < 3 * width; ++k) dst[k] = to_u8(src[k]);
     }
@@ -47,11 +48,11 @@ inline bool write_ppm_bytes(const std::string& path, const uint8_t* bytes, size_
     return std::fclose(f) == 0 && ok;
 }
 
-inline bool write_ppm16(const std::string& path, const float* pixels, size_t width, size_t height) {
+inline bool write_ppm16(const std::string& path, const float* pixels, size_t width, size_t height, bool flip = true) {
     std::vector<uint8_t> bytes(6 * width * height);
     #pragma omp parallel for
     for (size_t row = 0; row < height; ++row) {
-        const float* src = pixels + 3 * width * (height - 1 - row);
+        const float* src = pixels + 3 * width * (flip ? height - 1 - row : row);
         uint8_t* dst = bytes.data() + 6 * width * row;
         for (size_t k = 0; k < 3 * width; ++k) {
             float x = src[k] * 65535.0f;

@@ -8,7 +8,7 @@ from . import build as _build
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = 0, 1, 2, 3, 4
-NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED = 1, 2, 4
+NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, PAYLOAD_NO_FLIP = 1, 2, 4, 8
 MISS = 0xFFFFFFFF
 
 

@@ -102,6 +102,7 @@ struct Frame {
     uint32_t accumulate;       // add this launch's counters to out_counters instead of overwriting them
     uint32_t block_rows, shard_index, shard_count;
     uint32_t compact;          // outputs packed by local row
+    uint32_t no_flip;          // quantised payloads: output row = frame row (anim.cpp:117-119) instead of height-1-row (static.cpp:135-147)
     uint32_t shadows;
     // persistent primary wave: conservative screen rectangle of the scene, in local rows / columns of this launch,
     // cut into 8x4-pixel tiles (work item = tile * 32 + pixel in tile)
@@ -592,7 +593,7 @@ __global__ void __launch_bounds__(256) quantize_rect_kernel(const float* __restr
     const float top = BPC == 1 ? 255.0f : 65535.0f;
     for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < n; k += (size_t)gridDim.x * 256u) {
         const uint32_t rj = (uint32_t)(k / rw), i = i0 + (uint32_t)(k - (size_t)rj * rw);
-        const uint32_t lr = r0 + rj, j = frame_row(f, lr), row_out = f.H - 1u - j;
+        const uint32_t lr = r0 + rj, j = frame_row(f, lr), row_out = f.no_flip ? j : f.H - 1u - j;
         const float* p = px + 3 * ((size_t)(f.compact ? lr : j) * f.W + i);
         uint8_t* o = out + 3 * BPC * ((size_t)row_out * f.W + i);
 #pragma unroll
@@ -2214,6 +2215,17 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
     pool.submit(&job);
     const double t_submit = trace_timing ? now_us() : 0.0;
     struct Waiter { ceres_host::Pool& p; ceres_host::Job* j; ~Waiter() { p.wait(j); } } waiter{pool, &job};   // also on error paths
+    // ... and no return -- error paths included -- leaves kernels or DMA copies in flight that still write the caller's buffers
+    struct Drain {
+        ceres_scene* s; bool armed = true;
+        ~Drain() {
+            if (!armed) return;
+            cudaStreamSynchronize(s->copy_stream);
+            for (int k = 0; k < CERES_MAX_SUB; ++k) cudaStreamSynchronize(s->sub_stream[k]);
+            cudaStreamSynchronize(s->stream);
+            cudaGetLastError();
+        }
+    } drain{s};
 
     const uint64_t prim_outside = (uint64_t)width * (rows - (empty ? 0 : l1 - l0));
     s->last_d2h_bytes = empty ? 0 : (uint64_t)(l1 - l0) * (i1 - i0) * (ids ? 16u : 12u) + 2 * sizeof(unsigned long long);
@@ -2363,6 +2375,7 @@ int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[
         std::fprintf(stderr, "ceres_render timing [us]: segments %zu bands %zu | job built+submitted %.0f, launches issued %.0f, fill done %.0f, "
                      "kernels done %.0f, copies done %.0f\n", job.segs.size(), bands.size(), t_submit - t_begin, t_launched - t_begin,
                      t_filled - t_begin, t_kernels - t_begin, now_us() - t_begin);
+    drain.armed = false;       // everything was synchronised above
     if (int rc = frame_error_check(s)) return rc;
     if (counters) { counters[0] = s->h_out[0] + prim_outside; counters[1] = s->h_out[1]; }
     if (retained_req) {       // the bands' rectangles were noted above
@@ -2402,16 +2415,20 @@ static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float
     const uint32_t i0 = std::min<uint32_t>(f.cull_i0, (uint32_t)width), i1 = std::max(i0, std::min<uint32_t>(f.cull_i1, (uint32_t)width));
     const bool empty = l1 == l0 || i1 == i0;
     const size_t rowb = width * 3 * BPC;
-    auto out_row = [&](uint32_t lrow) -> size_t { return height - 1 - (size_t)frame_row_host(f, lrow); };
-    // host fill of everything outside the rectangle: local rows are ascending frame rows = DESCENDING output rows
+    const bool flip = (flags & CERES_PAYLOAD_NO_FLIP) == 0;
+    f.no_flip = flip ? 0u : 1u;
+    auto out_row = [&](uint32_t lrow) -> size_t { const size_t j = frame_row_host(f, lrow); return flip ? height - 1 - j : j; };
+    // the first (lowest) output row of local rows [a, b), which are contiguous in the output
+    auto low_row = [&](uint32_t a, uint32_t b) -> size_t { return flip ? out_row(b - 1) : out_row(a); };
+    // host fill of everything outside the rectangle: local rows are ascending frame rows = DESCENDING output rows when flipped
     ceres_host::Job job;
     {
         auto fill_rows = [&](uint32_t a, uint32_t b) {       // local rows [a, b), full width; merge rows contiguous in the output
             uint32_t r = a;
             while (r < b) {
                 uint32_t e = r + 1;
-                while (e < b && out_row(e) + 1 == out_row(e - 1)) ++e;
-                job.add(rgb8 + rowb * out_row(e - 1), rowb * (e - r), 0x00);
+                while (e < b && (flip ? out_row(e) + 1 == out_row(e - 1) : out_row(e) == out_row(e - 1) + 1)) ++e;
+                job.add(rgb8 + rowb * low_row(r, e), rowb * (e - r), 0x00);
                 r = e;
             }
         };
@@ -2438,7 +2455,7 @@ static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float
     // device payload and host payload have the same geometry: a run of local rows that is contiguous in the output is one 2-D copy
     auto copy_rows = [&](uint32_t a, uint32_t b, cudaStream_t bs) -> int {      // local rows [a, b), contiguous in the output
         if (b <= a) return CERES_OK;
-        const size_t off = (out_row(b - 1) * width + i0) * 3 * BPC;
+        const size_t off = (low_row(a, b) * width + i0) * 3 * BPC;
         CUDA_TRY(cudaMemcpy2DAsync(rgb8 + off, rowb, s->d_rgb8 + off, rowb, (size_t)(i1 - i0) * 3 * BPC, b - a, cudaMemcpyDeviceToHost, bs));
         return CERES_OK;
     };
@@ -2458,7 +2475,8 @@ static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float
         }
         if (int rc = copy_rows(r0, b0 * br, bs)) return rc;
         {
-            const size_t off = (out_row(b1 * br - 1) * width + i0) * 3 * BPC;        // first output row of the last whole block
+            // flipped: the LAST whole block has the lowest output rows; unflipped: the first one
+            const size_t off = ((flip ? out_row(b1 * br - 1) : out_row(b0 * br)) * width + i0) * 3 * BPC;
             cudaMemcpy3DParms p3 = {};
             p3.srcPtr = make_cudaPitchedPtr(s->d_rgb8 + off, rowb, rowb, (size_t)br * f.shard_count);
             p3.dstPtr = make_cudaPitchedPtr(rgb8 + off, rowb, rowb, (size_t)br * f.shard_count);

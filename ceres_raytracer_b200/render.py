@@ -14,7 +14,7 @@ from typing import Sequence
 import numpy as np
 
 from . import _capi
-from ._capi import NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, MISS, CeresError  # noqa: F401
+from ._capi import NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, PAYLOAD_NO_FLIP, MISS, CeresError  # noqa: F401
 
 NODE_DT = np.dtype([("bounds", "<f4", (6,)), ("primitive_count", "<u4"), ("first_child_or_primitive", "<u4")])
 NODE64_DT = np.dtype([("bounds", "<f8", (6,)), ("primitive_count", "<u8"), ("first_child_or_primitive", "<u8")])   # Bvh<double>::Node

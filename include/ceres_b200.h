@@ -53,6 +53,8 @@ enum {
                                    every call (render.hpp:107,117 overwrite every pixel; the result is the same frame).  The
                                    first call with the flag, a different buffer / size / shard, or a call without the flag in
                                    between re-establishes the whole frame.  Ignored by the paths that do not use it. */
+#define CERES_PAYLOAD_NO_FLIP 8u /* ceres_render_ppm8 / ppm16 (+ _shard): output row = frame row, as anim.cpp:117-119 copies pixels[j] into its
+                                   image rows in order; default: rows flipped, row 0 = frame row height-1, as static.cpp:135-147 writes them */
 #define CERES_COMPACT_ROWS 2u  /* sharded render: write the shard's rows packed, not at their frame position */
 
 #define CERES_MISS 0xFFFFFFFFu /* value of ids[] where the primary ray hit nothing */
@@ -216,7 +218,10 @@ int ceres_render_sequence(ceres_scene* scene, size_t n_frames, const float* cams
 
 /* Enqueues the frame on `stream` (a cudaStream_t; NULL = the scene's own stream, cudaStreamLegacy (0x1) = the
  * legacy default stream) and returns.  d_pixels / d_ids /
- * d_counters are DEVICE pointers on the scene's device (d_ids, d_counters nullable; d_counters = 2 x uint64). */
+ * d_counters are DEVICE pointers on the scene's device (d_ids, d_counters nullable; d_counters = 2 x uint64).
+ * The frames of one scene share its record queue and counters: a frame enqueued on another stream than the scene's previous
+ * frame is made to wait for that frame's end (an event recorded after every frame), so frames of one scene never overlap --
+ * use one scene per stream (ceres_render_sequence does, over the same resident geometry) to overlap frames. */
 int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
                         size_t width, size_t height, unsigned flags, const ceres_shard* shard, void* stream,
                         float* d_pixels, uint32_t* d_ids, uint64_t* d_counters);

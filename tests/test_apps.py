@@ -157,7 +157,7 @@ def test_anim_binary_matches_reference_turntable(tmp_path):
         assert f"Rays: {rays}\tHits: {hits}" in r.stdout
         total += rays
         img = read_ppm(str(tmp_path / f"turn_{k:04d}.ppm"))
-        d = img.astype(np.int16) - quantise(px).astype(np.int16)
+        d = img.astype(np.int16) - quantise(px)[::-1].astype(np.int16)       # anim frames are NOT flipped (anim.cpp:117-119)
         assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-5
         assert (img != 0).any()
     assert f"Total Rays: {total}" in r.stdout
@@ -173,7 +173,7 @@ def test_anim_binary_matches_reference_turntable(tmp_path):
         px, rays, hits, _ = s.render(cams2[k, :10], cams2[k, 10:13], W, H)
         x = px.astype(np.float32) * np.float32(65535)
         x = np.where(np.float32(65535) < x, np.float32(65535), x)
-        want = np.where(x < 0, np.float32(0), x).astype(np.uint16)[::-1]
+        want = np.where(x < 0, np.float32(0), x).astype(np.uint16)
         img = read_ppm(str(tmp_path / f"turn16_{k:04d}.ppm")).astype(np.int32)
         d = img - want.astype(np.int32)
         assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-4 and img.max() > 255
@@ -192,7 +192,7 @@ def test_anim_binary_matches_reference_turntable(tmp_path):
         px, (rays, hits), _ = s.render(cams[k, :10], cams[k, 10:13], W, H)
         assert f"Rays: {rays}\tHits: {hits}" in r.stdout
         img = read_ppm(str(tmp_path / f"turnd_{k:04d}.ppm"))
-        d = img.astype(np.int16) - quantise(px.astype(np.float32)).astype(np.int16)
+        d = img.astype(np.int16) - quantise(px.astype(np.float32))[::-1].astype(np.int16)      # unflipped, as anim.cpp:117-119
         assert np.abs(d).max() <= 1 and (d != 0).mean() <= 1e-5
         assert (img != 0).any()
     s.close()

@@ -397,6 +397,13 @@ def test_ppm16_host_path_equals_quantised_float_frame(cr, dragon, W, H):
     got, cnt16 = dragon.render_ppm16(cam, SUN, W, H)
     assert cnt16 == cnt and np.array_equal(got.view(np.uint8), want.view(np.uint8))
     assert (got != 0).any() and dragon.last_d2h_bytes < got.nbytes
+    # CERES_PAYLOAD_NO_FLIP: image row = frame row, as anim.cpp:117-119 fills its frames
+    got_nf, _ = dragon.render_ppm16(cam, SUN, W, H, flags=cr.PAYLOAD_NO_FLIP)
+    assert np.array_equal(got_nf.view(np.uint8), want[::-1].view(np.uint8))
+    got8_nf, _ = dragon.render_ppm8(cam, SUN, W, H, flags=cr.PAYLOAD_NO_FLIP, shard=(16, 1, 3))
+    full8, _ = dragon.render_ppm8(cam, SUN, W, H)
+    rows = cr.shard_rows(H, (16, 1, 3))
+    assert np.array_equal(got8_nf[rows], full8[::-1][rows]) and not got8_nf[np.setdiff1d(np.arange(H), rows)].any()
     # and the 8-bit path still agrees with its own definition after sharing the kernel
     got8, _ = dragon.render_ppm8(cam, SUN, W, H)
     assert np.array_equal(got8, cr.write_ppm(os.devnull, px))
