@@ -979,6 +979,8 @@ void ceres_scene_destroy(ceres_scene* s) {
 }
 
 size_t ceres_scene_device_bytes(const ceres_scene* s) { return s ? s->scene_bytes : 0; }
+uint32_t ceres_scene_stack_depth(const ceres_scene* s) { return s ? s->dev.stack_depth : 0u; }
+size_t ceres_scene_node_count(const ceres_scene* s) { return s ? s->node_count : 0; }
 uint64_t ceres_scene_last_d2h_bytes(const ceres_scene* s) { return s ? s->last_d2h_bytes : 0; }
 
 // ---- scene preparation on the device (scene_prep.cuh) ---------------------------------------------
@@ -1079,14 +1081,25 @@ int ceres_scene_download(ceres_scene* s, void* nodes_out, size_t node_count, voi
 // ---- BVH construction on the GPU (lbvh_build.cuh) -----------------------------------------------------
 namespace {
 // Working set of one GPU build (lbvh_build.cuh); everything stays on the device until the caller picks what it needs.
+int g_build_algorithm = 0, g_build_radius = 8;      // ceres_build_options: 0 = PLOC over the Morton order (default), 1 = radix tree only
+int g_build_max_leaf = 8; float g_build_ci = 1.5f;   // leaf collapsing: triangles per leaf at most (1 = off), cost of a triangle test in node steps
 struct LbvhWork {
     float* box = nullptr; unsigned int* scene = nullptr;
+    uint32_t* cid[2] = {nullptr, nullptr}; float* cbox[2] = {nullptr, nullptr}; uint32_t* nn = nullptr;       // PLOC
+    unsigned long long *flag = nullptr, *scan = nullptr; PlocState* st = nullptr; void* scan_tmp = nullptr; size_t scan_tmp_bytes = 0;
+    int rounds = 0;
+    uint32_t *c_cnt = nullptr, *c_col = nullptr, *c_rank = nullptr, *c_arr = nullptr, *idx3 = nullptr; float* c_cost = nullptr;   // leaf collapsing
+    uint32_t *c_keep = nullptr, *c_newid = nullptr, *c_fl = nullptr; LbvhNode* nodes2 = nullptr;
+    size_t node_count = 0;                                   // nodes of the final tree (2 leaves - 1)
     uint32_t *code = nullptr, *idx = nullptr, *code2 = nullptr, *idx2 = nullptr, *child = nullptr, *pi = nullptr, *pl = nullptr, *arr = nullptr;
     LbvhNode* nodes = nullptr; void* tmp = nullptr; size_t tmp_bytes = 0;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     ~LbvhWork() {
         cudaFree(box); cudaFree(scene); cudaFree(code); cudaFree(idx); cudaFree(code2); cudaFree(idx2);
         cudaFree(child); cudaFree(pi); cudaFree(pl); cudaFree(arr); cudaFree(nodes); cudaFree(tmp);
+        cudaFree(c_cnt); cudaFree(c_col); cudaFree(c_rank); cudaFree(c_arr); cudaFree(idx3); cudaFree(c_cost); cudaFree(c_keep); cudaFree(c_newid); cudaFree(c_fl);
+        cudaFree(nodes2);
+        cudaFree(cid[0]); cudaFree(cid[1]); cudaFree(cbox[0]); cudaFree(cbox[1]); cudaFree(nn); cudaFree(flag); cudaFree(scan); cudaFree(st); cudaFree(scan_tmp);
         if (e0) cudaEventDestroy(e0);
         if (e1) cudaEventDestroy(e1);
     }
@@ -1105,6 +1118,23 @@ int lbvh_run(const float4* d_tris, int n, LbvhWork& w, float* ms_out) {
     TRY_B(cudaMalloc((void**)&w.nodes, (2 * tc - 1) * sizeof(LbvhNode)));
     TRY_B(cub::DeviceRadixSort::SortPairs(nullptr, w.tmp_bytes, w.code, w.code2, w.idx, w.idx2, n, 0, 30));
     TRY_B(cudaMalloc(&w.tmp, w.tmp_bytes ? w.tmp_bytes : 16));
+    const bool ploc = g_build_algorithm == 0 && n > 2;
+    if (ploc) {
+        for (int k = 0; k < 2; ++k) { TRY_B(cudaMalloc((void**)&w.cid[k], tc * 4)); TRY_B(cudaMalloc((void**)&w.cbox[k], tc * 24)); }
+        TRY_B(cudaMalloc((void**)&w.nn, tc * 4));
+        TRY_B(cudaMalloc((void**)&w.flag, tc * 8)); TRY_B(cudaMalloc((void**)&w.scan, tc * 8));
+        TRY_B(cudaMalloc((void**)&w.st, sizeof(PlocState)));
+        TRY_B(cub::DeviceScan::ExclusiveSum(nullptr, w.scan_tmp_bytes, w.flag, w.scan, n));
+        TRY_B(cudaMalloc(&w.scan_tmp, w.scan_tmp_bytes ? w.scan_tmp_bytes : 16));
+    }
+    const bool collapse = n > 2;        // max_leaf 1: nothing collapses, the pass still puts leaves and inner nodes in depth-first order
+    if (collapse) {
+        TRY_B(cudaMalloc((void**)&w.c_cnt, tc * 4)); TRY_B(cudaMalloc((void**)&w.c_col, tc * 4)); TRY_B(cudaMalloc((void**)&w.c_rank, tc * 4));
+        TRY_B(cudaMalloc((void**)&w.c_arr, tc * 4)); TRY_B(cudaMalloc((void**)&w.idx3, tc * 4)); TRY_B(cudaMalloc((void**)&w.c_cost, tc * 4));
+        TRY_B(cudaMalloc((void**)&w.c_keep, tc * 4)); TRY_B(cudaMalloc((void**)&w.c_newid, tc * 4)); TRY_B(cudaMalloc((void**)&w.c_fl, tc * 4));
+        TRY_B(cudaMalloc((void**)&w.nodes2, (2 * tc - 1) * sizeof(LbvhNode)));
+    }
+    w.node_count = 2 * tc - 1;
     TRY_B(cudaEventCreate(&w.e0)); TRY_B(cudaEventCreate(&w.e1));
     const unsigned int scene_init[6] = {0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u};
     TRY_B(cudaMemcpy(w.scene, scene_init, sizeof scene_init, cudaMemcpyHostToDevice));
@@ -1116,10 +1146,47 @@ int lbvh_run(const float4* d_tris, int n, LbvhWork& w, float* ms_out) {
     g_launches += 2;
     if (n > 1) {
         TRY_B(cudaMemsetAsync(w.arr, 0, tc * 4, 0));
+        if (ploc) {
+            // locally-ordered clustering over the Morton order (lbvh_build.cuh): rounds until one cluster is left
+            const PlocState init{(uint32_t)n, (uint32_t)(n - 1), 0u, 0u};
+            TRY_B(cudaMemcpyAsync(w.st, &init, sizeof init, cudaMemcpyHostToDevice, 0));
+            ploc_init_kernel<<<grid, 256>>>(w.idx2, w.box, (uint32_t)n, w.cid[0], w.cbox[0]);
+            g_launches++;
+            uint32_t m = (uint32_t)n;
+            int cur = 0;
+            while (m > 1) {
+                const unsigned g = (m + 255u) / 256u;
+                ploc_nn_kernel<<<g, 256>>>(w.cbox[cur], w.st, g_build_radius, w.nn);
+                ploc_flag_kernel<<<g, 256>>>(w.nn, w.st, w.flag);
+                TRY_B(cub::DeviceScan::ExclusiveSum(w.scan_tmp, w.scan_tmp_bytes, w.flag, w.scan, (int)m));
+                ploc_totals_kernel<<<1, 1>>>(w.flag, w.scan, w.st);
+                ploc_merge_kernel<<<g, 256>>>(w.cid[cur], w.cbox[cur], w.nn, w.flag, w.scan, w.st, w.cid[cur ^ 1], w.cbox[cur ^ 1], w.child, w.pi, w.pl);
+                ploc_advance_kernel<<<1, 1>>>(w.st);
+                g_launches += 5;
+                PlocState now;
+                TRY_B(cudaMemcpy(&now, w.st, sizeof now, cudaMemcpyDeviceToHost));
+                if (now.m >= m || now.m == 0) return fail(CERES_ERR_CUDA, "ceres_build_lbvh: clustering made no progress (internal error)");
+                m = now.m; cur ^= 1; ++w.rounds;
+            }
+        } else
         lbvh_tree_kernel<<<grid, 256>>>(w.code2, n, w.child, w.pi, w.pl);
         lbvh_emit_kernel<<<grid, 256>>>(w.child, w.idx2, w.box, n, w.nodes);
         lbvh_fit_kernel<<<grid, 256>>>(w.pi, w.pl, w.arr, n, w.nodes);
         g_launches += 3;
+        if (collapse) {
+            // SAH leaf collapsing + depth-first leaf order + compaction of the surviving inner nodes (lbvh_build.cuh)
+            const CollapseParams q{1.0f, g_build_ci, (uint32_t)g_build_max_leaf};
+            TRY_B(cudaMemsetAsync(w.c_arr, 0, tc * 4, 0));
+            TRY_B(cudaMemsetAsync(w.nodes2, 0, (2 * tc - 1) * sizeof(LbvhNode), 0));
+            bvhc_cost_kernel<<<grid, 256>>>(w.child, w.pi, w.pl, w.nodes, n, q, w.c_arr, w.c_cnt, w.c_cost, w.c_col, w.c_fl);
+            bvhc_rank_kernel<<<(unsigned)((2 * tc - 1 + 255) / 256), 256>>>(w.child, w.pi, w.pl, w.c_cnt, w.c_col, w.c_fl, w.idx2, n, w.idx3, w.c_rank, w.c_keep, w.c_newid);
+            bvhc_emit_kernel<<<grid, 256>>>(w.child, w.c_cnt, w.c_col, w.c_rank, w.c_keep, w.c_newid, w.nodes, n, w.nodes2);
+            g_launches += 3;
+            uint32_t leaves = 0;                                  // leaves of the final tree = fl[root]
+            TRY_B(cudaMemcpy(&leaves, w.c_fl, 4, cudaMemcpyDeviceToHost));
+            w.node_count = 2 * (size_t)leaves - 1;
+            std::swap(w.nodes, w.nodes2); std::swap(w.idx2, w.idx3);
+        }
     }
     TRY_B(cudaEventRecord(w.e1, 0));
     TRY_B(cudaGetLastError());
@@ -1142,7 +1209,21 @@ int lbvh_check_args(const void* tris, size_t tri_count, int device, const char* 
 }
 }  // namespace
 
+int ceres_build_options(int algorithm, int radius, int max_leaf, float triangle_cost) {
+    if (algorithm < 0 || algorithm > 1 || radius < 0 || radius > 256 || max_leaf < 0 || max_leaf > 16 || !(triangle_cost >= 0.0f))
+        return fail(CERES_ERR_INVALID, "ceres_build_options: algorithm 0 (clustering) or 1 (radix tree), radius 1..256, max_leaf 1..16, triangle_cost > 0 (0 = defaults)");
+    g_build_algorithm = algorithm;
+    g_build_radius = radius ? radius : 8;
+    g_build_max_leaf = max_leaf ? max_leaf : 8;
+    g_build_ci = triangle_cost > 0.0f ? triangle_cost : 1.5f;
+    return CERES_OK;
+}
+
 int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms) {
+    return ceres_build_bvh(tris, tri_count, device, nodes_out, nullptr, prim_idx_out, build_ms);
+}
+
+int ceres_build_bvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* node_count_out, size_t* prim_idx_out, double* build_ms) {
     if (!nodes_out || !prim_idx_out) return fail(CERES_ERR_INVALID, "ceres_build_lbvh: null or empty argument");
     if (int rc = lbvh_check_args(tris, tri_count, device, "ceres_build_lbvh")) return rc;
     DeviceGuard guard(device);
@@ -1161,7 +1242,9 @@ int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes
         std::memcpy(nodes_out, &root, sizeof root);
         prim_idx_out[0] = 0;
         ms = 0.0f;
+        if (node_count_out) *node_count_out = 1;
     } else if (!rc) {
+        if (node_count_out) *node_count_out = w.node_count;
         std::vector<uint32_t> idx(tri_count);
         if (cudaMemcpy(nodes_out, w.nodes, (2 * tri_count - 1) * sizeof(LbvhNode), cudaMemcpyDeviceToHost) != cudaSuccess ||
             cudaMemcpy(idx.data(), w.idx2, tri_count * 4, cudaMemcpyDeviceToHost) != cudaSuccess)
@@ -1240,17 +1323,19 @@ int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_coun
         TRY_S(cudaMemcpy(d_norms9, norms, tri_count * 36, cudaMemcpyHostToDevice));
     }
     float ms = 0.0f;
+    size_t n_pairs = tri_count - 1;
     {
         LbvhWork w;
         if (int rc = lbvh_run(d_src, n, w, &ms)) return bail(rc);
-        const size_t pb = (tri_count - 1) * 64, tb = tri_count * 48, ib = tri_count * 4;
+        n_pairs = (w.node_count - 1) / 2;                    // leaf collapsing leaves fewer nodes than 2 n - 1
+        const size_t pb = n_pairs * 64, tb = tri_count * 48, ib = tri_count * 4;
         TRY_S(cudaMalloc(&s->d_pairs, pb));
         TRY_S(cudaMalloc(&s->d_tris, tb));
         TRY_S(cudaMalloc(&s->d_norms, tb));
         TRY_S(cudaMalloc((void**)&d_depth, sizeof(unsigned int)));
         TRY_S(cudaMemset(d_depth, 0, sizeof(unsigned int)));
         const unsigned grid = (unsigned)((tri_count + 255) / 256);
-        lbvh_pairs_kernel<<<grid, 256>>>(w.nodes, n, (float4*)s->d_pairs);
+        lbvh_pairs_kernel<<<(unsigned)((n_pairs + 255) / 256), 256>>>(w.nodes, (int)n_pairs + 1, (float4*)s->d_pairs);
         lbvh_slots_kernel<<<grid, 256>>>(d_src, d_norms9, w.idx2, (uint32_t)n, (float4*)s->d_tris, (float4*)s->d_norms);
         lbvh_depth_kernel<<<grid, 256>>>(w.pi, w.pl, n, d_depth);
         g_launches += 3;
@@ -1273,11 +1358,11 @@ int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_coun
     s->dev.norms = (const float4*)s->d_norms;
     s->dev.slot_id = (const uint32_t*)s->d_slot_id;
     s->dev.root_leaf_count = 0;
-    s->dev.n_pairs = (uint32_t)(tri_count - 1); s->dev.n_slots = (uint32_t)tri_count;
-    s->node_count = 2 * tri_count - 1;
-    s->n_pairs = (uint32_t)(tri_count - 1);
-    s->h_pair_first_child.resize(tri_count - 1);
-    for (size_t i = 0; i + 1 < tri_count; ++i) s->h_pair_first_child[i] = (uint32_t)(1 + 2 * i);
+    s->dev.n_pairs = (uint32_t)n_pairs; s->dev.n_slots = (uint32_t)tri_count;
+    s->node_count = 2 * n_pairs + 1;
+    s->n_pairs = (uint32_t)n_pairs;
+    s->h_pair_first_child.resize(n_pairs);
+    for (size_t i = 0; i < n_pairs; ++i) s->h_pair_first_child[i] = (uint32_t)(1 + 2 * i);
     if (build_ms) *build_ms = ms;
     *out = s;
     return CERES_OK;

@@ -21,6 +21,7 @@
 // One triangle per leaf; boxes are exact unions (std::min/std::max semantics), so HierarchyRefitter::refit reproduces
 // them bit for bit -- that is the structural test.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #define LBVH_LEAF 0x80000000u
 
@@ -150,5 +151,199 @@ __global__ void __launch_bounds__(256) lbvh_fit_kernel(const uint32_t* __restric
         if (p == 0u) return;
         __threadfence();
         p = up >> 1;
+    }
+}
+
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018; the reference sketches the same idea on the host in
+// lib/bvh/locally_ordered_clustering_builder.hpp:186-234) ---------------------------------------------------------------------
+// The Morton-sorted leaves are the initial clusters.  Every round each cluster looks `radius` places to either side for the
+// partner whose union with it has the smallest surface area; mutual choices merge into a new inner node, the array is compacted
+// (order kept) and the round repeats until one cluster is left.  The tree is as good as a binned-SAH build (dragon 4K: see
+// profiles/r2/sweeps.md) where the radix tree of the Morton codes alone is ~19 % slower to render.  Same intermediate form as
+// the radix tree (child[], par_inner[], par_leaf[], inner node 0 = root), so emit / fit / depth kernels are shared: inner nodes
+// are numbered DOWNWARDS from n - 2 as they are created, the last merge makes node 0.
+struct PlocState { uint32_t m, next_id, merges, pad; };      // clusters left, next inner id (exclusive upper end), merges of this round
+
+__device__ __forceinline__ float ploc_area(const float* a, const float* b) {
+    const float dx = fmaxf(a[1], b[1]) - fminf(a[0], b[0]), dy = fmaxf(a[3], b[3]) - fminf(a[2], b[2]), dz = fmaxf(a[5], b[5]) - fminf(a[4], b[4]);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// nn[i] = the cluster within `radius` positions of i whose union with i has the smallest half-area; ties go to the nearer
+// position and then to i ^ 1, so that runs of identical boxes (coincident triangles) pair up (0,1)(2,3)... instead of chaining
+__global__ void __launch_bounds__(256) ploc_nn_kernel(const float* __restrict__ cbox, const PlocState* st, int radius, uint32_t* __restrict__ nn) {
+    const int m = (int)st->m, i = (int)(blockIdx.x * 256u + threadIdx.x);
+    if (i >= m) return;
+    float me[6];
+    for (int q = 0; q < 6; ++q) me[q] = __ldg(cbox + 6ull * i + q);
+    float best = 3.4e38f; int bj = i;
+    const int lo = max(0, i - radius), hi = min(m - 1, i + radius);
+    for (int j = lo; j <= hi; ++j) {
+        if (j == i) continue;
+        float o[6];
+        for (int q = 0; q < 6; ++q) o[q] = __ldg(cbox + 6ull * j + q);
+        const float a = ploc_area(me, o);
+        const int dj = abs(j - i), db = abs(bj - i);
+        if (a < best || (a == best && (dj < db || (dj == db && j == (i ^ 1))))) { best = a; bj = j; }
+    }
+    nn[i] = (uint32_t)bj;
+}
+
+// flag[i] = valid | merge << 32: a mutual pair (i, nn[i]) survives at its lower position and merges there
+__global__ void __launch_bounds__(256) ploc_flag_kernel(const uint32_t* __restrict__ nn, const PlocState* st, unsigned long long* __restrict__ flag) {
+    const uint32_t m = st->m, i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= m) return;
+    const uint32_t j = nn[i];
+    const bool mutual = j != i && nn[j] == i;
+    flag[i] = (mutual && i > j ? 0ull : 1ull) | (mutual && i < j ? 1ull << 32 : 0ull);
+}
+
+__global__ void ploc_totals_kernel(const unsigned long long* __restrict__ flag, const unsigned long long* __restrict__ scan, PlocState* st) {
+    const uint32_t m = st->m;
+    const unsigned long long t = scan[m - 1] + flag[m - 1];
+    st->merges = (uint32_t)(t >> 32);
+    st->pad = (uint32_t)t;                 // clusters of the next round (applied by ploc_advance_kernel after the merge pass)
+}
+
+__global__ void __launch_bounds__(256) ploc_merge_kernel(const uint32_t* __restrict__ cid, const float* __restrict__ cbox, const uint32_t* __restrict__ nn,
+                                                         const unsigned long long* __restrict__ flag, const unsigned long long* __restrict__ scan,
+                                                         const PlocState* st, uint32_t* __restrict__ cid_out, float* __restrict__ cbox_out,
+                                                         uint32_t* __restrict__ child, uint32_t* __restrict__ par_inner, uint32_t* __restrict__ par_leaf) {
+    const uint32_t m = st->m, i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= m) return;
+    const unsigned long long fl = flag[i];
+    if (!(fl & 1ull)) return;                                   // merged into its partner's position
+    const uint32_t pos = (uint32_t)scan[i];
+    float b[6];
+    for (int q = 0; q < 6; ++q) b[q] = cbox[6ull * i + q];
+    uint32_t id = cid[i];
+    if (fl >> 32) {
+        const uint32_t j = nn[i], node = st->next_id - st->merges + (uint32_t)(scan[i] >> 32);
+        const uint32_t L = id, R = cid[j];
+        child[2 * node] = L; child[2 * node + 1] = R;
+        if (L & LBVH_LEAF) par_leaf[L & ~LBVH_LEAF] = 2u * node; else par_inner[L] = 2u * node;
+        if (R & LBVH_LEAF) par_leaf[R & ~LBVH_LEAF] = 2u * node + 1u; else par_inner[R] = 2u * node + 1u;
+        for (int d = 0; d < 3; ++d) {
+            b[2 * d] = min_std(b[2 * d], cbox[6ull * j + 2 * d]);
+            b[2 * d + 1] = max_std(b[2 * d + 1], cbox[6ull * j + 2 * d + 1]);
+        }
+        id = node;
+    }
+    cid_out[pos] = id;
+    for (int q = 0; q < 6; ++q) cbox_out[6ull * pos + q] = b[q];
+}
+
+__global__ void ploc_advance_kernel(PlocState* st) { st->next_id -= st->merges; st->m = st->pad; }
+
+// initial clusters: leaf k (sorted position) with the box of triangle idx[k]
+__global__ void __launch_bounds__(256) ploc_init_kernel(const uint32_t* __restrict__ idx, const float* __restrict__ box, uint32_t n,
+                                                        uint32_t* __restrict__ cid, float* __restrict__ cbox) {
+    const uint32_t k = blockIdx.x * 256u + threadIdx.x;
+    if (k >= n) return;
+    cid[k] = k | LBVH_LEAF;
+    for (int q = 0; q < 6; ++q) cbox[6ull * k + q] = box[6ull * idx[k] + q];
+}
+
+// ---- leaf collapsing (SAH) ---------------------------------------------------------------------------------------------------
+// Both builders above end with one triangle per leaf; the reference's SweepSah trees keep up to max_leaf_size triangles in a
+// leaf where that is cheaper (top_down_builder.hpp:41, sweep_sah_builder.hpp: a range stays a leaf when no split beats
+// count x area).  The same rule bottom-up: cost(node) = min(area x count x Ci, area x Ct + cost(left) + cost(right)); a node whose
+// first term wins (and whose count fits) becomes a leaf, the topmost such node on a path wins.  The leaves are renumbered in
+// depth-first order so that every subtree owns a contiguous range of slots, and the surviving inner nodes are renumbered in
+// pre-order.
+struct CollapseParams { float ct, ci; uint32_t max_leaf; };
+
+__device__ __forceinline__ const float* bvhc_box(const LbvhNode* nodes, const uint32_t* par_inner, uint32_t p) {
+    if (p == 0u) return nodes[0].bounds;
+    const uint32_t up = par_inner[p];
+    return nodes[1 + 2 * (up >> 1) + (up & 1u)].bounds;
+}
+__device__ __forceinline__ float bvhc_half_area(const float* b) {
+    const float dx = b[1] - b[0], dy = b[3] - b[2], dz = b[5] - b[4];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// one thread per leaf climbs while it is the second child to arrive: cnt[], cost[], collapse[] of the inner nodes
+__global__ void __launch_bounds__(256) bvhc_cost_kernel(const uint32_t* __restrict__ child, const uint32_t* __restrict__ par_inner,
+                                                        const uint32_t* __restrict__ par_leaf, const LbvhNode* __restrict__ nodes, int n, CollapseParams q,
+                                                        uint32_t* arrived, uint32_t* cnt, float* cost, uint32_t* collapse, uint32_t* fl) {
+    const int k = (int)(blockIdx.x * 256u + threadIdx.x);
+    if (k >= n) return;
+    uint32_t p = par_leaf[k] >> 1;
+    for (;;) {
+        if (atomicAdd(&arrived[p], 1u) == 0u) return;
+        __threadfence();
+        uint32_t c_n = 0, c_fl = 0; float c_cost = 0.0f;
+        for (int s = 0; s < 2; ++s) {
+            const uint32_t c = child[2 * p + s];
+            if (c & LBVH_LEAF) { c_n += 1u; c_fl += 1u; c_cost += bvhc_half_area(nodes[1 + 2 * p + s].bounds) * q.ci; }
+            else { c_n += __ldcg(cnt + c); c_fl += __ldcg(fl + c); c_cost += __ldcg(cost + c); }
+        }
+        const float a = bvhc_half_area(bvhc_box(nodes, par_inner, p));
+        const float as_leaf = a * (float)c_n * q.ci, as_tree = a * q.ct + c_cost;
+        const bool col = p != 0u && c_n <= q.max_leaf && as_leaf <= as_tree;
+        __stcg(cnt + p, c_n); __stcg(cost + p, col ? as_leaf : as_tree); __stcg(collapse + p, col ? 1u : 0u);
+        __stcg(fl + p, col ? 1u : c_fl);                        // leaves of the FINAL tree under p
+        if (p == 0u) return;
+        __threadfence();
+        p = par_inner[p] >> 1;
+    }
+}
+
+// thread t < n: leaf t; thread n + i: inner node i.  Depth-first rank of the node's first leaf (sum, over the ancestors it
+// hangs under on the right, of the left sibling's leaf count) and whether an ancestor collapses (then the node disappears).
+// A surviving inner node also gets its number in the final tree: its PRE-ORDER index among the inner nodes = ancestors +
+// sum over the subtrees hanging to the left of its path of (final leaves - 1) -- the order in which ceres_scene_create numbers
+// the pairs of a host-built tree, so that a descent walks forward in memory.
+__global__ void __launch_bounds__(256) bvhc_rank_kernel(const uint32_t* __restrict__ child, const uint32_t* __restrict__ par_inner,
+                                                        const uint32_t* __restrict__ par_leaf, const uint32_t* __restrict__ cnt,
+                                                        const uint32_t* __restrict__ collapse, const uint32_t* __restrict__ fl,
+                                                        const uint32_t* __restrict__ idx, int n,
+                                                        uint32_t* __restrict__ idx_out, uint32_t* __restrict__ rank_inner, uint32_t* __restrict__ keep,
+                                                        uint32_t* __restrict__ newid) {
+    const int t = (int)(blockIdx.x * 256u + threadIdx.x);
+    if (t >= 2 * n - 1) return;
+    const bool leaf = t < n;
+    const uint32_t me = leaf ? (uint32_t)t : (uint32_t)(t - n);
+    if (!leaf && me == 0u) { rank_inner[0] = 0u; keep[0] = 1u; newid[0] = 0u; return; }
+    uint32_t w = leaf ? par_leaf[me] : par_inner[me];
+    uint32_t rank = 0, pre = 0; bool dead = false;
+    for (;;) {
+        const uint32_t p = w >> 1;
+        pre += 1u;                                               // the ancestor itself
+        if (w & 1u) {
+            const uint32_t l = child[2 * p];
+            rank += (l & LBVH_LEAF) ? 1u : cnt[l];
+            pre += (l & LBVH_LEAF) ? 0u : fl[l] - 1u;            // inner nodes of the final tree in the left sibling's subtree
+        }
+        if (collapse[p]) dead = true;
+        if (p == 0u) break;
+        w = par_inner[p];
+    }
+    if (leaf) idx_out[rank] = idx[me];
+    else { rank_inner[me] = rank; keep[me] = (!dead && !collapse[me]) ? 1u : 0u; newid[me] = pre; }
+}
+
+// surviving inner node i (compact number newid[i]) writes its two children into the compact reference layout
+__global__ void __launch_bounds__(256) bvhc_emit_kernel(const uint32_t* __restrict__ child, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ collapse,
+                                                        const uint32_t* __restrict__ rank_inner, const uint32_t* __restrict__ keep,
+                                                        const uint32_t* __restrict__ newid, const LbvhNode* __restrict__ nodes, int n,
+                                                        LbvhNode* __restrict__ out) {
+    const int i = (int)(blockIdx.x * 256u + threadIdx.x);
+    if (i >= n - 1 || !keep[i]) return;
+    const uint32_t me = newid[i];
+    if (i == 0) {
+        for (int q = 0; q < 6; ++q) out[0].bounds[q] = nodes[0].bounds[q];
+        out[0].primitive_count = 0u; out[0].first_child_or_primitive = 1u;
+    }
+    const uint32_t base = rank_inner[i];
+    for (int s = 0; s < 2; ++s) {
+        const uint32_t c = child[2 * i + s];
+        LbvhNode nd = nodes[1 + 2 * i + s];                              // bounds of the child
+        const uint32_t first_rank = s == 0 ? base : base + ((child[2 * i] & LBVH_LEAF) ? 1u : cnt[child[2 * i]]);
+        if (c & LBVH_LEAF) { nd.primitive_count = 1u; nd.first_child_or_primitive = first_rank; }
+        else if (collapse[c]) { nd.primitive_count = cnt[c]; nd.first_child_or_primitive = first_rank; }
+        else { nd.primitive_count = 0u; nd.first_child_or_primitive = 1u + 2u * newid[c]; }
+        out[1 + 2 * me + s] = nd;
     }
 }

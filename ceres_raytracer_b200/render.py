@@ -93,6 +93,13 @@ def probe_host_fill_bandwidth(nbytes=256 << 20, repeats=3):
     return float(out.value)
 
 
+def build_options(algorithm=0, radius=0, max_leaf=0, triangle_cost=0.0):
+    """Which tree build_lbvh / Scene.from_lbvh make: algorithm 0 = locally-ordered clustering (default), 1 = radix tree of the
+    Morton codes; radius = neighbours searched on either side (0 = 8); max_leaf = SAH leaf collapsing up to that many triangles
+    (0 = 8, 1 = off); triangle_cost = cost of a triangle test in node steps (0 = 1.5).  Process-wide (ceres_build_options)."""
+    _capi.check(_capi.lib().ceres_build_options(int(algorithm), int(radius), int(max_leaf), float(triangle_cost)))
+
+
 def build_lbvh(triangles, device=0):
     """GPU linear-BVH build (ceres_build_lbvh): returns (nodes NODE_DT[2n-1], prim_indices uint64[n], build_ms) in the
     reference's layout for `triangles` float32[n, 12]."""
@@ -100,9 +107,9 @@ def build_lbvh(triangles, device=0):
     n = tris.shape[0]
     nodes = np.zeros(max(2 * n - 1, 1), NODE_DT)
     idx = np.zeros(max(n, 1), np.uint64)[:n]
-    ms = C.c_double(0.0)
-    _capi.check(_capi.lib().ceres_build_lbvh(_p(tris), n, int(device), _p(nodes), _p(idx), C.byref(ms)))
-    return nodes, idx, float(ms.value)
+    ms, count = C.c_double(0.0), C.c_size_t(0)
+    _capi.check(_capi.lib().ceres_build_bvh(_p(tris), n, int(device), _p(nodes), C.byref(count), _p(idx), C.byref(ms)))
+    return nodes[:count.value].copy(), idx, float(ms.value)
 
 
 class Scene:
@@ -137,7 +144,8 @@ class Scene:
         _capi.check(L.ceres_scene_create_lbvh(_p(tris), _p(norms), tris.shape[0], int(device), C.byref(h), C.byref(ms)))
         self = cls.__new__(cls)
         self._h, self._L, self.device = h, L, int(device)
-        self.node_count, self.tri_count = max(2 * int(tris.shape[0]) - 1, 1), int(tris.shape[0])
+        self.tri_count = int(tris.shape[0])
+        self.node_count = int(L.ceres_scene_node_count(h))
         self.build_ms = float(ms.value)
         return self
 
@@ -166,6 +174,10 @@ class Scene:
     def last_d2h_bytes(self):
         """Bytes the last host-frame render moved over PCIe (the scene's screen rectangle + counters)."""
         return int(self._L.ceres_scene_last_d2h_bytes(self._h))
+
+    @property
+    def stack_depth(self):
+        return int(self._L.ceres_scene_stack_depth(self._h))
 
     @property
     def last_rectangle(self):

@@ -104,6 +104,10 @@ void ceres_scene_destroy(ceres_scene* scene);
 int ceres_scene_set_tuning(ceres_scene* scene, const ceres_tuning* tuning);
 /* bytes of device memory held by the flattened scene */
 size_t ceres_scene_device_bytes(const ceres_scene* scene);
+/* entries of traversal stack the scene's tree can need (its depth; <= 64, single_ray_traverser.hpp:14) */
+uint32_t ceres_scene_stack_depth(const ceres_scene* scene);
+/* nodes of the scene's tree in the reference's numbering (what ceres_scene_download expects) */
+size_t ceres_scene_node_count(const ceres_scene* scene);
 /* bytes the last host-frame render (ceres_render / _shard / one frame of _sequence) moved over PCIe: the screen
  * rectangle of the scene's rows + the counters; everything else of the frame is zero-filled by host threads */
 uint64_t ceres_scene_last_d2h_bytes(const ceres_scene* scene);
@@ -128,15 +132,33 @@ int ceres_scene_refit(ceres_scene* scene);
 int ceres_scene_download(ceres_scene* scene, void* nodes_out, size_t node_count, void* tris_out, size_t tri_count);
 
 /* ---- BVH construction on the GPU ---------------------------------------------------------------
- * A linear BVH (Morton codes of the triangle centres, radix sort, Karras' radix tree; the GPU-friendly builder the
- * reference sketches in lib/bvh/linear_bvh_builder.hpp:118-185) in the REFERENCE's data structure: nodes_out =
- * (2 * tri_count - 1) x 32-byte bvh::Bvh<float>::Node with node 0 the root and siblings adjacent (bvh.hpp:25-30),
- * prim_idx_out = tri_count x size_t Bvh::primitive_indices, one triangle per leaf.  tris: HOST tri_count x 48-byte
+ * Morton codes of the triangle centres, a radix sort, then (default) locally-ordered clustering over that order with SAH leaf
+ * collapsing, or Karras' radix tree alone (ceres_build_options; the GPU-friendly builders the reference sketches in
+ * lib/bvh/locally_ordered_clustering_builder.hpp:186-234 and linear_bvh_builder.hpp:118-185) -- in the REFERENCE's data
+ * structure: nodes_out = up to (2 * tri_count - 1) x 32-byte bvh::Bvh<float>::Node with node 0 the root and siblings adjacent
+ * (bvh.hpp:25-30), inner nodes in pre-order, prim_idx_out = tri_count x size_t Bvh::primitive_indices in depth-first leaf order,
+ * up to max_leaf triangles per leaf.  tris: HOST tri_count x 48-byte
  * Triangle<float>.  Replaces the host build of anim.cpp:46-65 / static.cpp:98-107 where build time matters (10 M
  * triangles); the tree differs from SweepSah's, so exact-t ties may pick another triangle than the SweepSah tree would --
  * frames are bit-exact against the reference's traverser walking THIS tree.  build_ms (nullable): device time of the
  * build kernels without the transfers. */
 int ceres_build_lbvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* prim_idx_out, double* build_ms);
+/* The same build, reporting how many nodes the tree has: with leaf collapsing (below) fewer than 2 tri_count - 1; nodes_out must
+ * still hold 2 tri_count - 1 nodes (the tail is zero).  ceres_build_lbvh = this call without the count. */
+int ceres_build_bvh(const void* tris, size_t tri_count, int device, void* nodes_out, size_t* node_count_out, size_t* prim_idx_out,
+                    double* build_ms);
+/* What the build calls make over the Morton-sorted triangles (process-wide; 0 = default for every argument):
+ *   algorithm     0 (default) = parallel locally-ordered clustering (the idea of lib/bvh/locally_ordered_clustering_builder.hpp:
+ *                 186-234: every round each cluster merges with the neighbour within `radius` places whose union has the smallest
+ *                 area, if the choice is mutual); 1 = the radix tree of the Morton codes alone (linear_bvh_builder.hpp:118-185;
+ *                 faster to build, ~19 % slower to render)
+ *   radius        neighbours searched on either side (default 8)
+ *   max_leaf      SAH leaf collapsing: a subtree of at most max_leaf triangles becomes one leaf where area x count x
+ *                 triangle_cost <= area + cost(children) (the rule by which SweepSah stops splitting, top_down_builder.hpp:41);
+ *                 1 = off: one triangle per leaf, 2 tri_count - 1 nodes (default 8)
+ *   triangle_cost cost of one triangle test in node steps (default 1.5: a Moeller-Trumbore test is ~90 instructions of the frame
+ *                 kernel, a node-pair step ~60) */
+int ceres_build_options(int algorithm, int radius, int max_leaf, float triangle_cost);
 
 /* The same build, kept on the device: a scene whose tree never visits the host (the host-side flatten of
  * ceres_scene_create costs more than the build for 10 M triangles).  tris / norms as for ceres_scene_create

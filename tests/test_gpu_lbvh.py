@@ -18,8 +18,17 @@ def cr():
     return cr
 
 
+@pytest.fixture(params=[(0, 0), (0, 1), (1, 1), (1, 4)], ids=["clustering+collapse", "clustering", "radix-tree", "radix-tree+collapse4"], autouse=True)
+def algorithm(request, cr):
+    """Every test runs with both builders -- locally-ordered clustering (default) and the radix tree of the Morton codes -- with
+    and without SAH leaf collapsing."""
+    cr.build_options(request.param[0], 0, request.param[1])
+    yield request.param
+    cr.build_options()
+
+
 def validate(nodes, idx, n):
-    assert nodes.shape[0] == 2 * n - 1 and sorted(idx.tolist()) == list(range(n))
+    assert nodes.shape[0] <= 2 * n - 1 and nodes.shape[0] % 2 == 1 and sorted(idx.tolist()) == list(range(n))
     seen = np.zeros(nodes.shape[0], np.int32)
     slots = np.zeros(n, np.int32)
     depth_max, stack = 0, [(0, 1)]
@@ -65,8 +74,29 @@ def test_lbvh_edge_cases(cr):
     assert validate(nodes, idx, 37) <= 64
     pod = {"nodes": nodes, "prim_indices": idx, "triangles": many, "norms": np.zeros((37, 9), np.float32)}
     assert np.array_equal(port.refit(pod).view(np.uint32), nodes.view(np.uint32))
+    lots = np.concatenate([tri] * 5000)           # ... and a shallow one: identical boxes must pair up, not chain
+    nodes, idx, _ = cr.build_lbvh(lots)
+    assert validate(nodes, idx, 5000) <= 20
     with pytest.raises(cr.CeresError):
         cr.build_lbvh(np.zeros((0, 12), np.float32))
+
+
+def test_clustering_tree_needs_fewer_steps_than_the_radix_tree(cr, dragon_pod):
+    """The point of the clustering build: a tree of SAH quality.  Same frame, node-pair steps of the primary rays (closest-hit,
+    deterministic) counted by the statistics build: the clustered tree needs clearly fewer than the radix tree and is within
+    15 % of the reference's SweepSah tree."""
+    cam, W, H = cr.configs.DRAGON_CAMERA, 960, 540
+    steps = {}
+    for name, make in (("sweep", lambda: cr.Scene.from_pod(dragon_pod)),
+                       ("ploc", lambda: (cr.build_options(0), cr.Scene.from_lbvh(dragon_pod["triangles"], dragon_pod["norms"]))[1]),
+                       ("radix", lambda: (cr.build_options(1, 0, 1), cr.Scene.from_lbvh(dragon_pod["triangles"], dragon_pod["norms"]))[1])):
+        with make() as s:
+            s.set_stats(True)
+            s.render(cam, SUN, W, H)
+            st = s.get_stats()
+            steps[name] = st["S_hit"] + st["S_miss"] + st["S_shadow"]
+    assert steps["ploc"] < 0.9 * steps["radix"], steps
+    assert steps["ploc"] < 1.15 * steps["sweep"], steps
 
 
 def test_scene_from_lbvh_equals_scene_from_the_downloaded_tree(cr, dragon_pod):
@@ -77,7 +107,7 @@ def test_scene_from_lbvh_equals_scene_from_the_downloaded_tree(cr, dragon_pod):
     pod["nodes"], pod["prim_indices"] = nodes, idx
     cam = cr.configs.DRAGON_CAMERA
     with cr.Scene.from_pod(pod) as a, cr.Scene.from_lbvh(pod["triangles"], pod["norms"]) as b:
-        assert b.build_ms > 0 and b.node_count == a.node_count
+        assert b.build_ms > 0 and b.node_count == a.node_count == nodes.shape[0]
         na, ta = a.download()
         nb, tb = b.download()
         assert np.array_equal(na.view(np.uint32), nodes.view(np.uint32))
