@@ -44,6 +44,7 @@ struct Scene64 {
 struct Frame64 {
     double eye[3], dir[3], iu[3], iv[3], sun[3];
     uint32_t width, height, flags;
+    uint32_t x0, y0, x1, y1;        // pixels [x0, x1) x [y0, y1) of the frame are rendered by this launch (a row band of the screen rectangle)
     float* rgb; uint32_t* ids;      // the colours are float-valued (render.hpp:56-84): 3 floats per pixel on the device
     unsigned long long* counters;   // rays beyond W*H (= primary hits), hits
     int* rect;                      // min i, min j, max i, max j over the pixels whose primary ray hit
@@ -163,10 +164,10 @@ __device__ __forceinline__ void smooth_shading(D3 sun_line, const double* nm, D3
 // One thread per pixel; a warp covers an 8 x 4 tile, a 128-thread CTA a 16 x 8 block.
 __global__ void __launch_bounds__(128) render_kernel(const Scene64 sc, const Frame64 f) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t i = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t j = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    const uint32_t i = f.x0 + blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t j = f.y0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
     unsigned int primary_hit = 0, hits = 0;
-    if (i < f.width && j < f.height) {
+    if (i < f.x1 && j < f.y1) {
         const size_t pix = (size_t)f.width * j + i;
         const double u = sub(__ddiv_rn(mul(2.0, add((double)i, 0.5)), (double)f.width), 1.0);      // render.hpp:109-110
         const double v = sub(__ddiv_rn(mul(2.0, add((double)j, 0.5)), (double)f.height), 1.0);
@@ -220,8 +221,10 @@ struct ceres_scene_f64 {
     float* d_rgb = nullptr; size_t pixels_cap = 0;
     uint32_t* d_ids = nullptr; size_t ids_cap = 0;
     unsigned long long* d_counters = nullptr;           // 2 counters followed by the 4 ints of the hit rectangle
-    float* h_rgb = nullptr; uint32_t* h_ids = nullptr; size_t stage_cap = 0;      // page-locked staging of the hit rectangle
+    float* h_rgb = nullptr; uint32_t* h_ids = nullptr; size_t stage_cap = 0;      // page-locked staging of the screen rectangle
     size_t tri_count = 0, node_count = 0;
+    double bounds[6] = {0, 0, 0, 0, 0, 0};                  // root box (nodes[0].bounds): the conservative screen rectangle comes from it
+    cudaStream_t band_stream[4] = {}; cudaEvent_t band_done[4] = {};
 };
 
 namespace {
@@ -305,6 +308,7 @@ int ceres_scene_f64_create(const void* nodes_v, size_t node_count, const size_t*
     ceres_scene_f64* s = new (std::nothrow) ceres_scene_f64;
     if (!s) return fail(CERES_ERR_INVALID, "out of host memory");
     s->device = device; s->tri_count = tri_count; s->node_count = node_count;
+    for (int b = 0; b < 6; ++b) s->bounds[b] = root.bounds[b];
 #define TRY_D(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { fail(CERES_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); ceres_scene_f64_destroy(s); return CERES_ERR_CUDA; } } while (0)
     TRY_D(cudaMalloc(&s->d_pairs, pairs.size() * sizeof(f64::Child)));
     TRY_D(cudaMalloc((void**)&s->d_tris, tri_slots.size() * 8));
@@ -332,6 +336,7 @@ void ceres_scene_f64_destroy(ceres_scene_f64* s) {
     DeviceGuard guard(s->device);
     cudaFree(s->d_pairs); cudaFree(s->d_tris); cudaFree(s->d_norms); cudaFree(s->d_slot_id);
     cudaFree(s->d_rgb); cudaFree(s->d_ids); cudaFree(s->d_counters);
+    for (int k = 0; k < 4; ++k) { if (s->band_stream[k]) cudaStreamDestroy(s->band_stream[k]); if (s->band_done[k]) cudaEventDestroy(s->band_done[k]); }
     if (s->h_rgb) cudaFreeHost(s->h_rgb);
     if (s->h_ids) cudaFreeHost(s->h_ids);
     delete s;
@@ -373,71 +378,126 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
     }
     f.width = (uint32_t)width; f.height = (uint32_t)height; f.flags = flags;
     f.rgb = s->d_rgb; f.ids = ids ? s->d_ids : nullptr; f.counters = s->d_counters; f.rect = reinterpret_cast<int*>(s->d_counters + 2);
-    struct Out { unsigned long long c[2]; int rect[4]; } o = {{0, 0}, {0x7FFFFFFF, 0x7FFFFFFF, -1, -1}};
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    CUDA_TRY(cudaMemcpy(s->d_counters, &o, sizeof o, cudaMemcpyHostToDevice));
-    if (kernel_ms) { CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventRecord(e0, 0)); }
-    f64::render_kernel<<<dim3((unsigned)((width + 15) / 16), (unsigned)((height + 7) / 8)), 128>>>(s->dev, f);
-    g_launches++;
-    if (kernel_ms) cudaEventRecord(e1, 0);
-    cudaError_t err = cudaGetLastError();
-    if (err == cudaSuccess) err = cudaMemcpy(&o, s->d_counters, sizeof o, cudaMemcpyDeviceToHost);
-#ifdef CERES_CHECKED
-    if (err == cudaSuccess) {
-        unsigned long long w = 0;
-        err = cudaMemcpy(&w, s->d_counters + 4, sizeof w, cudaMemcpyDeviceToHost);
-        if (err == cudaSuccess && w) {
-            cudaMemset(s->d_counters + 4, 0, sizeof w);
-            if (e0) cudaEventDestroy(e0);
-            if (e1) cudaEventDestroy(e1);
-            return fail(CERES_ERR_CUDA, "ceres_render_f64: checked build: an index left its bound (bits " + std::to_string(w) + ")");
+    // Conservative screen rectangle of the scene (the float path's rule, in double: the root box inflated by 1e-4 of the scene
+    // scale, corners projected, one pixel of margin; a corner at or behind the eye plane disables it): pixels outside it cannot
+    // hit anything, so they are never traced -- their zeros are written by the host pool while the GPU works on the rest.
+    size_t x0 = 0, x1 = width, y0 = 0, y1 = height;
+    {
+        double scale = 0.0;
+        for (int k = 0; k < 6; ++k) scale = std::max(scale, std::fabs(s->bounds[k]));
+        for (int k = 0; k < 3; ++k) scale = std::max(scale, std::fabs(f.eye[k]));
+        auto dot = [](const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; };
+        const double iu2 = dot(f.iu, f.iu), iv2 = dot(f.iv, f.iv), d2 = dot(f.dir, f.dir);
+        bool ok = std::isfinite(scale) && scale > 0.0 && iu2 > 0.0 && iv2 > 0.0 && d2 > 0.0 && std::isfinite(iu2 + iv2 + d2) && !s->dev.root_leaf_count;
+        double umin = INFINITY, umax = -INFINITY, vmin = INFINITY, vmax = -INFINITY;
+        const double m = 1e-4 * scale;
+        for (int c = 0; c < 8 && ok; ++c) {
+            double p[3];
+            for (int k = 0; k < 3; ++k) p[k] = ((c >> k) & 1 ? s->bounds[2 * k + 1] + m : s->bounds[2 * k] - m) - f.eye[k];
+            const double z = dot(p, f.dir) / d2;
+            if (!(z > 1e-6 * scale)) { ok = false; break; }
+            const double u = dot(p, f.iu) / iu2 / z, v = dot(p, f.iv) / iv2 / z;
+            umin = std::min(umin, u); umax = std::max(umax, u); vmin = std::min(vmin, v); vmax = std::max(vmax, v);
+        }
+        if (ok && std::isfinite(umin + umax + vmin + vmax)) {
+            auto lo_px = [](double u, double n) { double x = std::floor((u + 1.0) * n / 2.0 - 0.5) - 1.0; return x < 0.0 ? 0.0 : (x > n ? n : x); };
+            auto hi_px = [](double u, double n) { double x = std::ceil((u + 1.0) * n / 2.0 - 0.5) + 2.0; return x < 0.0 ? 0.0 : (x > n ? n : x); };
+            x0 = (size_t)lo_px(umin, (double)width); x1 = std::max(x0, (size_t)hi_px(umax, (double)width));
+            y0 = (size_t)lo_px(vmin, (double)height); y1 = std::max(y0, (size_t)hi_px(vmax, (double)height));
         }
     }
-#endif
-    if (kernel_ms && err == cudaSuccess) { float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1); *kernel_ms = ms; }
-    if (e0) cudaEventDestroy(e0);
-    if (e1) cudaEventDestroy(e1);
-    // Only the rectangle of pixels that hit something crosses PCIe, as floats, into page-locked staging; host threads
-    // widen it into the caller's frame and write the zeros (ids: CERES_MISS) around it meanwhile.
-    const bool any = o.rect[2] >= o.rect[0] && o.rect[3] >= o.rect[1];
-    const size_t x0 = any ? (size_t)o.rect[0] : 0, y0 = any ? (size_t)o.rect[1] : 0;
-    const size_t rw = any ? (size_t)(o.rect[2] - o.rect[0] + 1) : 0, rh = any ? (size_t)(o.rect[3] - o.rect[1] + 1) : 0;
-    if (err == cudaSuccess && rw * rh > s->stage_cap) {
-        if (s->h_rgb) cudaFreeHost(s->h_rgb);
-        if (s->h_ids) cudaFreeHost(s->h_ids);
-        s->h_rgb = nullptr; s->h_ids = nullptr; s->stage_cap = 0;
-        err = cudaMallocHost((void**)&s->h_rgb, rw * rh * 12);
-        if (err == cudaSuccess) err = cudaMallocHost((void**)&s->h_ids, rw * rh * 4);
-        if (err == cudaSuccess) s->stage_cap = rw * rh;
-    }
-    if (err == cudaSuccess && any) {
-        err = cudaMemcpy2DAsync(s->h_rgb, rw * 12, s->d_rgb + 3 * (width * y0 + x0), width * 12, rw * 12, rh, cudaMemcpyDeviceToHost, 0);
-        if (err == cudaSuccess && ids) err = cudaMemcpy2DAsync(s->h_ids, rw * 4, s->d_ids + (width * y0 + x0), width * 4, rw * 4, rh, cudaMemcpyDeviceToHost, 0);
-    }
-    if (err == cudaSuccess) {
-        ceres_host::Job zeros, body;
+    const size_t rw = x1 - x0, rh = y1 - y0;
+    const bool any = rw > 0 && rh > 0;
+    // zeros (ids: CERES_MISS) outside the rectangle: host pool, from now on
+    ceres_host::Job zeros;
+    {
         auto outside = [&](unsigned char* base, size_t px_bytes, unsigned char byte) {
             if (!any) { zeros.add(base, npix * px_bytes, byte); return; }
             zeros.add(base, width * y0 * px_bytes, byte);
-            zeros.add(base + width * (y0 + rh) * px_bytes, width * (height - y0 - rh) * px_bytes, byte);
-            for (size_t j = y0; j < y0 + rh; ++j) {
+            zeros.add(base + width * y1 * px_bytes, width * (height - y1) * px_bytes, byte);
+            for (size_t j = y0; j < y1; ++j) {
                 unsigned char* row = base + width * j * px_bytes;
                 if (x0) zeros.segs.push_back({row, x0 * px_bytes, byte});
-                if (x0 + rw < width) zeros.segs.push_back({row + (x0 + rw) * px_bytes, (width - x0 - rw) * px_bytes, byte});
+                if (x1 < width) zeros.segs.push_back({row + x1 * px_bytes, (width - x1) * px_bytes, byte});
             }
         };
         outside(reinterpret_cast<unsigned char*>(pixels), 24, 0x00);
         if (ids) outside(reinterpret_cast<unsigned char*>(ids), 4, 0xFF);
-        ceres_host::Pool::instance().submit(&zeros);
-        err = cudaStreamSynchronize(0);
-        for (size_t j = 0; j < rh && err == cudaSuccess; ++j) {
-            body.add_widen(pixels + 3 * (width * (y0 + j) + x0), s->h_rgb + 3 * rw * j, 3 * rw);
-            if (ids) body.add_copy(ids + width * (y0 + j) + x0, s->h_ids + rw * j, rw * 4);
-        }
-        ceres_host::Pool::instance().submit(&body);
-        ceres_host::Pool::instance().wait(&zeros);
-        ceres_host::Pool::instance().wait(&body);
     }
+    ceres_host::Pool& pool = ceres_host::Pool::instance();
+    pool.submit(&zeros);
+    struct Waiter { ceres_host::Pool& p; ceres_host::Job* j; ~Waiter() { p.wait(j); } } waiter{pool, &zeros};
+    struct Out { unsigned long long c[2]; int rect[4]; } o = {{0, 0}, {0x7FFFFFFF, 0x7FFFFFFF, -1, -1}};
+    cudaError_t err = cudaSuccess;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    std::vector<std::unique_ptr<ceres_host::Job>> bodies;
+    struct BodyWaiter { ceres_host::Pool& p; std::vector<std::unique_ptr<ceres_host::Job>>& v; ~BodyWaiter() { for (auto& j : v) p.wait(j.get()); } } body_waiter{pool, bodies};
+    if (any) {
+        if (rw * rh > s->stage_cap) {
+            if (s->h_rgb) cudaFreeHost(s->h_rgb);
+            if (s->h_ids) cudaFreeHost(s->h_ids);
+            s->h_rgb = nullptr; s->h_ids = nullptr; s->stage_cap = 0;
+            CUDA_TRY(cudaMallocHost((void**)&s->h_rgb, rw * rh * 12));
+            CUDA_TRY(cudaMallocHost((void**)&s->h_ids, rw * rh * 4));
+            s->stage_cap = rw * rh;
+        }
+        for (int k = 0; k < 4; ++k) {
+            if (!s->band_stream[k]) CUDA_TRY(cudaStreamCreateWithFlags(&s->band_stream[k], cudaStreamNonBlocking));
+            if (!s->band_done[k]) CUDA_TRY(cudaEventCreateWithFlags(&s->band_done[k], cudaEventDisableTiming));
+        }
+        CUDA_TRY(cudaMemcpy(s->d_counters, &o, sizeof o, cudaMemcpyHostToDevice));
+        if (kernel_ms) { CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventRecord(e0, 0)); CUDA_TRY(cudaEventSynchronize(e0)); }
+        // Row bands of the rectangle, each on its own stream: kernel -> DMA of the band's float pixels into page-locked staging;
+        // the host widens a band into the caller's double frame as soon as its copy has landed, while later bands render.
+        const size_t nb = std::max<size_t>(1, std::min<size_t>(4, (rw * rh) >> 18));
+        const size_t band_rows = ((rh + nb - 1) / nb + 7) / 8 * 8;
+        size_t launched = 0;
+        for (size_t k = 0, r0 = y0; r0 < y1; ++k, r0 += band_rows) {
+            const size_t r1 = std::min(y1, r0 + band_rows);
+            f.x0 = (uint32_t)x0; f.x1 = (uint32_t)x1; f.y0 = (uint32_t)r0; f.y1 = (uint32_t)r1;
+            cudaStream_t st = s->band_stream[k];
+            f64::render_kernel<<<dim3((unsigned)((rw + 15) / 16), (unsigned)((r1 - r0 + 7) / 8)), 128, 0, st>>>(s->dev, f);
+            g_launches++;
+            err = cudaGetLastError();
+            if (err == cudaSuccess) err = cudaMemcpy2DAsync(s->h_rgb + 3 * rw * (r0 - y0), rw * 12, s->d_rgb + 3 * (width * r0 + x0), width * 12, rw * 12, r1 - r0, cudaMemcpyDeviceToHost, st);
+            if (err == cudaSuccess && ids) err = cudaMemcpy2DAsync(s->h_ids + rw * (r0 - y0), rw * 4, s->d_ids + (width * r0 + x0), width * 4, rw * 4, r1 - r0, cudaMemcpyDeviceToHost, st);
+            if (err == cudaSuccess) err = cudaEventRecord(s->band_done[k], st);
+            if (err != cudaSuccess) break;
+            launched = k + 1;
+        }
+        for (size_t k = 0, r0 = y0; k < launched; ++k, r0 += band_rows) {
+            const size_t r1 = std::min(y1, r0 + band_rows);
+            const cudaError_t e = cudaEventSynchronize(s->band_done[k]);
+            if (e != cudaSuccess) { if (err == cudaSuccess) err = e; continue; }
+            auto body = std::make_unique<ceres_host::Job>();
+            for (size_t j = r0; j < r1; ++j) {
+                body->add_widen(pixels + 3 * (width * j + x0), s->h_rgb + 3 * rw * (j - y0), 3 * rw);
+                if (ids) body->add_copy(ids + width * j + x0, s->h_ids + rw * (j - y0), rw * 4);
+            }
+            pool.submit(body.get());
+            bodies.push_back(std::move(body));
+        }
+        if (kernel_ms && err == cudaSuccess) {
+            // device time of the frame: first launch to last band done (the bands' streams have all been synchronised above)
+            cudaEventRecord(e1, 0); cudaEventSynchronize(e1);
+            float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1); *kernel_ms = ms;
+        }
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+        if (err == cudaSuccess) err = cudaMemcpy(&o, s->d_counters, sizeof o, cudaMemcpyDeviceToHost);
+#ifdef CERES_CHECKED
+        if (err == cudaSuccess) {
+            unsigned long long w = 0;
+            err = cudaMemcpy(&w, s->d_counters + 4, sizeof w, cudaMemcpyDeviceToHost);
+            if (err == cudaSuccess && w) {
+                cudaMemset(s->d_counters + 4, 0, sizeof w);
+                return fail(CERES_ERR_CUDA, "ceres_render_f64: checked build: an index left its bound (bits " + std::to_string(w) + ")");
+            }
+        }
+#endif
+    }
+    pool.wait(&zeros);
+    for (auto& j : bodies) pool.wait(j.get());
     if (err != cudaSuccess) return fail(CERES_ERR_CUDA, std::string("ceres_render_f64: ") + cudaGetErrorString(err));
     const unsigned long long c[2] = {o.c[0], o.c[1]};
     if (counters) { counters[0] = (uint64_t)npix + c[0]; counters[1] = c[1]; }      // render.hpp:115,138 / :119,148

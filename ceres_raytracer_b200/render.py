@@ -426,14 +426,18 @@ class SceneF64:
     def from_pod(cls, pod, device=0):
         return cls(pod["nodes"], pod["prim_indices"], pod["triangles"], pod.get("norms"), device=device)
 
-    def render(self, camera, sun_position, width, height, flags=0, want_ids=False):
-        """Returns (pixels float64[H, W, 3], ids uint32[H, W] or None, (rays, hits)); camera: Camera or 10 numbers."""
+    def render(self, camera, sun_position, width, height, flags=0, want_ids=False, pixels=None):
+        """Returns (pixels float64[H, W, 3], ids uint32[H, W] or None, (rays, hits)); camera: Camera or 10 numbers.  pixels: an
+        existing C-contiguous float64 frame to fill (the frame loop of anim.cpp:76-105 reuses one)."""
         cam = _capi.CameraF64()
         vals = (list(camera.eye) + list(camera.dir) + list(camera.up) + [camera.fov]) if hasattr(camera, "eye") else [float(x) for x in camera]
         for k in range(3):
             cam.eye[k], cam.dir[k], cam.up[k] = vals[k], vals[3 + k], vals[6 + k]
         cam.fov = vals[9]
-        pixels = np.empty((height, width, 3), np.float64)
+        if pixels is None:
+            pixels = np.empty((height, width, 3), np.float64)
+        elif pixels.dtype != np.float64 or not pixels.flags.c_contiguous or pixels.size != 3 * width * height:
+            raise ValueError("pixels must be a C-contiguous float64 buffer of 3*width*height")
         ids = np.empty((height, width), np.uint32) if want_ids else None
         sun = np.ascontiguousarray(sun_position, np.float64)
         cnt, ms = np.zeros(2, np.uint64), C.c_double(0.0)

@@ -24,7 +24,15 @@ with cr.SceneF64.from_pod(pod) as s, cr.Scene.from_pod(pod32) as s32:
             ts.append(time.perf_counter() - t0)
             ks.append(s.kernel_ms)
         k, t = min(ks), min(ts) * 1e3
-        line = f"{W}x{H}: rays {cnt[0]} hits {cnt[1]}; f64 kernel {k:.3f} ms = {cnt[0]/k/1e3:.0f} Mrays/s; whole call into a fresh pageable numpy frame {t:.1f} ms"
+        frame = np.full((H, W, 3), np.nan)
+        tr = []
+        for _ in range(8):
+            t0 = time.perf_counter()
+            px2, _, cnt2 = s.render(cam, sun, W, H, pixels=frame)
+            tr.append(time.perf_counter() - t0)
+        assert cnt2 == cnt and np.array_equal(px2, px)
+        line = (f"{W}x{H}: rays {cnt[0]} hits {cnt[1]}; f64 device time (bands: kernels + copies) {k:.3f} ms; whole call into a fresh pageable numpy "
+                f"frame {t:.1f} ms, into a REUSED pageable frame (anim.cpp:76) {min(tr)*1e3:.2f} ms (median {np.median(tr)*1e3:.2f})")
         s32.render(c, sun, W, H)
         t0 = time.perf_counter(); _, _, c32 = s32.render(c, sun, W, H); t32 = (time.perf_counter() - t0) * 1e3
         line += f"; float path whole call {t32:.2f} ms (hits {c32[1]})"
