@@ -117,6 +117,12 @@ private:
     Pool() {
         unsigned hw = std::thread::hardware_concurrency();
         unsigned n = hw >= 16 ? 7 : (hw >= 8 ? 3 : (hw >= 4 ? 1 : 0));     // + the submitting thread
+        // one process per GPU (torchrun sets LOCAL_WORLD_SIZE): the ranks of a box share its cores -- 8 pools of 8 threads on 32
+        // cores fill a shared frame slower than one pool does (profiles/r2/sweeps.md)
+        if (const char* e = std::getenv("LOCAL_WORLD_SIZE")) {
+            const unsigned ranks = (unsigned)std::max(1, std::atoi(e));
+            if (ranks > 1) n = std::min(n, std::max(1u, hw / ranks) - (hw / ranks > 1 ? 1u : 0u));
+        }
         if (const char* e = std::getenv("CERES_HOST_FILL_THREADS")) n = (unsigned)std::max(0, std::atoi(e));
         for (unsigned k = 0; k < n; ++k) threads_.emplace_back([this] { run(); });
     }

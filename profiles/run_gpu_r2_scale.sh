@@ -30,3 +30,7 @@ if [ "$NG" -ge 8 ]; then
   timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29538 profiles/probes/peer_timeline.py 2>&1 | grep -v Warning | grep "rank\|N 8" > gpurun_out/peer_timeline_$TAG.log
   cat gpurun_out/peer_timeline_$TAG.log
 fi
+if [ -n "$EXTRA" ] && [ "$NG" -ge 8 ]; then
+  run 8 29525 bench_seq4k_n8_$TAG --workload dragon_turntable_4k --steps 3 --warmup 3 --no-cpu-baseline
+  run 8 29526 bench_grid448_8k_n8_$TAG --workload grid448_8k_shadow --steps 5 --warmup 3 --no-cpu-baseline --sustain-s 0.3
+fi
