@@ -40,6 +40,15 @@ static thread_local std::string g_err;
 static std::atomic<uint64_t> g_launches{0};
 
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static thread_local int tl_sequence_depth = 0;       // this thread is inside ceres_render_sequence (its own frames are not "concurrent")
+// A scene handle is not thread-safe; the one place where the LIBRARY runs a second thread over it is ceres_render_sequence, so
+// that is where a concurrent call from the caller's side would race silently (geometry moved by a refit under the second
+// thread's frames, per-frame state shared by two renders).  Such calls fail loudly instead.
+#define CERES_REJECT_DURING_SEQUENCE(s, who)                                                                 \
+    do {                                                                                                     \
+        if ((s) && (s)->in_sequence.load(std::memory_order_acquire) && tl_sequence_depth == 0)               \
+            return fail(CERES_ERR_INVALID, std::string(who) + ": ceres_render_sequence is running on this scene in another thread"); \
+    } while (0)
 #define CUDA_TRY(expr)                                                                                      \
     do {                                                                                                    \
         cudaError_t e_ = (expr);                                                                            \
@@ -677,6 +686,7 @@ struct ceres_scene {
     } kept;
     ceres_scene* seq_view = nullptr;                        // second set of per-frame resources over the same geometry (sequences)
     bool borrowed = false;                                  // a view: the geometry belongs to the scene it was made from
+    std::atomic<int> in_sequence{0};                        // ceres_render_sequence is running on this scene (its second thread reads the geometry)
     uint32_t ext_epoch = 0;
     uint64_t rays_outside = 0;                              // primary rays of the last frame that were never launched (host path)
     uint32_t cur_nsub = 1;                                  // row bands of the frame being enqueued (render_rows)
@@ -986,6 +996,7 @@ uint64_t ceres_scene_last_d2h_bytes(const ceres_scene* s) { return s ? s->last_d
 // ---- scene preparation on the device (scene_prep.cuh) ---------------------------------------------
 // All four calls are synchronous on the scene's stream and must not overlap frames of this scene in flight.
 static int prep_triangles(ceres_scene* s, const PrepParams& q) {
+    CERES_REJECT_DURING_SEQUENCE(s, "ceres_scene_rotate/transform");
     DeviceGuard guard(s->device);
     const unsigned grid = (unsigned)std::min<size_t>(((size_t)s->tri_count + 255) / 256, (size_t)s->sm_count * 16);
     prep_triangles_kernel<<<grid, 256, 0, s->stream>>>((float4*)s->d_tris, s->tri_count, q);
@@ -1016,6 +1027,7 @@ int ceres_scene_transform(ceres_scene* s, const float a[9], const float v[3]) {
 
 int ceres_scene_refit(ceres_scene* s) {
     if (!s) return fail(CERES_ERR_INVALID, "ceres_scene_refit: null scene");
+    CERES_REJECT_DURING_SEQUENCE(s, "ceres_scene_refit");
     DeviceGuard guard(s->device);
     if (!s->d_root_bounds) CUDA_TRY(cudaMalloc((void**)&s->d_root_bounds, 6 * sizeof(float)));
     if (s->dev.root_leaf_count) {
@@ -2216,6 +2228,7 @@ int ceres_render_peer(ceres_scene* s, const ceres_camera* cam, const float sun[3
 int ceres_render_shard(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
                        unsigned flags, const ceres_shard* shard, float* pixels, uint32_t* ids, uint64_t counters[2]) {
     if (!s || !pixels) return fail(CERES_ERR_INVALID, "ceres_render: null argument");
+    CERES_REJECT_DURING_SEQUENCE(s, "ceres_render");
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
     // device staging is written in COMPACT form (the shard's rows packed); rows are scattered to their frame
@@ -2664,6 +2677,12 @@ int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, si
         if (int rc = scene_new(s->device, s->sm_count, &s->seq_view)) return rc;
         s->seq_view->borrowed = true;
     }
+    CERES_REJECT_DURING_SEQUENCE(s, "ceres_render_sequence");
+    struct InSequence {
+        ceres_scene* s;
+        explicit InSequence(ceres_scene* q) : s(q) { s->in_sequence.store(1, std::memory_order_release); ++tl_sequence_depth; }
+        ~InSequence() { --tl_sequence_depth; s->in_sequence.store(0, std::memory_order_release); }
+    } in_sequence(s);
     ceres_scene* v = s->seq_view;       // refreshed every call: a refit moves the boxes, set_tuning the knobs
     { unsigned long long* own = v->dev.check; v->dev = s->dev; v->dev.check = own; v->dev.timeline = nullptr; }
     v->d_pairs = s->d_pairs; v->d_tris = s->d_tris; v->d_norms = s->d_norms; v->d_slot_id = s->d_slot_id;

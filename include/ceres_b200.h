@@ -232,7 +232,10 @@ int ceres_render_multi(ceres_scene* const* scenes, int n, const ceres_camera* ca
 
 /* N frames with one upload of the camera path: cams = n_frames x 13 floats (eye[3],dir[3],up[3],fov,sun[3]),
  * the per-frame values of anim.cpp:87-89; pixels_all = n_frames frames back to back; counters_all (nullable)
- * 2 per frame.  Each frame takes the host-frame path of ceres_render (only the scene's screen rectangle crosses PCIe). */
+ * 2 per frame.  Each frame takes the host-frame path of ceres_render (only the scene's screen rectangle crosses PCIe); two
+ * frames are in flight at a time, the odd ones rendered from a second thread of the library over the same resident geometry.
+ * While the call runs, ceres_render*, ceres_scene_rotate / _transform / _refit on the same scene from another thread return
+ * CERES_ERR_INVALID instead of racing with it. */
 int ceres_render_sequence(ceres_scene* scene, size_t n_frames, const float* cams, size_t width, size_t height,
                           unsigned flags, float* pixels_all, uint64_t* counters_all);
 

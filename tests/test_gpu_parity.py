@@ -682,3 +682,32 @@ def test_scattered_shards_tight_copies_and_retained_frames(cr, dragon, count):
         hb.close(); hi.close()
         for s in scenes[1:]:
             s.close()
+
+
+def test_calls_during_a_sequence_fail_loudly(cr, dragon_pod):
+    """ceres_render_sequence is the one call in which the LIBRARY runs a second thread over a scene; a refit or a render issued
+    on that scene from another thread meanwhile is refused (it would race with the sequence's frames), and the sequence's
+    frames are untouched by the attempt."""
+    import threading
+    W, H, n = 1920, 1080, 40
+    c = cr.configs.DRAGON_CAMERA
+    cams = np.tile(np.array(list(c.eye) + list(c.dir) + list(c.up) + [c.fov] + list(SUN), np.float32), (n, 1))
+    with cr.Scene.from_pod(dragon_pod) as s:
+        want = s.render(c, SUN, W, H)
+        out = {}
+        t = threading.Thread(target=lambda: out.update(seq=s.render_sequence(cams, W, H)))
+        refused = other = 0
+        t.start()
+        while t.is_alive():
+            try:
+                s.refit()
+                other += 1
+            except cr.CeresError as e:
+                assert "ceres_render_sequence is running" in str(e)
+                refused += 1
+        t.join()
+        px_all, cnt = out["seq"]
+        for k in range(n):
+            assert np.array_equal(px_all[k].view(np.uint32), want[0].view(np.uint32)) and tuple(int(x) for x in cnt[k]) == want[2]
+        assert refused > 0
+        s.refit()                                   # and the scene is free again afterwards
