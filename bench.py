@@ -385,6 +385,21 @@ def run_sequence(args):
     assert int(cnt_e2e[:, 0].sum()) == int(d_cnt[mine].sum(dim=0)[0].item())
     d2h_seq = scene.last_d2h_bytes * len(mine)       # turntable: the rectangle is (nearly) the same for every frame
     hb.close()
+    # the same sequence as 8-bit payloads in anim's row order (ceres_render_sequence_payload): what apps/anim writes to disk
+    hb8 = cr.PinnedBuffer((len(mine), H, W, 3), np.uint8)
+    scene.render_sequence_payload(own[:2], W, H, flags=flags | cr.PAYLOAD_NO_FLIP, bytes_per_channel=1, out=hb8.array[:2])
+    t_8 = 0.0
+    for _ in range(steps_e2e):
+        barrier()
+        t0 = time.perf_counter()
+        _, cnt_8 = scene.render_sequence_payload(own, W, H, flags=flags | cr.PAYLOAD_NO_FLIP, bytes_per_channel=1, out=hb8.array)
+        t_8 += time.perf_counter() - t0
+    t = torch.tensor([1e3 * t_8 / steps_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_8 = float(t.item())
+    assert int(cnt_8[:, 0].sum()) == int(cnt_e2e[:, 0].sum())
+    hb8.close()
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -407,6 +422,8 @@ def run_sequence(args):
                        "l2": "flushed (256 MiB fill) before every timed pass; every frame rewrites the frame buffer"},
             "e2e": {"value": rays_total / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 13 * 4 * len(mine),
                     "d2h_bytes_per_step": d2h_seq, "host_frame_bytes": 3 * W * H * 4 * len(mine), "path": "ceres_render_sequence() -> page-locked host frames"},
+            "e2e_ppm8": {"value": rays_total / (ms_8 * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_8,
+                         "path": "ceres_render_sequence_payload(1 byte per channel, anim row order) -> page-locked 8-bit payloads"},
             "gpu_launches": launches, "kernels_ms": per_pass,
             "roofline": {"bound": "issue", "kernel": "frame_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,

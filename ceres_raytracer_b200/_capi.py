@@ -50,7 +50,7 @@ SYMBOLS = [
     "ceres_peer_frame_invalidate",
 ]
 SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download",
-            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard", "ceres_build_options", "ceres_scene_stack_depth", "ceres_build_bvh", "ceres_scene_node_count"]
+            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard", "ceres_build_options", "ceres_scene_stack_depth", "ceres_build_bvh", "ceres_scene_node_count", "ceres_render_sequence_payload"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -144,6 +144,7 @@ def lib():
     L.ceres_scene_stack_depth.argtypes = [vp]
     L.ceres_scene_stack_depth.restype = C.c_uint32
     L.ceres_scene_node_count.argtypes = [vp]
+    L.ceres_render_sequence_payload.argtypes = [vp, sz, vp, sz, sz, C.c_uint, C.c_int, vp, vp]
     L.ceres_scene_node_count.restype = sz
     L.ceres_build_is_checked.restype = C.c_int
     L.ceres_abi_version.restype = C.c_int

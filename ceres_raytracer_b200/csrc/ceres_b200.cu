@@ -839,6 +839,8 @@ static int scene_new(int device, int sm_count, ceres_scene** out) {
 #ifdef CERES_CHECKED
     s->dev.check = s->d_out + 10;
 #endif
+    // the initialisations above ran on the legacy stream; the scene's own streams are non-blocking and not ordered after it
+    if (cudaDeviceSynchronize() != cudaSuccess) { fail(CERES_ERR_CUDA, "scene_new: cudaDeviceSynchronize failed"); ceres_scene_destroy(s); return CERES_ERR_CUDA; }
     *out = s;
     return CERES_OK;
 }
@@ -958,6 +960,7 @@ int ceres_scene_create(const void* nodes_v, size_t node_count, const size_t* pri
     s->n_pairs = root_leaf_count ? 0u : (uint32_t)(pairs.size() / 16);
     s->h_pair_first_child = std::move(pair_first_child);
     s->h_slot_id = std::move(slot_id);
+    CUDA_TRY(cudaDeviceSynchronize());          // uploads on the legacy stream are complete before a non-blocking stream reads them
     *out = s;
     return CERES_OK;
 }
@@ -1376,6 +1379,7 @@ int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_coun
     s->h_pair_first_child.resize(n_pairs);
     for (size_t i = 0; i < n_pairs; ++i) s->h_pair_first_child[i] = (uint32_t)(1 + 2 * i);
     if (build_ms) *build_ms = ms;
+    CUDA_TRY(cudaDeviceSynchronize());          // build kernels on the legacy stream are complete before a non-blocking stream reads the scene
     *out = s;
     return CERES_OK;
 }
@@ -1471,6 +1475,7 @@ int ceres_scene_get_step_histogram(ceres_scene* s, uint64_t hist[128]) {
     DeviceGuard guard(s->device);
     CUDA_TRY(cudaMemcpy(hist, s->d_hist, 128 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     CUDA_TRY(cudaMemset(s->d_hist, 0, 128 * sizeof(uint64_t)));
+    CUDA_TRY(cudaDeviceSynchronize());
     return CERES_OK;
 }
 
@@ -1518,7 +1523,7 @@ int ceres_scene_frame_error(ceres_scene* s, uint64_t* bits) {
                 w |= 0x20000ull;
     }
 #endif
-    if (w) CUDA_TRY(cudaMemset(s->d_out + 10, 0, sizeof w));
+    if (w) { CUDA_TRY(cudaMemset(s->d_out + 10, 0, sizeof w)); CUDA_TRY(cudaDeviceSynchronize()); }
     *bits = w;
     return CERES_OK;
 }
@@ -1537,6 +1542,7 @@ int ceres_scene_set_stats(ceres_scene* s, int enable) {
         DeviceGuard guard(s->device);
         CUDA_TRY(cudaMalloc((void**)&s->d_hist, 128 * sizeof(unsigned long long)));
         CUDA_TRY(cudaMemset(s->d_hist, 0, 128 * sizeof(unsigned long long)));
+        CUDA_TRY(cudaDeviceSynchronize());
         s->dev.hist = s->d_hist;
     }
     s->stats = enable != 0;
@@ -1911,6 +1917,7 @@ static int frame_error_check(ceres_scene* s) {
     FrameCounters init[CERES_MAX_SUB] = {};
     for (auto& c : init) { c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu; }
     cudaMemcpy(s->d_ctr, init, sizeof init, cudaMemcpyHostToDevice);
+    cudaDeviceSynchronize();
     return fail(CERES_ERR_CUDA, std::string("frame kernel: ") + ((bits & 1u) ? "a bounded device-side wait expired" : "an index left its bound (checked build)") +
                                 " (error bits " + std::to_string(bits) + ", include/ceres_b200.h: ceres_scene_frame_error)");
 }
@@ -1924,6 +1931,9 @@ static int size_queue(ceres_scene* s, size_t records) {
     if (need_ready > s->ready_cap) {
         if (int rc = ensure(s->d_ready, s->ready_cap, need_ready)) return rc;
         CUDA_TRY(cudaMemset(s->d_ready, 0, s->ready_cap * sizeof(uint32_t)));      // the frame kernel keeps it all-zero between launches
+        // the memset runs on the legacy stream, the frames on NON-BLOCKING streams, which it does not order: without this wait a
+        // frame kernel could start first and have its ready[] credits wiped under it (seen once as an expired queue wait)
+        CUDA_TRY(cudaDeviceSynchronize());
     }
     return CERES_OK;
 }
@@ -2087,6 +2097,7 @@ int ceres_peer_frame_create(ceres_scene* s, size_t width, size_t height, int wan
         e = cudaIpcGetMemHandle(&h, pf->base);
         if (e == cudaSuccess) { std::memset(handle_out, 0, CERES_PEER_HANDLE_BYTES); std::memcpy(handle_out, &h, sizeof(h)); }
     }
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();      // legacy-stream memsets are complete before any rank's (non-blocking) stream stores
     if (e != cudaSuccess) { cudaFree(pf->base); delete pf; return fail(CERES_ERR_CUDA, std::string("ceres_peer_frame_create: ") + cudaGetErrorString(e)); }
     peer_layout(pf);
     *out = pf;
@@ -2108,7 +2119,8 @@ int ceres_peer_frame_open(ceres_scene* s, const unsigned char* handle, size_t wi
     pf->base = base; pf->mapped = true; pf->device = s->device; pf->world = world; pf->rank = rank;
     pf->W = width; pf->H = height; pf->with_ids = want_ids != 0;
     peer_layout(pf);
-    if (cudaMalloc((void**)&pf->d_gate, 2 * sizeof(uint32_t)) != cudaSuccess || cudaMemset(pf->d_gate, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {
+    if (cudaMalloc((void**)&pf->d_gate, 2 * sizeof(uint32_t)) != cudaSuccess || cudaMemset(pf->d_gate, 0, 2 * sizeof(uint32_t)) != cudaSuccess ||
+        cudaDeviceSynchronize() != cudaSuccess) {
         cudaIpcCloseMemHandle(base); cudaFree(pf->d_gate); delete pf;
         return fail(CERES_ERR_CUDA, std::string("ceres_peer_frame_open: ") + cudaGetErrorString(cudaGetLastError()));
     }
@@ -2139,7 +2151,8 @@ int ceres_peer_frame_alias(ceres_peer_frame* owner, ceres_scene* s, int rank, ce
         // the relay starts at the owner's current epoch: everything up to it has been announced
         if (cudaMalloc((void**)&pf->d_gate, 2 * sizeof(uint32_t)) != cudaSuccess ||
             cudaMemcpy(pf->d_gate, &pf->epoch, sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess ||
-            cudaMemcpy(pf->d_gate + 1, &pf->epoch, sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess) {
+            cudaMemcpy(pf->d_gate + 1, &pf->epoch, sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaDeviceSynchronize() != cudaSuccess) {
             cudaFree(pf->d_gate); delete pf;
             return fail(CERES_ERR_CUDA, std::string("ceres_peer_frame_alias: ") + cudaGetErrorString(cudaGetLastError()));
         }
@@ -2496,6 +2509,7 @@ template <int BPC>
 static int render_quantized(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height, unsigned flags,
                             const ceres_shard* shard, uint8_t* rgb8, uint64_t counters[2]) {
     if (!s || !rgb8) return fail(CERES_ERR_INVALID, "ceres_render_ppm8/16: null argument");
+    CERES_REJECT_DURING_SEQUENCE(s, "ceres_render_ppm8/16");
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
     const bool sharded = shard && shard->count > 1;
@@ -2650,9 +2664,25 @@ int ceres_render_multi(ceres_scene* const* scenes, int n, const ceres_camera* ca
     return CERES_OK;
 }
 
+static int render_sequence_impl(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height, unsigned flags,
+                                int bytes_per_channel, void* out_all, uint64_t* counters_all);
+
 int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height,
                           unsigned flags, float* pixels_all, uint64_t* counters_all) {
-    if (!s || !cams || !pixels_all) return fail(CERES_ERR_INVALID, "ceres_render_sequence: null argument");
+    return render_sequence_impl(s, n_frames, cams, width, height, flags, 0, pixels_all, counters_all);
+}
+
+int ceres_render_sequence_payload(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height, unsigned flags,
+                                  int bytes_per_channel, uint8_t* payload_all, uint64_t* counters_all) {
+    if (bytes_per_channel != 1 && bytes_per_channel != 2) return fail(CERES_ERR_INVALID, "ceres_render_sequence_payload: bytes_per_channel is 1 or 2");
+    return render_sequence_impl(s, n_frames, cams, width, height, flags, bytes_per_channel, payload_all, counters_all);
+}
+
+static int render_sequence_impl(ceres_scene* s, size_t n_frames, const float* cams, size_t width, size_t height, unsigned flags,
+                                int bpc, void* out_all, uint64_t* counters_all) {
+    float* pixels_all = static_cast<float*>(out_all);
+    uint8_t* payload_all = static_cast<uint8_t*>(out_all);
+    if (!s || !cams || !out_all) return fail(CERES_ERR_INVALID, "ceres_render_sequence: null argument");
     // Every frame goes through the host-frame path of ceres_render: only the rectangles that hold hit pixels cross PCIe
     // (row bands copied while later bands still render) and the zeros around them are written by the host-fill pool.
     // Two frames are in flight at a time: a second set of per-frame resources (streams, record queue, staging frame,
@@ -2664,8 +2694,10 @@ int ceres_render_sequence(ceres_scene* s, size_t n_frames, const float* cams, si
         ceres_camera cam;
         for (int q = 0; q < 3; ++q) { cam.eye[q] = c[q]; cam.dir[q] = c[3 + q]; cam.up[q] = c[6 + q]; }
         cam.fov = c[9];
-        return ceres_render(v, &cam, c + 10, width, height, flags, pixels_all + k * npix * 3, nullptr,
-                            counters_all ? counters_all + 2 * k : nullptr);
+        uint64_t* cnt = counters_all ? counters_all + 2 * k : nullptr;
+        if (bpc == 1) return ceres_render_ppm8(v, &cam, c + 10, width, height, flags, payload_all + k * npix * 3, cnt);
+        if (bpc == 2) return ceres_render_ppm16(v, &cam, c + 10, width, height, flags, payload_all + k * npix * 6, cnt);
+        return ceres_render(v, &cam, c + 10, width, height, flags, pixels_all + k * npix * 3, nullptr, cnt);
     };
     static const bool serial = std::getenv("CERES_SEQUENCE_SERIAL") != nullptr;
     if (n_frames < 2 || s->stats || s->profile || serial) {

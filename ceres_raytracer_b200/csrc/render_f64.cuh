@@ -324,6 +324,7 @@ int ceres_scene_f64_create(const void* nodes_v, size_t node_count, const size_t*
     s->dev.pairs = (const f64::Child*)s->d_pairs; s->dev.tris = s->d_tris; s->dev.norms = s->d_norms; s->dev.slot_id = s->d_slot_id;
     s->dev.root_leaf_count = root_leaf_count;
     s->dev.n_pairs = (uint32_t)(pairs.size() / 2); s->dev.n_slots = (uint32_t)tri_count;
+    cudaDeviceSynchronize();                     // uploads (legacy stream) complete before the non-blocking band streams read them
 #ifdef CERES_CHECKED
     s->dev.check = s->d_counters + 4;
 #endif
@@ -446,6 +447,7 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
             if (!s->band_done[k]) CUDA_TRY(cudaEventCreateWithFlags(&s->band_done[k], cudaEventDisableTiming));
         }
         CUDA_TRY(cudaMemcpy(s->d_counters, &o, sizeof o, cudaMemcpyHostToDevice));
+        CUDA_TRY(cudaStreamSynchronize(0));      // a small pageable upload may still be in flight; the band streams are non-blocking
         if (kernel_ms) { CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventRecord(e0, 0)); CUDA_TRY(cudaEventSynchronize(e0)); }
         // Row bands of the rectangle, each on its own stream: kernel -> DMA of the band's float pixels into page-locked staging;
         // the host widens a band into the caller's double frame as soon as its copy has landed, while later bands render.

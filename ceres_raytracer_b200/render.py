@@ -319,6 +319,16 @@ class Scene:
         _capi.check(self._L.ceres_render_sequence(self._h, n, _p(cams), width, height, flags, _p(pixels_all), _p(cnt)))
         return pixels_all, cnt
 
+    def render_sequence_payload(self, cams, width, height, flags=0, bytes_per_channel=1, out=None):
+        """The sequence as quantised P6 payloads: (uint8[n,H,W,3] or big-endian uint16[n,H,W,3], counters[n,2])."""
+        cams = np.ascontiguousarray(cams, np.float32).reshape(-1, 13)
+        n = cams.shape[0]
+        if out is None:
+            out = np.empty((n, height, width, 3), np.uint8 if bytes_per_channel == 1 else ">u2")
+        cnt = np.zeros((n, 2), np.uint64)
+        _capi.check(self._L.ceres_render_sequence_payload(self._h, n, _p(cams), width, height, flags, int(bytes_per_channel), _p(out), _p(cnt)))
+        return out, cnt
+
     def trace_rays(self, rays):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         ids = np.empty(rays.shape[0], np.uint32)

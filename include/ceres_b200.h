@@ -238,6 +238,10 @@ int ceres_render_multi(ceres_scene* const* scenes, int n, const ceres_camera* ca
  * CERES_ERR_INVALID instead of racing with it. */
 int ceres_render_sequence(ceres_scene* scene, size_t n_frames, const float* cams, size_t width, size_t height,
                           unsigned flags, float* pixels_all, uint64_t* counters_all);
+/* The same sequence as quantised P6 payloads (bytes_per_channel 1: ceres_render_ppm8, 2: ceres_render_ppm16 per frame; flags may
+ * carry CERES_PAYLOAD_NO_FLIP, the row order of anim.cpp:117-119): payload_all = n_frames x 3*width*height*bytes_per_channel. */
+int ceres_render_sequence_payload(ceres_scene* scene, size_t n_frames, const float* cams, size_t width, size_t height,
+                                  unsigned flags, int bytes_per_channel, uint8_t* payload_all, uint64_t* counters_all);
 
 /* ---- render: device buffers (asynchronous; used by bench.py, multi-GPU gather and the host calls above) ------- */
 

@@ -711,3 +711,19 @@ def test_calls_during_a_sequence_fail_loudly(cr, dragon_pod):
             assert np.array_equal(px_all[k].view(np.uint32), want[0].view(np.uint32)) and tuple(int(x) for x in cnt[k]) == want[2]
         assert refused > 0
         s.refit()                                   # and the scene is free again afterwards
+
+
+def test_sequence_as_payloads(cr, dragon):
+    """ceres_render_sequence_payload: every frame of a camera path as 8- / 16-bit P6 payload equals the single-frame calls."""
+    W, H, n = 640, 360, 5
+    c = cr.configs.DRAGON_CAMERA
+    cams = np.tile(np.array(list(c.eye) + list(c.dir) + list(c.up) + [c.fov] + list(SUN), np.float32), (n, 1))
+    cams[:, 0] += np.linspace(0.0, 2.0, n, dtype=np.float32)             # the eye moves: the frames differ
+    for bpc, single in ((1, dragon.render_ppm8), (2, dragon.render_ppm16)):
+        for flags in (0, cr.PAYLOAD_NO_FLIP):
+            out, cnt = dragon.render_sequence_payload(cams, W, H, flags=flags, bytes_per_channel=bpc)
+            for k in range(n):
+                cam = cr.Camera(tuple(cams[k, 0:3]), tuple(cams[k, 3:6]), tuple(cams[k, 6:9]), float(cams[k, 9]))
+                want, wc = single(cam, cams[k, 10:13], W, H, flags=flags)
+                assert np.array_equal(out[k].view(np.uint8), want.view(np.uint8)) and tuple(int(x) for x in cnt[k]) == wc
+            assert not np.array_equal(out[0], out[-1])
