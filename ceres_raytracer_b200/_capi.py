@@ -10,6 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, PAYLOAD_NO_FLIP = 1, 2, 4, 8
 MISS = 0xFFFFFFFF
+STATIC_MAX_PIXELS = 1 << 20     # CERES_STATIC_MAX_PIXELS (ceres_render_device_static)
 
 
 class CeresError(RuntimeError):
@@ -50,7 +51,7 @@ SYMBOLS = [
     "ceres_peer_frame_invalidate",
 ]
 SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download",
-            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard", "ceres_build_options", "ceres_scene_stack_depth", "ceres_build_bvh", "ceres_scene_node_count", "ceres_render_sequence_payload"]
+            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard", "ceres_build_options", "ceres_scene_stack_depth", "ceres_build_bvh", "ceres_scene_node_count", "ceres_render_sequence_payload", "ceres_render_device_static"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -90,6 +91,7 @@ def lib():
     L.ceres_render_multi.argtypes = [C.POINTER(vp), C.c_int, camp, vp, sz, sz, C.c_uint, vp, vp, vp]
     L.ceres_render_sequence.argtypes = [vp, sz, vp, sz, sz, C.c_uint, vp, vp]
     L.ceres_render_device.argtypes = [vp, camp, vp, sz, sz, C.c_uint, shp, vp, vp, vp, vp]
+    L.ceres_render_device_static.argtypes = [vp, camp, vp, sz, sz, C.c_uint, vp, vp, vp, vp]
     L.ceres_scene_set_stats.argtypes = [vp, C.c_int]
     L.ceres_scene_get_stats.argtypes = [vp, vp]
     L.ceres_trace_rays.argtypes = [vp, vp, sz, vp, vp]

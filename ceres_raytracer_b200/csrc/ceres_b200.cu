@@ -24,6 +24,7 @@
 #include <string>
 #include <vector>
 #include <atomic>
+#include <mutex>
 #include <memory>
 #include <immintrin.h>
 #include <chrono>
@@ -2024,6 +2025,133 @@ int ceres_render_device(ceres_scene* s, const ceres_camera* cam, const float sun
     }
     s->rays_outside = 0;
     return render_rows(s, f, 0, rows_local, st, CERES_SUBFRAMES_DEVICE, CLEAR_OUTSIDE, [](uint32_t, uint32_t, uint32_t, cudaStream_t) { return (int)CERES_OK; });
+}
+
+}  // extern "C"
+
+// ---- ceres_render_device_static: the frame kernel over scratch that is never allocated (include/ceres_b200.h) ----
+// The frame kernel's scratch -- the record queue, its ready[] credits, one FrameCounters slot, a (rays, hits) pair -- in a
+// file-scope device array instead of the scene's cudaMalloc'ed, grow-on-demand buffers.  Every GPU that loads the library
+// holds CERES_STATIC_SCRATCH_BYTES of it until exit.  Layout: [control 256 B][ready[] STATIC_READY_WORDS][queue MAX_PIXELS].
+#define STATIC_MAX_SMS 256u
+#define STATIC_READY_WORDS ((((size_t)CERES_STATIC_MAX_PIXELS >> READY_MIN_SHIFT) + 2 + (size_t)STATIC_MAX_SMS * 16 * (FRAME_THREADS / 32) + 63) / 64 * 64)
+#define STATIC_CTL_BYTES 256
+#define STATIC_COUNTERS_OFFSET 128
+#define STATIC_READY_OFFSET ((size_t)STATIC_CTL_BYTES)
+#define STATIC_QUEUE_OFFSET (STATIC_READY_OFFSET + STATIC_READY_WORDS * sizeof(uint32_t))
+#define STATIC_SCRATCH_BYTES (STATIC_QUEUE_OFFSET + (size_t)CERES_STATIC_MAX_PIXELS * sizeof(uint4))
+static_assert(sizeof(FrameCounters) <= STATIC_COUNTERS_OFFSET, "control block layout");
+static_assert(STATIC_SCRATCH_BYTES == CERES_STATIC_SCRATCH_BYTES, "include/ceres_b200.h states the size of the static scratch");
+static_assert(STATIC_QUEUE_OFFSET % 256 == 0, "queue alignment");
+
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// The array keeps the last call's contents (a call that faulted or expired may have left anything): put the words the
+// frame kernel expects in their initial state -- ready[] all zero, the counter slot armed, the (rays, hits) pair zero.
+// Device code names the array directly; only the host needs its address (static_scratch_setup).
+__global__ void static_scratch_arm_kernel(uint32_t ready_words) {
+    uint32_t* ready = (uint32_t*)(g_static_scratch + STATIC_READY_OFFSET);
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < ready_words; k += gridDim.x * blockDim.x) ready[k] = 0u;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        FrameCounters c = {};
+        c.ext[0] = 0xFFFFFFFFu; c.ext[2] = 0xFFFFFFFFu;
+        *(FrameCounters*)g_static_scratch = c;
+        unsigned long long* out = (unsigned long long*)(g_static_scratch + STATIC_COUNTERS_OFFSET);
+        out[0] = 0ull; out[1] = 0ull;
+    }
+}
+
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+struct StaticScratchDev { unsigned char* ptr = nullptr; };
+static StaticScratchDev g_static_dev[64];
+static std::mutex g_static_mu;
+
+static int static_scratch_setup(int device, unsigned char** out) {       // the caller has made `device` current
+    if (device < 0 || device >= 64) return fail(CERES_ERR_INVALID, "ceres_render_device_static: device index out of range");
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    StaticScratchDev& d = g_static_dev[device];
+    if (!d.ptr) {
+        int cur = -1;
+        CUDA_TRY(cudaGetDevice(&cur));
+        if (cur != device) return fail(CERES_ERR_CUDA, "ceres_render_device_static: the scene's device is not current");
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || ((uintptr_t)p & 255u)) return fail(CERES_ERR_CUDA, "ceres_render_device_static: bad address for the static scratch");
+        d.ptr = (unsigned char*)p;
+    }
+    *out = d.ptr;
+    return CERES_OK;
+}
+
+extern "C" {
+
+int ceres_render_device_static(ceres_scene* s, const ceres_camera* cam, const float sun[3], size_t width, size_t height,
+                               unsigned flags, void* stream_v, float* d_pixels, uint32_t* d_ids, uint64_t* d_counters) {
+    CERES_REJECT_DURING_SEQUENCE(s, "ceres_render_device_static");
+    if (width && height && (uint64_t)width * height > (uint64_t)CERES_STATIC_MAX_PIXELS)
+        return fail(CERES_ERR_INVALID, "ceres_render_device_static: " + std::to_string(width) + " x " + std::to_string(height) +
+                                       " pixels exceed CERES_STATIC_MAX_PIXELS (" + std::to_string(CERES_STATIC_MAX_PIXELS) +
+                                       "), the size the static scratch was built for; use ceres_render_device");
+    if (flags & ~CERES_NO_SHADOWS) return fail(CERES_ERR_INVALID, "ceres_render_device_static: the only flag it takes is CERES_NO_SHADOWS");
+    if (s && (s->stats || s->dev.timeline || s->tune.variant != 0))
+        return fail(CERES_ERR_UNSUPPORTED, "ceres_render_device_static: statistics, timeline and tuning variants are ceres_render_device's");
+    if (s && s->sm_count > (int)STATIC_MAX_SMS) return fail(CERES_ERR_UNSUPPORTED, "ceres_render_device_static: more SMs than the static scratch was built for");
+    Frame f; uint32_t rows_local = 0;
+    if (int rc = prepare_frame(s, cam, sun, width, height, flags, nullptr, d_pixels, d_ids, d_counters, f, rows_local)) return rc;
+    DeviceGuard guard(s->device);
+    if (!guard.ok) return fail(CERES_ERR_CUDA, "ceres_render_device_static: cudaSetDevice failed");
+    unsigned char* scratch = nullptr;
+    if (int rc = static_scratch_setup(s->device, &scratch)) return rc;
+    cudaStream_t st = stream_v ? (cudaStream_t)stream_v : s->stream;
+
+    // one launch over the whole frame (what launch_rows does for band 0 of 1, with the scratch pointers replaced)
+    f.row_begin = 0; f.row_end = rows_local; f.accumulate = 1u;
+    f.ctr = (FrameCounters*)scratch;
+    f.out_counters = d_counters ? (unsigned long long*)d_counters : (unsigned long long*)(scratch + STATIC_COUNTERS_OFFSET);
+    f.out_stats = nullptr;
+    f.ready = (uint32_t*)(scratch + STATIC_READY_OFFSET);
+    f.queue = (uint4*)(scratch + STATIC_QUEUE_OFFSET);
+    f.out_error = s->d_out + 10;                       // ceres_scene_frame_error() reads it as for every other frame of the scene
+    f.queue_cap = rows_local * f.W;
+    f.ready_cap = (uint32_t)ready_words(s, f.queue_cap);
+    f.pix_rows = f.H;
+    f.rect_x0 = f.cull_i0; f.rect_x1 = f.cull_i1; f.rect_row0 = f.cull_l0; f.rect_row1 = std::max(f.cull_l1, f.cull_l0);
+    f.tiles_x = (f.rect_x1 - f.rect_x0 + 7u) / 8u;
+    f.tiles_y = (f.rect_row1 - f.rect_row0 + 3u) / 4u;
+    f.work_items = f.tiles_x * f.tiles_y * 32u;        // <= 32 * (MAX_PIXELS / 32 + edge tiles): far below 2^32
+    f.clear_rows = 1u;                                 // a caller-owned device frame: the kernel zeroes what it does not write
+    const uint64_t warps_guess = (uint64_t)s->sm_count * 8u * (FRAME_THREADS / 32);
+    const bool share = s->tune.reserved[0] ? s->tune.reserved[0] == 2u : f.work_items / warps_guess < FRAME_SHARE_AUTO_PX;
+    f.share_period = (s->tune.reserved[2] & 0xFFu) ? (s->tune.reserved[2] & 0xFFu) : FRAME_SHARE_PERIOD;
+    f.share_min_idle = ((s->tune.reserved[2] >> 8) & 0xFFu) ? ((s->tune.reserved[2] >> 8) & 0xFFu) : FRAME_SHARE_MIN_IDLE;
+    const uint32_t want = s->tune.shadow_block ? s->tune.shadow_block : FRAME_DEFAULT_CHUNK;
+    f.chunk_shift = want <= 8u ? 3u : want <= 16u ? 4u : 5u;
+    if (f.ready_cap > STATIC_READY_WORDS) return fail(CERES_ERR_INVALID, "internal: static ready[] too small");
+
+    const size_t smem = (size_t)s->dev.stack_depth * 4 * FRAME_THREADS;
+    const int order = s->tune.shadow_order == 1 ? ORDER_NEAR : s->tune.shadow_order == 2 ? ORDER_LEFT : FRAME_DEFAULT_SHADOW_ORDER;
+    auto go = [&](auto kernel, int slot) -> int {
+        int& bps = s->trace_blocks_per_sm[slot];       // the same cache (and values) as launch_rows
+        if (bps == 0) {
+            if (s->tune.ctas_per_sm) bps = (int)std::min(16u, s->tune.ctas_per_sm);
+            else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, FRAME_THREADS, smem));
+            if (bps < 1) bps = 1;
+            if (bps > 16) bps = 16;
+        }
+        if (d_counters) CUDA_TRY(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint64_t), st));
+        static_scratch_arm_kernel<<<(unsigned)std::min<uint32_t>((f.ready_cap + 255u) / 256u, (uint32_t)s->sm_count * 4u), 256, 0, st>>>(f.ready_cap);
+        g_launches++;
+        CUDA_TRY(cudaGetLastError());
+        kernel<<<(unsigned)(s->sm_count * bps), FRAME_THREADS, smem, st>>>(s->dev, f);
+        g_launches++;
+        CUDA_TRY(cudaGetLastError());
+        return CERES_OK;
+    };
+    s->rays_outside = 0;
+    const bool near = order == ORDER_NEAR;
+    return share ? (near ? go(frame_kernel<false, ORDER_NEAR, true, false>, 0) : go(frame_kernel<false, ORDER_LEFT, true, false>, 2))
+                 : (near ? go(frame_kernel<false, ORDER_NEAR, false, false>, 4) : go(frame_kernel<false, ORDER_LEFT, false, false>, 6));
 }
 
 // ---- peer frame (include/ceres_b200.h: "one frame on N GPUs, fused with its gather over NVLink peer memory") ----

@@ -14,7 +14,7 @@ from typing import Sequence
 import numpy as np
 
 from . import _capi
-from ._capi import NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, PAYLOAD_NO_FLIP, MISS, CeresError  # noqa: F401
+from ._capi import NO_SHADOWS, COMPACT_ROWS, FRAME_RETAINED, PAYLOAD_NO_FLIP, MISS, STATIC_MAX_PIXELS, CeresError  # noqa: F401
 
 NODE_DT = np.dtype([("bounds", "<f4", (6,)), ("primitive_count", "<u4"), ("first_child_or_primitive", "<u4")])
 NODE64_DT = np.dtype([("bounds", "<f8", (6,)), ("primitive_count", "<u8"), ("first_child_or_primitive", "<u8")])   # Bvh<double>::Node
@@ -346,6 +346,18 @@ class Scene:
         sh = _shard(shard)
         _capi.check(self._L.ceres_render_device(
             self._h, C.byref(camera.c()), _p(sun), width, height, flags, C.byref(sh) if sh is not None else None,
+            C.c_void_p(stream), C.c_void_p(pixels.data_ptr()), C.c_void_p(ids.data_ptr()) if ids is not None else None,
+            C.c_void_p(counters.data_ptr()) if counters is not None else None))
+
+    def render_device_static(self, camera, sun_position, width, height, flags=0, pixels=None, ids=None, counters=None,
+                             stream=None):
+        """render_device over the library's static device scratch: the call allocates nothing (ceres_render_device_static,
+        include/ceres_b200.h; no counterpart in the reference).  width * height <= STATIC_MAX_PIXELS, whole frames only;
+        all calls on a device share the scratch, so calls that overlap on the GPU race."""
+        stream = _stream_handle(stream, self.device)
+        sun = np.asarray(sun_position, np.float32)
+        _capi.check(self._L.ceres_render_device_static(
+            self._h, C.byref(camera.c()), _p(sun), width, height, flags,
             C.c_void_p(stream), C.c_void_p(pixels.data_ptr()), C.c_void_p(ids.data_ptr()) if ids is not None else None,
             C.c_void_p(counters.data_ptr()) if counters is not None else None))
 

@@ -255,6 +255,26 @@ int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const fl
                         size_t width, size_t height, unsigned flags, const ceres_shard* shard, void* stream,
                         float* d_pixels, uint32_t* d_ids, uint64_t* d_counters);
 
+/* ceres_render_device for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same frame, same kernel, same outputs as ceres_render_device(shard = NULL); the difference is where the frame kernel's
+ * scratch lives (record queue, its ready[] credits, the counter slot): in a file-scope `static __device__` array of
+ * CERES_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit, instead of the scene's grow-on-demand
+ * cudaMalloc'ed buffers.  The call performs no cudaMalloc / cudaFree / allocating library routine -- only
+ * cudaGetSymbolAddress on the first call per device, then async memset + 2 kernel launches on `stream`.
+ * Limits: width * height <= CERES_STATIC_MAX_PIXELS (larger frames are refused with CERES_ERR_INVALID and a message that
+ * names the limit); whole frames only (no shard); flags: CERES_NO_SHADOWS only; statistics / timeline modes and tuning
+ * variants are refused (CERES_ERR_UNSUPPORTED).  d_ids / d_counters nullable as above.
+ * ALL calls on a device share the one array, whatever the scene or stream: the call re-initialises what must start at zero,
+ * but two calls that overlap on the GPU (different streams, or different scenes' default streams) RACE -- keep them in
+ * one stream or order them with events.  It does not touch the scene's own queue, so it does not wait for, or hold up,
+ * the scene's ceres_render_device frames. */
+#define CERES_STATIC_MAX_PIXELS (1u << 20)          /* e.g. 1024 x 1024, 1280 x 720 */
+#define CERES_STATIC_SCRATCH_BYTES 17367552u        /* 16 MiB of records + 576 KiB of credits + 256 B of counters */
+int ceres_render_device_static(ceres_scene* scene, const ceres_camera* camera, const float sun_position[3],
+                               size_t width, size_t height, unsigned flags, void* stream,
+                               float* d_pixels, uint32_t* d_ids, uint64_t* d_counters);
+
 /* ---- render: one frame on N GPUs, fused with its "gather" over NVLink peer memory ------------
  * One process per GPU.  Rank 0 owns the frame: a device allocation holding the float RGB frame (+ optional ids) and
  * a small control block; the other ranks map it (CUDA IPC) and their kernels store the pixels of their row blocks
