@@ -51,7 +51,7 @@ SYMBOLS = [
     "ceres_peer_frame_invalidate",
 ]
 SYMBOLS += ["ceres_render_ppm8", "ceres_render_ppm16", "ceres_probe_read_bandwidth", "ceres_build_lbvh", "ceres_scene_create_lbvh", "ceres_scene_f64_create", "ceres_scene_f64_destroy", "ceres_render_f64", "ceres_scene_get_step_histogram", "ceres_scene_last_d2h_bytes", "ceres_scene_rotate", "ceres_scene_transform", "ceres_scene_refit", "ceres_scene_download",
-            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard", "ceres_build_options", "ceres_scene_stack_depth", "ceres_build_bvh", "ceres_scene_node_count", "ceres_render_sequence_payload", "ceres_render_device_static"]
+            "ceres_scene_last_rectangle", "ceres_probe_host_fill_bandwidth", "ceres_scene_get_timeline", "ceres_scene_set_timeline", "ceres_scene_frame_error", "ceres_build_is_checked", "ceres_render_ppm8_shard", "ceres_render_ppm16_shard", "ceres_build_options", "ceres_scene_stack_depth", "ceres_build_bvh", "ceres_scene_node_count", "ceres_render_sequence_payload", "ceres_render_device_static", "ceres_render_f64_shard"]
 PEER_HANDLE_BYTES = 64
 
 _lib = None
@@ -129,6 +129,7 @@ def lib():
     L.ceres_scene_f64_destroy.argtypes = [vp]
     L.ceres_scene_f64_destroy.restype = None
     L.ceres_render_f64.argtypes = [vp, vp, vp, sz, sz, C.c_uint, vp, vp, vp, vp]
+    L.ceres_render_f64_shard.argtypes = [vp, vp, vp, sz, sz, C.c_uint, shp, vp, vp, vp, vp]
     L.ceres_scene_get_step_histogram.argtypes = [vp, vp]
     L.ceres_scene_last_d2h_bytes.argtypes = [vp]
     L.ceres_scene_last_d2h_bytes.restype = u64

@@ -44,7 +44,8 @@ struct Scene64 {
 struct Frame64 {
     double eye[3], dir[3], iu[3], iv[3], sun[3];
     uint32_t width, height, flags;
-    uint32_t x0, y0, x1, y1;        // pixels [x0, x1) x [y0, y1) of the frame are rendered by this launch (a row band of the screen rectangle)
+    uint32_t x0, y0, x1, y1;        // columns [x0, x1) x LOCAL rows [y0, y1) are rendered by this launch (a row band of the screen rectangle)
+    uint32_t blk_rows, sh_index, sh_count;   // row-block shard (ceres_shard): local row -> frame row; count <= 1: local row = frame row
     float* rgb; uint32_t* ids;      // the colours are float-valued (render.hpp:56-84): 3 floats per pixel on the device
     unsigned long long* counters;   // rays beyond W*H (= primary hits), hits
     int* rect;                      // min i, min j, max i, max j over the pixels whose primary ray hit
@@ -165,10 +166,12 @@ __device__ __forceinline__ void smooth_shading(D3 sun_line, const double* nm, D3
 __global__ void __launch_bounds__(128) render_kernel(const Scene64 sc, const Frame64 f) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t i = f.x0 + blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t j = f.y0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    const uint32_t lr = f.y0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+    uint32_t j = lr;                                                   // frame row of this local row
+    if (f.sh_count > 1u) { const uint32_t blk = lr / f.blk_rows; j = (blk * f.sh_count + f.sh_index) * f.blk_rows + (lr - blk * f.blk_rows); }
     unsigned int primary_hit = 0, hits = 0;
-    if (i < f.x1 && j < f.y1) {
-        const size_t pix = (size_t)f.width * j + i;
+    if (i < f.x1 && lr < f.y1) {
+        const size_t pix = (size_t)f.width * lr + i;                  // device buffers are packed by local row
         const double u = sub(__ddiv_rn(mul(2.0, add((double)i, 0.5)), (double)f.width), 1.0);      // render.hpp:109-110
         const double v = sub(__ddiv_rn(mul(2.0, add((double)j, 0.5)), (double)f.height), 1.0);
         const D3 view = normalize({add(add(mul(f.iu[0], u), mul(f.iv[0], v)), f.dir[0]), add(add(mul(f.iu[1], u), mul(f.iv[1], v)), f.dir[1]),
@@ -343,11 +346,22 @@ void ceres_scene_f64_destroy(ceres_scene_f64* s) {
     delete s;
 }
 
-int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height, unsigned flags,
-                     double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms) {
+// One frame, or one row-block shard of it (shard != null, count > 1: only the shard's rows of the full-size frame are
+// written -- zeros included -- and the counters are the shard's: rays = own rows * width + own primary hits).
+static int render_f64_impl(ceres_scene_f64* s, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height, unsigned flags,
+                           const ceres_shard* shard, double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms) {
     if (!s || !cam || !sun || !pixels) return fail(CERES_ERR_INVALID, "ceres_render_f64: null argument");
     if (!width || !height || (uint64_t)width * height >= (1ull << 31)) return fail(CERES_ERR_INVALID, "ceres_render_f64: bad image size");
     if ((height + 7) / 8 > 65535u) return fail(CERES_ERR_INVALID, "ceres_render_f64: image too tall");
+    const bool sharded = shard && shard->count > 1;
+    if (sharded && (shard->block_rows == 0 || shard->index >= shard->count)) return fail(CERES_ERR_INVALID, "ceres_render_f64: bad shard");
+    // the rows this call owns, as runs [first, second) of frame rows in ascending order (block b -> shard b % count)
+    std::vector<std::pair<size_t, size_t>> own;
+    size_t own_rows = 0;
+    if (!sharded) own.push_back({0, height});
+    else for (size_t b = shard->index; b * shard->block_rows < height; b += shard->count)
+        own.push_back({b * shard->block_rows, std::min<size_t>(height, (b + 1) * shard->block_rows)});
+    for (auto& r : own) own_rows += r.second - r.first;
     DeviceGuard guard(s->device);
     const size_t npix = width * height;
     if (s->pixels_cap < npix) {
@@ -407,19 +421,33 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
             y0 = (size_t)lo_px(vmin, (double)height); y1 = std::max(y0, (size_t)hi_px(vmax, (double)height));
         }
     }
-    const size_t rw = x1 - x0, rh = y1 - y0;
+    // the rectangle's rows in LOCAL rows of this shard (frame_row is increasing in the local row)
+    auto frame_row = [&](size_t lr) -> size_t {
+        if (!sharded) return lr;
+        const size_t blk = lr / shard->block_rows;
+        return (blk * shard->count + shard->index) * shard->block_rows + (lr - blk * shard->block_rows);
+    };
+    size_t l0 = 0;
+    while (l0 < own_rows && frame_row(l0) < y0) ++l0;
+    size_t l1 = l0;
+    while (l1 < own_rows && frame_row(l1) < y1) ++l1;
+    const size_t rw = x1 - x0, rh = l1 - l0;
     const bool any = rw > 0 && rh > 0;
+    f.blk_rows = sharded ? shard->block_rows : 0u; f.sh_index = sharded ? shard->index : 0u; f.sh_count = sharded ? shard->count : 1u;
     // zeros (ids: CERES_MISS) outside the rectangle: host pool, from now on
     ceres_host::Job zeros;
     {
         auto outside = [&](unsigned char* base, size_t px_bytes, unsigned char byte) {
-            if (!any) { zeros.add(base, npix * px_bytes, byte); return; }
-            zeros.add(base, width * y0 * px_bytes, byte);
-            zeros.add(base + width * y1 * px_bytes, width * (height - y1) * px_bytes, byte);
-            for (size_t j = y0; j < y1; ++j) {
-                unsigned char* row = base + width * j * px_bytes;
-                if (x0) zeros.segs.push_back({row, x0 * px_bytes, byte});
-                if (x1 < width) zeros.segs.push_back({row + x1 * px_bytes, (width - x1) * px_bytes, byte});
+            for (auto& r : own) {
+                if (!any) { zeros.add(base + width * r.first * px_bytes, width * (r.second - r.first) * px_bytes, byte); continue; }
+                const size_t a = std::min(r.second, std::max(r.first, y0)), b = std::max(a, std::min(r.second, y1));   // rows [a, b) cross the rectangle
+                if (a > r.first) zeros.add(base + width * r.first * px_bytes, width * (a - r.first) * px_bytes, byte);
+                if (r.second > b) zeros.add(base + width * b * px_bytes, width * (r.second - b) * px_bytes, byte);
+                for (size_t j = a; j < b; ++j) {
+                    unsigned char* row = base + width * j * px_bytes;
+                    if (x0) zeros.segs.push_back({row, x0 * px_bytes, byte});
+                    if (x1 < width) zeros.segs.push_back({row + x1 * px_bytes, (width - x1) * px_bytes, byte});
+                }
             }
         };
         outside(reinterpret_cast<unsigned char*>(pixels), 24, 0x00);
@@ -451,30 +479,34 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
         if (kernel_ms) { CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1)); CUDA_TRY(cudaEventRecord(e0, 0)); CUDA_TRY(cudaEventSynchronize(e0)); }
         // Row bands of the rectangle, each on its own stream: kernel -> DMA of the band's float pixels into page-locked staging;
         // the host widens a band into the caller's double frame as soon as its copy has landed, while later bands render.
+        // Row bands of the rectangle IN LOCAL ROWS (a shard's rows are packed on the device), each on its own stream:
+        // kernel -> DMA of the band's float pixels into page-locked staging; the host widens a band into the caller's double
+        // frame -- at its frame rows -- as soon as its copy has landed, while later bands render.
         const size_t nb = std::max<size_t>(1, std::min<size_t>(4, (rw * rh) >> 18));
         const size_t band_rows = ((rh + nb - 1) / nb + 7) / 8 * 8;
         size_t launched = 0;
-        for (size_t k = 0, r0 = y0; r0 < y1; ++k, r0 += band_rows) {
-            const size_t r1 = std::min(y1, r0 + band_rows);
+        for (size_t k = 0, r0 = l0; r0 < l1; ++k, r0 += band_rows) {
+            const size_t r1 = std::min(l1, r0 + band_rows);
             f.x0 = (uint32_t)x0; f.x1 = (uint32_t)x1; f.y0 = (uint32_t)r0; f.y1 = (uint32_t)r1;
             cudaStream_t st = s->band_stream[k];
             f64::render_kernel<<<dim3((unsigned)((rw + 15) / 16), (unsigned)((r1 - r0 + 7) / 8)), 128, 0, st>>>(s->dev, f);
             g_launches++;
             err = cudaGetLastError();
-            if (err == cudaSuccess) err = cudaMemcpy2DAsync(s->h_rgb + 3 * rw * (r0 - y0), rw * 12, s->d_rgb + 3 * (width * r0 + x0), width * 12, rw * 12, r1 - r0, cudaMemcpyDeviceToHost, st);
-            if (err == cudaSuccess && ids) err = cudaMemcpy2DAsync(s->h_ids + rw * (r0 - y0), rw * 4, s->d_ids + (width * r0 + x0), width * 4, rw * 4, r1 - r0, cudaMemcpyDeviceToHost, st);
+            if (err == cudaSuccess) err = cudaMemcpy2DAsync(s->h_rgb + 3 * rw * (r0 - l0), rw * 12, s->d_rgb + 3 * (width * r0 + x0), width * 12, rw * 12, r1 - r0, cudaMemcpyDeviceToHost, st);
+            if (err == cudaSuccess && ids) err = cudaMemcpy2DAsync(s->h_ids + rw * (r0 - l0), rw * 4, s->d_ids + (width * r0 + x0), width * 4, rw * 4, r1 - r0, cudaMemcpyDeviceToHost, st);
             if (err == cudaSuccess) err = cudaEventRecord(s->band_done[k], st);
             if (err != cudaSuccess) break;
             launched = k + 1;
         }
-        for (size_t k = 0, r0 = y0; k < launched; ++k, r0 += band_rows) {
-            const size_t r1 = std::min(y1, r0 + band_rows);
+        for (size_t k = 0, r0 = l0; k < launched; ++k, r0 += band_rows) {
+            const size_t r1 = std::min(l1, r0 + band_rows);
             const cudaError_t e = cudaEventSynchronize(s->band_done[k]);
             if (e != cudaSuccess) { if (err == cudaSuccess) err = e; continue; }
             auto body = std::make_unique<ceres_host::Job>();
-            for (size_t j = r0; j < r1; ++j) {
-                body->add_widen(pixels + 3 * (width * j + x0), s->h_rgb + 3 * rw * (j - y0), 3 * rw);
-                if (ids) body->add_copy(ids + width * j + x0, s->h_ids + rw * (j - y0), rw * 4);
+            for (size_t lr = r0; lr < r1; ++lr) {
+                const size_t j = frame_row(lr);
+                body->add_widen(pixels + 3 * (width * j + x0), s->h_rgb + 3 * rw * (lr - l0), 3 * rw);
+                if (ids) body->add_copy(ids + width * j + x0, s->h_ids + rw * (lr - l0), rw * 4);
             }
             pool.submit(body.get());
             bodies.push_back(std::move(body));
@@ -502,8 +534,18 @@ int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const doub
     for (auto& j : bodies) pool.wait(j.get());
     if (err != cudaSuccess) return fail(CERES_ERR_CUDA, std::string("ceres_render_f64: ") + cudaGetErrorString(err));
     const unsigned long long c[2] = {o.c[0], o.c[1]};
-    if (counters) { counters[0] = (uint64_t)npix + c[0]; counters[1] = c[1]; }      // render.hpp:115,138 / :119,148
+    if (counters) { counters[0] = (uint64_t)own_rows * width + c[0]; counters[1] = c[1]; }      // render.hpp:115,138 / :119,148
     return CERES_OK;
+}
+
+int ceres_render_f64(ceres_scene_f64* s, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height, unsigned flags,
+                     double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms) {
+    return render_f64_impl(s, cam, sun, width, height, flags, nullptr, pixels, ids, counters, kernel_ms);
+}
+
+int ceres_render_f64_shard(ceres_scene_f64* s, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height, unsigned flags,
+                           const ceres_shard* shard, double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms) {
+    return render_f64_impl(s, cam, sun, width, height, flags, shard, pixels, ids, counters, kernel_ms);
 }
 
 }  // extern "C"

@@ -448,9 +448,11 @@ class SceneF64:
     def from_pod(cls, pod, device=0):
         return cls(pod["nodes"], pod["prim_indices"], pod["triangles"], pod.get("norms"), device=device)
 
-    def render(self, camera, sun_position, width, height, flags=0, want_ids=False, pixels=None):
+    def render(self, camera, sun_position, width, height, flags=0, want_ids=False, pixels=None, shard=None, ids=None):
         """Returns (pixels float64[H, W, 3], ids uint32[H, W] or None, (rays, hits)); camera: Camera or 10 numbers.  pixels: an
-        existing C-contiguous float64 frame to fill (the frame loop of anim.cpp:76-105 reuses one)."""
+        existing C-contiguous float64 frame to fill (the frame loop of anim.cpp:76-105 reuses one).  shard = (block_rows,
+        index, count): only that shard's rows of the full-size pixels / ids are written and the counters are the shard's
+        (ceres_render_f64_shard); pass the same pixels / ids to every shard's call to assemble the frame."""
         cam = _capi.CameraF64()
         vals = (list(camera.eye) + list(camera.dir) + list(camera.up) + [camera.fov]) if hasattr(camera, "eye") else [float(x) for x in camera]
         for k in range(3):
@@ -460,10 +462,17 @@ class SceneF64:
             pixels = np.empty((height, width, 3), np.float64)
         elif pixels.dtype != np.float64 or not pixels.flags.c_contiguous or pixels.size != 3 * width * height:
             raise ValueError("pixels must be a C-contiguous float64 buffer of 3*width*height")
-        ids = np.empty((height, width), np.uint32) if want_ids else None
+        if ids is not None and (ids.dtype != np.uint32 or not ids.flags.c_contiguous or ids.size != width * height):
+            raise ValueError("ids must be a C-contiguous uint32 buffer of width*height")
+        if ids is None and want_ids:
+            ids = np.empty((height, width), np.uint32)
         sun = np.ascontiguousarray(sun_position, np.float64)
         cnt, ms = np.zeros(2, np.uint64), C.c_double(0.0)
-        _capi.check(self._L.ceres_render_f64(self._h, C.byref(cam), _p(sun), width, height, flags, _p(pixels), _p(ids), _p(cnt), C.byref(ms)))
+        sh = _shard(shard)
+        if sh is None:
+            _capi.check(self._L.ceres_render_f64(self._h, C.byref(cam), _p(sun), width, height, flags, _p(pixels), _p(ids), _p(cnt), C.byref(ms)))
+        else:
+            _capi.check(self._L.ceres_render_f64_shard(self._h, C.byref(cam), _p(sun), width, height, flags, C.byref(sh), _p(pixels), _p(ids), _p(cnt), C.byref(ms)))
         self.kernel_ms = float(ms.value)
         return pixels, ids, (int(cnt[0]), int(cnt[1]))
 

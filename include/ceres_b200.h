@@ -173,7 +173,10 @@ int ceres_scene_create_lbvh(const void* tris, const void* norms, size_t tri_coun
  * (obj_norms.hpp:113-115; nullable), prim_idx as for ceres_scene_create.  pixels: HOST 3 * width * height doubles,
  * layout 3 * (width * j + i) (render.hpp:107); ids (nullable): HOST width * height primitive indices, CERES_MISS where
  * nothing was hit; counters = the pair of render.hpp:155; flags: CERES_NO_SHADOWS.  kernel_ms (nullable): device time
- * of the frame's kernel.  One kernel, one device, no sharding: a completeness path next to the float one. */
+ * of the frame's kernels.  ceres_render_f64_shard: the float path's row-block sharding (ceres_shard; one scene per GPU,
+ * `pixels` / `ids` = the FULL-SIZE frame, of which the call writes only the shard's rows, zeros included; counters = the
+ * shard's: rays = own rows * width + own primary hits) -- the shards of a frame add up to ceres_render_f64's frame and
+ * counters exactly (pixels are independent, render.hpp:104). */
 typedef struct ceres_scene_f64 ceres_scene_f64;
 typedef struct ceres_camera_f64 {   /* Camera<double>, include/render.hpp:16-22 (fov in degrees) */
     double eye[3];
@@ -186,6 +189,9 @@ int ceres_scene_f64_create(const void* nodes, size_t node_count, const size_t* p
 void ceres_scene_f64_destroy(ceres_scene_f64* scene);
 int ceres_render_f64(ceres_scene_f64* scene, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height,
                      unsigned flags, double* pixels, uint32_t* ids, uint64_t counters[2], double* kernel_ms);
+int ceres_render_f64_shard(ceres_scene_f64* scene, const ceres_camera_f64* cam, const double sun[3], size_t width, size_t height,
+                           unsigned flags, const ceres_shard* shard, double* pixels, uint32_t* ids, uint64_t counters[2],
+                           double* kernel_ms);
 
 /* ---- render: host buffers (the drop-in for render.hpp:86-156) ------------------------------------------------ */
 

@@ -92,3 +92,36 @@ def test_f64_leaf_root_and_errors(cr):
     bad[0]["first_child_or_primitive"] = 7
     with pytest.raises(cr.CeresError):
         cr.SceneF64(bad, np.zeros(1, np.uint64), tri)
+
+
+@pytest.mark.parametrize("count,block_rows,W,H", [(2, 16, 640, 360), (8, 16, 640, 360), (3, 5, 333, 97), (8, 64, 200, 100)])
+def test_f64_row_block_shards_assemble_the_frame(cr, dragon_pod, count, block_rows, W, H):
+    """The float path's row-block sharding on the double path (anim.cpp:146-155 at scale; SURVEY.md 8(e): render the N
+    shards one after the other into ONE frame and require byte-equality with the unsharded frame).  Every shard writes all of
+    its own rows (zeros included) and nothing else; the shards' counters add up to the frame's."""
+    pod = f64.widen(dragon_pod)
+    c = cr.configs.DRAGON_CAMERA
+    cam = f64.cam_array(c.eye, c.dir, c.up, c.fov)
+    sun = np.array([-50., -20., 0.])
+    with cr.SceneF64.from_pod(pod) as s:
+        ref_px, ref_ids, ref_cnt = s.render(cam, sun, W, H, want_ids=True)
+        px = np.full((H, W, 3), np.nan)
+        ids = np.full((H, W), 12345, np.uint32)
+        rays = hits = 0
+        for k in range(count):
+            before_px, before_ids = px.copy(), ids.copy()
+            _, _, (r, h) = s.render(cam, sun, W, H, pixels=px, ids=ids, shard=(block_rows, k, count))
+            rows = cr.shard_rows(H, (block_rows, k, count))
+            others = np.setdiff1d(np.arange(H), rows)
+            assert np.array_equal(px[rows].view(np.uint64), ref_px[rows].view(np.uint64)) and np.array_equal(ids[rows], ref_ids[rows])
+            assert np.array_equal(px[others].view(np.uint64), before_px[others].view(np.uint64)), "a shard wrote outside its rows"
+            assert np.array_equal(ids[others], before_ids[others])
+            assert r == len(rows) * W + int((ref_ids[rows] != cr.MISS).sum())
+            rays += r
+            hits += h
+        assert np.array_equal(px.view(np.uint64), ref_px.view(np.uint64)) and np.array_equal(ids, ref_ids)
+        assert (rays, hits) == ref_cnt
+        with pytest.raises(cr.CeresError):
+            s.render(cam, sun, W, H, pixels=px, shard=(0, 1, 2))
+        with pytest.raises(cr.CeresError):
+            s.render(cam, sun, W, H, pixels=px, shard=(16, 2, 2))
