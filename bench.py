@@ -683,6 +683,10 @@ def main():
             hb16.close()
             extra["e2e_ppm8"] = ppm8
             extra["e2e_shim"] = shim_bench(pod, cam, sun, W, H, steps_e2e, rays_frame, hits_frame)
+            try:
+                extra["device_built_tree"] = device_tree_block(scene, pod, cam, sun, W, H, flags, dev)
+            except Exception as e:      # next-row measurement: never takes the headline down with it
+                extra["device_built_tree"] = {"error": str(e)}
         else:
             # N > 1: one HOST frame shared by the ranks (page-locked in every process); each rank renders its row blocks and
             # DMA-writes them in place over its own PCIe link; the counter barrier in the shared control page completes it.
@@ -817,6 +821,41 @@ def main():
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def device_tree_block(scene, pod, cam, sun, W, H, flags, dev, frames=20):
+    """N3: the same frame from the tree the LIBRARY builds on the device (ceres_scene_create_lbvh, default
+    builder) next to the caller's reference-built tree, both device-resident, back-to-back frames, CUDA events."""
+    import torch
+    import ceres_raytracer_b200 as cr
+    px = torch.empty(H * W * 3, dtype=torch.float32, device=dev)
+    cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+
+    def ms_per_frame(sc, ids=None):
+        for _ in range(3):
+            sc.render_device(cam, sun, W, H, flags=flags, pixels=px, ids=ids, counters=cnt)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(frames):
+            sc.render_device(cam, sun, W, H, flags=flags, pixels=px, counters=cnt)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / frames
+
+    ids_a = torch.empty(H * W, dtype=torch.int32, device=dev)
+    ms_ref = ms_per_frame(scene, ids_a)
+    cnt_ref = cnt.cpu().tolist()
+    cr.Scene.from_lbvh(pod["triangles"], pod["norms"], device=dev.index or 0).close()      # allocator / module warm-up
+    with cr.Scene.from_lbvh(pod["triangles"], pod["norms"], device=dev.index or 0) as s2:
+        ids_b = torch.empty(H * W, dtype=torch.int32, device=dev)
+        ms = ms_per_frame(s2, ids_b)
+        return {"builder": "level-synchronous top-down binned SAH + SAH leaf collapsing (ceres_scene_create_lbvh, default options)",
+                "triangles": int(pod["triangles"].shape[0]), "nodes": int(s2.node_count), "reference_tree_nodes": int(pod["nodes"].shape[0]),
+                "build_kernels_ms": s2.build_ms, "stack_depth": s2.stack_depth,
+                "ms_per_step": ms, "reference_tree_ms_per_step": ms_ref, "vs_reference_tree": ms / ms_ref,
+                "counters_equal": cnt.cpu().tolist() == cnt_ref, "hit_ids_differing": int((ids_a != ids_b).sum().item()),
+                "note": "frames back to back, L2 not flushed, both trees timed the same way here; ids may differ where two triangles are hit "
+                        "at exactly the same t (SURVEY.md 7.3-H2): parity of this tree is against the oracle walking it (tests/test_gpu_lbvh.py)"}
 
 
 def shim_bench(pod, cam, sun, W, H, frames, rays, hits):

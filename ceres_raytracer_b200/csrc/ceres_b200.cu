@@ -1097,13 +1097,15 @@ int ceres_scene_download(ceres_scene* s, void* nodes_out, size_t node_count, voi
 // ---- BVH construction on the GPU (lbvh_build.cuh) -----------------------------------------------------
 namespace {
 // Working set of one GPU build (lbvh_build.cuh); everything stays on the device until the caller picks what it needs.
-int g_build_algorithm = 0, g_build_radius = 8;      // ceres_build_options: 0 = PLOC over the Morton order (default), 1 = radix tree only
+int g_build_algorithm = 2, g_build_radius = 8;      // ceres_build_options: 2 = top-down binned SAH (default), 3 = PLOC over the Morton order, 1 = radix tree only
 int g_build_max_leaf = 8; float g_build_ci = 1.5f;   // leaf collapsing: triangles per leaf at most (1 = off), cost of a triangle test in node steps
 struct LbvhWork {
     float* box = nullptr; unsigned int* scene = nullptr;
     uint32_t* cid[2] = {nullptr, nullptr}; float* cbox[2] = {nullptr, nullptr}; uint32_t* nn = nullptr;       // PLOC
     unsigned long long *flag = nullptr, *scan = nullptr; PlocState* st = nullptr; void* scan_tmp = nullptr; size_t scan_tmp_bytes = 0;
     int rounds = 0;
+    SahTask* s_task = nullptr; uint32_t *s_node_of = nullptr, *s_open[2] = {nullptr, nullptr}, *s_open_few[2] = {nullptr, nullptr};   // top-down SAH
+    uint32_t *s_bins = nullptr, *s_bins_few = nullptr; SahState* s_st = nullptr;
     uint32_t *c_cnt = nullptr, *c_col = nullptr, *c_rank = nullptr, *c_arr = nullptr, *idx3 = nullptr; float* c_cost = nullptr;   // leaf collapsing
     uint32_t *c_keep = nullptr, *c_newid = nullptr, *c_fl = nullptr; LbvhNode* nodes2 = nullptr;
     size_t node_count = 0;                                   // nodes of the final tree (2 leaves - 1)
@@ -1115,6 +1117,8 @@ struct LbvhWork {
         cudaFree(child); cudaFree(pi); cudaFree(pl); cudaFree(arr); cudaFree(nodes); cudaFree(tmp);
         cudaFree(c_cnt); cudaFree(c_col); cudaFree(c_rank); cudaFree(c_arr); cudaFree(idx3); cudaFree(c_cost); cudaFree(c_keep); cudaFree(c_newid); cudaFree(c_fl);
         cudaFree(nodes2);
+        cudaFree(s_task); cudaFree(s_node_of); cudaFree(s_open[0]); cudaFree(s_open[1]); cudaFree(s_open_few[0]); cudaFree(s_open_few[1]);
+        cudaFree(s_bins); cudaFree(s_bins_few); cudaFree(s_st);
         cudaFree(cid[0]); cudaFree(cid[1]); cudaFree(cbox[0]); cudaFree(cbox[1]); cudaFree(nn); cudaFree(flag); cudaFree(scan); cudaFree(st); cudaFree(scan_tmp);
         if (e0) cudaEventDestroy(e0);
         if (e1) cudaEventDestroy(e1);
@@ -1134,7 +1138,18 @@ int lbvh_run(const float4* d_tris, int n, LbvhWork& w, float* ms_out) {
     TRY_B(cudaMalloc((void**)&w.nodes, (2 * tc - 1) * sizeof(LbvhNode)));
     TRY_B(cub::DeviceRadixSort::SortPairs(nullptr, w.tmp_bytes, w.code, w.code2, w.idx, w.idx2, n, 0, 30));
     TRY_B(cudaMalloc(&w.tmp, w.tmp_bytes ? w.tmp_bytes : 16));
-    const bool ploc = g_build_algorithm == 0 && n > 2;
+    const bool sah = g_build_algorithm == 2 && n > 2;
+    const bool ploc = g_build_algorithm == 3 && n > 2;
+    const size_t sah_max_open = tc / (SAH_FEW + 1) + 1, sah_max_few = tc / 3 + 1;      // an open task has more than SAH_FEW members, or at least 3
+    if (sah) {
+        TRY_B(cudaMalloc((void**)&w.cid[0], tc * 4)); TRY_B(cudaMalloc((void**)&w.cbox[0], tc * 24));
+        TRY_B(cudaMalloc((void**)&w.s_task, (2 * tc + 2) * sizeof(SahTask)));
+        TRY_B(cudaMalloc((void**)&w.s_node_of, tc * 4));
+        for (int k = 0; k < 2; ++k) { TRY_B(cudaMalloc((void**)&w.s_open[k], sah_max_open * 4)); TRY_B(cudaMalloc((void**)&w.s_open_few[k], sah_max_few * 4)); }
+        TRY_B(cudaMalloc((void**)&w.s_bins, sah_max_open * SAH_TASK_WORDS * 4));
+        TRY_B(cudaMalloc((void**)&w.s_bins_few, sah_max_few * SAH_TASK_WORDS_FEW * 4));
+        TRY_B(cudaMalloc((void**)&w.s_st, sizeof(SahState)));
+    }
     if (ploc) {
         for (int k = 0; k < 2; ++k) { TRY_B(cudaMalloc((void**)&w.cid[k], tc * 4)); TRY_B(cudaMalloc((void**)&w.cbox[k], tc * 24)); }
         TRY_B(cudaMalloc((void**)&w.nn, tc * 4));
@@ -1184,6 +1199,52 @@ int lbvh_run(const float4* d_tris, int n, LbvhWork& w, float* ms_out) {
                 if (now.m >= m || now.m == 0) return fail(CERES_ERR_CUDA, "ceres_build_lbvh: clustering made no progress (internal error)");
                 m = now.m; cur ^= 1; ++w.rounds;
             }
+        } else if (sah) {
+            // top-down binned SAH over the Morton-sorted triangles, one level per iteration (lbvh_build.cuh)
+            ploc_init_kernel<<<grid, 256>>>(w.idx2, w.box, (uint32_t)n, w.cid[0], w.cbox[0]);
+            const SahState init{1u, 1u, 0u, 0u, 0u, {0u, 0u, 0u}};
+            TRY_B(cudaMemcpyAsync(w.s_st, &init, sizeof init, cudaMemcpyHostToDevice, 0));
+            const uint32_t zero_open = 0u;
+            const bool root_few = (uint32_t)n <= SAH_FEW;
+            TRY_B(cudaMemcpyAsync(root_few ? w.s_open_few[0] : w.s_open[0], &zero_open, 4, cudaMemcpyHostToDevice, 0));      // level 0: the root task
+            sah_root_kernel<<<grid, 256>>>(w.scene, (uint32_t)n, w.s_task, w.s_node_of);
+            g_launches += 2;
+            uint32_t n_open = root_few ? 0u : 1u, n_few = root_few ? 1u : 0u, first_new = 1u;
+            int cur = 0;
+            int sms = 148;
+            { int dev_ = 0; if (cudaGetDevice(&dev_) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev_); }
+            const unsigned persistent = (unsigned)sms * 4u;        // 43 KB of shared memory per CTA at most: 4-5 CTAs per SM
+            static const bool trace = std::getenv("CERES_BUILD_TRACE") != nullptr;     // per-level wall time (every level ends with a readback)
+            auto t_prev = std::chrono::steady_clock::now();
+            while (n_open + n_few) {
+                if (++w.rounds > 160) return fail(CERES_ERR_CUDA, "ceres_build_bvh: the top-down build did not finish in 160 levels (internal error)");
+                if (n_open) TRY_B(cudaMemsetAsync(w.s_bins, 0, (size_t)n_open * SAH_TASK_WORDS * 4, 0));
+                if (n_few) TRY_B(cudaMemsetAsync(w.s_bins_few, 0, (size_t)n_few * SAH_TASK_WORDS_FEW * 4, 0));
+                const bool small = !n_few && n_open <= SAH_SMALL_LEVEL && grid > persistent;       // few tasks, many members each: privatised in shared memory
+                if (small) sah_bin_small_kernel<<<persistent, 256, (size_t)n_open * SAH_TASK_WORDS * 4>>>(w.cbox[0], (uint32_t)n, w.s_task, w.s_node_of, w.s_bins, n_open);
+                else sah_bin_kernel<<<grid, 256>>>(w.cbox[0], (uint32_t)n, w.s_task, w.s_node_of, w.s_bins, w.s_bins_few);
+                if (n_open) sah_split_kernel<SAH_BINS><<<(n_open + 127u) / 128u, 128>>>(w.s_open[cur], n_open, w.s_task, w.s_bins, w.s_st);
+                if (n_few) sah_split_kernel<SAH_BINS_FEW><<<(n_few + 127u) / 128u, 128>>>(w.s_open_few[cur], n_few, w.s_task, w.s_bins_few, w.s_st);
+                if (small) sah_assign_small_kernel<<<persistent, 256, (size_t)2 * n_open * SAH_ACC_WORDS * 4>>>(w.cbox[0], (uint32_t)n, w.s_task, w.s_node_of, w.s_open[cur], n_open);
+                else sah_assign_kernel<<<grid, 256>>>(w.cbox[0], (uint32_t)n, w.s_task, w.s_node_of);
+                const uint32_t created = 2u * (n_open + n_few);
+                sah_link_kernel<<<(created + 255u) / 256u, 256>>>(first_new, created, w.s_task, w.cid[0], w.child, w.pi, w.pl, w.s_open[cur ^ 1], w.s_open_few[cur ^ 1], w.s_st);
+                g_launches += 5;
+                SahState now;
+                TRY_B(cudaMemcpy(&now, w.s_st, sizeof now, cudaMemcpyDeviceToHost));
+                if (now.error || now.next_task != first_new + created || now.n_open > sah_max_open || now.n_open_few > sah_max_few)
+                    return fail(CERES_ERR_CUDA, "ceres_build_bvh: the top-down build lost a member (internal error)");
+                if (trace) {
+                    const auto t_now = std::chrono::steady_clock::now();
+                    std::fprintf(stderr, "sah level %d: %u + %u open tasks -> %u + %u, %.3f ms\n", w.rounds, n_open, n_few, now.n_open, now.n_open_few,
+                                 std::chrono::duration<double, std::milli>(t_now - t_prev).count());
+                    t_prev = t_now;
+                }
+                first_new += created; n_open = now.n_open; n_few = now.n_open_few; cur ^= 1;
+                const uint32_t z[2] = {0u, 0u};
+                TRY_B(cudaMemcpy(&w.s_st->n_open, z, 8, cudaMemcpyHostToDevice));
+                if (!(n_open + n_few) && now.next_inner != (uint32_t)n - 1u) return fail(CERES_ERR_CUDA, "ceres_build_bvh: the top-down build made the wrong number of nodes (internal error)");
+            }
         } else
         lbvh_tree_kernel<<<grid, 256>>>(w.code2, n, w.child, w.pi, w.pl);
         lbvh_emit_kernel<<<grid, 256>>>(w.child, w.idx2, w.box, n, w.nodes);
@@ -1226,9 +1287,9 @@ int lbvh_check_args(const void* tris, size_t tri_count, int device, const char* 
 }  // namespace
 
 int ceres_build_options(int algorithm, int radius, int max_leaf, float triangle_cost) {
-    if (algorithm < 0 || algorithm > 1 || radius < 0 || radius > 256 || max_leaf < 0 || max_leaf > 16 || !(triangle_cost >= 0.0f))
-        return fail(CERES_ERR_INVALID, "ceres_build_options: algorithm 0 (clustering) or 1 (radix tree), radius 1..256, max_leaf 1..16, triangle_cost > 0 (0 = defaults)");
-    g_build_algorithm = algorithm;
+    if (algorithm < 0 || algorithm > 3 || radius < 0 || radius > 256 || max_leaf < 0 || max_leaf > 16 || !(triangle_cost >= 0.0f))
+        return fail(CERES_ERR_INVALID, "ceres_build_options: algorithm 0 = 2 (top-down binned SAH), 1 (radix tree) or 3 (clustering), radius 1..256, max_leaf 1..16, triangle_cost > 0 (0 = defaults)");
+    g_build_algorithm = algorithm ? algorithm : 2;
     g_build_radius = radius ? radius : 8;
     g_build_max_leaf = max_leaf ? max_leaf : 8;
     g_build_ci = triangle_cost > 0.0f ? triangle_cost : 1.5f;

@@ -347,3 +347,286 @@ __global__ void __launch_bounds__(256) bvhc_emit_kernel(const uint32_t* __restri
         out[1 + 2 * me + s] = nd;
     }
 }
+
+// ---- top-down binned SAH over the clusters (algorithm 2) ---------------------------------------------------------------------
+// What the reference's own builders do on the host -- BinnedSahBuilder (static.cpp:106-107, binned_sah_builder.hpp) -- as a
+// level-synchronous device pass: every open node ("task") bins the centroids of its members over its centroid bounds, takes
+// the split with the smallest area(left) x count(left) + area(right) x count(right) over the three axes, and its members move
+// to the two child tasks.  No member ever moves in memory: node_of[i] names the task of cluster i, bins and child bounds are
+// accumulated with atomics on order-preserving uints.  profiles/tree_lab.py (a CPU restatement judged by the reference
+// traverser's node-step counter on the dragon frame) is what picked this over the bottom-up clustering: 1.03 x the steps of the reference's SweepSah
+// tree against 1.22 x, with 16 % fewer triangle tests -- and what sized the bins: 16 per axis, 4 for tasks of at most 16
+// members (+0.1 % steps, a quarter of the memory and of the atomics of the deep levels).
+// Same intermediate form as the builders above (child[], par_inner[], par_leaf[], inner node 0 = root): emit / fit / collapse
+// are shared.  Inner ids are handed out from 1 upwards by an atomic counter; m clusters make exactly m - 1 inner nodes.
+#define SAH_BINS 16                         // tasks of more than SAH_FEW members
+#define SAH_BINS_FEW 4
+#define SAH_FEW 16u
+#define SAH_BIN_WORDS 7u                    // ~min x,y,z (as atomicMax of the complement), max x,y,z, count: all-zero = empty
+#define SAH_TASK_WORDS (3u * SAH_BINS * SAH_BIN_WORDS)
+#define SAH_TASK_WORDS_FEW (3u * SAH_BINS_FEW * SAH_BIN_WORDS)
+#define SAH_NONE 0xFFFFFFFFu
+#define SAH_FEW_SLOT 0x80000000u            // SahTask::slot: index into the level's list of small tasks (their own, narrower bins)
+#define SAH_FALLBACK 0x80000000u
+
+struct SahTask {
+    uint32_t cb[6];                         // centroid bounds of the members: ~ord(min), ord(max) per axis (zero = empty)
+    uint32_t count, imin, imax;             // members; smallest / largest member index (imin kept as the complement: zero = empty)
+    uint32_t inner;                         // inner node id of this task (count >= 2), set by the link pass
+    uint32_t parent;                        // parent inner id << 1 | side
+    uint32_t slot;                          // index into this level's bins (| SAH_FEW_SLOT for a small task); SAH_NONE = closed
+    uint32_t split;                         // axis << 8 | last bin of the left side; SAH_FALLBACK | first member index of the right side
+    uint32_t child0;                        // task id of the left child (right = + 1)
+    uint32_t pad_[2];
+};
+static_assert(sizeof(SahTask) == 64, "one task per 64 bytes");
+
+struct SahState { uint32_t next_task, next_inner, n_open, n_open_few, error, pad_[3]; };
+
+__device__ __forceinline__ float sah_centroid(const float* __restrict__ b, int d) { return mul(add(b[2 * d], b[2 * d + 1]), 0.5f); }
+__device__ __forceinline__ int sah_bin(float c, float lo, float ext, int nb) {
+    const int b = (int)(mul((float)nb, __fdiv_rn(sub(c, lo), ext)));
+    return b < 0 ? 0 : b > nb - 1 ? nb - 1 : b;
+}
+
+// Warp-aggregated atomicMax / atomicAdd: the lanes of `peers` (a __match_any_sync group: same destination) reduce among
+// themselves and their first lane issues the one atomic.  The clusters are in Morton order, so at the upper levels a whole warp
+// shares one task and a few bins -- without this the same few words take an atomic from every one of the 10 M members
+// (850 ms instead of 64 ms for the 10.5 M-triangle scene).
+#ifndef SAH_AGGREGATE
+#define SAH_AGGREGATE 1
+#endif
+__device__ __forceinline__ void sah_max(uint32_t* dst, uint32_t v, uint32_t peers, bool leader) {
+#if SAH_AGGREGATE
+    v = __reduce_max_sync(peers, v);
+    if (leader) atomicMax(dst, v);
+#else
+    atomicMax(dst, v);
+#endif
+}
+__device__ __forceinline__ void sah_add(uint32_t* dst, uint32_t v, uint32_t peers, bool leader) {
+#if SAH_AGGREGATE
+    v = __reduce_add_sync(peers, v);
+    if (leader) atomicAdd(dst, v);
+#else
+    atomicAdd(dst, v);
+#endif
+}
+
+// root task: every cluster is a member; `scene` = the ordered-uint bounds of the centres (lbvh_boxes_kernel), which are the
+// root's centroid bounds when the clusters are the triangles themselves
+__global__ void __launch_bounds__(256) sah_root_kernel(const unsigned int* __restrict__ scene, uint32_t m, SahTask* task, uint32_t* __restrict__ node_of) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= m) return;
+    node_of[i] = 0u;
+    if (i == 0) {
+        SahTask t = {};
+        for (int d = 0; d < 3; ++d) { t.cb[2 * d] = ~scene[2 * d]; t.cb[2 * d + 1] = scene[2 * d + 1]; }
+        t.count = m; t.imin = ~0u; t.imax = m - 1u; t.inner = 0u; t.parent = 0u; t.slot = m > SAH_FEW ? 0u : SAH_FEW_SLOT;
+        task[0] = t;
+    }
+}
+
+// member i adds its box to the bins of its task; big / few = the level's two bin arrays in global memory, or (big only) a
+// CTA's private copy
+__device__ __forceinline__ void sah_bin_member(uint32_t i, const float* __restrict__ cbox, const SahTask* __restrict__ task,
+                                               const uint32_t* __restrict__ node_of, uint32_t* big, uint32_t* few) {
+    const SahTask& t = task[node_of[i]];
+    const uint32_t slot = t.slot;
+    if (slot == SAH_NONE) return;
+    const bool is_few = (slot & SAH_FEW_SLOT) != 0u;
+    const int nb = is_few ? SAH_BINS_FEW : SAH_BINS;
+    uint32_t* base = is_few ? few + (size_t)(slot & ~SAH_FEW_SLOT) * SAH_TASK_WORDS_FEW : big + (size_t)slot * SAH_TASK_WORDS;
+    float b[6];
+    for (int q = 0; q < 6; ++q) b[q] = __ldg(cbox + 6ull * i + q);
+    uint32_t ob[6];
+    for (int d = 0; d < 3; ++d) { ob[2 * d] = ~lbvh_ord(b[2 * d]); ob[2 * d + 1] = lbvh_ord(b[2 * d + 1]); }
+    for (int d = 0; d < 3; ++d) {
+        const float lo = lbvh_unord(~t.cb[2 * d]), hi = lbvh_unord(t.cb[2 * d + 1]);
+        const float ext = sub(hi, lo);
+        if (!(ext > 0.0f)) continue;
+        const uint32_t bin = (uint32_t)sah_bin(sah_centroid(b, d), lo, ext, nb);
+        uint32_t* w = base + ((size_t)d * nb + bin) * SAH_BIN_WORDS;
+#if SAH_AGGREGATE
+        const uint32_t peers = __match_any_sync(__activemask(), ((unsigned long long)slot << 8) | bin);     // lanes that got here with the same bin
+#else
+        const uint32_t peers = 0u;
+#endif
+        const bool leader = (threadIdx.x & 31u) == (uint32_t)(__ffs(peers) - 1);
+        for (int q = 0; q < 6; ++q) sah_max(w + q, ob[q], peers, leader);
+        sah_add(w + 6, 1u, peers, leader);
+    }
+}
+
+__global__ void __launch_bounds__(256) sah_bin_kernel(const float* __restrict__ cbox, uint32_t m, const SahTask* __restrict__ task,
+                                                      const uint32_t* __restrict__ node_of, uint32_t* bins, uint32_t* bins_few) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i < m) sah_bin_member(i, cbox, task, node_of, bins, bins_few);
+}
+
+// The first levels have a handful of tasks with millions of members each: every CTA of a persistent grid bins into its own
+// copy in shared memory and adds the copy to the global bins once (n_open <= SAH_SMALL_LEVEL big tasks, no small ones: at
+// most 42 KB).  Levels 1-6 of the 10.5 M-triangle scene: 25.4 ms -> 6.1 ms.
+#define SAH_SMALL_LEVEL 32u
+__global__ void __launch_bounds__(256) sah_bin_small_kernel(const float* __restrict__ cbox, uint32_t m, const SahTask* __restrict__ task,
+                                                            const uint32_t* __restrict__ node_of, uint32_t* bins, uint32_t n_open) {
+    extern __shared__ uint32_t sah_sh[];
+    const uint32_t words = n_open * SAH_TASK_WORDS;
+    for (uint32_t k = threadIdx.x; k < words; k += 256u) sah_sh[k] = 0u;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < m; i += gridDim.x * 256u) sah_bin_member(i, cbox, task, node_of, sah_sh, nullptr);
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < words; k += 256u) {
+        const uint32_t v = sah_sh[k];
+        if (!v) continue;
+        if (k % SAH_BIN_WORDS == 6u) atomicAdd(bins + k, v); else atomicMax(bins + k, v);
+    }
+}
+
+// one thread per open task: the best split over 3 axes x (NB - 1) planes; allocates the two child tasks
+template <int NB>
+__global__ void __launch_bounds__(128) sah_split_kernel(const uint32_t* __restrict__ open, uint32_t n_open, SahTask* task, const uint32_t* __restrict__ bins,
+                                                        SahState* st) {
+    const uint32_t s = blockIdx.x * 128u + threadIdx.x;
+    if (s >= n_open) return;
+    const uint32_t tid = open[s];
+    SahTask& t = task[tid];
+    float best = 3.4e38f; uint32_t best_split = SAH_NONE;
+    for (int d = 0; d < 3; ++d) {
+        const float lo = lbvh_unord(~t.cb[2 * d]), hi = lbvh_unord(t.cb[2 * d + 1]);
+        if (!(sub(hi, lo) > 0.0f)) continue;
+        const uint32_t* w = bins + (size_t)s * (3u * NB * SAH_BIN_WORDS) + (size_t)d * NB * SAH_BIN_WORDS;
+        float left_cost[NB - 1]; uint32_t left_n[NB - 1];
+        uint32_t acc[6] = {0, 0, 0, 0, 0, 0}, n = 0;
+        for (int k = 0; k < NB - 1; ++k) {
+            for (int q = 0; q < 6; ++q) acc[q] = max(acc[q], w[k * SAH_BIN_WORDS + q]);
+            n += w[k * SAH_BIN_WORDS + 6];
+            float a = 0.0f;
+            if (n) {
+                const float dx = lbvh_unord(acc[1]) - lbvh_unord(~acc[0]), dy = lbvh_unord(acc[3]) - lbvh_unord(~acc[2]), dz = lbvh_unord(acc[5]) - lbvh_unord(~acc[4]);
+                a = dx * dy + dy * dz + dz * dx;
+            }
+            left_cost[k] = a * (float)n; left_n[k] = n;
+        }
+        for (int q = 0; q < 6; ++q) acc[q] = 0;
+        n = 0;
+        for (int k = NB - 2; k >= 0; --k) {
+            for (int q = 0; q < 6; ++q) acc[q] = max(acc[q], w[(k + 1) * SAH_BIN_WORDS + q]);
+            n += w[(k + 1) * SAH_BIN_WORDS + 6];
+            if (!n || !left_n[k]) continue;
+            const float dx = lbvh_unord(acc[1]) - lbvh_unord(~acc[0]), dy = lbvh_unord(acc[3]) - lbvh_unord(~acc[2]), dz = lbvh_unord(acc[5]) - lbvh_unord(~acc[4]);
+            const float c = left_cost[k] + (dx * dy + dy * dz + dz * dx) * (float)n;
+            if (c < best) { best = c; best_split = ((uint32_t)d << 8) | (uint32_t)k; }
+        }
+    }
+    if (best_split == SAH_NONE) {
+        // every centroid on one point (or non-finite costs): cut the member list in the middle of its index range
+        const uint32_t imin = ~t.imin, imax = t.imax;
+        best_split = SAH_FALLBACK | (imin + (imax - imin + 1u) / 2u);
+    }
+    t.split = best_split;
+    const uint32_t c0 = atomicAdd(&st->next_task, 2u);
+    t.child0 = c0;
+    for (uint32_t k = 0; k < 2u; ++k) {
+        SahTask c = {};
+        c.parent = (t.inner << 1) | k; c.slot = SAH_NONE; c.inner = SAH_NONE;
+        task[c0 + k] = c;
+    }
+}
+
+// The first 9 words of a SahTask -- cb[6], count, imin, imax -- are what the members of a new task accumulate: max for all
+// but the count.
+#define SAH_ACC_WORDS 9u
+static_assert(offsetof(SahTask, count) == 24 && offsetof(SahTask, imin) == 28 && offsetof(SahTask, imax) == 32, "accumulated words first");
+
+// member i moves to the child task its parent's split sends it to; SMALL: the children's words are accumulated in shared memory
+template <bool SMALL>
+__device__ __forceinline__ void sah_assign_member(uint32_t i, const float* __restrict__ cbox, SahTask* task, uint32_t* __restrict__ node_of, uint32_t* sh) {
+    const SahTask& t = task[node_of[i]];
+    if (t.slot == SAH_NONE) return;
+    const float* b = cbox + 6ull * i;
+    uint32_t side;
+    if (t.split & SAH_FALLBACK) side = i >= (t.split & ~SAH_FALLBACK) ? 1u : 0u;
+    else {
+        const int d = (int)(t.split >> 8), k = (int)(t.split & 0xFFu);
+        const float lo = lbvh_unord(~t.cb[2 * d]), hi = lbvh_unord(t.cb[2 * d + 1]);
+        side = sah_bin(sah_centroid(b, d), lo, sub(hi, lo), (t.slot & SAH_FEW_SLOT) ? SAH_BINS_FEW : SAH_BINS) > k ? 1u : 0u;
+    }
+    const uint32_t ct = t.child0 + side;
+    node_of[i] = ct;
+    uint32_t* acc = SMALL ? sh + (2u * t.slot + side) * SAH_ACC_WORDS : reinterpret_cast<uint32_t*>(&task[ct]);
+#if SAH_AGGREGATE
+    const uint32_t peers = __match_any_sync(__activemask(), ct);
+#else
+    const uint32_t peers = 0u;
+#endif
+    const bool leader = (threadIdx.x & 31u) == (uint32_t)(__ffs(peers) - 1);
+    for (int d = 0; d < 3; ++d) {
+        const uint32_t o = lbvh_ord(sah_centroid(b, d));
+        sah_max(acc + 2 * d, ~o, peers, leader); sah_max(acc + 2 * d + 1, o, peers, leader);
+    }
+    sah_add(acc + 6, 1u, peers, leader);
+    sah_max(acc + 7, ~i, peers, leader); sah_max(acc + 8, i, peers, leader);
+}
+
+__global__ void __launch_bounds__(256) sah_assign_kernel(const float* __restrict__ cbox, uint32_t m, SahTask* task, uint32_t* __restrict__ node_of) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i < m) sah_assign_member<false>(i, cbox, task, node_of, nullptr);
+}
+
+__global__ void __launch_bounds__(256) sah_assign_small_kernel(const float* __restrict__ cbox, uint32_t m, SahTask* task, uint32_t* __restrict__ node_of,
+                                                               const uint32_t* __restrict__ open, uint32_t n_open) {
+    extern __shared__ uint32_t sah_sh[];
+    const uint32_t words = 2u * n_open * SAH_ACC_WORDS;
+    for (uint32_t k = threadIdx.x; k < words; k += 256u) sah_sh[k] = 0u;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < m; i += gridDim.x * 256u) sah_assign_member<true>(i, cbox, task, node_of, sah_sh);
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < words; k += 256u) {
+        const uint32_t v = sah_sh[k];
+        if (!v) continue;
+        const uint32_t c = k / SAH_ACC_WORDS, f = k - c * SAH_ACC_WORDS;
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&task[task[open[c >> 1]].child0 + (c & 1u)]) + f;
+        if (f == 6u) atomicAdd(dst, v); else atomicMax(dst, v);
+    }
+}
+
+__device__ __forceinline__ void sah_set_parent(uint32_t ptr, uint32_t where, uint32_t* __restrict__ par_inner, uint32_t* __restrict__ par_leaf) {
+    if (ptr & LBVH_LEAF) par_leaf[ptr & ~LBVH_LEAF] = where; else par_inner[ptr] = where;
+}
+
+// one thread per task created at this level: hook the task into the tree and, with 3 members or more, open it for the next level
+__global__ void __launch_bounds__(256) sah_link_kernel(uint32_t first, uint32_t count, SahTask* task, const uint32_t* __restrict__ cid,
+                                                       uint32_t* __restrict__ child, uint32_t* __restrict__ par_inner, uint32_t* __restrict__ par_leaf,
+                                                       uint32_t* __restrict__ open_next, uint32_t* __restrict__ open_next_few, SahState* st) {
+    const uint32_t j = blockIdx.x * 256u + threadIdx.x;
+    if (j >= count) return;
+    SahTask& t = task[first + j];
+    const uint32_t where = t.parent, n = t.count;
+    if (n == 0u) { st->error = 1u; return; }
+    if (n == 1u) {
+        const uint32_t ptr = cid[t.imax];
+        child[where] = ptr;
+        sah_set_parent(ptr, where, par_inner, par_leaf);
+        return;
+    }
+    const uint32_t id = atomicAdd(&st->next_inner, 1u);
+    t.inner = id;
+    child[where] = id;
+    par_inner[id] = where;
+    if (n == 2u) {
+        const uint32_t a = cid[~t.imin], b = cid[t.imax];
+        child[2 * id] = a; child[2 * id + 1] = b;
+        sah_set_parent(a, 2 * id, par_inner, par_leaf); sah_set_parent(b, 2 * id + 1, par_inner, par_leaf);
+        return;
+    }
+    if (n > SAH_FEW) {
+        const uint32_t slot = atomicAdd(&st->n_open, 1u);
+        open_next[slot] = first + j;
+        t.slot = slot;
+    } else {
+        const uint32_t slot = atomicAdd(&st->n_open_few, 1u);
+        open_next_few[slot] = first + j;
+        t.slot = slot | SAH_FEW_SLOT;
+    }
+}

@@ -94,8 +94,8 @@ def probe_host_fill_bandwidth(nbytes=256 << 20, repeats=3):
 
 
 def build_options(algorithm=0, radius=0, max_leaf=0, triangle_cost=0.0):
-    """Which tree build_lbvh / Scene.from_lbvh make: algorithm 0 = locally-ordered clustering (default), 1 = radix tree of the
-    Morton codes; radius = neighbours searched on either side (0 = 8); max_leaf = SAH leaf collapsing up to that many triangles
+    """Which tree build_lbvh / Scene.from_lbvh make: algorithm 0 = 2 = top-down binned SAH (default), 3 = locally-ordered
+    clustering, 1 = radix tree of the Morton codes; radius = clustering neighbours per side (0 = 8); max_leaf = SAH leaf collapsing
     (0 = 8, 1 = off); triangle_cost = cost of a triangle test in node steps (0 = 1.5).  Process-wide (ceres_build_options)."""
     _capi.check(_capi.lib().ceres_build_options(int(algorithm), int(radius), int(max_leaf), float(triangle_cost)))
 

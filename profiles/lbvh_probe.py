@@ -13,7 +13,7 @@ import ceres_raytracer_b200 as cr
 wl = sys.argv[1] if len(sys.argv) > 1 else "dragon_4k_shadow"
 # configurations: algorithm:radius:max_leaf:triangle_cost, comma separated
 cfgs = [tuple(float(v) if k == 3 else int(v) for k, v in enumerate(c.split(":"))) for c in
-        (sys.argv[2] if len(sys.argv) > 2 else "1:0:1:1,0:16:1:1,0:16:4:1,0:16:8:1,0:16:8:1.5,0:16:8:2,0:8:8:1.5,1:0:8:1.5").split(",")]
+        (sys.argv[2] if len(sys.argv) > 2 else "1:0:1:1,1:0:8:1.5,3:16:1:1,3:8:8:1.5,2:0:1:1,2:0:8:1,2:0:8:1.5").split(",")]
 pod, cam, sun, W, H, flags, scene = bench.load_workload(wl, device=0)
 if scene is None:
     scene = cr.Scene.from_pod(pod)
@@ -48,7 +48,7 @@ for algo, radius, max_leaf, ci in cfgs:
     ids = torch.empty(H * W, dtype=torch.int32, device=dev)
     t = frame_ms(s3, ids)
     diff = int((ids.cpu().numpy() != ids_ref.cpu().numpy()).sum())
-    name = ("radix tree" if algo == 1 else f"clustering r{radius or 8}") + f", leaves <= {max_leaf} (Ci {ci:g})"
+    name = ("radix tree" if algo == 1 else "top-down binned SAH" if algo in (0, 2) else f"clustering r{radius or 8}") + f", leaves <= {max_leaf} (Ci {ci:g})"
     print(f"  {name:40s} {s3.node_count:9d} nodes: build kernels {s3.build_ms:8.3f} ms, upload + build + scene {t_call*1e3:8.1f} ms, stack depth {s3.stack_depth:2d}; "
           f"{t:.3f} ms/frame = {t / t_ref:.3f} x the reference tree; counters {cnt.cpu().tolist()}; ids differing {diff}", flush=True)
     s3.close()

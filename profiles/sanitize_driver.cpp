@@ -107,6 +107,15 @@ int main(int argc, char** argv) {
         CU(cudaDeviceSynchronize());
         CU(cudaMemcpy(px2.data(), d_px, px2.size() * 4, cudaMemcpyDeviceToHost));
         if (std::memcmp(px.data(), px2.data(), px.size() * 4)) { std::fprintf(stderr, "device frame differs from the host frame\n"); return 1; }
+        // the same frame over the library's static scratch, twice (the second call runs over what the first left there)
+        for (int rep = 0; rep < 2; ++rep) {
+            CU(cudaMemset(d_px, 0xFF, 3 * W * H * 4));
+            CHECK(ceres_render_device_static(s, &cam, sun, W, H, 0, nullptr, d_px, d_ids, d_cnt));
+            CU(cudaDeviceSynchronize());
+            CU(cudaMemcpy(px2.data(), d_px, px2.size() * 4, cudaMemcpyDeviceToHost));
+            if (std::memcmp(px.data(), px2.data(), px.size() * 4)) { std::fprintf(stderr, "static-scratch frame differs from the host frame\n"); return 1; }
+        }
+        if (ceres_render_device_static(s, &cam, sun, 4096, 4096, 0, nullptr, d_px, d_ids, d_cnt) == CERES_OK) { std::fprintf(stderr, "static scratch: an oversized frame was accepted\n"); return 1; }
         ceres_shard sh = {CERES_TILE_BLOCK_ROWS, 1, 3};
         CHECK(ceres_render_device(s, &cam, sun, W, H, CERES_COMPACT_ROWS, &sh, nullptr, d_px, d_ids, d_cnt));
         CU(cudaDeviceSynchronize());
@@ -178,15 +187,19 @@ int main(int argc, char** argv) {
     // 9. BVH build on the GPU, host copy and device-resident
     {
         std::vector<unsigned char> nd((2 * nt - 1) * 32); std::vector<size_t> pi(nt); double ms = 0;
-        CHECK(ceres_build_lbvh(tris, nt, 0, nd.data(), pi.data(), &ms));
-        ceres_scene* sl = nullptr;
-        CHECK(ceres_scene_create_lbvh(tris, norms, nt, 0, &sl, &ms));
-        CHECK(ceres_render(sl, &cam, sun, W, H, 0, px2.data(), nullptr, c));
-        if (c[0] != c0[0]) { std::fprintf(stderr, "lbvh scene: rays differ\n"); return 1; }
-        CHECK(ceres_scene_refit(sl));
-        CHECK(ceres_render(sl, &cam, sun, W, H, 0, px2.data(), nullptr, c));
-        NOERR(sl, "GPU-built scene");
-        ceres_scene_destroy(sl);
+        for (int algo = 1; algo <= 3; ++algo) {         // radix tree, top-down binned SAH (the default), locally-ordered clustering
+            CHECK(ceres_build_options(algo, 0, 0, 0.0f));
+            CHECK(ceres_build_lbvh(tris, nt, 0, nd.data(), pi.data(), &ms));
+            ceres_scene* sl = nullptr;
+            CHECK(ceres_scene_create_lbvh(tris, norms, nt, 0, &sl, &ms));
+            CHECK(ceres_render(sl, &cam, sun, W, H, 0, px2.data(), nullptr, c));
+            if (c[0] != c0[0]) { std::fprintf(stderr, "lbvh scene (algorithm %d): rays differ\n", algo); return 1; }
+            CHECK(ceres_scene_refit(sl));
+            CHECK(ceres_render(sl, &cam, sun, W, H, 0, px2.data(), nullptr, c));
+            NOERR(sl, "GPU-built scene");
+            ceres_scene_destroy(sl);
+        }
+        CHECK(ceres_build_options(0, 0, 0, 0.0f));
     }
     // 10. Scalar = double
     {
@@ -200,6 +213,18 @@ int main(int argc, char** argv) {
         std::vector<double> pd(3 * W * H); std::vector<uint32_t> idd(W * H);
         CHECK(ceres_render_f64(d, &cd, sd, W, H, 0, pd.data(), idd.data(), c, nullptr));
         std::printf("double frame: rays %llu hits %llu\n", (unsigned long long)c[0], (unsigned long long)c[1]);
+        {   // the same frame from 3 row-block shards into a second buffer
+            std::vector<double> ps(3 * W * H, -1.0); std::vector<uint32_t> ids2(W * H, 7u);
+            uint64_t sum[2] = {0, 0}, cs[2];
+            for (uint32_t k = 0; k < 3; ++k) {
+                ceres_shard sh = {CERES_TILE_BLOCK_ROWS, k, 3};
+                CHECK(ceres_render_f64_shard(d, &cd, sd, W, H, 0, &sh, ps.data(), ids2.data(), cs, nullptr));
+                sum[0] += cs[0]; sum[1] += cs[1];
+            }
+            if (std::memcmp(ps.data(), pd.data(), pd.size() * 8) || std::memcmp(ids2.data(), idd.data(), idd.size() * 4) || sum[0] != c[0] || sum[1] != c[1]) {
+                std::fprintf(stderr, "double frame: the shards do not add up to the frame\n"); return 1;
+            }
+        }
         ceres_scene_f64_destroy(d);
     }
     double gbs = 0;
