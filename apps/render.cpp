@@ -13,7 +13,8 @@
 // of static.cpp:96-133.
 //
 // Additive flags: --dir x y z  --up x y z  --fov deg  --sun x y z  --width W  --height H  -o file.ppm
-//   --no-shadow (primary rays only, BASELINE configs 1-2)  --builder binned|sweep  --gpus N (interleaved 16-row blocks,
+//   --no-shadow (primary rays only, BASELINE configs 1-2)  --builder binned|sweep|device (device: the tree is built on
+//   the GPU, ceres_build_bvh -- top-down binned SAH in milliseconds, into the same Bvh structure)  --gpus N (interleaved 16-row blocks,
 //   one host thread per GPU)  --dump-ids file.u32  --dump-rgb file.f32  --frames K (repeat the render call K times)
 //   --ppm8 (quantise + flip on the GPU and copy the 8-bit image: static.cpp:135-147 done on the device, 1 GPU)
 #include <algorithm>
@@ -60,7 +61,7 @@ struct Options {
 [[noreturn]] void usage(const char* msg) {
     std::cerr << "render: " << msg << "\n"
               << "usage: render [file.obj] [--eye x y z] [--rotate x|y|z deg] [--dir x y z] [--up x y z] [--fov deg]\n"
-              << "              [--sun x y z] [--width W] [--height H] [-o out.ppm] [--no-shadow] [--builder binned|sweep]\n"
+              << "              [--sun x y z] [--width W] [--height H] [-o out.ppm] [--no-shadow] [--builder binned|sweep|device]\n"
               << "              [--gpus N] [--dump-ids f.u32] [--dump-rgb f.f32] [--frames K] [--ppm8]\n";
     std::exit(2);
 }
@@ -104,7 +105,7 @@ Options parse(int argc, char** argv) {
         if (!have_up) o.camera.up = Vector3(0, 1, 0);
         if (!have_rot) { o.rotation_axis = 0; o.rotation_degrees = 0; }
     }
-    if (o.builder != "binned" && o.builder != "sweep") usage("--builder is binned or sweep");
+    if (o.builder != "binned" && o.builder != "sweep" && o.builder != "device") usage("--builder is binned, sweep or device");
     if (o.gpus < 1 || o.frames < 1 || !o.width || !o.height) usage("bad --gpus/--frames/--width/--height");
     return o;
 }
@@ -133,9 +134,23 @@ int main(int argc, char** argv) {
 
     Bvh bvh;
     const size_t reference_count = triangles.size();
-    std::cout << "Building BVH ( using " << (opt.builder == "binned" ? "BinnedSahBuilder" : "SweepSahBuilder") << " )..." << std::endl;
+    std::cout << "Building BVH ( using " << (opt.builder == "binned" ? "BinnedSahBuilder" : opt.builder == "device" ? "the B200 binned-SAH builder" : "SweepSahBuilder")
+              << " )..." << std::endl;
     auto t0 = std::chrono::high_resolution_clock::now();
-    {
+    if (opt.builder == "device") {
+        // same data structure, filled by the library: bvh.nodes (32-byte nodes, root 0, siblings adjacent) and
+        // bvh.primitive_indices (bvh.hpp:25-30,93-96)
+        static_assert(sizeof(Bvh::Node) == 32 && sizeof(Triangle) == 48, "reference POD layouts");
+        bvh.nodes = std::make_unique<Bvh::Node[]>(2 * reference_count - 1);
+        bvh.primitive_indices = std::make_unique<size_t[]>(reference_count);
+        size_t node_count = 0; double build_ms = 0;
+        if (ceres_build_bvh(triangles.data(), reference_count, 0, bvh.nodes.get(), &node_count, bvh.primitive_indices.get(), &build_ms) != CERES_OK) {
+            std::cerr << "render: " << ceres_last_error() << std::endl;
+            return 1;
+        }
+        bvh.node_count = node_count;
+        std::cout << "(device build kernels: " << build_ms << " ms)" << std::endl;
+    } else {
         auto bc = bvh::compute_bounding_boxes_and_centers(triangles.data(), triangles.size());
         auto global_bbox = bvh::compute_bounding_boxes_union(bc.first.get(), triangles.size());
         if (opt.builder == "binned") {                                   // static.cpp:106-107

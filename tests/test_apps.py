@@ -114,6 +114,35 @@ def test_render_binary_matches_reference(tmp_path, builder, bcode, extra):
 
 @pytest.mark.gpu
 @needs_binaries
+def test_render_binary_with_the_device_built_tree(tmp_path):
+    """--builder device: the tree comes from ceres_build_bvh (top-down binned SAH on the GPU) in the reference's own Bvh
+    structure.  Another tree than SweepSah's, so the hit ids may differ where two triangles are hit at exactly the same t
+    (SURVEY.md 7.3-H2); everything a tie cannot change -- the counters, which pixels are hit, the colour of every pixel
+    whose id agrees -- must equal the reference's frame from its own tree."""
+    obj = str(tmp_path / "torus.obj")
+    write_torus_obj(obj)
+    W, H = 640, 360
+    cmd = [RENDER, obj, "--eye", "0.3", "1.2", "-3.0", "--dir", "-0.1", "-0.35", "1", "--rotate", "y", "-145", "--sun", "-50", "60", "-20",
+           "--width", str(W), "--height", str(H), "-o", str(tmp_path / "render.ppm"), "--builder", "device",
+           "--dump-rgb", str(tmp_path / "rgb.f32"), "--dump-ids", str(tmp_path / "ids.u32")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "B200 binned-SAH builder" in r.stdout and "device build kernels" in r.stdout and "BVH of" in r.stdout
+    s = ref.RefScene.load_obj(obj, rot_axis=1, rot_deg=-145.0, builder=0)
+    cam = ref.cam_array((0.3, 1.2, -3.0), (-0.1, -0.35, 1), (0, 1, 0), 60)
+    o = s.render_ex(cam, np.array([-50, 60, -20], np.float32), W, H, 0)
+    s.close()
+    assert f"Rays: {o['stats']['rays']}\tHits: {o['stats']['hits']}" in r.stdout
+    ids = np.fromfile(str(tmp_path / "ids.u32"), np.uint32).reshape(H, W)
+    rgb = np.fromfile(str(tmp_path / "rgb.f32"), np.float32).reshape(H, W, 3)
+    assert np.array_equal(ids == ref.MISS, o["ids"] == ref.MISS)
+    same = ids == o["ids"]
+    assert same.mean() > 0.999
+    assert np.abs(rgb - o["pixels"])[same].max() <= RGB_ATOL
+
+
+@pytest.mark.gpu
+@needs_binaries
 def test_render_binary_ppm8_writes_the_same_file(tmp_path):
     """--ppm8 (quantise + flip on the device, 8-bit rectangle DMA) and the default float path write identical PPMs."""
     obj = str(tmp_path / "torus.obj")

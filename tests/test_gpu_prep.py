@@ -78,3 +78,29 @@ def test_instanced_grid_scene(cr, dragon_pod):
         grid["nodes"] = want
         check_frame(cr, s, grid, cam, sun, 1280, 720, 0)
         check_frame(cr, s, grid, cam, sun, 640, 360, cr.NO_SHADOWS)
+
+
+def test_device_built_tree_of_the_10m_triangle_scene(cr, dragon_pod):
+    """N3 at the size it exists for: the 10.5 M-triangle instanced-dragon scene (BASELINE config 5) built on the device by the
+    default builder (top-down binned SAH).  Size-independent properties against the frame from the reference-built tree of the
+    same triangles: everything a tie between two triangles at exactly the same t cannot change -- the two counters, which pixels
+    hit, which pixels are lit -- is equal, and the ids differ on a few dozen pixels at most; the tree is small enough for the
+    traversal stack and the build stays under the 50 ms bar (profiles/r2/sweeps.md: 38.5 ms)."""
+    import bench
+    pod, cam, sun, W, H, flags, scene = bench.load_workload("grid448_4k_shadow", device=0)
+    try:
+        n = len(pod["triangles"])
+        assert n == 448 * len(dragon_pod["triangles"])
+        px_a, ids_a, cnt_a = scene.render(cam, sun, W, H, flags=flags, want_ids=True)
+        cr.build_options()
+        with cr.Scene.from_lbvh(pod["triangles"], pod["norms"]) as s:
+            assert s.node_count % 2 == 1 and s.node_count <= 2 * n - 1 and s.stack_depth <= 64
+            assert 0 < s.build_ms < 50.0 * 2, s.build_ms          # twice the bar: a shared box may be slower than the measured 38.5 ms
+            px_b, ids_b, cnt_b = s.render(cam, sun, W, H, flags=flags, want_ids=True)
+        assert cnt_a == cnt_b and cnt_a[1] > 1_000_000
+        assert np.array_equal(ids_a == cr.MISS, ids_b == cr.MISS)
+        differ = ids_a != ids_b
+        assert int(differ.sum()) <= 64, int(differ.sum())
+        assert np.array_equal(px_a[~differ].view(np.uint32), px_b[~differ].view(np.uint32))
+    finally:
+        scene.close()
