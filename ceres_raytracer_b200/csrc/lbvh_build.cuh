@@ -630,3 +630,148 @@ __global__ void __launch_bounds__(256) sah_link_kernel(uint32_t first, uint32_t 
         t.slot = slot | SAH_FEW_SLOT;
     }
 }
+
+// ---- CTA-level accumulation for the bin and assign passes ----------------------------------------------------------------------
+// ncu of the warp-aggregated passes on the 10.5 M-triangle scene: instruction-bound (a redux whose lanes carry different member
+// masks runs once per group: 900 warp instructions per warp at a mid level, 2 400 at a deep one, 9 of 32 lanes active) and then
+// still 7 global atomics per group.  Here a CTA takes SAH_CTA_MEMBERS consecutive members, gives every destination record it
+// meets (a task's bins; a child task's 9 accumulated words) a region of a shared-memory pool through a small hash table,
+// accumulates with shared-memory atomics and adds each non-zero word to global memory once.  The members are in Morton order,
+// so a CTA meets few records: one to three tasks at the mid levels, ~60 small ones at the deepest.  Records that do not fit
+// the pool go straight to global memory.  Results are sums / maxima: identical to the other schemes bit for bit.
+#define SAH_CTA_MEMBERS 512u
+#define SAH_HASH 1024u
+#define SAH_POOL_WORDS 6144u
+#define SAH_EMPTY 0xFFFFFFFFu
+#define SAH_OVERFLOW 0xFFFFFFFFu
+
+struct SahCta {
+    uint32_t keys[SAH_HASH];
+    uint32_t offs[SAH_HASH];
+    uint32_t list[SAH_CTA_MEMBERS];       // hash entries in use
+    uint32_t pool[SAH_POOL_WORDS];
+    uint32_t bump, n_list;
+};
+
+__device__ __forceinline__ void sah_cta_begin(SahCta& c) {
+    for (uint32_t k = threadIdx.x; k < SAH_HASH; k += 256u) c.keys[k] = SAH_EMPTY;
+    for (uint32_t k = threadIdx.x; k < SAH_POOL_WORDS; k += 256u) c.pool[k] = 0u;
+    if (threadIdx.x == 0) { c.bump = 0u; c.n_list = 0u; }
+    __syncthreads();
+}
+__device__ __forceinline__ uint32_t sah_cta_insert(SahCta& c, uint32_t key) {       // returns the hash entry of `key`
+    uint32_t h = (key * 2654435761u) >> 22;                                        // 10 bits
+    for (;;) {
+        const uint32_t old = atomicCAS(&c.keys[h], SAH_EMPTY, key);
+        if (old == SAH_EMPTY || old == key) return h;
+        h = (h + 1u) & (SAH_HASH - 1u);
+    }
+}
+// after every member has inserted its key: each used entry gets `words(key)` words of the pool (or SAH_OVERFLOW)
+template <class Words>
+__device__ __forceinline__ void sah_cta_allocate(SahCta& c, Words words) {
+    __syncthreads();
+    for (uint32_t e = threadIdx.x; e < SAH_HASH; e += 256u) {
+        const uint32_t key = c.keys[e];
+        if (key == SAH_EMPTY) continue;
+        const uint32_t n = words(key), off = atomicAdd(&c.bump, n);
+        if (off + n <= SAH_POOL_WORDS) { c.offs[e] = off; c.list[atomicAdd(&c.n_list, 1u)] = e; }
+        else c.offs[e] = SAH_OVERFLOW;
+    }
+    __syncthreads();
+}
+// after the accumulation: a warp per record adds the non-zero words to dst(key); word w of a record is a count when is_add(w)
+template <class Words, class Dst, class IsAdd>
+__device__ __forceinline__ void sah_cta_flush(SahCta& c, Words words, Dst dst, IsAdd is_add) {
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t q = threadIdx.x >> 5; q < c.n_list; q += 8u) {
+        const uint32_t e = c.list[q], key = c.keys[e], off = c.offs[e], n = words(key);
+        uint32_t* g = dst(key);
+        for (uint32_t w = lane; w < n; w += 32u) {
+            const uint32_t v = c.pool[off + w];
+            if (!v) continue;
+            if (is_add(w)) atomicAdd(g + w, v); else atomicMax(g + w, v);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) sah_bin_cta_kernel(const float* __restrict__ cbox, uint32_t m, const SahTask* __restrict__ task,
+                                                          const uint32_t* __restrict__ node_of, uint32_t* bins, uint32_t* bins_few) {
+    __shared__ SahCta c;
+    sah_cta_begin(c);
+    constexpr uint32_t PER = SAH_CTA_MEMBERS / 256u;
+    uint32_t tsk[PER], entry[PER];
+    for (uint32_t u = 0; u < PER; ++u) {
+        const uint32_t i = blockIdx.x * SAH_CTA_MEMBERS + u * 256u + threadIdx.x;
+        tsk[u] = SAH_NONE; entry[u] = 0u;
+        if (i >= m) continue;
+        const uint32_t t = node_of[i], slot = task[t].slot;
+        if (slot == SAH_NONE) continue;
+        tsk[u] = t; entry[u] = sah_cta_insert(c, slot);
+    }
+    auto words = [](uint32_t slot) { return (slot & SAH_FEW_SLOT) ? SAH_TASK_WORDS_FEW : SAH_TASK_WORDS; };
+    auto dst = [&](uint32_t slot) { return (slot & SAH_FEW_SLOT) ? bins_few + (size_t)(slot & ~SAH_FEW_SLOT) * SAH_TASK_WORDS_FEW : bins + (size_t)slot * SAH_TASK_WORDS; };
+    sah_cta_allocate(c, words);
+    for (uint32_t u = 0; u < PER; ++u) {
+        if (tsk[u] == SAH_NONE) continue;
+        const uint32_t i = blockIdx.x * SAH_CTA_MEMBERS + u * 256u + threadIdx.x;
+        const SahTask& t = task[tsk[u]];
+        const uint32_t slot = t.slot, off = c.offs[entry[u]];
+        const int nb = (slot & SAH_FEW_SLOT) ? SAH_BINS_FEW : SAH_BINS;
+        uint32_t* base = off != SAH_OVERFLOW ? c.pool + off : dst(slot);
+        float b[6];
+        for (int q = 0; q < 6; ++q) b[q] = __ldg(cbox + 6ull * i + q);
+        for (int d = 0; d < 3; ++d) {
+            const float lo = lbvh_unord(~t.cb[2 * d]), hi = lbvh_unord(t.cb[2 * d + 1]);
+            const float ext = sub(hi, lo);
+            if (!(ext > 0.0f)) continue;
+            uint32_t* w = base + ((size_t)d * nb + (uint32_t)sah_bin(sah_centroid(b, d), lo, ext, nb)) * SAH_BIN_WORDS;
+            for (int q = 0; q < 3; ++q) { atomicMax(w + 2 * q, ~lbvh_ord(b[2 * q])); atomicMax(w + 2 * q + 1, lbvh_ord(b[2 * q + 1])); }
+            atomicAdd(w + 6, 1u);
+        }
+    }
+    sah_cta_flush(c, words, dst, [](uint32_t w) { return w % SAH_BIN_WORDS == 6u; });
+}
+
+__global__ void __launch_bounds__(256) sah_assign_cta_kernel(const float* __restrict__ cbox, uint32_t m, SahTask* task, uint32_t* __restrict__ node_of) {
+    __shared__ SahCta c;
+    sah_cta_begin(c);
+    constexpr uint32_t PER = SAH_CTA_MEMBERS / 256u;
+    uint32_t child[PER], entry[PER];
+    for (uint32_t u = 0; u < PER; ++u) {
+        const uint32_t i = blockIdx.x * SAH_CTA_MEMBERS + u * 256u + threadIdx.x;
+        child[u] = SAH_NONE; entry[u] = 0u;
+        if (i >= m) continue;
+        const SahTask& t = task[node_of[i]];
+        if (t.slot == SAH_NONE) continue;
+        const float* b = cbox + 6ull * i;
+        uint32_t side;
+        if (t.split & SAH_FALLBACK) side = i >= (t.split & ~SAH_FALLBACK) ? 1u : 0u;
+        else {
+            const int d = (int)(t.split >> 8), k = (int)(t.split & 0xFFu);
+            const float lo = lbvh_unord(~t.cb[2 * d]), hi = lbvh_unord(t.cb[2 * d + 1]);
+            side = sah_bin(sah_centroid(b, d), lo, sub(hi, lo), (t.slot & SAH_FEW_SLOT) ? SAH_BINS_FEW : SAH_BINS) > k ? 1u : 0u;
+        }
+        child[u] = t.child0 + side;
+        node_of[i] = child[u];
+        entry[u] = sah_cta_insert(c, child[u]);
+    }
+    auto words = [](uint32_t) { return SAH_ACC_WORDS; };
+    auto dst = [&](uint32_t ct) { return reinterpret_cast<uint32_t*>(&task[ct]); };
+    sah_cta_allocate(c, words);
+    for (uint32_t u = 0; u < PER; ++u) {
+        if (child[u] == SAH_NONE) continue;
+        const uint32_t i = blockIdx.x * SAH_CTA_MEMBERS + u * 256u + threadIdx.x;
+        const uint32_t off = c.offs[entry[u]];
+        uint32_t* acc = off != SAH_OVERFLOW ? c.pool + off : dst(child[u]);
+        const float* b = cbox + 6ull * i;
+        for (int d = 0; d < 3; ++d) {
+            const uint32_t o = lbvh_ord(sah_centroid(b, d));
+            atomicMax(acc + 2 * d, ~o); atomicMax(acc + 2 * d + 1, o);
+        }
+        atomicAdd(acc + 6, 1u);
+        atomicMax(acc + 7, ~i); atomicMax(acc + 8, i);
+    }
+    sah_cta_flush(c, words, dst, [](uint32_t w) { return w == 6u; });
+}

@@ -206,6 +206,14 @@ def binned_top(tree, cid, weight, nbins=16):
             return int(cid[ix[0]])
         nbins = nb_big if len(ix) > ADAPT[0] else ADAPT[1]
         c = cen[ix]; lo = c.min(0); hi = c.max(0)
+        if nbins == 2 and (hi > lo).any():
+            # "2 bins" = no SAH evaluation at all: cut the longest axis of the centroid bounds in the middle
+            ax = int(np.argmax(hi - lo))
+            mid = lo[ax] + 0.5 * (hi[ax] - lo[ax])
+            left, right = ix[c[:, ax] < mid], ix[c[:, ax] >= mid]
+            if len(left) and len(right):
+                L = build(left); R = build(right)
+                return int(tree.new_nodes(np.array([L]), np.array([R]))[0])
         best = (np.inf, None)
         for ax in range(3):
             ext = hi[ax] - lo[ax]
