@@ -82,6 +82,31 @@ def test_lbvh_edge_cases(cr):
         cr.build_lbvh(np.zeros((0, 12), np.float32))
 
 
+def test_builders_on_a_hostile_triangle_soup(cr):
+    """4 000 triangles a mesh would never contain: sizes from 1e-4 to 1e3 in one scene, slivers, zero-area triangles, exact
+    duplicates, clusters on one point, everything shifted far from the origin.  Every builder must still return a valid tree whose
+    boxes the refit reproduces bit for bit and whose frame equals the oracle's walk of the same tree."""
+    rng = np.random.default_rng(77)
+    n = 4000
+    centre = rng.uniform(-50, 50, size=(n, 3)) + np.array([4096.0, -2048.0, 512.0])
+    centre[:600] = centre[0]                                            # 600 triangles around one point
+    size = 10.0 ** rng.uniform(-4, 3, size=(n, 1, 1))
+    size[:600] = 1e-3
+    v = centre[:, None, :] + rng.normal(size=(n, 3, 3)) * size
+    v[1000:1100, 2] = v[1000:1100, 1]                                   # zero area: two corners coincide
+    v[1100:1200, 2] = 0.5 * (v[1100:1200, 0] + v[1100:1200, 1])         # zero area: collinear
+    v[1200:1400] = v[1400:1600]                                         # exact duplicates
+    v[1600:1700, 1] = v[1600:1700, 0] + 1e-6 * rng.normal(size=(100, 3))  # slivers
+    tris = port.make_triangles(v.reshape(n, 9).astype(np.float32)).reshape(n, 12)
+    nodes, idx, _ = cr.build_lbvh(tris)
+    assert validate(nodes, idx, n) <= 64
+    pod = {"nodes": nodes, "prim_indices": idx, "triangles": tris, "norms": np.tile(np.array([0, 0, 1], np.float32), (n, 3))}
+    assert np.array_equal(port.refit(pod).view(np.uint32), nodes.view(np.uint32))
+    cam = cr.Camera((4096.0, -2048.0, 512.0 - 400.0), (0, 0, 1), (0, 1, 0), 40.0)
+    with cr.Scene.from_pod(pod) as s:
+        check_frame(cr, s, pod, cam, np.array([4000, -1000, -5000], np.float32), 480, 270, 0)
+
+
 def test_clustering_tree_needs_fewer_steps_than_the_radix_tree(cr, dragon_pod):
     """The point of the clustering build: a tree of SAH quality.  Same frame, node-pair steps of the primary rays (closest-hit,
     deterministic) counted by the statistics build: the clustered tree needs clearly fewer than the radix tree and is within
