@@ -273,7 +273,8 @@ int ceres_render_device(ceres_scene* scene, const ceres_camera* camera, const fl
  * scratch lives (record queue, its ready[] credits, the counter slot): in a file-scope `static __device__` array of
  * CERES_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit, instead of the scene's grow-on-demand
  * cudaMalloc'ed buffers.  The call performs no cudaMalloc / cudaFree / allocating library routine -- only
- * cudaGetSymbolAddress on the first call per device, then async memset + 2 kernel launches on `stream`.
+ * cudaGetSymbolAddress on the first call per device, then async memset + 2 kernel launches on `stream`: after one warm-up
+ * call it can be captured into a CUDA graph and replayed (tests/test_zz_no_alloc.py does).
  * Limits: width * height <= CERES_STATIC_MAX_PIXELS (larger frames are refused with CERES_ERR_INVALID and a message that
  * names the limit); whole frames only (no shard); flags: CERES_NO_SHADOWS only; statistics / timeline modes and tuning
  * variants are refused (CERES_ERR_UNSUPPORTED).  d_ids / d_counters nullable as above.

@@ -137,9 +137,12 @@ def binned_top2(tree, cid, weight, nbins=16, longest=False, loose=False):
     cb = tree.boxes[cid]
     cen = (0.5 * (cb[:, 0::2] + cb[:, 1::2])).astype(np.float32)
 
+    nb_big = nbins
+
     def build(ix, lo, hi):
         if len(ix) == 1:
             return int(cid[ix[0]])
+        nbins = nb_big if len(ix) > ADAPT[0] else ADAPT[1]
         c = cen[ix]
         if not loose or lo is None:
             lo = c.min(0); hi = c.max(0)

@@ -150,3 +150,26 @@ def test_the_call_allocates_no_device_memory(cr, dragon):
     torch.cuda.synchronize()
     free1, _ = torch.cuda.mem_get_info()
     assert free1 == free0, f"free device memory moved by {free0 - free1} bytes over 20 calls"
+
+
+def test_the_call_can_be_captured_in_a_cuda_graph(cr, dragon):
+    """The reason the entry point exists: a caller under CUDA graph capture.  After one warm-up call (which takes the scratch's
+    address) the call is captured on a stream -- nothing in it allocates or synchronises -- and the graph replayed three times
+    gives the frame of ceres_render_device every time."""
+    import torch
+    cam, W, H = cr.configs.DRAGON_CAMERA, 1280, 720
+    ref = both(dragon, cam, W, H, 0)[0]
+    px = torch.full((H * W * 3,), float("nan"), dtype=torch.float32, device="cuda")
+    ids = torch.zeros(H * W, dtype=torch.int32, device="cuda")
+    cnt = torch.zeros(2, dtype=torch.int64, device="cuda")
+    dragon.render_device_static(cam, SUN, W, H, pixels=px, ids=ids, counters=cnt)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        dragon.render_device_static(cam, SUN, W, H, pixels=px, ids=ids, counters=cnt)
+    for _ in range(3):
+        px.fill_(float("nan")); ids.zero_(); cnt.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        assert_same(ref, (px.cpu().numpy().view(np.uint32), ids.cpu().numpy().view(np.uint32), tuple(cnt.cpu().tolist())))
+    del g
