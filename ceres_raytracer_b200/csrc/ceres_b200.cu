@@ -1255,14 +1255,13 @@ int lbvh_run(const float4* d_tris, int n, LbvhWork& w, float* ms_out) {
         } else
         lbvh_tree_kernel<<<grid, 256>>>(w.code2, n, w.child, w.pi, w.pl);
         lbvh_emit_kernel<<<grid, 256>>>(w.child, w.idx2, w.box, n, w.nodes);
-        lbvh_fit_kernel<<<grid, 256>>>(w.pi, w.pl, w.arr, n, w.nodes);
+        if (!collapse) lbvh_fit_kernel<<<grid, 256>>>(w.pi, w.pl, w.arr, n, w.nodes);
         g_launches += 3;
         if (collapse) {
-            // SAH leaf collapsing + depth-first leaf order + compaction of the surviving inner nodes (lbvh_build.cuh)
+            // bottom-up boxes + SAH leaf collapsing (one climb), depth-first leaf order, compaction of the surviving inner nodes
             const CollapseParams q{1.0f, g_build_ci, (uint32_t)g_build_max_leaf};
-            TRY_B(cudaMemsetAsync(w.c_arr, 0, tc * 4, 0));
             TRY_B(cudaMemsetAsync(w.nodes2, 0, (2 * tc - 1) * sizeof(LbvhNode), 0));
-            bvhc_cost_kernel<<<grid, 256>>>(w.child, w.pi, w.pl, w.nodes, n, q, w.c_arr, w.c_cnt, w.c_cost, w.c_col, w.c_fl);
+            bvhc_fit_cost_kernel<<<grid, 256>>>(w.child, w.pi, w.pl, w.nodes, n, q, w.arr, w.c_cnt, w.c_cost, w.c_col, w.c_fl);
             bvhc_rank_kernel<<<(unsigned)((2 * tc - 1 + 255) / 256), 256>>>(w.child, w.pi, w.pl, w.c_cnt, w.c_col, w.c_fl, w.idx2, n, w.idx3, w.c_rank, w.c_keep, w.c_newid);
             bvhc_emit_kernel<<<grid, 256>>>(w.child, w.c_cnt, w.c_col, w.c_rank, w.c_keep, w.c_newid, w.nodes, n, w.nodes2);
             g_launches += 3;

@@ -37,14 +37,17 @@ __device__ __forceinline__ float lbvh_unord(unsigned int u) {
 __global__ void __launch_bounds__(256) lbvh_boxes_kernel(const float4* __restrict__ tris, uint32_t n, float* __restrict__ box,
                                                          unsigned int* scene) {
     const uint32_t k = blockIdx.x * 256u + threadIdx.x;
-    if (k >= n) return;
-    float b[6];
-    leaf_box(tris, k, 1u, b);
-    for (int d = 0; d < 6; ++d) box[6ull * k + d] = b[d];
+    const bool live = k < n;
+    float b[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    if (live) {
+        leaf_box(tris, k, 1u, b);
+        for (int d = 0; d < 6; ++d) box[6ull * k + d] = b[d];
+    }
+    // six words for the whole scene: one atomic per warp, not per triangle
     for (int d = 0; d < 3; ++d) {
-        const float c = mul(add(b[2 * d], b[2 * d + 1]), 0.5f);
-        atomicMin(&scene[2 * d], lbvh_ord(c));
-        atomicMax(&scene[2 * d + 1], lbvh_ord(c));
+        const unsigned int c = lbvh_ord(mul(add(b[2 * d], b[2 * d + 1]), 0.5f));
+        const unsigned int lo = __reduce_min_sync(0xFFFFFFFFu, live ? c : 0xFFFFFFFFu), hi = __reduce_max_sync(0xFFFFFFFFu, live ? c : 0u);
+        if ((threadIdx.x & 31u) == 0u && lo <= hi) { atomicMin(&scene[2 * d], lo); atomicMax(&scene[2 * d + 1], hi); }
     }
 }
 
@@ -287,6 +290,45 @@ __global__ void __launch_bounds__(256) bvhc_cost_kernel(const uint32_t* __restri
         if (p == 0u) return;
         __threadfence();
         p = par_inner[p] >> 1;
+    }
+}
+
+// lbvh_fit_kernel and bvhc_cost_kernel in one climb (both go from every leaf to the root behind the same arrival counters): the
+// second thread to arrive at inner node p unites the children's boxes, stores the box where p lives, and evaluates p's leaf /
+// subtree costs from it.  Same arithmetic as the two kernels, one pass over the tree less.
+__global__ void __launch_bounds__(256) bvhc_fit_cost_kernel(const uint32_t* __restrict__ child, const uint32_t* __restrict__ par_inner,
+                                                            const uint32_t* __restrict__ par_leaf, LbvhNode* nodes, int n, CollapseParams q,
+                                                            uint32_t* arrived, uint32_t* cnt, float* cost, uint32_t* collapse, uint32_t* fl) {
+    const int k = (int)(blockIdx.x * 256u + threadIdx.x);
+    if (k >= n) return;
+    uint32_t p = par_leaf[k] >> 1;
+    for (;;) {
+        if (atomicAdd(&arrived[p], 1u) == 0u) return;           // the sibling subtree is not finished yet
+        __threadfence();
+        const float* l = nodes[1 + 2 * p].bounds; const float* r = nodes[2 + 2 * p].bounds;
+        float lb[6], rb[6], u[6];
+        for (int d = 0; d < 6; ++d) { lb[d] = __ldcg(l + d); rb[d] = __ldcg(r + d); }
+        for (int d = 0; d < 3; ++d) {                            // left.extend(right), bounding_box.hpp:23-27
+            u[2 * d] = min_std(lb[2 * d], rb[2 * d]);
+            u[2 * d + 1] = max_std(lb[2 * d + 1], rb[2 * d + 1]);
+        }
+        const uint32_t up = p == 0u ? 0u : par_inner[p];
+        float* dst = p == 0u ? nodes[0].bounds : nodes[1 + 2 * (up >> 1) + (up & 1u)].bounds;
+        for (int d = 0; d < 6; ++d) __stcg(dst + d, u[d]);
+        uint32_t c_n = 0, c_fl = 0; float c_cost = 0.0f;
+        for (int s = 0; s < 2; ++s) {
+            const uint32_t c = child[2 * p + s];
+            if (c & LBVH_LEAF) { c_n += 1u; c_fl += 1u; c_cost += bvhc_half_area(s ? rb : lb) * q.ci; }
+            else { c_n += __ldcg(cnt + c); c_fl += __ldcg(fl + c); c_cost += __ldcg(cost + c); }
+        }
+        const float a = bvhc_half_area(u);
+        const float as_leaf = a * (float)c_n * q.ci, as_tree = a * q.ct + c_cost;
+        const bool col = p != 0u && c_n <= q.max_leaf && as_leaf <= as_tree;
+        __stcg(cnt + p, c_n); __stcg(cost + p, col ? as_leaf : as_tree); __stcg(collapse + p, col ? 1u : 0u);
+        __stcg(fl + p, col ? 1u : c_fl);                        // leaves of the FINAL tree under p
+        if (p == 0u) return;
+        __threadfence();
+        p = up >> 1;
     }
 }
 

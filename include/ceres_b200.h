@@ -152,7 +152,7 @@ int ceres_build_bvh(const void* tris, size_t tri_count, int device, void* nodes_
  *   algorithm     0 (default) = 2 = top-down binned SAH, one level per pass: every open node bins its members' centroids (16 bins per
  *                 axis over its centroid bounds; 4 for nodes of at most 16 triangles), splits where area x count is smallest over
  *                 the three axes, members never move in memory (binned_sah_builder.hpp on the host; renders 1-5 % FASTER than the
- *                 reference's SweepSah tree, builds 10.5 M triangles in 37 ms);
+ *                 reference's SweepSah tree, builds 10.5 M triangles in 35 ms);
  *                 3 = parallel locally-ordered clustering (the idea of lib/bvh/locally_ordered_clustering_builder.hpp:186-234:
  *                 every round each cluster merges with the neighbour within `radius` places whose union has the smallest area, if
  *                 the choice is mutual; 3 x faster to build, 6-9 % slower to render than SweepSah's tree);
